@@ -1,0 +1,132 @@
+/* qi_b200.h — C ABI of the B200-native Qwen-Image denoising hot path (libqi_b200.so).
+ *
+ * The reference (AliciaCW/vllm-omni-draft) has no FFI of its own: its hot path is
+ * `self.transformer(hidden_states=..., encoder_hidden_states=..., timestep=..., ...)`
+ * (src/qwen_image/runner_adapter.py:128-137, src/qwen_image_gen/model.py:122-129) and
+ * `pipe(**gen_kwargs)` (src/performance_enhancement/test_performance.py:277), both executed by the
+ * un-vendored `diffusers` package on ATen/cuBLAS kernels.  These entry points are the operators
+ * that call decomposes into (SURVEY.md §8b "What the C-ABI replacement must export"); each comment
+ * names the upstream operator it replaces.  INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions: every pointer is a DEVICE pointer unless it says "host"; all activations/weights are
+ * bf16 (uint16 storage), row-major, innermost dimension contiguous; `ld*` / `*_stride` are in
+ * ELEMENTS; every function enqueues on `stream` and returns 0 or a negative qi_status.  No
+ * allocation happens inside the library; the caller owns every buffer.  There is no CPU fallback:
+ * on a machine without an sm_100 GPU every compute entry point returns QI_ERR_CUDA.
+ */
+#ifndef QI_B200_H_
+#define QI_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* qi_stream_t; /* == cudaStream_t */
+
+enum qi_status {
+  QI_STATUS_OK = 0,
+  QI_STATUS_ERR_ARG = -1,         /* malformed argument (null pointer, bad alignment/shape) */
+  QI_STATUS_ERR_CUDA = -2,        /* CUDA runtime error at launch (see qi_last_cuda_error) */
+  QI_STATUS_ERR_DRIVER = -3,      /* tensor-map encode failed */
+  QI_STATUS_ERR_UNSUPPORTED = -4  /* shape outside the compiled instantiations */
+};
+
+enum qi_epilogue {
+  QI_EPI_BIAS = 0,           /* C = A W^T + b                         (to_q/k/v, add_*_proj, img_in, ...) */
+  QI_EPI_BIAS_GELU_TANH = 1, /* C = gelu_tanh(A W^T + b)              (FeedForward net.0: GELU(approximate="tanh")) */
+  QI_EPI_GATED_RESIDUAL = 2  /* C = R + gate[batch] * (A W^T + b)     (x = x + gate * attn/mlp output) */
+};
+
+int qi_version(void);
+const char* qi_last_cuda_error(void); /* host string, valid until the next failing call */
+int qi_device_sm_count(void);
+
+/* ---- K3: tcgen05 bf16 GEMM with fused epilogues (replaces nn.Linear + the elementwise ops after it).
+ * Up to two independent problems (the img and txt streams of one MMDiT block) run in ONE persistent
+ * launch.  A is [batch, m, k] (row stride lda, batch stride a_batch_stride), W is the nn.Linear
+ * weight [n, k] contiguous, C is [batch, m, n] (ldc, c_batch_stride).  k % 64 == 0, n % 8 == 0. */
+typedef struct {
+  const void* a;
+  long long lda;
+  long long a_batch_stride;
+  const void* w;
+  const void* bias; /* [n] or NULL */
+  void* c;
+  long long ldc;
+  long long c_batch_stride;
+  const void* residual; /* QI_EPI_GATED_RESIDUAL: R, may alias c */
+  long long ld_res;
+  long long res_batch_stride;
+  const void* gate; /* QI_EPI_GATED_RESIDUAL: [batch, n] */
+  long long gate_batch_stride;
+  int m;     /* rows per batch item */
+  int batch;
+  int n;
+  int k;
+  int epilogue; /* enum qi_epilogue */
+} qi_gemm_problem_t;
+
+int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
+                 qi_stream_t stream);
+
+/* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
+ * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).
+ * q, k, v, o are [batch, seq, heads, head_dim] views with a common row stride ld (elements between
+ * consecutive tokens) and batch stride; head_dim in {64, 128}.  Keys kv_start..kv_start+kv_len of the
+ * k/v views are attended by queries 0..seq_q (Ulysses passes full-sequence K/V of its local heads). */
+int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int batch, int seq_q,
+                     int seq_kv, int heads, int head_dim, long long ld_q, long long ld_kv,
+                     long long ld_o, long long q_batch_stride, long long kv_batch_stride,
+                     long long o_batch_stride, float softmax_scale, qi_stream_t stream);
+
+/* ---- K1: LayerNorm(no affine, eps) fused with adaLN modulation: y = LN(x) * (1 + scale[b]) + shift[b]
+ * (replaces img_norm1/2, txt_norm1/2 + QwenImageTransformerBlock._modulate, and AdaLayerNormContinuous).
+ * shift/scale point at the first element of batch 0; batch b is mod_batch_stride elements further. */
+int qi_adaln_modulate(const void* x, void* y, int rows, int d, int ld_x, int ld_y, const void* shift,
+                      const void* scale, long long mod_batch_stride, int rows_per_batch, float eps,
+                      qi_stream_t stream);
+
+/* RMSNorm with learned weight (replaces txt_norm = RMSNorm(joint_attention_dim, eps=1e-6)). */
+int qi_rmsnorm_affine(const void* x, void* y, int rows, int d, int ld_x, int ld_y, const void* weight,
+                      float eps, qi_stream_t stream);
+
+/* ---- K2: per-head RMSNorm of q and k (norm_q/norm_k for image rows, norm_added_q/k for text rows)
+ * fused with the MSRoPE complex rotation (apply_rotary_emb_qwen, use_real=False), in place on the
+ * joint qkv buffer [rows = batch*seq, ld] whose row is [q(heads*hd) | k(heads*hd) | v(...)].
+ * freqs_cos_sin: fp32 [seq, head_dim/2, 2] = (cos, sin), joint order (text rows first). */
+int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq, int s_txt,
+                   const void* wq_img, const void* wk_img, const void* wq_txt, const void* wk_txt,
+                   const void* freqs_cos_sin, float eps, qi_stream_t stream);
+
+/* ---- K5: true-CFG combine + per-token norm rescale + FlowMatch Euler update in one pass
+ * (replaces QwenImagePipeline's comb_pred/cond_norm/noise_norm lines and
+ * FlowMatchEulerDiscreteScheduler.step).  uncond == NULL skips CFG.  dt = sigma_next - sigma is read
+ * from dt_dev (device fp32) when non-NULL, else from the scalar.  channels must be 64. */
+int qi_cfg_euler_step(const void* cond, const void* uncond, const void* latents, void* out,
+                      long long tokens, int channels, float true_cfg_scale, const float* dt_dev,
+                      float dt, qi_stream_t stream);
+
+/* ---- small-M linear (M <= a few rows): y = act_out(act_in(x) W^T + b); used for the timestep
+ * embedder, the per-block modulation Linear(SiLU(temb)) and norm_out.linear.  HBM-bound on W. */
+int qi_small_linear(const void* x, const void* w, const void* bias, void* y, int m, int n, int k,
+                    int ld_x, int ld_y, int silu_in, int silu_out, qi_stream_t stream);
+
+/* Timesteps(256, flip_sin_to_cos=True, downscale_freq_shift=0, scale=1000): t fp32 [m] -> bf16 [m,256]. */
+int qi_timestep_sinusoid(const float* t, void* out, int m, qi_stream_t stream);
+
+/* ---- host-side integer tables (bit-exact parts of the path; no GPU needed).
+ * MSRoPE position ids (QwenEmbedRope): img_pos [sum F*H*W, 3], txt_pos [txt_len, 3] (int32, host).
+ * shapes: num_images triples (F,H,W).  Returns 0, or QI_STATUS_ERR_ARG if a text position would
+ * exceed the 4096-entry table. */
+int qi_rope_position_ids(const int* shapes /* host */, int num_images, int txt_len,
+                         int32_t* img_pos /* host */, int32_t* txt_pos /* host */);
+/* Token permutation of _pack_latents: for packed element index i of [ (Hl/2)(Wl/2), C*4 ] gives the
+ * flat source index into [C, Hl, Wl].  idx: host int64 [(Hl/2)*(Wl/2)*C*4]. */
+int qi_pack_latents_index(int channels, int hl, int wl, int64_t* idx /* host */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QI_B200_H_ */

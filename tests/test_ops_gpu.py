@@ -1,0 +1,177 @@
+"""GPU parity of each C-ABI kernel against the oracle's op (same seeded inputs).
+Tolerances: bf16 outputs -> rel-L2 <= 1e-2 (BASELINE.json north_star), usually far tighter."""
+import math
+
+import pytest
+import torch
+
+from oracle import qwen_image_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from vllm_omni_draft_b200 import ops
+    return ops
+
+
+def _rand(shape, seed, scale=1.0, device="cuda"):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16).to(device)
+
+
+def test_cfg_euler_step_matches_oracle(cuda_device):
+    ops = _ops()
+    B, S = 2, 4096 + 3
+    c, u, x = _rand((B, S, 64), 1), _rand((B, S, 64), 2), _rand((B, S, 64), 3)
+    sig = torch.tensor([0.7446114, 0.4266735])
+    out = torch.empty_like(x)
+    ops.cfg_euler_step(c, u, x, out, 4.0, dt=float(sig[1] - sig[0]))
+    ref = O.scheduler_step(O.true_cfg_combine(c.cpu(), u.cpu(), 4.0), x.cpu(), sig[0], sig[1])
+    diff = (out.cpu().float() - ref.float()).abs()
+    # op-by-op bf16 rounding is reproduced; only fp32 summation order inside the norms may differ
+    assert (diff > 0).float().mean() < 0.02, f"mismatch fraction {(diff > 0).float().mean()}"
+    assert O.rel_l2(out.cpu(), ref) < 2e-3
+    # no-CFG path and device dt
+    dt_dev = torch.tensor([float(sig[1] - sig[0])], device="cuda")
+    out2 = torch.empty_like(x)
+    ops.cfg_euler_step(c, None, x, out2, 1.0, dt_dev=dt_dev)
+    ref2 = O.scheduler_step(c.cpu(), x.cpu(), sig[0], sig[1])
+    assert torch.equal(out2.cpu(), ref2)
+
+
+@pytest.mark.parametrize("d", [256, 3072])
+def test_adaln_modulate(cuda_device, d):
+    ops = _ops()
+    B, S = 2, 333
+    x = _rand((B * S, d), 4, 2.0)
+    mod = _rand((B, 6 * d), 5, 0.3)
+    out = torch.empty_like(x)
+    ops.adaln_modulate(x, mod[:, 0:d], mod[:, d:2 * d], out, S)
+    xf = x.cpu().float().view(B, S, d)
+    ref = O.layer_norm(xf) * (1 + mod.cpu().float()[:, None, d:2 * d]) + mod.cpu().float()[:, None, 0:d]
+    assert O.rel_l2(out.cpu().view(B, S, d), ref) < 4e-3
+
+
+def test_rmsnorm_affine(cuda_device):
+    ops = _ops()
+    x, w = _rand((77, 3584), 6, 1.5), _rand((3584,), 7, 0.2) + 1
+    out = torch.empty_like(x)
+    ops.rmsnorm_affine(x, w, out)
+    ref = O.rms_norm(x.cpu(), w.cpu())
+    assert O.rel_l2(out.cpu(), ref) < 1e-3
+
+
+@pytest.mark.parametrize("heads,hd,axes", [(4, 64, (8, 28, 28)), (24, 128, (16, 56, 56))])
+def test_qknorm_rope(cuda_device, heads, hd, axes):
+    ops = _ops()
+    from vllm_omni_draft_b200 import rope
+    B, s_txt, hh, ww = 2, 19, 6, 10
+    s_img = hh * ww
+    S = s_txt + s_img
+    d = heads * hd
+    qkv = _rand((B * S, 3 * d), 8, 1.3)
+    ws = [_rand((hd,), 9 + i, 0.2) + 1 for i in range(4)]
+    cfg = O.OracleConfig(attention_head_dim=hd, num_attention_heads=heads, axes_dims_rope=axes)
+    img_f, txt_f = O.rope_freqs(cfg, [(1, hh, ww)], s_txt)
+    freqs = rope.joint_cos_sin(axes, 10000.0, [(1, hh, ww)], s_txt).cuda()
+    ref = qkv.cpu().clone().view(B, S, 3, heads, hd)
+    wq_i, wk_i, wq_t, wk_t = [w.cpu() for w in ws]
+    q, k = ref[:, :, 0], ref[:, :, 1]
+    rq = torch.cat([O.apply_rope(O.rms_norm(q[:, :s_txt], wq_t), txt_f),
+                    O.apply_rope(O.rms_norm(q[:, s_txt:], wq_i), img_f)], 1)
+    rk = torch.cat([O.apply_rope(O.rms_norm(k[:, :s_txt], wk_t), txt_f),
+                    O.apply_rope(O.rms_norm(k[:, s_txt:], wk_i), img_f)], 1)
+    v_before = ref[:, :, 2].clone()
+    ops.qknorm_rope(qkv, heads, hd, S, s_txt, ws[0], ws[1], ws[2], ws[3], freqs)
+    got = qkv.cpu().view(B, S, 3, heads, hd)
+    assert torch.equal(got[:, :, 2], v_before), "v must be untouched"
+    assert O.rel_l2(got[:, :, 0], rq) < 2e-3
+    assert O.rel_l2(got[:, :, 1], rk) < 2e-3
+
+
+def test_small_linear_and_sinusoid(cuda_device):
+    ops = _ops()
+    x, w, b = _rand((3, 256), 20), _rand((512, 256), 21, 0.05), _rand((512,), 22, 0.1)
+    out = torch.empty(3, 512, device="cuda", dtype=torch.bfloat16)
+    ops.small_linear(x, w, b, out, silu_in=True)
+    ref = torch.nn.functional.linear(torch.nn.functional.silu(x.cpu()).float(), w.cpu().float(), b.cpu().float())
+    assert O.rel_l2(out.cpu(), ref) < 5e-3
+    t = torch.tensor([1.0, 0.7446, 0.02], device="cuda")
+    sin = torch.empty(3, 256, device="cuda", dtype=torch.bfloat16)
+    ops.timestep_sinusoid(t, sin)
+    assert O.rel_l2(sin.cpu(), O.timestep_sinusoid(t.cpu())) < 5e-3
+
+
+GEMM_CASES = [
+    # (B, M, N, K, epilogue)
+    (1, 128, 128, 64, 0),
+    (1, 128, 256, 256, 0),
+    (1, 300, 768, 256, 0),
+    (2, 200, 1024, 256, 1),
+    (1, 4608, 3072, 3072, 2),
+    (2, 257, 64, 1024, 0),
+    (1, 4096, 9216, 3072, 0),
+]
+
+
+@pytest.mark.parametrize("B,M,N,K,epi", GEMM_CASES)
+def test_gemm(cuda_device, B, M, N, K, epi):
+    ops = _ops()
+    a = _rand((B, M, K), 30, 1.0)
+    w = _rand((N, K), 31, 0.05)
+    bias = _rand((N,), 32, 0.5)
+    out = torch.zeros(B, M, N, device="cuda", dtype=torch.bfloat16)
+    res = _rand((B, M, N), 33) if epi == 2 else None
+    gate = _rand((B, N), 34) if epi == 2 else None
+    ops.gemm([ops.gemm_problem(a, w, bias, out, epi, res, gate)])
+    torch.cuda.synchronize()
+    y = torch.matmul(a.float(), w.float().t()) + bias.float()
+    if epi == 1:
+        y = torch.nn.functional.gelu(y, approximate="tanh")
+    elif epi == 2:
+        y = res.float() + gate.float()[:, None, :] * y
+    err = O.rel_l2(out.cpu(), y.cpu())
+    assert err < 5e-3, f"rel_l2={err}"
+
+
+def test_gemm_two_problems_strided(cuda_device):
+    """img + txt stream in one launch, writing into a joint [B, S, 3d] buffer (as the block does)."""
+    ops = _ops()
+    B, s_txt, s_img, d = 2, 40, 200, 256
+    S = s_txt + s_img
+    xi, xt = _rand((B, s_img, d), 40), _rand((B, s_txt, d), 41)
+    wi, wt = _rand((3 * d, d), 42, 0.05), _rand((3 * d, d), 43, 0.05)
+    bi, bt = _rand((3 * d,), 44), _rand((3 * d,), 45)
+    joint = torch.zeros(B, S, 3 * d, device="cuda", dtype=torch.bfloat16)
+    ops.gemm([ops.gemm_problem(xi, wi, bi, joint[:, s_txt:], 0),
+              ops.gemm_problem(xt, wt, bt, joint[:, :s_txt], 0)])
+    ref_i = xi.float() @ wi.float().t() + bi.float()
+    ref_t = xt.float() @ wt.float().t() + bt.float()
+    assert O.rel_l2(joint[:, s_txt:].cpu(), ref_i.cpu()) < 5e-3
+    assert O.rel_l2(joint[:, :s_txt].cpu(), ref_t.cpu()) < 5e-3
+
+
+ATT_CASES = [
+    # (B, S, H, Dh)
+    (1, 256, 2, 128),
+    (1, 128, 1, 64),
+    (2, 288, 4, 64),
+    (1, 1000, 3, 128),
+    (1, 4608, 24, 128),
+]
+
+
+@pytest.mark.parametrize("B,S,H,Dh", ATT_CASES)
+def test_attention(cuda_device, B, S, H, Dh):
+    ops = _ops()
+    d = H * Dh
+    qkv = _rand((B, S, 3 * d), 50, 1.0)
+    q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
+    out = torch.zeros(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
+    ops.attention(q, k, v, out)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.scaled_dot_product_attention(
+        q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
+    err = O.rel_l2(out.cpu(), ref.cpu())
+    assert err < 1e-2, f"rel_l2={err}"

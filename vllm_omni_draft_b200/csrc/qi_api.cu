@@ -1,0 +1,127 @@
+// Host-side support for libqi_b200.so: driver entry point for tensor-map encoding, device query,
+// and the integer (bit-exact) host tables of the path: MSRoPE position ids and the pack permutation.
+#include "qi_common.cuh"
+#include "../../include/qi_b200.h"
+#include <cudaTypedefs.h>
+#include <mutex>
+#include <string>
+
+static std::string g_last_error;
+
+static void set_err(const std::string& s) { g_last_error = s; }
+
+extern "C" int qi_version(void) { return 100; }
+extern "C" const char* qi_last_cuda_error(void) { return g_last_error.c_str(); }
+
+int qi_num_sms() {
+  static int sms = -2;
+  if (sms == -2) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+      set_err(std::string("no CUDA device: ") + cudaGetErrorString(cudaGetLastError()));
+      return -1;  // do not cache: a later call may run after a device appears
+    }
+    int major = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (major != 10) {
+      set_err("libqi_b200 requires an sm_100 (B200) device; there is no fallback path");
+      return -1;
+    }
+    sms = n;
+  }
+  return sms;
+}
+extern "C" int qi_device_sm_count(void) { return qi_num_sms(); }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+int qi_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                        const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_err("cuTensorMapEncodeTiled driver entry point unavailable");
+    return QI_ERR_DRIVER;
+  }
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bdim[5];
+  cuuint32_t estr[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bdim[i] = box[i];
+    estr[i] = 1;
+  }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+                  gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_err("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return QI_ERR_DRIVER;
+  }
+  return QI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// MSRoPE integer positions (QwenEmbedRope with scale_rope=True).
+// ---------------------------------------------------------------------------------------------
+extern "C" int qi_rope_position_ids(const int* shapes, int num_images, int txt_len,
+                                    int32_t* img_pos, int32_t* txt_pos) {
+  if (!shapes || num_images <= 0 || txt_len < 0 || !img_pos || (txt_len > 0 && !txt_pos))
+    return QI_ERR_ARG;
+  int max_vid = 0;
+  size_t o = 0;
+  for (int i = 0; i < num_images; ++i) {
+    const int F = shapes[3 * i], H = shapes[3 * i + 1], W = shapes[3 * i + 2];
+    if (F <= 0 || H <= 0 || W <= 0) return QI_ERR_ARG;
+    const int hneg = H - H / 2, wneg = W - W / 2;
+    if (i + F > 4096 || hneg > 4096 || wneg > 4096) return QI_ERR_ARG;
+    for (int f = 0; f < F; ++f)
+      for (int h = 0; h < H; ++h)
+        for (int w = 0; w < W; ++w) {
+          img_pos[o++] = i + f;
+          img_pos[o++] = h < hneg ? h - hneg : h - hneg;   // [-hneg..-1, 0..H/2-1]
+          img_pos[o++] = w < wneg ? w - wneg : w - wneg;
+        }
+    const int m = H / 2 > W / 2 ? H / 2 : W / 2;
+    if (m > max_vid) max_vid = m;
+  }
+  if (max_vid + txt_len > 4096) return QI_ERR_ARG;
+  for (int t = 0; t < txt_len; ++t) {
+    txt_pos[3 * t] = txt_pos[3 * t + 1] = txt_pos[3 * t + 2] = max_vid + t;
+  }
+  return QI_OK;
+}
+
+// _pack_latents: view(B,C,Hl/2,2,Wl/2,2).permute(0,2,4,1,3,5).reshape(B,(Hl/2)(Wl/2),C*4)
+extern "C" int qi_pack_latents_index(int channels, int hl, int wl, int64_t* idx) {
+  if (!idx || channels <= 0 || hl <= 0 || wl <= 0 || (hl & 1) || (wl & 1)) return QI_ERR_ARG;
+  const int H2 = hl / 2, W2 = wl / 2;
+  size_t o = 0;
+  for (int i = 0; i < H2; ++i)
+    for (int j = 0; j < W2; ++j)
+      for (int c = 0; c < channels; ++c)
+        for (int di = 0; di < 2; ++di)
+          for (int dj = 0; dj < 2; ++dj)
+            idx[o++] = ((int64_t)c * hl + (2 * i + di)) * wl + (2 * j + dj);
+  return QI_OK;
+}

@@ -1,0 +1,363 @@
+// K4: joint text+image flash attention forward for sm_100a (non-causal, no mask, dropout 0).
+//
+// One CTA owns two 128-query tiles of one (batch, head) and streams 128-key K/V tiles through a
+// 2-stage TMA ring.  tcgen05.mma computes S_t = Q_t K^T into TMEM (fp32, 128 columns per tile);
+// a softmax warpgroup per Q tile (one thread per query row) reads S_t with tcgen05.ld, does the
+// online-softmax update in the exp2 domain, and writes P_t as packed bf16 back over S_t's columns
+// (tcgen05.st); tcgen05.mma (A from TMEM) then accumulates O_t += P_t V into TMEM.  The two Q tiles
+// ping-pong so the tensor pipe works on one tile while the other tile's softmax runs.
+// O is rescaled lazily: only when a row's running max grows by more than 2^8.
+//
+// Warps: 0-3 softmax tile 0, 4-7 softmax tile 1, 8 TMA producer, 9 MMA issuer / TMEM owner.
+#include "qi_common.cuh"
+#include "../../include/qi_b200.h"
+
+namespace qi {
+
+constexpr int ATT_BM = 128;   // query rows per tile
+constexpr int ATT_BN = 128;   // keys per tile
+constexpr int ATT_THREADS = 320;
+constexpr int ATT_KV_STAGES = 2;
+
+template <int DH>
+struct AttCfg {
+  static constexpr int SUB = ATT_BM * 128;             // one [128 rows x 64 bf16] swizzled sub-tile
+  static constexpr int NSUB = DH / 64;                 // sub-tiles per operand tile
+  static constexpr int TILE_BYTES = SUB * NSUB;        // Q, K or V tile
+  static constexpr int Q_OFF = 0;
+  static constexpr int K_OFF = 2 * TILE_BYTES;
+  static constexpr int V_OFF = K_OFF + ATT_KV_STAGES * TILE_BYTES;
+  static constexpr int BAR_OFF = V_OFF + ATT_KV_STAGES * TILE_BYTES;
+  static constexpr int SMEM_BYTES = BAR_OFF + 256 + 1024;
+  // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,256+DH) O1 [384,384+DH)
+  static constexpr int S_COL0 = 0, S_COL1 = 128, O_COL0 = 256, O_COL1 = 384;
+};
+
+struct AttParams {
+  CUtensorMap tmap_q, tmap_k, tmap_v;
+  __nv_bfloat16* o;
+  long long ld_o, o_bs;
+  int seq_q, seq_kv, heads;
+  float scale_log2;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DH>
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attention_fwd_kernel(const __grid_constant__ AttParams P) {
+  using Cfg = AttCfg<DH>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::BAR_OFF);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* k_empty = bars + 3;   // [2]
+  uint64_t* v_full = bars + 5;    // [2]
+  uint64_t* v_empty = bars + 7;   // [2]
+  uint64_t* s_full = bars + 9;    // [2]  per Q tile
+  uint64_t* p_full = bars + 11;   // [2]
+  uint64_t* o_done = bars + 13;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * (2 * ATT_BM);
+  const int head = blockIdx.y;
+  const int b = blockIdx.z;
+  const int n_kv = (P.seq_kv + ATT_BN - 1) / ATT_BN;
+
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&P.tmap_q);
+    tma_prefetch_desc(&P.tmap_k);
+    tma_prefetch_desc(&P.tmap_v);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_done[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 8) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
+      for (int t = 0; t < 2; ++t)
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_q, q_full,
+                      s * 64, head, q0 + t * ATT_BM, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&k_empty[st], ph ^ 1);
+        mbar_expect_tx(&k_full[st], Cfg::TILE_BYTES);
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::K_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_k,
+                      &k_full[st], s * 64, head, j * ATT_BN, b);
+        mbar_wait(&v_empty[st], ph ^ 1);
+        mbar_expect_tx(&v_full[st], Cfg::TILE_BYTES);
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::V_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_v,
+                      &v_full[st], s * 64, head, j * ATT_BN, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
+      const uint32_t s_col[2] = {tmem_base + Cfg::S_COL0, tmem_base + Cfg::S_COL1};
+      const uint32_t o_col[2] = {tmem_base + Cfg::O_COL0, tmem_base + Cfg::O_COL1};
+      const uint32_t q_addr = smem_u32(smem + Cfg::Q_OFF);
+      const uint32_t k_addr = smem_u32(smem + Cfg::K_OFF);
+      const uint32_t v_addr = smem_u32(smem + Cfg::V_OFF);
+
+      auto issue_qk = [&](int t, int st) {
+#pragma unroll
+        for (int s = 0; s < Cfg::NSUB; ++s) {
+          const uint64_t da = make_smem_desc(q_addr + t * Cfg::TILE_BYTES + s * Cfg::SUB, 0, 1024);
+          const uint64_t db = make_smem_desc(k_addr + st * Cfg::TILE_BYTES + s * Cfg::SUB, 0, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_ss(s_col[t], da + 2 * k, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
+        }
+      };
+      auto issue_pv = [&](int t, int st, bool accumulate) {
+#pragma unroll
+        for (int k = 0; k < ATT_BN / 16; ++k) {
+          // V sub-tile rows are keys (128 B each): 16 keys per MMA = 2048 B; the second 64 columns
+          // of the head dim live one sub-tile (LBO) further.
+          const uint64_t db =
+              make_smem_desc(v_addr + st * Cfg::TILE_BYTES + k * 2048, Cfg::SUB, 1024);
+          mma_ts(o_col[t], s_col[t] + k * 8, db, idesc_pv, (accumulate || k != 0) ? 1u : 0u);
+        }
+      };
+
+      mbar_wait(q_full, 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      issue_qk(0, 0);
+      tc_commit(&s_full[0]);
+      issue_qk(1, 0);
+      tc_commit(&s_full[1]);
+      tc_commit(&k_empty[0]);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const bool has_next = (j + 1) < n_kv;
+        const int stn = (j + 1) & 1;
+        const uint32_t phn = ((j + 1) >> 1) & 1;
+        mbar_wait(&v_full[st], ph);
+        for (int t = 0; t < 2; ++t) {
+          mbar_wait(&p_full[t], j & 1);
+          tc_fence_after();
+          issue_pv(t, st, j > 0);
+          if (t == 1) tc_commit(&v_empty[st]);
+          if (has_next) {
+            if (t == 0) {
+              mbar_wait(&k_full[stn], phn);
+              tc_fence_after();
+            }
+            issue_qk(t, stn);
+            tc_commit(&s_full[t]);
+            if (t == 1) tc_commit(&k_empty[stn]);
+          } else {
+            tc_commit(&o_done[t]);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ softmax warpgroups
+    const int t = warp >> 2;                 // Q tile
+    const int quad = warp & 3;               // TMEM lane quadrant
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_off + (t == 0 ? Cfg::S_COL0 : Cfg::S_COL1);
+    const uint32_t o_addr = tmem_base + lane_off + (t == 0 ? Cfg::O_COL0 : Cfg::O_COL1);
+    float m_ref = -INFINITY;   // reference max (scaled, log2 domain) used for P and O
+    float l_sum = 0.f;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s_full[t], j & 1);
+      tc_fence_after();
+      const int kv_valid = min(ATT_BN, P.seq_kv - j * ATT_BN);
+      // pass 1: row max
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < ATT_BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(s_addr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float v = __uint_as_float(r[i]);
+          mx = (c * 32 + i < kv_valid) ? fmaxf(mx, v) : mx;
+        }
+      }
+      const float m_new = fmaxf(m_ref, mx * P.scale_log2);
+      const bool need = (m_new - m_ref) > 8.0f;   // also true on the first tile (m_ref = -inf)
+      if (__any_sync(0xffffffffu, need)) {
+        const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on tile 0
+        if (need) {
+          l_sum *= f;
+          m_ref = m_new;
+        }
+        if (j > 0) {
+#pragma unroll 1
+          for (int c = 0; c < DH / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(o_addr + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
+            tmem_st32(o_addr + c * 32, r);
+          }
+        }
+      }
+      // pass 2: P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
+      const float neg_m = -m_ref;
+#pragma unroll 1
+      for (int c = 0; c < ATT_BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(s_addr + c * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int col = c * 32 + 2 * i;
+          float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * i]), P.scale_log2, neg_m));
+          float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * i + 1]), P.scale_log2, neg_m));
+          p0 = (col < kv_valid) ? p0 : 0.f;
+          p1 = (col + 1 < kv_valid) ? p1 : 0.f;
+          l_sum += p0 + p1;
+          pk[i] = pack_bf16(p0, p1);
+        }
+        tmem_st16(s_addr + c * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[t]);
+    }
+    // final: O / l -> bf16 -> global
+    mbar_wait(&o_done[t], 0);
+    tc_fence_after();
+    const int row = q0 + t * ATT_BM + quad * 32 + lane;
+    const float inv = 1.f / l_sum;
+    __nv_bfloat16* orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
+#pragma unroll 1
+    for (int c = 0; c < DH / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + c * 32, r);
+      tmem_ld_wait();
+      if (row < P.seq_q) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 o;
+          o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+          o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+          o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+          o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = o;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+}  // namespace qi
+
+using namespace qi;
+
+template <int DH>
+static int launch_attention(const void* q, const void* k, const void* v, void* o, int batch,
+                            int seq_q, int seq_kv, int heads, long long ld_q, long long ld_kv,
+                            long long ld_o, long long q_bs, long long kv_bs, long long o_bs,
+                            float scale, cudaStream_t stream) {
+  AttParams P;
+  memset(&P, 0, sizeof(P));
+  const uint32_t box[4] = {64, 1, ATT_BM, 1};
+  {
+    uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_q, (uint64_t)batch};
+    uint64_t str[3] = {(uint64_t)DH * 2, (uint64_t)ld_q * 2,
+                       (uint64_t)(batch > 1 ? q_bs : ld_q * (long long)seq_q) * 2};
+    int rc = qi_encode_tmap_bf16(&P.tmap_q, q, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_kv, (uint64_t)batch};
+    uint64_t str[3] = {(uint64_t)DH * 2, (uint64_t)ld_kv * 2,
+                       (uint64_t)(batch > 1 ? kv_bs : ld_kv * (long long)seq_kv) * 2};
+    int rc = qi_encode_tmap_bf16(&P.tmap_k, k, 4, dims, str, box);
+    if (rc) return rc;
+    rc = qi_encode_tmap_bf16(&P.tmap_v, v, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  P.o = (__nv_bfloat16*)o;
+  P.ld_o = ld_o;
+  P.o_bs = o_bs;
+  P.seq_q = seq_q;
+  P.seq_kv = seq_kv;
+  P.heads = heads;
+  P.scale_log2 = scale * 1.4426950408889634f;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(attention_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             AttCfg<DH>::SMEM_BYTES) != cudaSuccess)
+      return QI_ERR_CUDA;
+    attr_set = true;
+  }
+  dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
+  attention_fwd_kernel<DH><<<grid, ATT_THREADS, AttCfg<DH>::SMEM_BYTES, stream>>>(P);
+  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  return QI_OK;
+}
+
+extern "C" int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int batch,
+                                int seq_q, int seq_kv, int heads, int head_dim, long long ld_q,
+                                long long ld_kv, long long ld_o, long long q_batch_stride,
+                                long long kv_batch_stride, long long o_batch_stride,
+                                float softmax_scale, cudaStream_t stream) {
+  if (!q || !k || !v || !o) return QI_ERR_ARG;
+  if (batch <= 0 || seq_q <= 0 || seq_kv <= 0 || heads <= 0) return QI_ERR_ARG;
+  if (ld_q % 8 || ld_kv % 8 || ld_o % 8 || q_batch_stride % 8 || kv_batch_stride % 8 ||
+      o_batch_stride % 8)
+    return QI_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) |
+       reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(o)) & 15)
+    return QI_ERR_ARG;
+  if (qi_num_sms() <= 0) return QI_ERR_CUDA;
+  if (head_dim == 128)
+    return launch_attention<128>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
+                                 q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
+                                 stream);
+  if (head_dim == 64)
+    return launch_attention<64>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
+                                q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
+                                stream);
+  return QI_ERR_UNSUPPORTED;
+}

@@ -1,0 +1,378 @@
+// Memory-bound kernels of the Qwen-Image denoising path (sm_100a):
+//   K1  qi_adaln_modulate      LayerNorm(no affine) fused with adaLN shift/scale   (A.3)
+//       qi_rmsnorm_affine      RMSNorm with learned weight (txt_norm)              (A.1)
+//   K2  qi_qknorm_rope         per-head QK RMSNorm + MSRoPE rotation, in place     (A.4)
+//   K5  qi_cfg_euler_step      true-CFG combine + norm rescale + FlowMatch Euler   (A.6)
+//       qi_small_linear        M<=32 rows x [N,K] bf16 weights (time embed, modulation, norm_out)
+//       qi_timestep_sinusoid   256-wide sinusoidal projection of t                 (A.2)
+// All use 128-bit global accesses, one warp per row (or per group of heads/tokens), and
+// warp-shuffle reductions; no shared memory is needed because no datum is reused across warps.
+#include "qi_common.cuh"
+
+namespace qi {
+
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+  return *reinterpret_cast<const uint4*>(p);
+}
+__device__ __forceinline__ uint4 ldg128_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg128(void* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }
+
+__device__ __forceinline__ void unpack8(uint4 u, float (&f)[8]) {
+  float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
+                    pack_bf16(f[6], f[7]));
+}
+template <int W>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+  for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: one warp per row.  NCHUNK = d / 256 (each lane owns NCHUNK x 8 contiguous bf16).
+// MODE 0: y = LN(x) * (1 + scale[b]) + shift[b]     MODE 1: y = bf16(x * rsqrt(ms+eps)) * w
+// ---------------------------------------------------------------------------------------------
+template <int NCHUNK, int MODE>
+__global__ void __launch_bounds__(128) norm_rows_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int rows, int ld_x, int ld_y,
+    const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale,
+    long long mod_batch_stride, int rows_per_batch, float eps) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  constexpr int D = NCHUNK * 256;
+  const __nv_bfloat16* xr = x + (size_t)warp * ld_x;
+  uint4 raw[NCHUNK];
+#pragma unroll
+  for (int c = 0; c < NCHUNK; ++c) raw[c] = ldg128_stream(xr + (c * 32 + lane) * 8);
+  float v[NCHUNK][8];
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < NCHUNK; ++c) {
+    unpack8(raw[c], v[c]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += (MODE == 0) ? v[c][j] : v[c][j] * v[c][j];
+  }
+  s = group_sum<32>(s);
+  float mean = 0.f, rstd;
+  if (MODE == 0) {
+    mean = s * (1.f / D);
+    float q = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCHUNK; ++c)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float t = v[c][j] - mean;
+        q += t * t;
+      }
+    q = group_sum<32>(q);
+    rstd = rsqrtf(q * (1.f / D) + eps);
+  } else {
+    rstd = rsqrtf(s * (1.f / D) + eps);
+  }
+  const int b = warp / rows_per_batch;
+  const __nv_bfloat16* sh = (MODE == 0) ? shift + (size_t)b * mod_batch_stride : nullptr;
+  const __nv_bfloat16* sc = scale + ((MODE == 0) ? (size_t)b * mod_batch_stride : 0);
+  __nv_bfloat16* yr = y + (size_t)warp * ld_y;
+#pragma unroll
+  for (int c = 0; c < NCHUNK; ++c) {
+    const int off = (c * 32 + lane) * 8;
+    float w[8], o[8];
+    unpack8(ldg128(sc + off), w);
+    if (MODE == 0) {
+      float h[8];
+      unpack8(ldg128(sh + off), h);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mean) * rstd * (1.f + w[j]) + h[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = bf16_round(v[c][j] * rstd) * w[j];
+    }
+    stg128(yr + off, pack8(o));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: QK RMSNorm + RoPE in place on the joint qkv buffer [rows, ld] (q at col 0, k at col d).
+// A group of DH/8 lanes owns one head vector; a warp owns 32/(DH/8) consecutive head vectors.
+// Rounding order follows upstream: bf16(x*rstd) -> bf16(*w) -> fp32 complex rotate -> bf16.
+// ---------------------------------------------------------------------------------------------
+template <int DH>
+__global__ void __launch_bounds__(256) qknorm_rope_kernel(
+    __nv_bfloat16* __restrict__ qkv, int rows, int ld, int heads, int seq, int s_txt,
+    const __nv_bfloat16* __restrict__ wq_img, const __nv_bfloat16* __restrict__ wk_img,
+    const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
+    const float2* __restrict__ freqs /* [seq, DH/2] (cos, sin), joint order txt first */,
+    float eps) {
+  constexpr int LPH = DH / 8;          // lanes per head vector
+  constexpr int VPW = 32 / LPH;        // head vectors per warp
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPH;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long item = warp * VPW + lane / LPH;   // (row, qk, head), head fastest
+  const long long total = (long long)rows * 2 * heads;
+  const bool active = item < total;
+  const long long it = active ? item : total - 1;
+  const int row = (int)(it / (2 * heads));
+  const int rem = (int)(it % (2 * heads));
+  const int qk = rem / heads, head = rem % heads;
+  const int pos = row % seq;
+  const bool is_txt = pos < s_txt;
+  __nv_bfloat16* p = qkv + (size_t)row * ld + (size_t)rem * DH + sub * 8;
+  const __nv_bfloat16* w = (qk == 0) ? (is_txt ? wq_txt : wq_img) : (is_txt ? wk_txt : wk_img);
+  (void)head;
+  float v[8], wv[8];
+  unpack8(ldg128(p), v);
+  unpack8(ldg128(w + sub * 8), wv);
+  const float4* fp = reinterpret_cast<const float4*>(freqs + (size_t)pos * (DH / 2) + sub * 4);
+  const float4 f01 = fp[0], f23 = fp[1];
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) ss += v[j] * v[j];
+  ss = group_sum<LPH>(ss);
+  const float rstd = rsqrtf(ss * (1.f / DH) + eps);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = bf16_round(bf16_round(v[j] * rstd) * wv[j]);
+  const float cs[4] = {f01.x, f01.z, f23.x, f23.z};
+  const float sn[4] = {f01.y, f01.w, f23.y, f23.w};
+  float o[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float a = v[2 * j], b = v[2 * j + 1];
+    o[2 * j] = a * cs[j] - b * sn[j];
+    o[2 * j + 1] = a * sn[j] + b * cs[j];
+  }
+  if (active) stg128(p, pack8(o));
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5: one group of 8 lanes per token (64 channels = 8 lanes x 8 bf16).  Rounding follows the
+// eager bf16 pipeline op by op: comb, the two norms, their ratio, the product,
+// dt*v (dt itself rounded to bf16 by type promotion), then the fp32 accumulate and final cast.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) cfg_euler_kernel(
+    const __nv_bfloat16* __restrict__ cond, const __nv_bfloat16* __restrict__ uncond,
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, long long tokens,
+    float cfg_scale, const float* __restrict__ dt_ptr, float dt_scalar) {
+  const long long tok = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int sub = threadIdx.x & 7;
+  const bool active = tok < tokens;
+  const size_t off = (size_t)(active ? tok : tokens - 1) * 64 + sub * 8;
+  const float dt = bf16_round(dt_ptr ? *dt_ptr : dt_scalar);
+  float c[8], xv[8], v[8];
+  unpack8(ldg128_stream(cond + off), c);
+  unpack8(ldg128_stream(x + off), xv);
+  if (uncond != nullptr) {
+    float u[8], comb[8];
+    unpack8(ldg128_stream(uncond + off), u);
+    float cn = 0.f, nn = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      comb[j] = bf16_round(u[j] + bf16_round(cfg_scale * bf16_round(c[j] - u[j])));
+      cn += c[j] * c[j];
+      nn += comb[j] * comb[j];
+    }
+    cn = group_sum<8>(cn);
+    nn = group_sum<8>(nn);
+    const float ratio = bf16_round(bf16_round(sqrtf(cn)) / bf16_round(sqrtf(nn)));
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = bf16_round(comb[j] * ratio);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = c[j];
+  }
+  float o[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j] = xv[j] + bf16_round(dt * v[j]);
+  if (active) stg128(out + off, pack8(o));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Small-M linear: y[m, n] = act_out( sum_k act_in(x[m,k]) * W[n,k] + bias[n] ), M <= 32.
+// One warp per output column n: the weight row is streamed once (128-bit loads) and reused for
+// every m from registers; x stays L1/L2 resident.  HBM-bound on the weight bytes.
+// ---------------------------------------------------------------------------------------------
+template <int MT>
+__global__ void __launch_bounds__(256) small_linear_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ W,
+    const __nv_bfloat16* __restrict__ bias, __nv_bfloat16* __restrict__ y, int M, int N, int K,
+    int ld_x, int ld_y, int silu_in, int silu_out) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const int m0 = blockIdx.y * MT;
+  float acc[MT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+  const __nv_bfloat16* wr = W + (size_t)n * K;
+  for (int k = lane * 8; k < K; k += 256) {
+    float w[8];
+    unpack8(ldg128_stream(wr + k), w);
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      if (m0 + m < M) {
+        float xv[8];
+        unpack8(ldg128(x + (size_t)(m0 + m) * ld_x + k), xv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = xv[j];
+          if (silu_in) a = bf16_round(a / (1.f + __expf(-a)));
+          acc[m] = fmaf(a, w[j], acc[m]);
+        }
+      }
+    }
+  }
+  const float bv = bias ? __bfloat162float(bias[n]) : 0.f;
+#pragma unroll
+  for (int m = 0; m < MT; ++m) {
+    float s = group_sum<32>(acc[m]);
+    if (lane == 0 && m0 + m < M) {
+      s += bv;
+      if (silu_out) {
+        s = bf16_round(s);
+        s = s / (1.f + __expf(-s));
+      }
+      y[(size_t)(m0 + m) * ld_y + n] = __float2bfloat16_rn(s);
+    }
+  }
+}
+
+// t [M] fp32 (already rounded the way the caller wants) -> [M, 256] bf16 = [cos(1000 t f_k), sin]
+__global__ void timestep_sinusoid_kernel(const float* __restrict__ t, __nv_bfloat16* __restrict__ out,
+                                         int M) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M * 128) return;
+  const int m = i / 128, k = i % 128;
+  const float f = expf(-9.210340371976184f * (float)k / 128.f);
+  const float a = 1000.f * (t[m] * f);
+  out[(size_t)m * 256 + k] = __float2bfloat16_rn(cosf(a));
+  out[(size_t)m * 256 + 128 + k] = __float2bfloat16_rn(sinf(a));
+}
+
+}  // namespace qi
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+using namespace qi;
+
+#define QI_CHECK_LAUNCH()                              \
+  do {                                                 \
+    cudaError_t e__ = cudaGetLastError();              \
+    if (e__ != cudaSuccess) return QI_ERR_CUDA;        \
+  } while (0)
+
+template <int MODE>
+static int launch_norm_rows(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
+                            const void* shift, const void* scale, long long mod_stride,
+                            int rows_per_batch, float eps, cudaStream_t st) {
+  if (rows <= 0) return QI_OK;
+  if (d % 256 != 0 || ld_x % 8 != 0 || ld_y % 8 != 0) return QI_ERR_ARG;
+  const int blocks = (rows + 3) / 4;
+#define QI_NORM_CASE(NC)                                                                     \
+  case NC:                                                                                   \
+    norm_rows_kernel<NC, MODE><<<blocks, 128, 0, st>>>(                                      \
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, ld_x, ld_y,                        \
+        (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, \
+        eps);                                                                                \
+    break;
+  switch (d / 256) {
+    QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(4) QI_NORM_CASE(6) QI_NORM_CASE(8)
+    QI_NORM_CASE(12) QI_NORM_CASE(14) QI_NORM_CASE(16)
+    default: return QI_ERR_UNSUPPORTED;
+  }
+#undef QI_NORM_CASE
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_adaln_modulate(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
+                                 const void* shift, const void* scale, long long mod_batch_stride,
+                                 int rows_per_batch, float eps, cudaStream_t stream) {
+  if (!x || !y || !shift || !scale || rows_per_batch <= 0) return QI_ERR_ARG;
+  return launch_norm_rows<0>(x, y, rows, d, ld_x, ld_y, shift, scale, mod_batch_stride,
+                             rows_per_batch, eps, stream);
+}
+
+extern "C" int qi_rmsnorm_affine(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
+                                 const void* weight, float eps, cudaStream_t stream) {
+  if (!x || !y || !weight) return QI_ERR_ARG;
+  return launch_norm_rows<1>(x, y, rows, d, ld_x, ld_y, nullptr, weight, 0, 1 << 30, eps, stream);
+}
+
+extern "C" int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq,
+                              int s_txt, const void* wq_img, const void* wk_img,
+                              const void* wq_txt, const void* wk_txt, const void* freqs_cos_sin,
+                              float eps, cudaStream_t stream) {
+  if (!qkv || !wq_img || !wk_img || !wq_txt || !wk_txt || !freqs_cos_sin) return QI_ERR_ARG;
+  if (rows <= 0) return QI_OK;
+  if (ld % 8 != 0 || seq <= 0 || rows % seq != 0) return QI_ERR_ARG;
+  const long long items = (long long)rows * 2 * heads;
+  if (head_dim == 128) {
+    const long long warps = (items + 1) / 2;
+    const int blocks = (int)((warps + 7) / 8);
+    qknorm_rope_kernel<128><<<blocks, 256, 0, stream>>>(
+        (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
+        (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
+        (const float2*)freqs_cos_sin, eps);
+  } else if (head_dim == 64) {
+    const long long warps = (items + 3) / 4;
+    const int blocks = (int)((warps + 7) / 8);
+    qknorm_rope_kernel<64><<<blocks, 256, 0, stream>>>(
+        (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
+        (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
+        (const float2*)freqs_cos_sin, eps);
+  } else {
+    return QI_ERR_UNSUPPORTED;
+  }
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_cfg_euler_step(const void* cond, const void* uncond, const void* latents,
+                                 void* out, long long tokens, int channels, float true_cfg_scale,
+                                 const float* dt_dev, float dt, cudaStream_t stream) {
+  if (!cond || !latents || !out) return QI_ERR_ARG;
+  if (channels != 64) return QI_ERR_UNSUPPORTED;
+  if (tokens <= 0) return QI_OK;
+  const long long threads = tokens * 8;
+  const int blocks = (int)((threads + 255) / 256);
+  cfg_euler_kernel<<<blocks, 256, 0, stream>>>((const __nv_bfloat16*)cond,
+                                               (const __nv_bfloat16*)uncond,
+                                               (const __nv_bfloat16*)latents, (__nv_bfloat16*)out,
+                                               tokens, true_cfg_scale, dt_dev, dt);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, void* y, int M,
+                               int N, int K, int ld_x, int ld_y, int silu_in, int silu_out,
+                               cudaStream_t stream) {
+  if (!x || !W || !y) return QI_ERR_ARG;
+  if (M <= 0 || N <= 0) return QI_OK;
+  if (K % 8 != 0 || ld_x % 8 != 0) return QI_ERR_ARG;
+  dim3 grid((N + 7) / 8, (M + 3) / 4);
+  small_linear_kernel<4><<<grid, 256, 0, stream>>>(
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)W, (const __nv_bfloat16*)bias,
+      (__nv_bfloat16*)y, M, N, K, ld_x, ld_y, silu_in, silu_out);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_timestep_sinusoid(const float* t, void* out, int M, cudaStream_t stream) {
+  if (!t || !out) return QI_ERR_ARG;
+  if (M <= 0) return QI_OK;
+  timestep_sinusoid_kernel<<<(M * 128 + 127) / 128, 128, 0, stream>>>(t, (__nv_bfloat16*)out, M);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}

@@ -1,0 +1,352 @@
+// K3: persistent, warp-specialised tcgen05 bf16 GEMM for sm_100a with fused epilogues.
+//
+//   C[b, m, n] = epi( sum_k A[b, m, k] * W[n, k] + bias[n] )
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (+ TMEM owner),
+// warps 2..5 = epilogue (TMEM -> registers -> bias/GELU/gated-residual -> bf16 -> global).
+// Tile 128 x BN x 64, UMMA 128 x BN x 16, operands K-major in 128B-swizzled shared memory filled by
+// TMA, fp32 accumulators double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps
+// the main loop of tile i+1.  Up to two problems (img + txt stream) share one persistent launch.
+#include "qi_common.cuh"
+#include "../../include/qi_b200.h"
+
+namespace qi {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int GEMM_THREADS = 192;
+
+struct GemmProb {
+  void* c;
+  const __nv_bfloat16* bias;
+  const __nv_bfloat16* residual;
+  const __nv_bfloat16* gate;
+  long long ldc, c_bs, ld_res, res_bs, gate_bs;
+  int m, batch, n, k;
+  int epilogue;
+  int tiles_m;       // per batch item
+  int tiles_m_total; // tiles_m * batch
+  int tiles_n;
+  int tile_begin;    // first global tile index of this problem
+};
+
+struct GemmLaunch {
+  CUtensorMap tmap_a[2];
+  CUtensorMap tmap_b[2];
+  GemmProb prob[2];
+  int num_problems;
+  int total_tiles;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int TMEM_COLS = 2 * BN;  // 512 or 256: power of two
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct TileCoord {
+  int p, b, m0, n0;
+};
+__device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int BN) {
+  TileCoord tc;
+  tc.p = (L.num_problems > 1 && t >= L.prob[1].tile_begin) ? 1 : 0;
+  const GemmProb& P = L.prob[tc.p];
+  const int lt = t - P.tile_begin;
+  const int mt = lt % P.tiles_m_total;
+  const int nt = lt / P.tiles_m_total;
+  tc.b = mt / P.tiles_m;
+  tc.m0 = (mt % P.tiles_m) * BM;
+  tc.n0 = nt * BN;
+  return tc;
+}
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * x * (1.f + t);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full = empty_bar + Cfg::STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int p = 0; p < L.num_problems; ++p) {
+      tma_prefetch_desc(&L.tmap_a[p]);
+      tma_prefetch_desc(&L.tmap_b[p]);
+    }
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
+        const TileCoord tc = decode_tile(L, t, BN);
+        const int kblocks = L.prob[tc.p].k / BK;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* sb = sa + Cfg::A_BYTES;
+          mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          tma_load_3d(sa, &L.tmap_a[tc.p], &full_bar[stage], kb * BK, tc.m0, tc.b);
+          tma_load_2d(sb, &L.tmap_b[tc.p], &full_bar[stage], kb * BK, tc.n0);
+          if (++stage == Cfg::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
+        const TileCoord tc = decode_tile(L, t, BN);
+        const int kblocks = L.prob[tc.p].k / BK;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint32_t sb = sa + Cfg::A_BYTES;
+          const uint64_t da = make_smem_desc(sa, 0, 1024);
+          const uint64_t db = make_smem_desc(sb, 0, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // advance 16 bf16 = 32 bytes inside the 128B swizzle row: +2 in the (>>4) address field
+            mma_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == Cfg::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tc_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue warps (2..5)
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
+      const TileCoord tc = decode_tile(L, t, BN);
+      const GemmProb& P = L.prob[tc.p];
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = tc.m0 + q * 32 + lane;
+      const bool row_ok = row < P.m;
+      __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)tc.b * P.c_bs +
+                            (size_t)row * P.ldc;
+      const __nv_bfloat16* rrow =
+          P.residual ? P.residual + (size_t)tc.b * P.res_bs + (size_t)row * P.ld_res : nullptr;
+      const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)tc.b * P.gate_bs : nullptr;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(taddr + c * 32, r);
+        tmem_ld_wait();
+        if (c == BN / 32 - 1) {
+          // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        const int n_base = tc.n0 + c * 32;
+        if (n_base >= P.n) continue;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int n = n_base + g * 8;
+          if (n >= P.n) break;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+          if (P.bias) {
+            const uint4 bu = *reinterpret_cast<const uint4*>(P.bias + n);
+            const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y), b2 = unpack_bf16(bu.z),
+                         b3 = unpack_bf16(bu.w);
+            v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+            v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+          }
+          if (P.epilogue == QI_EPI_BIAS_GELU_TANH) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+          } else if (P.epilogue == QI_EPI_GATED_RESIDUAL) {
+            const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
+            const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
+                         g3 = unpack_bf16(gu.w);
+            const float gt[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+            float rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (row_ok) {
+              const uint4 ru = *reinterpret_cast<const uint4*>(rrow + n);
+              const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
+                           r3 = unpack_bf16(ru.w);
+              rs[0] = r0.x; rs[1] = r0.y; rs[2] = r1.x; rs[3] = r1.y;
+              rs[4] = r2.x; rs[5] = r2.y; rs[6] = r3.x; rs[7] = r3.y;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = rs[j] + gt[j] * v[j];
+          }
+          if (row_ok) {
+            const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
+                                       pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+            *reinterpret_cast<uint4*>(crow + n) = o;
+          }
+        }
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+}  // namespace qi
+
+using namespace qi;
+
+static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int BN, int tile_begin) {
+  if (!in.a || !in.w || !in.c) return QI_ERR_ARG;
+  if (in.m <= 0 || in.batch <= 0 || in.n <= 0 || in.k <= 0) return QI_ERR_ARG;
+  if (in.k % BK != 0 || in.n % 8 != 0) return QI_ERR_UNSUPPORTED;
+  if (in.lda % 8 != 0 || in.ldc % 8 != 0 || in.a_batch_stride % 8 != 0 || in.c_batch_stride % 8 != 0)
+    return QI_ERR_ARG;
+  if (in.epilogue < 0 || in.epilogue > 2) return QI_ERR_ARG;
+  if (in.epilogue == QI_EPI_GATED_RESIDUAL &&
+      (!in.residual || !in.gate || in.ld_res % 8 != 0 || in.res_batch_stride % 8 != 0 ||
+       in.gate_batch_stride % 8 != 0))
+    return QI_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(in.a) | reinterpret_cast<uintptr_t>(in.w) |
+       reinterpret_cast<uintptr_t>(in.c)) & 15)
+    return QI_ERR_ARG;
+  GemmProb& P = L.prob[i];
+  P.c = in.c;
+  P.bias = (const __nv_bfloat16*)in.bias;
+  P.residual = in.epilogue == QI_EPI_GATED_RESIDUAL ? (const __nv_bfloat16*)in.residual : nullptr;
+  P.gate = in.epilogue == QI_EPI_GATED_RESIDUAL ? (const __nv_bfloat16*)in.gate : nullptr;
+  P.ldc = in.ldc; P.c_bs = in.c_batch_stride;
+  P.ld_res = in.ld_res; P.res_bs = in.res_batch_stride; P.gate_bs = in.gate_batch_stride;
+  P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
+  P.epilogue = in.epilogue;
+  P.tiles_m = (in.m + BM - 1) / BM;
+  P.tiles_m_total = P.tiles_m * in.batch;
+  P.tiles_n = (in.n + BN - 1) / BN;
+  P.tile_begin = tile_begin;
+  // A: [batch, m, k]  (innermost first for the tensor map)
+  {
+    uint64_t dims[3] = {(uint64_t)in.k, (uint64_t)in.m, (uint64_t)in.batch};
+    uint64_t strides[2] = {(uint64_t)in.lda * 2, (uint64_t)(in.batch > 1 ? in.a_batch_stride : in.lda * (long long)in.m) * 2};
+    uint32_t box[3] = {BK, BM, 1};
+    int rc = qi_encode_tmap_bf16(&L.tmap_a[i], in.a, 3, dims, strides, box);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)in.k, (uint64_t)in.n};
+    uint64_t strides[1] = {(uint64_t)in.k * 2};
+    uint32_t box[2] = {BK, (uint32_t)BN};
+    int rc = qi_encode_tmap_bf16(&L.tmap_b[i], in.w, 2, dims, strides, box);
+    if (rc) return rc;
+  }
+  return QI_OK;
+}
+
+template <int BN>
+static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
+  GemmLaunch L;
+  memset(&L, 0, sizeof(L));
+  L.num_problems = num;
+  int tiles = 0;
+  for (int i = 0; i < num; ++i) {
+    int rc = fill_problem(L, i, problems[i], BN, tiles);
+    if (rc) return rc;
+    tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
+  }
+  L.total_tiles = tiles;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             GemmCfg<BN>::SMEM_BYTES) != cudaSuccess)
+      return QI_ERR_CUDA;
+    attr_set = true;
+  }
+  const int sms = qi_num_sms();
+  if (sms <= 0) return QI_ERR_CUDA;
+  const int grid = tiles < sms ? tiles : sms;
+  gemm_bf16_kernel<BN><<<grid, GEMM_THREADS, GemmCfg<BN>::SMEM_BYTES, stream>>>(L);
+  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  return QI_OK;
+}
+
+extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
+                            cudaStream_t stream) {
+  if (!problems || num_problems < 1 || num_problems > 2) return QI_ERR_ARG;
+  const int sms = qi_num_sms();
+  if (sms <= 0) return QI_ERR_CUDA;
+  // Pick BN=256 when every problem's N is a multiple of 256 and the 256-wide tiling still gives at
+  // least one full wave; otherwise BN=128 (more, smaller tiles for the short text stream).
+  long long tiles256 = 0;
+  bool ok256 = true;
+  for (int i = 0; i < num_problems; ++i) {
+    const qi_gemm_problem_t& p = problems[i];
+    if (p.n % 256 != 0) ok256 = false;
+    tiles256 += (long long)((p.m + BM - 1) / BM) * p.batch * ((p.n + 255) / 256);
+  }
+  if (ok256 && tiles256 >= sms) return launch_gemm<256>(problems, num_problems, stream);
+  return launch_gemm<128>(problems, num_problems, stream);
+}

@@ -1,0 +1,200 @@
+"""Tensor-level wrappers over the C ABI (include/qi_b200.h).  PyTorch only supplies device memory and
+the current CUDA stream; every function here enqueues exactly one hand-written sm_100a kernel and
+raises RuntimeError if the library is missing or reports an error (no fallback)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import GemmProblem, check
+
+EPI_BIAS, EPI_BIAS_GELU_TANH, EPI_GATED_RESIDUAL = 0, 1, 2
+
+# kernel launches issued through this module (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _req_bf16(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is None:
+            continue
+        if t.dtype != torch.bfloat16 or not t.is_cuda:
+            raise ValueError("expected CUDA bf16 tensors on the hot path")
+        if t.stride(-1) != 1:
+            raise ValueError("innermost dimension must be contiguous")
+
+
+def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
+                 epilogue: int = EPI_BIAS, residual: Optional[torch.Tensor] = None,
+                 gate: Optional[torch.Tensor] = None) -> GemmProblem:
+    """a: [B, M, K] or [M, K] view (row/batch strides arbitrary, K contiguous); w: [N, K] contiguous;
+    out: [B, M, N] / [M, N] view; residual like out; gate [B, N] view."""
+    _req_bf16(a, w, bias, out, residual, gate)
+    if a.dim() == 2:
+        a = a.unsqueeze(0)
+    if out.dim() == 2:
+        out = out.unsqueeze(0)
+    B, M, K = a.shape
+    N = w.shape[0]
+    if w.shape[1] != K or not w.is_contiguous() or tuple(out.shape) != (B, M, N):
+        raise ValueError(f"gemm shape mismatch: a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
+    p = GemmProblem()
+    p.a, p.lda, p.a_batch_stride = a.data_ptr(), a.stride(1), a.stride(0)
+    p.w, p.bias = w.data_ptr(), _ptr(bias)
+    p.c, p.ldc, p.c_batch_stride = out.data_ptr(), out.stride(1), out.stride(0)
+    if epilogue == EPI_GATED_RESIDUAL:
+        if residual is None or gate is None:
+            raise ValueError("gated-residual epilogue needs residual and gate")
+        if residual.dim() == 2:
+            residual = residual.unsqueeze(0)
+        if gate.dim() == 1:
+            gate = gate.unsqueeze(0)
+        p.residual, p.ld_res, p.res_batch_stride = residual.data_ptr(), residual.stride(1), residual.stride(0)
+        p.gate, p.gate_batch_stride = gate.data_ptr(), gate.stride(0)
+    p.m, p.batch, p.n, p.k, p.epilogue = M, B, N, K, epilogue
+    return p
+
+
+def gemm(problems: Sequence[GemmProblem]) -> None:
+    """One persistent tcgen05 launch for 1 or 2 problems (img + txt stream)."""
+    global launch_count
+    n = len(problems)
+    arr = (GemmProblem * n)(*problems)
+    check(_lib.lib().qi_gemm_bf16(arr, n, _stream()), "qi_gemm_bf16")
+    launch_count += 1
+
+
+def linear(a, w, bias, out=None, epilogue=EPI_BIAS, residual=None, gate=None) -> torch.Tensor:
+    if out is None:
+        out = torch.empty(*a.shape[:-1], w.shape[0], device=a.device, dtype=a.dtype)
+    gemm([gemm_problem(a, w, bias, out, epilogue, residual, gate)])
+    return out
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor,
+              softmax_scale: Optional[float] = None) -> torch.Tensor:
+    """q,k,v,out: [B, S, H, Dh] views (Dh contiguous, head stride Dh)."""
+    global launch_count
+    _req_bf16(q, k, v, out)
+    B, Sq, H, Dh = q.shape
+    Skv = k.shape[1]
+    for t in (q, k, v, out):
+        if t.stride(2) != Dh:
+            raise ValueError("heads must be packed contiguously inside a token row")
+    if k.stride() != v.stride():
+        raise ValueError("k and v must share strides")
+    scale = softmax_scale if softmax_scale is not None else Dh ** -0.5
+    check(_lib.lib().qi_attention_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, Sq, Skv, H, Dh,
+                                      q.stride(1), k.stride(1), out.stride(1), q.stride(0), k.stride(0),
+                                      out.stride(0), float(scale), _stream()), "qi_attention_fwd")
+    launch_count += 1
+    return out
+
+
+def adaln_modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor, out: torch.Tensor,
+                   rows_per_batch: int, eps: float = 1e-6) -> torch.Tensor:
+    """x/out: [rows, d] views; shift/scale: [B, d] views sharing one batch stride."""
+    global launch_count
+    _req_bf16(x, shift, scale, out)
+    rows, d = x.shape
+    if shift.stride(0) != scale.stride(0) and shift.shape[0] > 1:
+        raise ValueError("shift/scale must share the batch stride")
+    check(_lib.lib().qi_adaln_modulate(x.data_ptr(), out.data_ptr(), rows, d, x.stride(0), out.stride(0),
+                                       shift.data_ptr(), scale.data_ptr(), shift.stride(0), rows_per_batch,
+                                       float(eps), _stream()), "qi_adaln_modulate")
+    launch_count += 1
+    return out
+
+
+def rmsnorm_affine(x: torch.Tensor, weight: torch.Tensor, out: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
+    global launch_count
+    _req_bf16(x, weight, out)
+    rows, d = x.shape
+    check(_lib.lib().qi_rmsnorm_affine(x.data_ptr(), out.data_ptr(), rows, d, x.stride(0), out.stride(0),
+                                       weight.data_ptr(), float(eps), _stream()), "qi_rmsnorm_affine")
+    launch_count += 1
+    return out
+
+
+def qknorm_rope(qkv: torch.Tensor, heads: int, head_dim: int, seq: int, s_txt: int,
+                wq_img, wk_img, wq_txt, wk_txt, freqs: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
+    """qkv: [rows=B*seq, ld] view, in place.  freqs: fp32 [seq, head_dim/2, 2] (cos, sin), txt rows first."""
+    global launch_count
+    _req_bf16(qkv, wq_img, wk_img, wq_txt, wk_txt)
+    if freqs.dtype != torch.float32 or not freqs.is_contiguous() or tuple(freqs.shape) != (seq, head_dim // 2, 2):
+        raise ValueError("freqs must be contiguous fp32 [seq, head_dim/2, 2]")
+    check(_lib.lib().qi_qknorm_rope(qkv.data_ptr(), qkv.shape[0], qkv.stride(0), heads, head_dim, seq, s_txt,
+                                    wq_img.data_ptr(), wk_img.data_ptr(), wq_txt.data_ptr(), wk_txt.data_ptr(),
+                                    freqs.data_ptr(), float(eps), _stream()), "qi_qknorm_rope")
+    launch_count += 1
+    return qkv
+
+
+def cfg_euler_step(cond: torch.Tensor, uncond: Optional[torch.Tensor], latents: torch.Tensor,
+                   out: torch.Tensor, true_cfg_scale: float, dt: float = 0.0,
+                   dt_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    global launch_count
+    _req_bf16(cond, uncond, latents, out)
+    for t in (cond, uncond, latents, out):
+        if t is not None and not t.is_contiguous():
+            raise ValueError("cfg_euler_step needs contiguous tensors")
+    tokens = cond.numel() // cond.shape[-1]
+    check(_lib.lib().qi_cfg_euler_step(cond.data_ptr(), _ptr(uncond), latents.data_ptr(), out.data_ptr(), tokens,
+                                       cond.shape[-1], float(true_cfg_scale), _ptr(dt_dev), float(dt),
+                                       _stream()), "qi_cfg_euler_step")
+    launch_count += 1
+    return out
+
+
+def small_linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
+                 silu_in: bool = False, silu_out: bool = False) -> torch.Tensor:
+    global launch_count
+    _req_bf16(x, w, bias, out)
+    M, K = x.shape
+    N = w.shape[0]
+    check(_lib.lib().qi_small_linear(x.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), M, N, K, x.stride(0),
+                                     out.stride(0), int(silu_in), int(silu_out), _stream()), "qi_small_linear")
+    launch_count += 1
+    return out
+
+
+def timestep_sinusoid(t: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    global launch_count
+    if t.dtype != torch.float32 or not t.is_cuda:
+        raise ValueError("timestep must be CUDA fp32")
+    check(_lib.lib().qi_timestep_sinusoid(t.data_ptr(), out.data_ptr(), t.numel(), _stream()), "qi_timestep_sinusoid")
+    launch_count += 1
+    return out
+
+
+# ------------------------------------------------------------------ host integer tables (no GPU)
+def rope_position_ids(img_shapes: Sequence[Tuple[int, int, int]], txt_len: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    n = len(img_shapes)
+    flat = (C.c_int * (3 * n))(*[int(v) for s in img_shapes for v in s])
+    s_img = sum(f * h * w for f, h, w in img_shapes)
+    img = torch.empty(s_img, 3, dtype=torch.int32)
+    txt = torch.empty(max(txt_len, 0), 3, dtype=torch.int32)
+    rc = _lib.lib().qi_rope_position_ids(flat, n, txt_len, C.cast(img.data_ptr(), C.POINTER(C.c_int32)),
+                                         C.cast(txt.data_ptr(), C.POINTER(C.c_int32)))
+    if rc != 0:
+        raise ValueError("invalid img_shapes / text length for the 4096-entry MSRoPE table")
+    return img, txt
+
+
+def pack_latents_index(channels: int, hl: int, wl: int) -> torch.Tensor:
+    idx = torch.empty((hl // 2) * (wl // 2) * channels * 4, dtype=torch.int64)
+    rc = _lib.lib().qi_pack_latents_index(channels, hl, wl, C.cast(idx.data_ptr(), C.POINTER(C.c_int64)))
+    if rc != 0:
+        raise ValueError("latent height/width must be positive and even")
+    return idx
