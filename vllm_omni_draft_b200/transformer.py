@@ -1,0 +1,337 @@
+"""Drop-in for the transformer the reference calls every denoising step.
+
+Boundary #1: ``transformer(hidden_states=, encoder_hidden_states=,
+encoder_hidden_states_mask=, timestep=, img_shapes=, txt_seq_lens=, guidance=, return_dict=)``
+-> object with ``.sample`` — call sites src/qwen_image/runner_adapter.py:128-140 and
+src/qwen_image_gen/model.py:122-134 of the reference; the class it replaces is diffusers'
+``QwenImageTransformer2DModel`` (operator list: src/doc/archive/QwenImage_Diffusers_Interface.md).
+
+PyTorch is the host layer only: parameter storage, workspace allocation, stream.  Every FLOP of the
+forward runs in libqi_b200.so (hand-written sm_100a kernels).  Per MMDiT block the launch sequence is
+
+    K1 x2  adaLN-LN-modulate (img, txt)            -> xn
+    K3     QKV GEMM, img+txt in one persistent launch -> joint qkv [B, S, 3d] (text rows first)
+    K2     QK-RMSNorm + MSRoPE in place on qkv
+    K4     joint flash attention                    -> attn [B, S, d]
+    K3     out-proj GEMM + gated residual (in place on h / e)
+    K1 x2  adaLN-LN-modulate with mod2
+    K3     MLP-up GEMM + GELU-tanh
+    K3     MLP-down GEMM + gated residual (in place)
+
+All 2L+1 modulation Linears share one stacked weight [L*12d + 2d, d]; one HBM-bound launch produces
+the whole modulation vector of a forward, or — hoisted — one tcgen05 GEMM produces it for every
+step of a schedule before the loop starts (temb depends only on t).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from types import SimpleNamespace
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import ops, rope
+from .config import MMDiTConfig
+
+
+@dataclass
+class Transformer2DModelOutput:
+    sample: torch.Tensor
+
+
+class _Workspace:
+    def __init__(self, cfg: MMDiTConfig, B: int, s_img: int, s_txt: int, device, dtype):
+        d = cfg.inner_dim
+        S = s_img + s_txt
+        e = lambda *shape: torch.empty(*shape, device=device, dtype=dtype)
+        self.h = e(B, s_img, d)
+        self.e = e(B, s_txt, d)
+        self.xn_img = e(B, s_img, d)
+        self.xn_txt = e(B, s_txt, d)
+        self.txt_normed = e(B, s_txt, cfg.joint_attention_dim)
+        self.qkv = e(B, S, 3 * d)
+        self.attn = e(B, S, d)
+        self.mlp_img = e(B, s_img, 4 * d)
+        self.mlp_txt = e(B, s_txt, 4 * d)
+        self.sinus = e(B, 256)
+        self.t1 = e(B, d)
+        self.temb = e(B, d)
+        self.t32 = torch.empty(B, device=device, dtype=torch.float32)
+
+
+class B200QwenImageTransformer2DModel(nn.Module):
+    def __init__(self, config: Optional[MMDiTConfig] = None, device="cuda", dtype=torch.bfloat16):
+        super().__init__()
+        if dtype != torch.bfloat16:
+            raise ValueError("the B200 hot path computes in bf16 (fp32 accumulate) only")
+        self.cfg = config or MMDiTConfig()
+        cfg = self.cfg
+        d, L = cfg.inner_dim, cfg.num_layers
+        self.config = SimpleNamespace(in_channels=cfg.in_channels, out_channels=cfg.out_channels,
+                                      guidance_embeds=cfg.guidance_embeds, num_layers=L,
+                                      attention_head_dim=cfg.attention_head_dim,
+                                      num_attention_heads=cfg.num_attention_heads,
+                                      joint_attention_dim=cfg.joint_attention_dim,
+                                      patch_size=cfg.patch_size, axes_dims_rope=cfg.axes_dims_rope)
+        self._attention_backend = "qi_tcgen05_flash"
+
+        def P(*shape):
+            return nn.Parameter(torch.empty(*shape, device=device, dtype=dtype), requires_grad=False)
+
+        self.img_in_w, self.img_in_b = P(d, cfg.in_channels), P(d)
+        self.txt_norm_w = P(cfg.joint_attention_dim)
+        self.txt_in_w, self.txt_in_b = P(d, cfg.joint_attention_dim), P(d)
+        self.time_w1, self.time_b1 = P(d, 256), P(d)
+        self.time_w2, self.time_b2 = P(d, d), P(d)
+        # stacked modulation: rows [(l*2+s)*6d, +6d) for block l stream s (0 img, 1 txt); last 2d = norm_out
+        self.n_mod = L * 12 * d + 2 * d
+        self.mod_w, self.mod_b = P(self.n_mod, d), P(self.n_mod)
+        self.qkv_w = P(L, 2, 3 * d, d)      # [block, stream, (q|k|v) out, in]
+        self.qkv_b = P(L, 2, 3 * d)
+        self.qk_norm_w = P(L, 4, cfg.attention_head_dim)   # norm_q, norm_k, norm_added_q, norm_added_k
+        self.out_w, self.out_b = P(L, 2, d, d), P(L, 2, d)
+        self.mlp_up_w, self.mlp_up_b = P(L, 2, 4 * d, d), P(L, 2, 4 * d)
+        self.mlp_down_w, self.mlp_down_b = P(L, 2, d, 4 * d), P(L, 2, d)
+        self.proj_out_w, self.proj_out_b = P(cfg.proj_out_dim, d), P(cfg.proj_out_dim)
+        self._ws: Dict[Tuple[int, int, int], _Workspace] = {}
+        self._freqs: Dict[tuple, torch.Tensor] = {}
+        self._mod_table: Optional[torch.Tensor] = None      # [steps, n_mod] hoisted modulation
+        self._mod_steps: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ host-layer conveniences
+    @property
+    def dtype(self):
+        return self.img_in_w.dtype
+
+    @property
+    def device(self):
+        return self.img_in_w.device
+
+    def set_attention_backend(self, name: str) -> None:
+        """Reference selects '_flash_3_hub' (test_performance.py:324); here there is exactly one
+        attention kernel (qi_attention_fwd), so the name is recorded and otherwise ignored."""
+        self._attention_backend = str(name)
+
+    @classmethod
+    def from_pretrained(cls, model_id, subfolder: Optional[str] = None, torch_dtype=torch.bfloat16,
+                        device_map=None, config: Optional[MMDiTConfig] = None, device="cuda"):
+        """Host-layer weight loading (reference: model.py:52-57).  Accepts a local directory holding
+        diffusers-named ``*.safetensors`` shards; there is no network access to a hub."""
+        import glob
+        import os
+        path = os.path.join(model_id, subfolder) if subfolder else model_id
+        files = sorted(glob.glob(os.path.join(path, "*.safetensors")))
+        if not files:
+            raise RuntimeError(f"Failed to load QwenImage components: no safetensors under {path!r}")
+        try:
+            from safetensors.torch import load_file
+        except ImportError as e:  # pragma: no cover
+            raise ImportError("safetensors is required to load checkpoints") from e
+        sd = {}
+        for f in files:
+            sd.update(load_file(f))
+        m = cls(config, device=device, dtype=torch_dtype)
+        m.load_diffusers_state_dict(sd)
+        return m
+
+    @torch.no_grad()
+    def load_diffusers_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        """Pack a diffusers-named state dict into the fused layout."""
+        cfg, d = self.cfg, self.cfg.inner_dim
+        cp = lambda dst, src: dst.copy_(src.to(dst.dtype))
+        cp(self.img_in_w, sd["img_in.weight"]); cp(self.img_in_b, sd["img_in.bias"])
+        cp(self.txt_norm_w, sd["txt_norm.weight"])
+        cp(self.txt_in_w, sd["txt_in.weight"]); cp(self.txt_in_b, sd["txt_in.bias"])
+        t = "time_text_embed.timestep_embedder."
+        cp(self.time_w1, sd[t + "linear_1.weight"]); cp(self.time_b1, sd[t + "linear_1.bias"])
+        cp(self.time_w2, sd[t + "linear_2.weight"]); cp(self.time_b2, sd[t + "linear_2.bias"])
+        for l in range(cfg.num_layers):
+            p = f"transformer_blocks.{l}."
+            for s, name in enumerate(("img_mod.1", "txt_mod.1")):
+                r0 = (l * 2 + s) * 6 * d
+                cp(self.mod_w[r0:r0 + 6 * d], sd[p + name + ".weight"])
+                cp(self.mod_b[r0:r0 + 6 * d], sd[p + name + ".bias"])
+            for s, names in enumerate((("to_q", "to_k", "to_v"), ("add_q_proj", "add_k_proj", "add_v_proj"))):
+                for j, n in enumerate(names):
+                    cp(self.qkv_w[l, s, j * d:(j + 1) * d], sd[p + "attn." + n + ".weight"])
+                    cp(self.qkv_b[l, s, j * d:(j + 1) * d], sd[p + "attn." + n + ".bias"])
+            for j, n in enumerate(("norm_q", "norm_k", "norm_added_q", "norm_added_k")):
+                cp(self.qk_norm_w[l, j], sd[p + "attn." + n + ".weight"])
+            for s, n in enumerate(("attn.to_out.0", "attn.to_add_out")):
+                cp(self.out_w[l, s], sd[p + n + ".weight"]); cp(self.out_b[l, s], sd[p + n + ".bias"])
+            for s, n in enumerate(("img_mlp", "txt_mlp")):
+                cp(self.mlp_up_w[l, s], sd[p + n + ".net.0.proj.weight"])
+                cp(self.mlp_up_b[l, s], sd[p + n + ".net.0.proj.bias"])
+                cp(self.mlp_down_w[l, s], sd[p + n + ".net.2.weight"])
+                cp(self.mlp_down_b[l, s], sd[p + n + ".net.2.bias"])
+        r0 = cfg.num_layers * 12 * d
+        cp(self.mod_w[r0:], sd["norm_out.linear.weight"]); cp(self.mod_b[r0:], sd["norm_out.linear.bias"])
+        cp(self.proj_out_w, sd["proj_out.weight"]); cp(self.proj_out_b, sd["proj_out.bias"])
+        self._mod_table = None
+
+    @torch.no_grad()
+    def init_random_(self, seed: int = 0, weight_std: float = 0.02) -> "B200QwenImageTransformer2DModel":
+        """Random-init on the device for benchmarking at 20B scale (Linear.weight
+        ~ N(0, 0.02^2), bias 0, norm weights 1).  Uses the device generator, not the CPU one."""
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        for name, p in self.named_parameters():
+            if name in ("txt_norm_w", "qk_norm_w"):
+                p.fill_(1.0)
+            elif name.endswith("_b"):
+                p.zero_()
+            else:
+                flat = p.view(-1)
+                step = 1 << 28
+                for i in range(0, flat.numel(), step):
+                    n = min(step, flat.numel() - i)
+                    flat[i:i + n] = (torch.randn(n, device=self.device, generator=g) * weight_std).to(p.dtype)
+        self._mod_table = None
+        return self
+
+    # ------------------------------------------------------------------ modulation
+    def _time_embed(self, t32: torch.Tensor, ws_sinus, ws_t1, ws_temb) -> torch.Tensor:
+        ops.timestep_sinusoid(t32, ws_sinus)
+        ops.small_linear(ws_sinus, self.time_w1, self.time_b1, ws_t1, silu_out=True)
+        ops.small_linear(ws_t1, self.time_w2, self.time_b2, ws_temb)
+        return ws_temb
+
+    @torch.no_grad()
+    def prepare_schedule(self, timesteps_over_1000: torch.Tensor) -> None:
+        """Hoist every modulation Linear out of the denoising loop: temb depends only on t, so the
+        [steps, L*12d+2d] modulation table is one tcgen05 GEMM over all steps.  `timesteps_over_1000`
+        holds the values the pipeline would pass as `timestep` (already rounded to bf16)."""
+        t = timesteps_over_1000.to(self.device, torch.bfloat16).to(torch.float32).contiguous()
+        n, d = t.numel(), self.cfg.inner_dim
+        e = lambda *s: torch.empty(*s, device=self.device, dtype=self.dtype)
+        sinus, t1, temb = e(n, 256), e(n, d), e(n, d)
+        self._time_embed(t, sinus, t1, temb)
+        silu = torch.nn.functional.silu(temb)   # host-layer glue on [steps, d]; 0.3 MB, once per image
+        table = e(n, self.n_mod)
+        ops.gemm([ops.gemm_problem(silu, self.mod_w, self.mod_b, table, ops.EPI_BIAS)])
+        self._mod_table, self._mod_steps = table, t
+
+    def clear_schedule(self) -> None:
+        self._mod_table = self._mod_steps = None
+
+    def _modulation(self, ws: _Workspace, timestep: torch.Tensor, B: int, step_index: Optional[int]):
+        """Returns (mod [rows, n_mod] view, batch_stride) — batch_stride 0 broadcasts one row."""
+        if step_index is not None and self._mod_table is not None:
+            return self._mod_table[step_index:step_index + 1], 0
+        ws.t32.copy_(timestep.to(self.device).to(self.dtype).to(torch.float32))   # upstream rounds t to bf16
+        temb = self._time_embed(ws.t32, ws.sinus, ws.t1, ws.temb)
+        key = ("mod", B)
+        if key not in self._freqs:
+            self._freqs[key] = torch.empty(B, self.n_mod, device=self.device, dtype=self.dtype)
+        mod = self._freqs[key]
+        ops.small_linear(temb, self.mod_w, self.mod_b, mod, silu_in=True)
+        return mod, self.n_mod
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def forward(self, hidden_states: torch.Tensor, encoder_hidden_states: torch.Tensor = None,
+                encoder_hidden_states_mask: torch.Tensor = None, timestep: torch.Tensor = None,
+                img_shapes=None, txt_seq_lens=None, guidance: torch.Tensor = None,
+                attention_kwargs=None, controlnet_block_samples=None, return_dict: bool = True,
+                _step_index: Optional[int] = None, _mod_override: Optional[torch.Tensor] = None):
+        cfg = self.cfg
+        if hidden_states.dim() != 3 or hidden_states.shape[-1] != cfg.in_channels:
+            raise ValueError(f"hidden_states must be [B, S_img, {cfg.in_channels}]")
+        if encoder_hidden_states is None or encoder_hidden_states.dim() != 3 \
+                or encoder_hidden_states.shape[-1] != cfg.joint_attention_dim:
+            raise ValueError(f"encoder_hidden_states must be [B, S_txt, {cfg.joint_attention_dim}]")
+        if controlnet_block_samples is not None:
+            raise NotImplementedError("controlnet residuals are outside the hot path")
+        if timestep is None and _step_index is None:
+            raise ValueError("timestep is required")
+        B, s_img, _ = hidden_states.shape
+        s_txt = encoder_hidden_states.shape[1]
+        if encoder_hidden_states.shape[0] != B:
+            raise ValueError("Batch size mismatch between latents and prompt embeddings")
+        d, H, Dh, L = cfg.inner_dim, cfg.num_attention_heads, cfg.attention_head_dim, cfg.num_layers
+        S = s_txt + s_img
+        if img_shapes is None:
+            side = int(round(math.sqrt(s_img)))
+            if side * side != s_img:
+                raise ValueError("img_shapes is required for non-square token grids")
+            shapes = ((1, side, side),)
+        else:
+            shapes = rope.normalize_img_shapes(img_shapes)
+        if sum(f * h * w for f, h, w in shapes) != s_img:
+            raise ValueError("img_shapes does not match the number of image tokens")
+        max_txt = int(max(txt_seq_lens)) if txt_seq_lens is not None else s_txt
+        if max_txt != s_txt:
+            raise ValueError("max(txt_seq_lens) must equal the text sequence length")
+        dev, dt = self.device, self.dtype
+        x_in = hidden_states.to(dev, dt).contiguous()
+        enc = encoder_hidden_states.to(dev, dt).contiguous()
+
+        key = (B, s_img, s_txt)
+        ws = self._ws.get(key)
+        if ws is None:
+            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
+        fkey = (shapes, s_txt)
+        freqs = self._freqs.get(fkey)
+        if freqs is None:
+            freqs = self._freqs[fkey] = rope.joint_cos_sin(cfg.axes_dims_rope, cfg.rope_theta, shapes, s_txt).to(dev)
+
+        if _mod_override is not None:
+            mod, mbs = _mod_override, 0
+        else:
+            mod, mbs = self._modulation(ws, timestep, B, _step_index)
+
+        def mod_slices(row0):
+            # (shift, scale, gate) views [Bm, d] of one adaLN triple starting at column row0
+            return mod[:, row0:row0 + d], mod[:, row0 + d:row0 + 2 * d], mod[:, row0 + 2 * d:row0 + 3 * d]
+
+        def bview(t):  # [1 or B, d] view whose batch stride is 0 when the row is shared
+            return t if mbs != 0 else t.expand(B, d)
+
+        # input projections
+        ops.rmsnorm_affine(enc.view(B * s_txt, -1), self.txt_norm_w, ws.txt_normed.view(B * s_txt, -1))
+        ops.gemm([ops.gemm_problem(x_in, self.img_in_w, self.img_in_b, ws.h),
+                  ops.gemm_problem(ws.txt_normed, self.txt_in_w, self.txt_in_b, ws.e)])
+        h, e = ws.h, ws.e
+        h2, e2 = h.view(B * s_img, d), e.view(B * s_txt, d)
+        xi2, xt2 = ws.xn_img.view(B * s_img, d), ws.xn_txt.view(B * s_txt, d)
+        qkv_img, qkv_txt = ws.qkv[:, s_txt:], ws.qkv[:, :s_txt]
+        att_img, att_txt = ws.attn[:, s_txt:], ws.attn[:, :s_txt]
+        q = ws.qkv[:, :, 0:d].unflatten(-1, (H, Dh))
+        k = ws.qkv[:, :, d:2 * d].unflatten(-1, (H, Dh))
+        v = ws.qkv[:, :, 2 * d:3 * d].unflatten(-1, (H, Dh))
+        attn4 = ws.attn.unflatten(-1, (H, Dh))
+        G = ops.EPI_GATED_RESIDUAL
+        for l in range(L):
+            bi, bt = (l * 2) * 6 * d, (l * 2 + 1) * 6 * d
+            sh_i1, sc_i1, g_i1 = mod_slices(bi)
+            sh_i2, sc_i2, g_i2 = mod_slices(bi + 3 * d)
+            sh_t1, sc_t1, g_t1 = mod_slices(bt)
+            sh_t2, sc_t2, g_t2 = mod_slices(bt + 3 * d)
+            ops.adaln_modulate(h2, bview(sh_i1), bview(sc_i1), xi2, s_img)
+            ops.adaln_modulate(e2, bview(sh_t1), bview(sc_t1), xt2, s_txt)
+            ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
+                      ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
+            nw = self.qk_norm_w[l]
+            ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
+            ops.attention(q, k, v, attn4)
+            ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
+                      ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
+            ops.adaln_modulate(h2, bview(sh_i2), bview(sc_i2), xi2, s_img)
+            ops.adaln_modulate(e2, bview(sh_t2), bview(sc_t2), xt2, s_txt)
+            ops.gemm([ops.gemm_problem(ws.xn_img, self.mlp_up_w[l, 0], self.mlp_up_b[l, 0], ws.mlp_img,
+                                       ops.EPI_BIAS_GELU_TANH),
+                      ops.gemm_problem(ws.xn_txt, self.mlp_up_w[l, 1], self.mlp_up_b[l, 1], ws.mlp_txt,
+                                       ops.EPI_BIAS_GELU_TANH)])
+            ops.gemm([ops.gemm_problem(ws.mlp_img, self.mlp_down_w[l, 0], self.mlp_down_b[l, 0], h, G, h,
+                                       bview(g_i2)),
+                      ops.gemm_problem(ws.mlp_txt, self.mlp_down_w[l, 1], self.mlp_down_b[l, 1], e, G, e,
+                                       bview(g_t2))])
+        # norm_out (AdaLayerNormContinuous: chunk order is (scale, shift)) + proj_out
+        r0 = L * 12 * d
+        ops.adaln_modulate(h2, bview(mod[:, r0 + d:r0 + 2 * d]), bview(mod[:, r0:r0 + d]), xi2, s_img)
+        out = torch.empty(B, s_img, cfg.proj_out_dim, device=dev, dtype=dt)
+        ops.gemm([ops.gemm_problem(ws.xn_img, self.proj_out_w, self.proj_out_b, out)])
+        if not return_dict:
+            return (out,)
+        return Transformer2DModelOutput(sample=out)
