@@ -1,0 +1,179 @@
+"""CPU suite (-m "not gpu"): oracle vs committed golden vectors, bit-exact integer tables through the
+C ABI, host logic (scheduler, packing, validation), and the shared library's exported symbols."""
+import ctypes
+import hashlib
+import os
+import re
+
+import pytest
+import torch
+
+from oracle import qwen_image_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def sha(t):
+    return hashlib.sha256(t.contiguous().numpy().tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def built():
+    import __graft_entry__ as g
+    g.build()
+    from vllm_omni_draft_b200 import _lib
+    return _lib
+
+
+# ------------------------------------------------------------------ oracle vs golden
+def test_oracle_reproduces_golden_forward_and_loop():
+    gold = torch.load(os.path.join(GOLD, "tiny_cfg1.pt"))
+    cfg = O.tiny_config()
+    sd = O.init_state_dict(cfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
+    lat, cond, uncond, mask, shapes = O.synthetic_inputs(cfg, 256, 256, 32)
+    fwd = O.transformer_forward(sd, cfg, lat, cond, mask, torch.tensor([0.7446]).bfloat16().float(), shapes, [32])
+    assert O.rel_l2(fwd, gold["forward_sample"]) < 1e-5
+    final, trace = O.denoise_loop(sd, cfg, lat, cond, mask, uncond, mask, 4, 4.0, img_shapes=shapes, return_all=True)
+    assert O.rel_l2(torch.stack(trace), gold["step_latents"]) < 1e-5
+    assert O.rel_l2(final, gold["final"]) < 1e-5
+
+
+def test_oracle_scheduler_known_answers():
+    gold = torch.load(os.path.join(GOLD, "tiny_cfg1.pt"))
+    ts, sig = O.flowmatch_sigmas(4, 256)
+    assert torch.equal(sig, gold["sigmas4"]) and torch.equal(ts, gold["timesteps4"])
+    # closed-form facts of the Qwen-Image schedule: starts at 1, terminal sigma 0.02, trailing 0
+    ts50, sig50 = O.flowmatch_sigmas(50, 4096)
+    assert sig50[0] == 1.0 and abs(float(sig50[-2]) - 0.02) < 1e-6 and sig50[-1] == 0
+    assert torch.all(sig50[1:] < sig50[:-1])
+    assert abs(O.calculate_shift(4096) - 0.693548) < 1e-5      # mu ~= 0.6935 at 4096 tokens
+    assert torch.equal(sig50, gold["sigmas50_4096"])
+
+
+def test_oracle_bf16_tracks_fp32():
+    cfg = O.tiny_config()
+    sd = O.init_state_dict(cfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
+    lat, cond, uncond, mask, shapes = O.synthetic_inputs(cfg, 256, 256, 32)
+    ref = O.denoise_loop(sd, cfg, lat, cond, mask, uncond, mask, 2, 4.0, img_shapes=shapes)
+    sdb = {k: v.bfloat16() for k, v in sd.items()}
+    got = O.denoise_loop(sdb, cfg, lat.bfloat16(), cond.bfloat16(), mask, uncond.bfloat16(), mask, 2, 4.0,
+                         img_shapes=shapes)
+    assert O.rel_l2(got.float(), ref) < 1e-2
+
+
+def test_oracle_rope_and_pack_properties():
+    # rotation preserves the norm of every (even, odd) pair; pack/unpack is a bijection
+    cfg = O.tiny_config()
+    img_f, txt_f = O.rope_freqs(cfg, [(1, 5, 7)], 9)
+    x = torch.randn(1, 35, 4, 64)
+    y = O.apply_rope(x, img_f)
+    assert torch.allclose(x.view(1, 35, 4, 32, 2).norm(dim=-1), y.view(1, 35, 4, 32, 2).norm(dim=-1), atol=1e-5)
+    lat = torch.randn(2, 16, 1, 10, 14)
+    assert torch.equal(O.unpack_latents(O.pack_latents(lat.transpose(1, 2)), 10, 14), lat)
+    with pytest.raises(ValueError):
+        O.rope_position_ids([(1, 128, 128)], 4096)
+
+
+# ------------------------------------------------------------------ C ABI: load + symbols
+def test_library_exports_every_declared_symbol(built):
+    header = open(os.path.join(ROOT, "include", "qi_b200.h")).read()
+    declared = set(re.findall(r"\b(qi_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(built.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in qi_b200.h but not exported"
+    assert declared == set(built.EXPORTED_SYMBOLS)
+    assert built.lib().qi_version() == 100
+
+
+def test_compute_entry_points_fail_loudly_without_gpu(built):
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from vllm_omni_draft_b200 import _lib
+    p = _lib.GemmProblem()
+    assert built.lib().qi_gemm_bf16(ctypes.byref(p), 1, None) != 0
+    assert built.lib().qi_device_sm_count() < 0
+    with pytest.raises(RuntimeError):
+        _lib.check(-2, "qi_gemm_bf16")
+
+
+# ------------------------------------------------------------------ bit-exact integer tables
+def test_rope_position_ids_bit_exact(built):
+    from vllm_omni_draft_b200 import ops
+    tables = torch.load(os.path.join(GOLD, "int_tables.pt"))
+    for (f, h, w), txt in (((1, 16, 16), 32), ((1, 64, 64), 512), ((1, 83, 83), 512), ((1, 128, 128), 512)):
+        ip, tp = ops.rope_position_ids([(f, h, w)], txt)
+        oi, ot = O.rope_position_ids([(f, h, w)], txt)
+        assert torch.equal(ip.long(), oi) and torch.equal(tp.long(), ot)
+        assert sha(torch.cat([tp, ip])) == tables[f"rope_sha_{h}x{w}_{txt}"]
+    ip, tp = ops.rope_position_ids([(1, 16, 16)], 32)
+    assert torch.equal(torch.cat([tp, ip]), tables["rope_pos_16x16_32"])
+    ip, tp = ops.rope_position_ids([(1, 8, 8), (1, 6, 10)], 7)
+    assert torch.equal(torch.cat([tp, ip]), tables["rope_pos_two_images"])
+    with pytest.raises(ValueError):
+        ops.rope_position_ids([(1, 128, 128)], 4096)      # 64 + 4096 > 4096-entry table
+    ops.rope_position_ids([(1, 128, 128)], 4032)          # the reference's "max 4064"-style bound
+
+
+def test_pack_index_bit_exact(built):
+    from vllm_omni_draft_b200 import ops
+    from vllm_omni_draft_b200.pipeline import pack_latents, unpack_latents
+    tables = torch.load(os.path.join(GOLD, "int_tables.pt"))
+    for hl in (32, 128, 166):
+        idx = ops.pack_latents_index(16, hl, hl)
+        assert sha(idx) == tables[f"pack_sha_{hl}"]
+        src = torch.arange(16 * hl * hl, dtype=torch.int64).view(1, 16, hl, hl)
+        assert torch.equal(pack_latents(src).reshape(-1), idx)
+    assert torch.equal(ops.pack_latents_index(16, 32, 32).int(), tables["pack_idx_32"])
+    x = torch.randn(3, 16, 1, 12, 20)
+    assert torch.equal(unpack_latents(pack_latents(x.transpose(1, 2)), 12, 20), x)
+    with pytest.raises(ValueError):
+        ops.pack_latents_index(16, 31, 32)
+
+
+def test_joint_rope_table_matches_oracle_bitwise(built):
+    from vllm_omni_draft_b200 import rope
+    for cfg, shapes, txt in ((O.tiny_config(), [(1, 16, 16)], 32), (O.qwen_image_20b_config(), [(1, 9, 13)], 21)):
+        tab = rope.joint_cos_sin(cfg.axes_dims_rope, cfg.rope_theta, shapes, txt)
+        i, t = O.rope_freqs(cfg, shapes, txt)
+        assert torch.equal(tab, torch.view_as_real(torch.cat([t, i], 0)))
+    assert rope.normalize_img_shapes([[(1, 4, 4)], [(1, 4, 4)]]) == ((1, 4, 4),)
+    assert rope.normalize_img_shapes([(1, 4, 4)]) == ((1, 4, 4),)
+
+
+# ------------------------------------------------------------------ host logic
+def test_schedule_matches_oracle():
+    from vllm_omni_draft_b200.pipeline import FlowMatchEulerSchedule, calculate_shift, latent_hw
+    for n, s in ((4, 256), (50, 4096), (50, 6889), (28, 16384), (2, 4096)):
+        sch = FlowMatchEulerSchedule(n, s)
+        ts, sig = O.flowmatch_sigmas(n, s)
+        assert torch.equal(sch.sigmas, sig) and torch.equal(sch.timesteps, ts)
+        assert torch.equal(sch.dts, sig[1:] - sig[:-1])
+    assert calculate_shift(4096) == O.calculate_shift(4096)
+    assert latent_hw(1024, 1024) == (128, 128) and latent_hw(1328, 1328) == (166, 166)
+    with pytest.raises(ValueError):
+        FlowMatchEulerSchedule(0, 256)
+
+
+def test_config_and_input_validation():
+    from vllm_omni_draft_b200.config import MMDiTConfig, RunConfig
+    from vllm_omni_draft_b200.adapter import QwenImageCustomInputs, validate_custom_inputs
+    assert MMDiTConfig().inner_dim == 3072 and MMDiTConfig.tiny().inner_dim == 256
+    with pytest.raises(ValueError):
+        RunConfig.from_env(bogus=1)
+    ok = QwenImageCustomInputs(prompt_embeds=torch.zeros(1, 4, 8), prompt_embeds_mask=torch.ones(1, 4),
+                               image_latents=torch.zeros(1, 16, 4, 4))
+    validate_custom_inputs(ok)
+    for bad in (dict(prompt_embeds=torch.zeros(4, 8)), dict(prompt_embeds_mask=torch.ones(4)),
+                dict(image_latents=torch.zeros(16, 4, 4)), dict(prompt_embeds_mask=torch.ones(2, 4))):
+        kw = dict(prompt_embeds=torch.zeros(1, 4, 8), prompt_embeds_mask=torch.ones(1, 4),
+                  image_latents=torch.zeros(1, 16, 4, 4))
+        kw.update(bad)
+        with pytest.raises(ValueError):
+            validate_custom_inputs(QwenImageCustomInputs(**kw))
+    with pytest.raises(ValueError):
+        validate_custom_inputs(QwenImageCustomInputs(prompt_embeds=torch.zeros(1, 4, 8),
+                                                     prompt_embeds_mask=torch.ones(1, 4),
+                                                     image_latents=torch.zeros(1, 16, 4, 4),
+                                                     img_shapes=[(1, 2, 2)], txt_seq_lens=[4, 4]))

@@ -1,0 +1,290 @@
+"""CFG-parallel / Ulysses sequence-parallel launcher (one process per GPU, torch.distributed + NCCL).
+
+The reference has no parallelism of any kind; this is the partitioning
+BASELINE.json's north_star asks for:
+
+* CFG-parallel (2 branches): ranks of branch 0 run the cond forward, branch 1 the uncond forward;
+  ONE collective per step — an all-gather of the local noise-prediction shard inside each
+  (cond, uncond) pair — after which both ranks run the fused CFG+Euler kernel redundantly on
+  identical inputs, so the latents never need a broadcast.
+* Ulysses SP (degree P inside a branch): the joint [txt; img] token sequence is sharded over P
+  ranks; every op except attention is token-local.  Around attention the head<->sequence all-to-all
+  turns [S/P tokens, H heads] into [S tokens, H/P heads] and back (NCCL all_to_all_single over
+  NVLink).  Key order after the exchange is rank-major, which is harmless: attention without a mask
+  is invariant to key order and RoPE has already been applied.
+
+Rank layout for world = 2 * P:  branch = rank // P,  sp_rank = rank % P.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def init_distributed(n_gpus: int) -> Tuple[int, int, int]:
+    """Reads RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* (torchrun); returns (world, rank, local_rank)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    if n_gpus != world and world > 1:
+        raise ValueError(f"--gpus {n_gpus} does not match WORLD_SIZE {world}")
+    return world, rank, local_rank
+
+
+@dataclass
+class ParallelLayout:
+    world: int
+    rank: int
+    cfg_degree: int       # 1 or 2
+    sp_degree: int
+    branch: int           # 0 cond, 1 uncond
+    sp_rank: int
+
+    @staticmethod
+    def make(world: int, rank: int, do_cfg: bool = True) -> "ParallelLayout":
+        if world < 1 or rank < 0 or rank >= world:
+            raise ValueError("bad world/rank")
+        cfg_degree = 2 if (do_cfg and world >= 2 and world % 2 == 0) else 1
+        sp = world // cfg_degree
+        return ParallelLayout(world, rank, cfg_degree, sp, rank // sp if cfg_degree == 2 else 0, rank % sp)
+
+    def sp_ranks(self) -> List[int]:
+        base = self.branch * self.sp_degree if self.cfg_degree == 2 else 0
+        return list(range(base, base + self.sp_degree))
+
+    def pair_ranks(self) -> List[int]:
+        return [self.sp_rank, self.sp_degree + self.sp_rank] if self.cfg_degree == 2 else [self.rank]
+
+
+def shard_bounds(n: int, parts: int, idx: int) -> Tuple[int, int]:
+    """Even split; Ulysses here requires divisibility (ragged shards are SURVEY §7 'hard part')."""
+    if n % parts != 0:
+        raise ValueError(f"sequence length {n} is not divisible by the sequence-parallel degree {parts}")
+    step = n // parts
+    return idx * step, (idx + 1) * step
+
+
+# ------------------------------------------------------------------ Ulysses exchanges (backend-agnostic)
+class UlyssesContext:
+    """head<->sequence all-to-all around attention for one sequence-parallel group."""
+
+    def __init__(self, group, size: int, rank: int):
+        self.group, self.size, self.rank = group, size, rank
+
+    def scatter_heads(self, qkv_local: torch.Tensor, heads: int, head_dim: int,
+                      send: Optional[torch.Tensor] = None, recv: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[S_loc, 3*H*Dh] (token-sharded, all heads) -> [P*S_loc, 3, H/P, Dh] (all tokens, rank-major
+        order, local heads)."""
+        P = self.size
+        s_loc = qkv_local.shape[0]
+        hs = heads // P
+        src = qkv_local.view(s_loc, 3, P, hs, head_dim).permute(2, 0, 1, 3, 4)
+        if send is None:
+            send = torch.empty(P, s_loc, 3, hs, head_dim, device=qkv_local.device, dtype=qkv_local.dtype)
+        send.copy_(src)
+        if recv is None:
+            recv = torch.empty_like(send)
+        dist.all_to_all_single(recv.view(-1), send.view(-1), group=self.group)
+        return recv.view(P * s_loc, 3, hs, head_dim)
+
+    def gather_heads(self, o_full: torch.Tensor, recv: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[P*S_loc, H/P, Dh] (all tokens, local heads) -> [P, S_loc, H/P*Dh]: chunk p holds head group
+        p of the local tokens (the out-projection GEMM reads it as a K-chunked A operand)."""
+        P = self.size
+        s_loc = o_full.shape[0] // P
+        send = o_full.reshape(P, s_loc, -1)
+        if recv is None:
+            recv = torch.empty_like(send)
+        dist.all_to_all_single(recv.view(-1), send.view(-1), group=self.group)
+        return recv
+
+
+# ------------------------------------------------------------------ denoiser
+class ParallelDenoiser:
+    """Owns one rank's model replica and denoising session; `step(i)` advances the (local shard of
+    the) latents by one scheduler step on every rank."""
+
+    def __init__(self, cfg, device, world: int = 1, rank: int = 0, seed: int = 0, use_cuda_graph: bool = True,
+                 state_dict=None):
+        from .pipeline import B200QwenImagePipeline
+        from .transformer import B200QwenImageTransformer2DModel
+        self.cfg, self.device, self.world, self.rank = cfg, device, world, rank
+        self.layout = ParallelLayout.make(world, rank)
+        self.tr = B200QwenImageTransformer2DModel(cfg, device=device)
+        if state_dict is not None:
+            self.tr.load_diffusers_state_dict(state_dict)
+        else:
+            self.tr.init_random_(seed)            # same seed on every rank -> replicated weights
+        self.pipe = B200QwenImagePipeline(self.tr)
+        self.use_cuda_graph = use_cuda_graph and world == 1
+        self.sp_group = self.pair_group = None
+        if world > 1:
+            lay = self.layout
+            # every rank must create every group, in the same order
+            for b in range(lay.cfg_degree):
+                ranks = list(range(b * lay.sp_degree, (b + 1) * lay.sp_degree))
+                g = dist.new_group(ranks)
+                if b == lay.branch:
+                    self.sp_group = g
+            if lay.cfg_degree == 2:
+                for s in range(lay.sp_degree):
+                    g = dist.new_group([s, lay.sp_degree + s])
+                    if s == lay.sp_rank:
+                        self.pair_group = g
+            if lay.sp_degree > 1:
+                self.tr.set_sequence_parallel(UlyssesContext(self.sp_group, lay.sp_degree, lay.sp_rank))
+        self.sess = None
+        self.launches_per_step = None
+
+    # -------------------------------------------------------------- setup / IO
+    def setup(self, cond_h, uncond_h, lat_h, height, width, num_inference_steps, true_cfg_scale=4.0):
+        from . import ops
+        from .pipeline import DenoiseSession, latent_hw
+        lay, dev, dt = self.layout, self.device, self.tr.dtype
+        Hl, Wl = latent_hw(height, width)
+        self.s_img, self.s_txt = lat_h.shape[1], cond_h.shape[1]
+        self.i0, self.i1 = shard_bounds(self.s_img, lay.sp_degree, lay.sp_rank)
+        self.t0, self.t1 = shard_bounds(self.s_txt, lay.sp_degree, lay.sp_rank)
+        self.scale = float(true_cfg_scale)
+        if lay.cfg_degree == 1:
+            cond, uncond = cond_h.to(dev, dt), (uncond_h.to(dev, dt) if uncond_h is not None else None)
+        else:
+            mine = cond_h if lay.branch == 0 else uncond_h
+            cond, uncond = mine.to(dev, dt), None
+        cond = cond[:, self.t0:self.t1].contiguous()
+        if uncond is not None:
+            uncond = uncond[:, self.t0:self.t1].contiguous()
+        lat = lat_h.to(dev, dt)[:, self.i0:self.i1].contiguous()
+        if lay.sp_degree > 1:
+            self.tr.set_sequence_shard((1, Hl // 2, Wl // 2), self.s_img, self.s_txt, (self.i0, self.i1),
+                                       (self.t0, self.t1))
+        if self.world == 1:
+            n0 = ops.launch_count
+            self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
+                                       use_cuda_graph=self.use_cuda_graph)
+            if self.use_cuda_graph:
+                # launches recorded while capturing one step (+2 refresh copies are torch memcpys)
+                self.launches_per_step = (ops.launch_count - n0 - 4) // 2
+        else:
+            self.sess = DenoiseSession(self.pipe, cond, None, lat, Hl, Wl, num_inference_steps, self.scale,
+                                       use_cuda_graph=False, image_seq_len=self.s_img)
+            self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
+
+    def load_inputs(self, cond_h, uncond_h, lat_h):
+        lay = self.layout
+        mine = cond_h if (lay.cfg_degree == 1 or lay.branch == 0) else uncond_h
+        self.sess.cond.copy_(mine[:, self.t0:self.t1], non_blocking=True)
+        if self.sess.uncond is not None:
+            self.sess.uncond.copy_(uncond_h[:, self.t0:self.t1], non_blocking=True)
+        self.sess.load_latents(lat_h[:, self.i0:self.i1])
+
+    def read_latents(self, out_h):
+        out_h[:, self.i0:self.i1].copy_(self.sess.latents, non_blocking=True)
+
+    # -------------------------------------------------------------- one step
+    def step(self, i: int) -> None:
+        from . import ops
+        if self.world == 1:
+            self.sess.step(i)
+            return
+        s = self.sess
+        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, img_shapes=s.shapes,
+                       txt_seq_lens=[s.s_txt], return_dict=False, _step_index=i)[0]
+        if self.layout.cfg_degree == 2:
+            dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
+            c, u = self.pair_buf[0], self.pair_buf[1]
+        else:
+            c, u = pred, None
+        ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=s.dts[i:i + 1])
+        s.cur, s.nxt = s.nxt, s.cur
+
+    def close(self):
+        if self.sess is not None:
+            self.sess.close()
+            self.sess = None
+
+    # -------------------------------------------------------------- per-kernel roofline numbers
+    def kernel_rooflines(self, burst_tf, sustained_tf, hbm_gbs, src) -> dict:
+        """Times the hot kernels alone with CUDA events at the cfg-2 shapes, cycling through the 60
+        blocks' weights so every launch reads operands that are not L2-resident."""
+        from . import ops
+        tr, cfg = self.tr, self.cfg
+        d, H, Dh, L = cfg.inner_dim, cfg.num_attention_heads, cfg.attention_head_dim, cfg.num_layers
+        key = next(iter(tr._ws))
+        ws = tr._ws[key]
+        B, s_img, s_txt = key
+        S = s_img + s_txt
+        reps = max(L, 20)
+
+        def timed(fn):
+            for l in range(3):
+                fn(l % L)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for r in range(reps):
+                fn(r % L)
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / reps * 1e-3
+
+        out = {}
+        rows = (s_img + s_txt) * B
+
+        def up(l):
+            ops.gemm([ops.gemm_problem(ws.xn_img, tr.mlp_up_w[l, 0], tr.mlp_up_b[l, 0], ws.mlp_img, ops.EPI_BIAS_GELU_TANH),
+                      ops.gemm_problem(ws.xn_txt, tr.mlp_up_w[l, 1], tr.mlp_up_b[l, 1], ws.mlp_txt, ops.EPI_BIAS_GELU_TANH)])
+        t = timed(up)
+        fl = 2.0 * rows * 4 * d * d
+        dom = {"bound": "tensor", "kernel": "gemm_bf16_kernel<256> (MLP-up + GELU, img+txt in one launch)",
+               "achieved": fl / t / 1e12, "peak": sustained_tf, "unit": "TFLOP/s",
+               "frac": fl / t / 1e12 / sustained_tf, "traffic": None, "peak_source": src + " (sustained cuBLAS bf16)",
+               "launch_us": t * 1e6, "frac_of_nominal_2250": fl / t / 1e12 / 2250.0}
+        out["roofline"] = dom
+        kern = {}
+
+        def down(l):
+            G = ops.EPI_GATED_RESIDUAL
+            g = tr.mod_b[:d].view(1, d).expand(B, d)
+            ops.gemm([ops.gemm_problem(ws.mlp_img, tr.mlp_down_w[l, 0], tr.mlp_down_b[l, 0], ws.xn_img, G, ws.xn_img, g),
+                      ops.gemm_problem(ws.mlp_txt, tr.mlp_down_w[l, 1], tr.mlp_down_b[l, 1], ws.xn_txt, G, ws.xn_txt, g)])
+        t = timed(down)
+        kern["gemm_mlp_down_gated"] = {"us": t * 1e6, "tflops": fl / t / 1e12}
+
+        def qkvp(l):
+            ops.gemm([ops.gemm_problem(ws.xn_img, tr.qkv_w[l, 0], tr.qkv_b[l, 0], ws.qkv[:, s_txt:]),
+                      ops.gemm_problem(ws.xn_txt, tr.qkv_w[l, 1], tr.qkv_b[l, 1], ws.qkv[:, :s_txt])])
+        t = timed(qkvp)
+        kern["gemm_qkv"] = {"us": t * 1e6, "tflops": 2.0 * rows * 3 * d * d / t / 1e12}
+        q = ws.qkv[:, :, 0:d].unflatten(-1, (H, Dh))
+        k = ws.qkv[:, :, d:2 * d].unflatten(-1, (H, Dh))
+        v = ws.qkv[:, :, 2 * d:].unflatten(-1, (H, Dh))
+        o = ws.attn.unflatten(-1, (H, Dh))
+        t = timed(lambda l: ops.attention(q, k, v, o))
+        kern["attention"] = {"us": t * 1e6, "tflops": 4.0 * B * S * S * d / t / 1e12,
+                             "frac_of_sustained": 4.0 * B * S * S * d / t / 1e12 / sustained_tf}
+        mod = tr.mod_b.view(1, -1)
+        x2 = ws.h.view(B * s_img, d)
+        t = timed(lambda l: ops.adaln_modulate(x2, mod[:, :d].expand(B, d), mod[:, d:2 * d].expand(B, d),
+                                               ws.xn_img.view(B * s_img, d), s_img))
+        kern["adaln_modulate_img"] = {"us": t * 1e6, "gbs": 4.0 * B * s_img * d / t / 1e9,
+                                      "frac_of_hbm": 4.0 * B * s_img * d / t / 1e9 / hbm_gbs,
+                                      "note": "4096x3072 bf16 read+write = 50 MB, L2-resident between repeats"}
+        nw = tr.qk_norm_w[0]
+        fr = next(v_ for k_, v_ in tr._freqs.items() if isinstance(k_[0], tuple))
+        t = timed(lambda l: ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], fr))
+        kern["qknorm_rope"] = {"us": t * 1e6, "gbs": 8.0 * B * S * d / t / 1e9,
+                               "frac_of_hbm": 8.0 * B * S * d / t / 1e9 / hbm_gbs}
+        out["kernels"] = kern
+        return out

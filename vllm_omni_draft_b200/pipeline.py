@@ -1,0 +1,250 @@
+"""Drop-in for the pipeline call the reference benchmarks.
+
+Boundary #2: ``pipe(prompt_embeds=, prompt_embeds_mask=, negative_prompt_embeds=,
+negative_prompt_embeds_mask=, true_cfg_scale=, num_inference_steps=, generator=,
+num_images_per_prompt=, height=, width=, latents=, output_type=).images`` — reference call sites
+src/performance_enhancement/test_pipeline.py:247-266 and test_performance.py:244-266, 277 (the
+``MOCK_TEST`` branch feeds random ``prompt_embeds`` exactly like this path's synthetic runs).
+
+Host layer (PyTorch): latent preparation and packing, the FlowMatch sigma schedule (numpy float32,
+as upstream), the step loop, CUDA-graph capture/replay.  Device work: two transformer forwards and
+one fused true-CFG + Euler kernel per step, all in libqi_b200.so.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Any, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+from .transformer import B200QwenImageTransformer2DModel
+
+
+@dataclass
+class QwenImagePipelineOutput:
+    images: Any
+
+
+# ------------------------------------------------------------------ latent plumbing (bit-exact)
+def pack_latents(latents: torch.Tensor) -> torch.Tensor:
+    """[B,16,Hl,Wl] / [B,1,16,Hl,Wl] -> [B,(Hl/2)(Wl/2),64]; pure index permutation (A.6)."""
+    if latents.dim() == 5:
+        latents = latents[:, 0] if latents.shape[1] == 1 else latents.squeeze(2)
+    B, C, Hl, Wl = latents.shape
+    if Hl % 2 or Wl % 2:
+        raise ValueError("latent height/width must be even")
+    x = latents.reshape(B, C, Hl // 2, 2, Wl // 2, 2).permute(0, 2, 4, 1, 3, 5)
+    return x.reshape(B, (Hl // 2) * (Wl // 2), C * 4)
+
+
+def unpack_latents(tokens: torch.Tensor, Hl: int, Wl: int) -> torch.Tensor:
+    B, _, ch = tokens.shape
+    x = tokens.reshape(B, Hl // 2, Wl // 2, ch // 4, 2, 2).permute(0, 3, 1, 4, 2, 5)
+    return x.reshape(B, ch // 4, 1, Hl, Wl)
+
+
+def latent_hw(height: int, width: int, vae_scale_factor: int = 8) -> Tuple[int, int]:
+    return 2 * (int(height) // (vae_scale_factor * 2)), 2 * (int(width) // (vae_scale_factor * 2))
+
+
+# ------------------------------------------------------------------ scheduler (host, numpy fp32)
+def calculate_shift(image_seq_len, base_seq_len=256, max_seq_len=8192, base_shift=0.5, max_shift=0.9):
+    m = (max_shift - base_shift) / (max_seq_len - base_seq_len)
+    b = base_shift - m * base_seq_len
+    return image_seq_len * m + b
+
+
+class FlowMatchEulerSchedule:
+    """FlowMatchEulerDiscreteScheduler.set_timesteps with the Qwen-Image scheduler config
+    (dynamic exponential shift, terminal stretch to 0.02); the step itself is the K5 kernel."""
+
+    def __init__(self, num_inference_steps: int, image_seq_len: int, shift_terminal: float = 0.02):
+        if num_inference_steps < 1:
+            raise ValueError("num_inference_steps must be >= 1")
+        sig = np.linspace(1.0, 1.0 / num_inference_steps, num_inference_steps).astype(np.float32)
+        mu = calculate_shift(image_seq_len)
+        sig = math.exp(mu) / (math.exp(mu) + (1 / sig - 1) ** 1.0)
+        one_minus = 1 - sig
+        scale = one_minus[-1] / (1 - shift_terminal)
+        sig = 1 - one_minus / scale
+        sigmas = torch.from_numpy(np.asarray(sig)).to(torch.float32)
+        self.timesteps = sigmas * 1000.0
+        self.sigmas = torch.cat([sigmas, torch.zeros(1)])
+        self.dts = self.sigmas[1:] - self.sigmas[:-1]          # fp32, as scheduler.step computes it
+
+    def transformer_timesteps(self, dtype=torch.bfloat16) -> torch.Tensor:
+        """What the loop passes as `timestep`: t.to(latents.dtype) / 1000, evaluated in bf16."""
+        return self.timesteps.to(dtype) / 1000
+
+
+class DenoiseSession:
+    """State of one denoising run: resident embeddings, ping-pong latent buffers, the hoisted
+    modulation table and (optionally) one captured CUDA graph of a full step.  `step(i)` advances
+    the latents by one scheduler step; `load_latents` / `latents` are the host-facing ends."""
+
+    def __init__(self, pipe: "B200QwenImagePipeline", cond: torch.Tensor, uncond: Optional[torch.Tensor],
+                 latents: torch.Tensor, Hl: int, Wl: int, num_inference_steps: int, true_cfg_scale: float,
+                 use_cuda_graph: bool = False, image_seq_len: Optional[int] = None):
+        tr = pipe.transformer
+        dev, dt = tr.device, tr.dtype
+        self.pipe, self.tr = pipe, tr
+        self.cond, self.uncond = cond, uncond
+        self.scale = float(true_cfg_scale)
+        B, s_img, _ = latents.shape
+        self.s_txt = cond.shape[1]
+        self.shapes = [[(1, Hl // 2, Wl // 2)]] * B
+        self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img)
+        tr.prepare_schedule(self.sched.transformer_timesteps(dt))
+        self.dts = self.sched.dts.to(dev)
+        self.cur = latents.contiguous().clone()
+        self.nxt = torch.empty_like(self.cur)
+        self.graph = None
+        if use_cuda_graph:
+            # One graph = one full step on fixed buffers; per step only the modulation row and dt are
+            # refreshed by two small device copies enqueued before the replay.
+            self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=dt)
+            self.dt_cur = torch.empty(1, device=dev, dtype=torch.float32)
+            self.mod_cur.copy_(tr._mod_table[0:1])
+            self.dt_cur.copy_(self.dts[0:1])
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):     # warm-up launch outside capture (sets func attributes)
+                pipe._step(self.cur, self.nxt, cond, uncond, self.shapes, self.s_txt, 0, self.dt_cur,
+                           self.scale, mod=self.mod_cur)
+            torch.cuda.current_stream().wait_stream(side)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                pipe._step(self.cur, self.nxt, cond, uncond, self.shapes, self.s_txt, 0, self.dt_cur,
+                           self.scale, mod=self.mod_cur)
+                self.cur.copy_(self.nxt)
+
+    @property
+    def latents(self) -> torch.Tensor:
+        return self.cur
+
+    def load_latents(self, host_or_dev: torch.Tensor) -> None:
+        self.cur.copy_(host_or_dev, non_blocking=True)
+
+    def step(self, i: int) -> None:
+        if self.graph is not None:
+            self.mod_cur.copy_(self.tr._mod_table[i:i + 1])
+            self.dt_cur.copy_(self.dts[i:i + 1])
+            self.graph.replay()
+        else:
+            self.pipe._step(self.cur, self.nxt, self.cond, self.uncond, self.shapes, self.s_txt, i,
+                            self.dts[i:i + 1], self.scale)
+            self.cur, self.nxt = self.nxt, self.cur
+
+    def close(self) -> None:
+        self.tr.clear_schedule()
+        self.graph = None
+
+
+class B200QwenImagePipeline:
+    def __init__(self, transformer: B200QwenImageTransformer2DModel, vae: Optional[torch.nn.Module] = None,
+                 text_encoder=None, vae_scale_factor: int = 8):
+        self.transformer = transformer
+        self.vae = vae
+        self.text_encoder = text_encoder
+        self.vae_scale_factor = vae_scale_factor
+        self.use_cuda_graph = False
+        self._graph = None
+        self._graph_key = None
+        self.last_step_latents: List[torch.Tensor] = []
+
+    def to(self, device):
+        self.transformer.to(device)
+        if self.vae is not None:
+            self.vae.to(device)
+        return self
+
+    @property
+    def device(self):
+        return self.transformer.device
+
+    # -------------------------------------------------------------- one denoising step (device)
+    def _step(self, latents, out_latents, cond, uncond, shapes, s_txt, i, dt_dev, scale, mod=None):
+        tr = self.transformer
+        kw = dict(img_shapes=shapes, txt_seq_lens=[s_txt], return_dict=False)
+        if mod is not None:
+            kw["_mod_override"] = mod
+        else:
+            kw["_step_index"] = i
+        c = tr(hidden_states=latents, encoder_hidden_states=cond, **kw)[0]
+        u = None
+        if uncond is not None:
+            u = tr(hidden_states=latents, encoder_hidden_states=uncond, **kw)[0]
+        ops.cfg_euler_step(c, u, latents, out_latents, scale, dt_dev=dt_dev)
+
+    @torch.no_grad()
+    def __call__(self, image=None, prompt=None, negative_prompt=None, true_cfg_scale: float = 4.0,
+                 height: Optional[int] = None, width: Optional[int] = None, num_inference_steps: int = 50,
+                 sigmas=None, guidance_scale: Optional[float] = None, num_images_per_prompt: int = 1,
+                 generator: Optional[torch.Generator] = None, latents: Optional[torch.Tensor] = None,
+                 prompt_embeds: Optional[torch.Tensor] = None, prompt_embeds_mask: Optional[torch.Tensor] = None,
+                 negative_prompt_embeds: Optional[torch.Tensor] = None,
+                 negative_prompt_embeds_mask: Optional[torch.Tensor] = None,
+                 output_type: str = "latent", return_dict: bool = True, record_steps: bool = False):
+        if image is not None:
+            raise NotImplementedError("edit mode (reference-image latents) is SURVEY §8 row f2, not built yet")
+        if prompt_embeds is None:
+            if prompt is None:
+                raise ValueError("Provide either `prompt` or `prompt_embeds`")
+            raise ValueError("prompt strings need the Qwen2.5-VL encoder (out of scope); pass prompt_embeds")
+        if prompt_embeds.dim() != 3:
+            raise ValueError("prompt_embeds must be 3D [B, T_txt, D_txt]")
+        if prompt_embeds_mask is not None and prompt_embeds_mask.dim() != 2:
+            raise ValueError("prompt_embeds_mask must be 2D [B, T_txt]")
+        if sigmas is not None:
+            raise NotImplementedError("custom sigmas are not supported; the default linspace(1, 1/N, N) is used")
+        dev, dt = self.device, self.transformer.dtype
+        height = height or 1024
+        width = width or 1024
+        Hl, Wl = latent_hw(height, width, self.vae_scale_factor)
+        cond = prompt_embeds.to(dev, dt)
+        if num_images_per_prompt > 1:
+            cond = cond.repeat_interleave(num_images_per_prompt, dim=0)
+        B, s_txt, _ = cond.shape
+        do_cfg = true_cfg_scale > 1 and negative_prompt_embeds is not None
+        uncond = None
+        if do_cfg:
+            uncond = negative_prompt_embeds.to(dev, dt)
+            if num_images_per_prompt > 1:
+                uncond = uncond.repeat_interleave(num_images_per_prompt, dim=0)
+            if uncond.shape != cond.shape:
+                raise ValueError("negative_prompt_embeds must match prompt_embeds in shape")
+        if latents is None:
+            g = generator
+            noise = torch.randn(B, 1, 16, Hl, Wl, generator=g, device=g.device if g is not None else "cpu",
+                                dtype=torch.float32)
+            latents = pack_latents(noise)
+        elif latents.dim() != 3:
+            latents = pack_latents(latents)
+        s_img = latents.shape[1]
+        if s_img != (Hl // 2) * (Wl // 2):
+            raise ValueError("latents do not match height/width")
+        sess = DenoiseSession(self, cond, uncond, latents.to(dev, dt), Hl, Wl, num_inference_steps,
+                              true_cfg_scale, use_cuda_graph=self.use_cuda_graph)
+        self.last_step_latents = []
+        for i in range(num_inference_steps):
+            sess.step(i)
+            if record_steps:
+                self.last_step_latents.append(sess.latents.clone())
+        final = sess.latents
+        sess.close()
+
+        if output_type == "latent":
+            images = final
+        elif output_type == "unpacked":
+            images = unpack_latents(final, Hl, Wl)
+        else:
+            if self.vae is None:
+                raise NotImplementedError(
+                    "pixel output needs the VAE decoder (SURVEY §8 row f1); use output_type='latent'")
+            images = self.vae.decode(unpack_latents(final, Hl, Wl))
+        if not return_dict:
+            return (images,)
+        return QwenImagePipelineOutput(images=images)
