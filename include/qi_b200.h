@@ -46,7 +46,8 @@ int qi_device_sm_count(void);
 /* ---- K3: tcgen05 bf16 GEMM with fused epilogues (replaces nn.Linear + the elementwise ops after it).
  * Up to two independent problems (the img and txt streams of one MMDiT block) run in ONE persistent
  * launch.  A is [batch, m, k] (row stride lda, batch stride a_batch_stride), W is the nn.Linear
- * weight [n, k] contiguous, C is [batch, m, n] (ldc, c_batch_stride).  k % 64 == 0, n % 8 == 0. */
+ * weight [n, k] contiguous, C is [batch, m, n] (ldc, c_batch_stride).  k % 64 == 0, n % 8 == 0.
+ * A zero-initialised struct with a/w/c/m/batch/n/k set is a plain C = A W^T. */
 typedef struct {
   const void* a;
   long long lda;
@@ -66,6 +67,10 @@ typedef struct {
   int n;
   int k;
   int epilogue; /* enum qi_epilogue */
+  /* Optional K-chunked A (Ulysses: attention output arrives as [head_group][m][k_chunk]):
+   * element (row, kk) of chunk c lives at a + c*a_k_chunk_stride + row*lda + kk.  0 = A is plain [m, k]. */
+  int a_k_chunk;
+  long long a_k_chunk_stride;
 } qi_gemm_problem_t;
 
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,

@@ -40,7 +40,7 @@ def test_cfg_euler_step_matches_oracle(cuda_device):
     assert torch.equal(out2.cpu(), ref2)
 
 
-@pytest.mark.parametrize("d", [256, 3072])
+@pytest.mark.parametrize("d", [128, 256, 3072, 3584])
 def test_adaln_modulate(cuda_device, d):
     ops = _ops()
     B, S = 2, 333

@@ -27,6 +27,7 @@ class GemmProblem(C.Structure):
         ("residual", _vp), ("ld_res", _ll), ("res_batch_stride", _ll),
         ("gate", _vp), ("gate_batch_stride", _ll),
         ("m", _i), ("batch", _i), ("n", _i), ("k", _i), ("epilogue", _i),
+        ("a_k_chunk", _i), ("a_k_chunk_stride", _ll),
     ]
 
 

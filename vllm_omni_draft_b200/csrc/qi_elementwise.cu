@@ -102,6 +102,63 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(
   }
 }
 
+
+// Generic-width variant (any d % 8 == 0): the row is re-read from L1/L2 for the second and third
+// pass instead of being held in registers.  Only used for widths without a register instantiation
+// (e.g. the tiny test config's joint_attention_dim = 128).
+template <int MODE>
+__global__ void __launch_bounds__(128) norm_rows_generic_kernel(
+    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int rows, int d, int ld_x,
+    int ld_y, const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale,
+    long long mod_batch_stride, int rows_per_batch, float eps) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const __nv_bfloat16* xr = x + (size_t)warp * ld_x;
+  float s = 0.f;
+  for (int off = lane * 8; off < d; off += 256) {
+    float v[8];
+    unpack8(ldg128(xr + off), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += (MODE == 0) ? v[j] : v[j] * v[j];
+  }
+  s = group_sum<32>(s);
+  float mean = 0.f, rstd;
+  if (MODE == 0) {
+    mean = s / d;
+    float q = 0.f;
+    for (int off = lane * 8; off < d; off += 256) {
+      float v[8];
+      unpack8(ldg128(xr + off), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
+    }
+    q = group_sum<32>(q);
+    rstd = rsqrtf(q / d + eps);
+  } else {
+    rstd = rsqrtf(s / d + eps);
+  }
+  const int b = warp / rows_per_batch;
+  const __nv_bfloat16* sh = (MODE == 0) ? shift + (size_t)b * mod_batch_stride : nullptr;
+  const __nv_bfloat16* sc = scale + ((MODE == 0) ? (size_t)b * mod_batch_stride : 0);
+  __nv_bfloat16* yr = y + (size_t)warp * ld_y;
+  for (int off = lane * 8; off < d; off += 256) {
+    float v[8], w[8], o[8];
+    unpack8(ldg128(xr + off), v);
+    unpack8(ldg128(sc + off), w);
+    if (MODE == 0) {
+      float h[8];
+      unpack8(ldg128(sh + off), h);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[j] - mean) * rstd * (1.f + w[j]) + h[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = bf16_round(v[j] * rstd) * w[j];
+    }
+    stg128(yr + off, pack8(o));
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // K2: QK RMSNorm + RoPE in place on the joint qkv buffer [rows, ld] (q at col 0, k at col d).
 // A group of DH/8 lanes owns one head vector; a warp owns 32/(DH/8) consecutive head vectors.
@@ -277,7 +334,7 @@ static int launch_norm_rows(const void* x, void* y, int rows, int d, int ld_x, i
                             const void* shift, const void* scale, long long mod_stride,
                             int rows_per_batch, float eps, cudaStream_t st) {
   if (rows <= 0) return QI_OK;
-  if (d % 256 != 0 || ld_x % 8 != 0 || ld_y % 8 != 0) return QI_ERR_ARG;
+  if (d % 8 != 0 || ld_x % 8 != 0 || ld_y % 8 != 0) return QI_ERR_ARG;
   const int blocks = (rows + 3) / 4;
 #define QI_NORM_CASE(NC)                                                                     \
   case NC:                                                                                   \
@@ -286,10 +343,13 @@ static int launch_norm_rows(const void* x, void* y, int rows, int d, int ld_x, i
         (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, \
         eps);                                                                                \
     break;
-  switch (d / 256) {
-    QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(4) QI_NORM_CASE(6) QI_NORM_CASE(8)
-    QI_NORM_CASE(12) QI_NORM_CASE(14) QI_NORM_CASE(16)
-    default: return QI_ERR_UNSUPPORTED;
+  switch (d % 256 == 0 ? d / 256 : 0) {
+    QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(4) QI_NORM_CASE(8)
+    QI_NORM_CASE(12) QI_NORM_CASE(14)
+    default:
+      norm_rows_generic_kernel<MODE><<<blocks, 128, 0, st>>>(
+          (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, d, ld_x, ld_y,
+          (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, eps);
   }
 #undef QI_NORM_CASE
   QI_CHECK_LAUNCH();

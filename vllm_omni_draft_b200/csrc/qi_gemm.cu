@@ -28,6 +28,7 @@ struct GemmProb {
   int tiles_m_total; // tiles_m * batch
   int tiles_n;
   int tile_begin;    // first global tile index of this problem
+  int k_chunk;       // A's K axis is split into chunks of this many elements (== k when unsplit)
 };
 
 struct GemmLaunch {
@@ -121,7 +122,9 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
           uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
           uint8_t* sb = sa + Cfg::A_BYTES;
           mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-          tma_load_3d(sa, &L.tmap_a[tc.p], &full_bar[stage], kb * BK, tc.m0, tc.b);
+          const int kidx = kb * BK;
+          const int kc = L.prob[tc.p].k_chunk;
+          tma_load_4d(sa, &L.tmap_a[tc.p], &full_bar[stage], kidx % kc, tc.m0, kidx / kc, tc.b);
           tma_load_2d(sb, &L.tmap_b[tc.p], &full_bar[stage], kb * BK, tc.n0);
           if (++stage == Cfg::STAGES) {
             stage = 0;
@@ -288,12 +291,20 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.tiles_m_total = P.tiles_m * in.batch;
   P.tiles_n = (in.n + BN - 1) / BN;
   P.tile_begin = tile_begin;
-  // A: [batch, m, k]  (innermost first for the tensor map)
+  // A: [batch, k_chunks, m, k_chunk]  (innermost first for the tensor map)
   {
-    uint64_t dims[3] = {(uint64_t)in.k, (uint64_t)in.m, (uint64_t)in.batch};
-    uint64_t strides[2] = {(uint64_t)in.lda * 2, (uint64_t)(in.batch > 1 ? in.a_batch_stride : in.lda * (long long)in.m) * 2};
-    uint32_t box[3] = {BK, BM, 1};
-    int rc = qi_encode_tmap_bf16(&L.tmap_a[i], in.a, 3, dims, strides, box);
+    const int kc = in.a_k_chunk > 0 ? in.a_k_chunk : in.k;
+    if (kc % BK != 0 || in.k % kc != 0) return QI_ERR_ARG;
+    if (in.a_k_chunk > 0 && in.a_k_chunk_stride % 8 != 0) return QI_ERR_ARG;
+    P.k_chunk = kc;
+    const int nchunks = in.k / kc;
+    const uint64_t row_bytes = (uint64_t)in.lda * 2;
+    uint64_t dims[4] = {(uint64_t)kc, (uint64_t)in.m, (uint64_t)nchunks, (uint64_t)in.batch};
+    uint64_t strides[3] = {row_bytes,
+                           nchunks > 1 ? (uint64_t)in.a_k_chunk_stride * 2 : row_bytes * (uint64_t)in.m,
+                           in.batch > 1 ? (uint64_t)in.a_batch_stride * 2 : row_bytes * (uint64_t)in.m};
+    uint32_t box[4] = {BK, BM, 1, 1};
+    int rc = qi_encode_tmap_bf16(&L.tmap_a[i], in.a, 4, dims, strides, box);
     if (rc) return rc;
   }
   {

@@ -37,15 +37,23 @@ def _req_bf16(*ts: torch.Tensor) -> None:
 
 def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                  epilogue: int = EPI_BIAS, residual: Optional[torch.Tensor] = None,
-                 gate: Optional[torch.Tensor] = None) -> GemmProblem:
-    """a: [B, M, K] or [M, K] view (row/batch strides arbitrary, K contiguous); w: [N, K] contiguous;
+                 gate: Optional[torch.Tensor] = None, a_k_chunked: bool = False) -> GemmProblem:
+    """a_k_chunked: a is [chunks, M, Kc] and stands for the [M, chunks*Kc] matrix whose K axis is
+    the concatenation of the chunks (batch 1).  Otherwise a: [B, M, K] or [M, K] view (row/batch strides arbitrary, K contiguous); w: [N, K] contiguous;
     out: [B, M, N] / [M, N] view; residual like out; gate [B, N] view."""
     _req_bf16(a, w, bias, out, residual, gate)
+    chunk = None
+    if a_k_chunked:
+        nch, M_, kc = a.shape
+        chunk = (kc, a.stride(0))
+        a = a[0].unsqueeze(0)
     if a.dim() == 2:
         a = a.unsqueeze(0)
     if out.dim() == 2:
         out = out.unsqueeze(0)
     B, M, K = a.shape
+    if chunk is not None:
+        K = nch * kc
     N = w.shape[0]
     if w.shape[1] != K or not w.is_contiguous() or tuple(out.shape) != (B, M, N):
         raise ValueError(f"gemm shape mismatch: a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
@@ -63,6 +71,8 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
         p.residual, p.ld_res, p.res_batch_stride = residual.data_ptr(), residual.stride(1), residual.stride(0)
         p.gate, p.gate_batch_stride = gate.data_ptr(), gate.stride(0)
     p.m, p.batch, p.n, p.k, p.epilogue = M, B, N, K, epilogue
+    if chunk is not None:
+        p.a_k_chunk, p.a_k_chunk_stride = chunk
     return p
 
 

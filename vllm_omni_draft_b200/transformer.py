@@ -243,7 +243,7 @@ class B200QwenImageTransformer2DModel(nn.Module):
             raise ValueError(f"encoder_hidden_states must be [B, S_txt, {cfg.joint_attention_dim}]")
         if controlnet_block_samples is not None:
             raise NotImplementedError("controlnet residuals are outside the hot path")
-        if timestep is None and _step_index is None:
+        if timestep is None and _step_index is None and _mod_override is None:
             raise ValueError("timestep is required")
         B, s_img, _ = hidden_states.shape
         s_txt = encoder_hidden_states.shape[1]
