@@ -16,7 +16,7 @@ namespace qi {
 
 constexpr int ATT_BM = 128;   // query rows per tile
 constexpr int ATT_BN = 128;   // keys per tile
-constexpr int ATT_THREADS = 320;
+constexpr int ATT_THREADS = 384;   // 3 warpgroups: softmax 0, softmax 1, {TMA, MMA, 2 idle}
 constexpr int ATT_KV_STAGES = 2;
 
 template <int DH>
@@ -93,6 +93,13 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+
+  // register re-balance: the data-movement warpgroup gives its registers to the softmax warpgroups
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+  }
 
   if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
@@ -185,7 +192,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp < 8) {
     // ------------------------------------------------------------------ softmax warpgroups
     const int t = warp >> 2;                 // Q tile
     const int quad = warp & 3;               // TMEM lane quadrant
@@ -198,18 +205,25 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
       const int kv_valid = min(ATT_BN, P.seq_kv - j * ATT_BN);
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < ATT_BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(s_addr + c * 32, r);
-        tmem_ld_wait();
+      // S row (128 fp32) into registers with one wait: four x32 loads in flight
+      uint32_t r[ATT_BN / 32][32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float v = __uint_as_float(r[i]);
-          mx = (c * 32 + i < kv_valid) ? fmaxf(mx, v) : mx;
-        }
+      for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
+      tmem_ld_wait();
+      float mx = -INFINITY;
+      if (kv_valid == ATT_BN) {
+#pragma unroll
+        for (int c = 0; c < ATT_BN / 32; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < ATT_BN / 32; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: exp2 -> 0
+            mx = fmaxf(mx, __uint_as_float(r[c][i]));
+          }
       }
       const float m_new = fmaxf(m_ref, mx * P.scale_log2);
       const bool need = (m_new - m_ref) > 8.0f;   // also true on the first tile (m_ref = -inf)
@@ -222,35 +236,32 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         if (j > 0) {
 #pragma unroll 1
           for (int c = 0; c < DH / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld32(o_addr + c * 32, r);
+            uint32_t o[32];
+            tmem_ld32(o_addr + c * 32, o);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
-            tmem_st32(o_addr + c * 32, r);
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+            tmem_st32(o_addr + c * 32, o);
           }
         }
       }
-      // pass 2: P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
+      // P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
       const float neg_m = -m_ref;
-#pragma unroll 1
+      float ls0 = 0.f, ls1 = 0.f;
+#pragma unroll
       for (int c = 0; c < ATT_BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(s_addr + c * 32, r);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const int col = c * 32 + 2 * i;
-          float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * i]), P.scale_log2, neg_m));
-          float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * i + 1]), P.scale_log2, neg_m));
-          p0 = (col < kv_valid) ? p0 : 0.f;
-          p1 = (col + 1 < kv_valid) ? p1 : 0.f;
-          l_sum += p0 + p1;
+          const float p0 = fast_exp2(fmaf(__uint_as_float(r[c][2 * i]), P.scale_log2, neg_m));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(r[c][2 * i + 1]), P.scale_log2, neg_m));
+          ls0 += p0;
+          ls1 += p1;
           pk[i] = pack_bf16(p0, p1);
         }
         tmem_st16(s_addr + c * 16, pk);
       }
+      l_sum += ls0 + ls1;
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
