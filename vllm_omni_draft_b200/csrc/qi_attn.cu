@@ -94,15 +94,11 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // register re-balance: the data-movement warpgroup gives its registers to the softmax warpgroups
-  if (warp >= 8) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
-  } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
-  }
-
+  // Register re-balance (setmaxnreg is per warpgroup and must sit inside each role's own branch so
+  // that ptxas allocates every role against its own budget): warps 8-11 shrink, softmax warps grow.
   if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (lane == 0) {
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
       for (int t = 0; t < 2; ++t)
@@ -127,6 +123,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     __syncwarp();
   } else if (warp == 9) {
     // ------------------------------------------------------------------ MMA issuer
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (lane == 0) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
@@ -192,8 +189,11 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else if (warp < 8) {
+  } else if (warp >= 10) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+  } else {
     // ------------------------------------------------------------------ softmax warpgroups
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
     const int t = warp >> 2;                 // Q tile
     const int quad = warp & 3;               // TMEM lane quadrant
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;

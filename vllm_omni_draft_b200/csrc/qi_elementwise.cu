@@ -42,63 +42,81 @@ __device__ __forceinline__ float group_sum(float v) {
 // K1: one warp per row.  NCHUNK = d / 256 (each lane owns NCHUNK x 8 contiguous bf16).
 // MODE 0: y = LN(x) * (1 + scale[b]) + shift[b]     MODE 1: y = bf16(x * rsqrt(ms+eps)) * w
 // ---------------------------------------------------------------------------------------------
-template <int NCHUNK, int MODE>
+// Block-per-row variant: 128 threads own one row, CPT 16-byte chunks per thread (d = CPT * 1024).
+// ~40 registers per thread, so an SM keeps 16 rows (~100 KB of loads) in flight; the two
+// reductions (mean, then centred variance) go warp shuffle -> 4 partials in shared memory.
+template <int CPT, int MODE>
 __global__ void __launch_bounds__(128) norm_rows_kernel(
     const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int rows, int ld_x, int ld_y,
     const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale,
     long long mod_batch_stride, int rows_per_batch, float eps) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (warp >= rows) return;
-  constexpr int D = NCHUNK * 256;
-  const __nv_bfloat16* xr = x + (size_t)warp * ld_x;
-  uint4 raw[NCHUNK];
+  __shared__ float red[2][4];
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wid = tid >> 5;
+  constexpr int D = CPT * 1024;
+  const __nv_bfloat16* xr = x + (size_t)row * ld_x;
+  float v[CPT][8];
+  {
+    uint4 raw[CPT];
 #pragma unroll
-  for (int c = 0; c < NCHUNK; ++c) raw[c] = ldg128_stream(xr + (c * 32 + lane) * 8);
-  float v[NCHUNK][8];
+    for (int c = 0; c < CPT; ++c) raw[c] = ldg128_stream(xr + (c * 128 + tid) * 8);
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) unpack8(raw[c], v[c]);
+  }
+  // modulation vectors do not depend on the row statistics: issue their loads now
+  const int b = row / rows_per_batch;
+  const __nv_bfloat16* sh = (MODE == 0) ? shift + (size_t)b * mod_batch_stride : nullptr;
+  const __nv_bfloat16* sc = scale + ((MODE == 0) ? (size_t)b * mod_batch_stride : 0);
+  uint4 wraw[CPT], hraw[CPT];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    wraw[c] = ldg128(sc + (c * 128 + tid) * 8);
+    if (MODE == 0) hraw[c] = ldg128(sh + (c * 128 + tid) * 8);
+  }
   float s = 0.f;
 #pragma unroll
-  for (int c = 0; c < NCHUNK; ++c) {
-    unpack8(raw[c], v[c]);
+  for (int c = 0; c < CPT; ++c)
 #pragma unroll
     for (int j = 0; j < 8; ++j) s += (MODE == 0) ? v[c][j] : v[c][j] * v[c][j];
-  }
   s = group_sum<32>(s);
+  if (lane == 0) red[0][wid] = s;
+  __syncthreads();
+  s = red[0][0] + red[0][1] + red[0][2] + red[0][3];
   float mean = 0.f, rstd;
   if (MODE == 0) {
     mean = s * (1.f / D);
     float q = 0.f;
 #pragma unroll
-    for (int c = 0; c < NCHUNK; ++c)
+    for (int c = 0; c < CPT; ++c)
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float t = v[c][j] - mean;
-        q += t * t;
+        const float t = v[c][j] - mean;
+        q = fmaf(t, t, q);
       }
     q = group_sum<32>(q);
+    if (lane == 0) red[1][wid] = q;
+    __syncthreads();
+    q = red[1][0] + red[1][1] + red[1][2] + red[1][3];
     rstd = rsqrtf(q * (1.f / D) + eps);
   } else {
     rstd = rsqrtf(s * (1.f / D) + eps);
   }
-  const int b = warp / rows_per_batch;
-  const __nv_bfloat16* sh = (MODE == 0) ? shift + (size_t)b * mod_batch_stride : nullptr;
-  const __nv_bfloat16* sc = scale + ((MODE == 0) ? (size_t)b * mod_batch_stride : 0);
-  __nv_bfloat16* yr = y + (size_t)warp * ld_y;
+  __nv_bfloat16* yr = y + (size_t)row * ld_y;
 #pragma unroll
-  for (int c = 0; c < NCHUNK; ++c) {
-    const int off = (c * 32 + lane) * 8;
+  for (int c = 0; c < CPT; ++c) {
     float w[8], o[8];
-    unpack8(ldg128(sc + off), w);
+    unpack8(wraw[c], w);
     if (MODE == 0) {
       float h[8];
-      unpack8(ldg128(sh + off), h);
+      unpack8(hraw[c], h);
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mean) * rstd * (1.f + w[j]) + h[j];
     } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = bf16_round(v[c][j] * rstd) * w[j];
     }
-    stg128(yr + off, pack8(o));
+    stg128(yr + (c * 128 + tid) * 8, pack8(o));
   }
 }
 
@@ -171,45 +189,59 @@ __global__ void __launch_bounds__(256) qknorm_rope_kernel(
     const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
     const float2* __restrict__ freqs /* [seq, DH/2] (cos, sin), joint order txt first */,
     float eps) {
-  constexpr int LPH = DH / 8;          // lanes per head vector
-  constexpr int VPW = 32 / LPH;        // head vectors per warp
+  // One warp per token row.  A group of LPH = DH/8 lanes owns one head vector (8 bf16 per lane);
+  // the warp walks the row's 2*heads head vectors (q heads then k heads, contiguous in memory)
+  // VPW at a time.  The row's rotation table and the norm weights are loaded once per row.
+  constexpr int LPH = DH / 8;
+  constexpr int VPW = 32 / LPH;
   const int lane = threadIdx.x & 31;
   const int sub = lane % LPH;
-  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const long long item = warp * VPW + lane / LPH;   // (row, qk, head), head fastest
-  const long long total = (long long)rows * 2 * heads;
-  const bool active = item < total;
-  const long long it = active ? item : total - 1;
-  const int row = (int)(it / (2 * heads));
-  const int rem = (int)(it % (2 * heads));
-  const int qk = rem / heads, head = rem % heads;
+  const int grp = lane / LPH;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
   const int pos = row % seq;
   const bool is_txt = pos < s_txt;
-  __nv_bfloat16* p = qkv + (size_t)row * ld + (size_t)rem * DH + sub * 8;
-  const __nv_bfloat16* w = (qk == 0) ? (is_txt ? wq_txt : wq_img) : (is_txt ? wk_txt : wk_img);
-  (void)head;
-  float v[8], wv[8];
-  unpack8(ldg128(p), v);
-  unpack8(ldg128(w + sub * 8), wv);
   const float4* fp = reinterpret_cast<const float4*>(freqs + (size_t)pos * (DH / 2) + sub * 4);
   const float4 f01 = fp[0], f23 = fp[1];
-  float ss = 0.f;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) ss += v[j] * v[j];
-  ss = group_sum<LPH>(ss);
-  const float rstd = rsqrtf(ss * (1.f / DH) + eps);
-#pragma unroll
-  for (int j = 0; j < 8; ++j) v[j] = bf16_round(bf16_round(v[j] * rstd) * wv[j]);
   const float cs[4] = {f01.x, f01.z, f23.x, f23.z};
   const float sn[4] = {f01.y, f01.w, f23.y, f23.w};
-  float o[8];
+  float wq[8], wk[8];
+  unpack8(ldg128((is_txt ? wq_txt : wq_img) + sub * 8), wq);
+  unpack8(ldg128((is_txt ? wk_txt : wk_img) + sub * 8), wk);
+  __nv_bfloat16* base = qkv + (size_t)row * ld + sub * 8;
+  const int nvec = 2 * heads;
+  constexpr int UNROLL = 4;
+  for (int v0 = grp; v0 < nvec; v0 += VPW * UNROLL) {
+    uint4 raw[UNROLL];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float a = v[2 * j], b = v[2 * j + 1];
-    o[2 * j] = a * cs[j] - b * sn[j];
-    o[2 * j + 1] = a * sn[j] + b * cs[j];
+    for (int u = 0; u < UNROLL; ++u) {
+      const int vi = v0 + u * VPW;
+      if (vi < nvec) raw[u] = ldg128(base + (size_t)vi * DH);
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int vi = v0 + u * VPW;
+      // all lanes of a group share vi, so the shuffles inside group_sum stay convergent per group;
+      // groups past the end still execute them on stale registers and simply skip the store
+      float v[8];
+      unpack8(raw[u], v);
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(v[j], v[j], ss);
+      ss = group_sum<LPH>(ss);
+      const float rstd = rsqrtf(ss * (1.f / DH) + eps);
+      const bool is_k = vi >= heads;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a = bf16_round(bf16_round(v[2 * j] * rstd) * (is_k ? wk[2 * j] : wq[2 * j]));
+        const float bb = bf16_round(bf16_round(v[2 * j + 1] * rstd) * (is_k ? wk[2 * j + 1] : wq[2 * j + 1]));
+        o[2 * j] = a * cs[j] - bb * sn[j];
+        o[2 * j + 1] = a * sn[j] + bb * cs[j];
+      }
+      if (vi < nvec) stg128(base + (size_t)vi * DH, pack8(o));
+    }
   }
-  if (active) stg128(p, pack8(o));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -335,19 +367,18 @@ static int launch_norm_rows(const void* x, void* y, int rows, int d, int ld_x, i
                             int rows_per_batch, float eps, cudaStream_t st) {
   if (rows <= 0) return QI_OK;
   if (d % 8 != 0 || ld_x % 8 != 0 || ld_y % 8 != 0) return QI_ERR_ARG;
-  const int blocks = (rows + 3) / 4;
+  const int blocks_generic = (rows + 3) / 4;
 #define QI_NORM_CASE(NC)                                                                     \
   case NC:                                                                                   \
-    norm_rows_kernel<NC, MODE><<<blocks, 128, 0, st>>>(                                      \
+    norm_rows_kernel<NC, MODE><<<rows, 128, 0, st>>>(                                        \
         (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, ld_x, ld_y,                        \
         (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, \
         eps);                                                                                \
     break;
-  switch (d % 256 == 0 ? d / 256 : 0) {
-    QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(4) QI_NORM_CASE(8)
-    QI_NORM_CASE(12) QI_NORM_CASE(14)
+  switch (d % 1024 == 0 ? d / 1024 : 0) {
+    QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(3) QI_NORM_CASE(4)
     default:
-      norm_rows_generic_kernel<MODE><<<blocks, 128, 0, st>>>(
+      norm_rows_generic_kernel<MODE><<<blocks_generic, 128, 0, st>>>(
           (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, d, ld_x, ld_y,
           (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, eps);
   }
@@ -377,17 +408,13 @@ extern "C" int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_d
   if (!qkv || !wq_img || !wk_img || !wq_txt || !wk_txt || !freqs_cos_sin) return QI_ERR_ARG;
   if (rows <= 0) return QI_OK;
   if (ld % 8 != 0 || seq <= 0 || rows % seq != 0) return QI_ERR_ARG;
-  const long long items = (long long)rows * 2 * heads;
+  const int blocks = (rows + 7) / 8;
   if (head_dim == 128) {
-    const long long warps = (items + 1) / 2;
-    const int blocks = (int)((warps + 7) / 8);
     qknorm_rope_kernel<128><<<blocks, 256, 0, stream>>>(
         (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps);
   } else if (head_dim == 64) {
-    const long long warps = (items + 3) / 4;
-    const int blocks = (int)((warps + 7) / 8);
     qknorm_rope_kernel<64><<<blocks, 256, 0, stream>>>(
         (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
