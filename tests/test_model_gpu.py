@@ -118,3 +118,21 @@ def test_block_at_20b_width(cuda_device):
     out = tr(hidden_states=lat, encoder_hidden_states=cond, encoder_hidden_states_mask=mask, timestep=t,
              img_shapes=[[(1, hh, ww)]], txt_seq_lens=[s_txt]).sample
     assert O.rel_l2(out.float().cpu(), ref) < TOL
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_multi_gpu_parity(cuda_device, n):
+    """CFG-parallel (n=2) and CFG x Ulysses (n=4, 8) runs must reproduce the oracle's latents."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    port = 29600 + n
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(root, "tools", "mgpu_parity.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "MGPU_PARITY" in r.stdout

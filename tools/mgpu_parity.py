@@ -1,0 +1,50 @@
+"""torchrun entry: CFG-parallel / Ulysses denoising on N GPUs vs the oracle (tiny config).
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/mgpu_parity.py"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import qwen_image_oracle as O  # noqa: E402
+from vllm_omni_draft_b200.config import MMDiTConfig  # noqa: E402
+from vllm_omni_draft_b200.launcher import ParallelDenoiser, init_distributed  # noqa: E402
+
+
+def main():
+    world, rank, local_rank = init_distributed(int(os.environ.get("WORLD_SIZE", "1")))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    ocfg = O.tiny_config()
+    sd = O.init_state_dict(ocfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
+    lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, 256, 256, 32)
+    steps = 4
+    den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=False, state_dict=sd)
+    den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), 256, 256, steps, true_cfg_scale=4.0)
+    for i in range(steps):
+        den.step(i)
+    out = torch.zeros(1, lat.shape[1], 64, dtype=torch.bfloat16).pin_memory()
+    den.read_latents(out)
+    torch.cuda.synchronize()
+    full = out.to(dev)
+    if world > 1:
+        # every rank filled only its own token shard; sum over the SP ranks of the cond branch
+        if den.layout.branch != 0:
+            full.zero_()
+        dist.all_reduce(full)
+    den.close()
+    if rank == 0:
+        ref = O.denoise_loop(sd, ocfg, lat, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
+        err = O.rel_l2(full.float().cpu(), ref)
+        lay = den.layout
+        print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} rel_l2={err:.4e}", flush=True)
+        if not err < 1e-2:
+            sys.exit(1)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

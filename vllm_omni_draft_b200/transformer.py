@@ -59,6 +59,19 @@ class _Workspace:
         self.t1 = e(B, d)
         self.temb = e(B, d)
         self.t32 = torch.empty(B, device=device, dtype=torch.float32)
+        self.sp = None
+
+    def alloc_sp(self, cfg: MMDiTConfig, P: int, device, dtype):
+        """Ulysses exchange buffers (B == 1): send/recv [P, S_loc, 3, H/P, Dh], attention output
+        [P*S_loc, H/P, Dh], and the head-gathered result [P, S_loc, (H/P)*Dh]."""
+        s_loc = self.qkv.shape[1]
+        hs, dh = cfg.num_attention_heads // P, cfg.attention_head_dim
+        e = lambda *shape: torch.empty(*shape, device=device, dtype=dtype)
+        self.a2a_send = e(P, s_loc, 3, hs, dh)
+        self.a2a_recv = e(P, s_loc, 3, hs, dh)
+        self.o_full = e(P * s_loc, hs, dh)
+        self.a2a_back = e(P, s_loc, hs * dh)
+        self.sp = P
 
 
 class B200QwenImageTransformer2DModel(nn.Module):
@@ -99,6 +112,25 @@ class B200QwenImageTransformer2DModel(nn.Module):
         self._freqs: Dict[tuple, torch.Tensor] = {}
         self._mod_table: Optional[torch.Tensor] = None      # [steps, n_mod] hoisted modulation
         self._mod_steps: Optional[torch.Tensor] = None
+        self._sp = None              # UlyssesContext when sequence-parallel
+        self._sp_freqs: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ sequence parallelism (Ulysses)
+    def set_sequence_parallel(self, ctx) -> None:
+        """ctx: launcher.UlyssesContext (group, size, rank).  Heads must divide by the degree."""
+        if ctx is not None and self.cfg.num_attention_heads % ctx.size != 0:
+            raise ValueError("num_attention_heads must be divisible by the sequence-parallel degree")
+        self._sp = ctx
+        self._ws.clear()
+
+    def set_sequence_shard(self, img_shape, s_img_full: int, s_txt_full: int, img_range, txt_range) -> None:
+        """This rank owns image tokens [i0, i1) and text tokens [t0, t1) of the full sequence; its
+        RoPE rows are the matching rows of the full joint table (text rows first)."""
+        shapes = (tuple(int(v) for v in img_shape),)
+        full = rope.joint_cos_sin(self.cfg.axes_dims_rope, self.cfg.rope_theta, shapes, s_txt_full)
+        (i0, i1), (t0, t1) = img_range, txt_range
+        local = torch.cat([full[t0:t1], full[s_txt_full + i0:s_txt_full + i1]], dim=0).contiguous()
+        self._sp_freqs = local.to(self.device)
 
     # ------------------------------------------------------------------ host-layer conveniences
     @property
@@ -258,8 +290,14 @@ class B200QwenImageTransformer2DModel(nn.Module):
             shapes = ((1, side, side),)
         else:
             shapes = rope.normalize_img_shapes(img_shapes)
-        if sum(f * h * w for f, h, w in shapes) != s_img:
+        sp = self._sp
+        if sp is None and sum(f * h * w for f, h, w in shapes) != s_img:
             raise ValueError("img_shapes does not match the number of image tokens")
+        if sp is not None:
+            if B != 1:
+                raise NotImplementedError("Ulysses sequence parallelism is implemented for batch 1")
+            if self._sp_freqs is None or self._sp_freqs.shape[0] != s_img + s_txt:
+                raise ValueError("call set_sequence_shard() before a sequence-parallel forward")
         max_txt = int(max(txt_seq_lens)) if txt_seq_lens is not None else s_txt
         if max_txt != s_txt:
             raise ValueError("max(txt_seq_lens) must equal the text sequence length")
@@ -271,10 +309,15 @@ class B200QwenImageTransformer2DModel(nn.Module):
         ws = self._ws.get(key)
         if ws is None:
             ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
-        fkey = (shapes, s_txt)
-        freqs = self._freqs.get(fkey)
-        if freqs is None:
-            freqs = self._freqs[fkey] = rope.joint_cos_sin(cfg.axes_dims_rope, cfg.rope_theta, shapes, s_txt).to(dev)
+        if sp is not None:
+            freqs = self._sp_freqs
+            if ws.sp != sp.size:
+                ws.alloc_sp(cfg, sp.size, dev, dt)
+        else:
+            fkey = (shapes, s_txt)
+            freqs = self._freqs.get(fkey)
+            if freqs is None:
+                freqs = self._freqs[fkey] = rope.joint_cos_sin(cfg.axes_dims_rope, cfg.rope_theta, shapes, s_txt).to(dev)
 
         if _mod_override is not None:
             mod, mbs = _mod_override, 0
@@ -314,9 +357,20 @@ class B200QwenImageTransformer2DModel(nn.Module):
                       ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
             nw = self.qk_norm_w[l]
             ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
-            ops.attention(q, k, v, attn4)
-            ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
-                      ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
+            if sp is None:
+                ops.attention(q, k, v, attn4)
+                ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
+                          ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
+            else:
+                # head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
+                full = sp.scatter_heads(ws.qkv.view(S, 3 * d), H, Dh, ws.a2a_send, ws.a2a_recv)
+                ops.attention(full[:, 0].unsqueeze(0), full[:, 1].unsqueeze(0), full[:, 2].unsqueeze(0),
+                              ws.o_full.unsqueeze(0))
+                back = sp.gather_heads(ws.o_full, ws.a2a_back)
+                ops.gemm([ops.gemm_problem(back[:, s_txt:], self.out_w[l, 0], self.out_b[l, 0], h, G, h,
+                                           bview(g_i1), a_k_chunked=True),
+                          ops.gemm_problem(back[:, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
+                                           bview(g_t1), a_k_chunked=True)])
             ops.adaln_modulate(h2, bview(sh_i2), bview(sc_i2), xi2, s_img)
             ops.adaln_modulate(e2, bview(sh_t2), bview(sc_t2), xt2, s_txt)
             ops.gemm([ops.gemm_problem(ws.xn_img, self.mlp_up_w[l, 0], self.mlp_up_b[l, 0], ws.mlp_img,
