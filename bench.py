@@ -230,6 +230,8 @@ def main():
 
     if rank != 0:
         den.close()
+        if world > 1:
+            torch.distributed.destroy_process_group()
         return
 
     burst, sustained, hbm, src = load_peaks()
@@ -249,8 +251,11 @@ def main():
     if args.layers:
         line["invalid"] = "debug run with --layers"
     # ---------------- roofline of the dominant kernel + per-kernel table (rank 0, single GPU work)
-    line.update(den.kernel_rooflines(burst, sustained, hbm, src))
     den.close()
+    del den
+    torch.cuda.empty_cache()
+    from vllm_omni_draft_b200.roofline import kernel_rooflines
+    line.update(kernel_rooflines(burst, sustained, hbm, src))
     if world == 1 and not args.no_cpu_baseline and args.workload == "cfg2":
         times, threads = cpu_reference_sample(s_img, s_txt, 2, repeats=2)
         t_sample = min(times)
@@ -259,6 +264,8 @@ def main():
                                 "sample": "2 of 60 MMDiT blocks of one cond forward at full cfg-2 shapes, fp32 oracle, "
                                           "best of 2, extrapolated x30 x2 forwards"}
     print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -213,78 +213,3 @@ class ParallelDenoiser:
         if self.sess is not None:
             self.sess.close()
             self.sess = None
-
-    # -------------------------------------------------------------- per-kernel roofline numbers
-    def kernel_rooflines(self, burst_tf, sustained_tf, hbm_gbs, src) -> dict:
-        """Times the hot kernels alone with CUDA events at the cfg-2 shapes, cycling through the 60
-        blocks' weights so every launch reads operands that are not L2-resident."""
-        from . import ops
-        tr, cfg = self.tr, self.cfg
-        d, H, Dh, L = cfg.inner_dim, cfg.num_attention_heads, cfg.attention_head_dim, cfg.num_layers
-        key = next(iter(tr._ws))
-        ws = tr._ws[key]
-        B, s_img, s_txt = key
-        S = s_img + s_txt
-        reps = max(L, 20)
-
-        def timed(fn):
-            for l in range(3):
-                fn(l % L)
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for r in range(reps):
-                fn(r % L)
-            e1.record()
-            torch.cuda.synchronize()
-            return e0.elapsed_time(e1) / reps * 1e-3
-
-        out = {}
-        rows = (s_img + s_txt) * B
-
-        def up(l):
-            ops.gemm([ops.gemm_problem(ws.xn_img, tr.mlp_up_w[l, 0], tr.mlp_up_b[l, 0], ws.mlp_img, ops.EPI_BIAS_GELU_TANH),
-                      ops.gemm_problem(ws.xn_txt, tr.mlp_up_w[l, 1], tr.mlp_up_b[l, 1], ws.mlp_txt, ops.EPI_BIAS_GELU_TANH)])
-        t = timed(up)
-        fl = 2.0 * rows * 4 * d * d
-        dom = {"bound": "tensor", "kernel": "gemm_bf16_kernel<256> (MLP-up + GELU, img+txt in one launch)",
-               "achieved": fl / t / 1e12, "peak": sustained_tf, "unit": "TFLOP/s",
-               "frac": fl / t / 1e12 / sustained_tf, "traffic": None, "peak_source": src + " (sustained cuBLAS bf16)",
-               "launch_us": t * 1e6, "frac_of_nominal_2250": fl / t / 1e12 / 2250.0}
-        out["roofline"] = dom
-        kern = {}
-
-        def down(l):
-            G = ops.EPI_GATED_RESIDUAL
-            g = tr.mod_b[:d].view(1, d).expand(B, d)
-            ops.gemm([ops.gemm_problem(ws.mlp_img, tr.mlp_down_w[l, 0], tr.mlp_down_b[l, 0], ws.xn_img, G, ws.xn_img, g),
-                      ops.gemm_problem(ws.mlp_txt, tr.mlp_down_w[l, 1], tr.mlp_down_b[l, 1], ws.xn_txt, G, ws.xn_txt, g)])
-        t = timed(down)
-        kern["gemm_mlp_down_gated"] = {"us": t * 1e6, "tflops": fl / t / 1e12}
-
-        def qkvp(l):
-            ops.gemm([ops.gemm_problem(ws.xn_img, tr.qkv_w[l, 0], tr.qkv_b[l, 0], ws.qkv[:, s_txt:]),
-                      ops.gemm_problem(ws.xn_txt, tr.qkv_w[l, 1], tr.qkv_b[l, 1], ws.qkv[:, :s_txt])])
-        t = timed(qkvp)
-        kern["gemm_qkv"] = {"us": t * 1e6, "tflops": 2.0 * rows * 3 * d * d / t / 1e12}
-        q = ws.qkv[:, :, 0:d].unflatten(-1, (H, Dh))
-        k = ws.qkv[:, :, d:2 * d].unflatten(-1, (H, Dh))
-        v = ws.qkv[:, :, 2 * d:].unflatten(-1, (H, Dh))
-        o = ws.attn.unflatten(-1, (H, Dh))
-        t = timed(lambda l: ops.attention(q, k, v, o))
-        kern["attention"] = {"us": t * 1e6, "tflops": 4.0 * B * S * S * d / t / 1e12,
-                             "frac_of_sustained": 4.0 * B * S * S * d / t / 1e12 / sustained_tf}
-        mod = tr.mod_b.view(1, -1)
-        x2 = ws.h.view(B * s_img, d)
-        t = timed(lambda l: ops.adaln_modulate(x2, mod[:, :d].expand(B, d), mod[:, d:2 * d].expand(B, d),
-                                               ws.xn_img.view(B * s_img, d), s_img))
-        kern["adaln_modulate_img"] = {"us": t * 1e6, "gbs": 4.0 * B * s_img * d / t / 1e9,
-                                      "frac_of_hbm": 4.0 * B * s_img * d / t / 1e9 / hbm_gbs,
-                                      "note": "4096x3072 bf16 read+write = 50 MB, L2-resident between repeats"}
-        nw = tr.qk_norm_w[0]
-        fr = next(v_ for k_, v_ in tr._freqs.items() if isinstance(k_[0], tuple))
-        t = timed(lambda l: ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], fr))
-        kern["qknorm_rope"] = {"us": t * 1e6, "gbs": 8.0 * B * S * d / t / 1e9,
-                               "frac_of_hbm": 8.0 * B * S * d / t / 1e9 / hbm_gbs}
-        out["kernels"] = kern
-        return out
