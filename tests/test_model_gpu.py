@@ -120,8 +120,8 @@ def test_block_at_20b_width(cuda_device):
     assert O.rel_l2(out.float().cpu(), ref) < TOL
 
 
-@pytest.mark.parametrize("n", [2, 4, 8])
-def test_multi_gpu_parity(cuda_device, n):
+@pytest.mark.parametrize("n,graph", [(2, "0"), (2, "1"), (4, "1"), (8, "1")])
+def test_multi_gpu_parity(cuda_device, n, graph):
     """CFG-parallel (n=2) and CFG x Ulysses (n=4, 8) runs must reproduce the oracle's latents."""
     import os
     import subprocess
@@ -133,6 +133,6 @@ def test_multi_gpu_parity(cuda_device, n):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
                         "--master-addr", "127.0.0.1", "--master-port", str(port),
                         os.path.join(root, "tools", "mgpu_parity.py")],
-                       capture_output=True, text=True, timeout=600)
+                       capture_output=True, text=True, timeout=600, env=dict(os.environ, QI_GRAPH=graph))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "MGPU_PARITY" in r.stdout

@@ -20,7 +20,7 @@ def main():
     sd = O.init_state_dict(ocfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
     lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, 256, 256, 32)
     steps = 4
-    den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=False, state_dict=sd)
+    den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=os.environ.get("QI_GRAPH", "0") == "1", state_dict=sd)
     den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), 256, 256, steps, true_cfg_scale=4.0)
     for i in range(steps):
         den.step(i)
@@ -33,12 +33,13 @@ def main():
         if den.layout.branch != 0:
             full.zero_()
         dist.all_reduce(full)
+    graph_on = den.graph is not None
     den.close()
     if rank == 0:
         ref = O.denoise_loop(sd, ocfg, lat, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
         err = O.rel_l2(full.float().cpu(), ref)
         lay = den.layout
-        print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} rel_l2={err:.4e}", flush=True)
+        print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} graph={graph_on} rel_l2={err:.4e}", flush=True)
         if not err < 1e-2:
             sys.exit(1)
     if world > 1:

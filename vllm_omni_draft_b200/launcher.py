@@ -127,7 +127,8 @@ class ParallelDenoiser:
         else:
             self.tr.init_random_(seed)            # same seed on every rank -> replicated weights
         self.pipe = B200QwenImagePipeline(self.tr)
-        self.use_cuda_graph = use_cuda_graph and world == 1
+        self.use_cuda_graph = use_cuda_graph
+        self.graph = None
         self.sp_group = self.pair_group = None
         if world > 1:
             lay = self.layout
@@ -180,6 +181,38 @@ class ParallelDenoiser:
             self.sess = DenoiseSession(self.pipe, cond, None, lat, Hl, Wl, num_inference_steps, self.scale,
                                        use_cuda_graph=False, image_seq_len=self.s_img)
             self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
+            if self.use_cuda_graph:
+                # One graph per rank = forward + pair all-gather + K5 (+ the Ulysses all-to-alls inside the
+                # forward).  NCCL communicators are created by an eager warm-up step first; capture is
+                # thread-local so the NCCL watchdog thread cannot invalidate it.
+                tr, s = self.tr, self.sess
+                self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=dt)
+                self.dt_cur = torch.empty(1, device=dev, dtype=torch.float32)
+                self.mod_cur.copy_(tr._mod_table[0:1])
+                self.dt_cur.copy_(s.dts[0:1])
+                keep = s.cur.clone()
+                self._step_body(self.mod_cur, self.dt_cur)
+                torch.cuda.synchronize()
+                dist.barrier()
+                n0 = ops.launch_count
+                self.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+                    self._step_body(self.mod_cur, self.dt_cur)
+                self.launches_per_step = ops.launch_count - n0
+                s.cur.copy_(keep)
+
+    def _step_body(self, mod, dt_dev) -> None:
+        from . import ops
+        s = self.sess
+        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, img_shapes=s.shapes,
+                       txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod)[0]
+        if self.layout.cfg_degree == 2:
+            dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
+            c, u = self.pair_buf[0], self.pair_buf[1]
+        else:
+            c, u = pred, None
+        ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
+        s.cur.copy_(s.nxt)
 
     def load_inputs(self, cond_h, uncond_h, lat_h):
         lay = self.layout
@@ -199,17 +232,15 @@ class ParallelDenoiser:
             self.sess.step(i)
             return
         s = self.sess
-        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, img_shapes=s.shapes,
-                       txt_seq_lens=[s.s_txt], return_dict=False, _step_index=i)[0]
-        if self.layout.cfg_degree == 2:
-            dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
-            c, u = self.pair_buf[0], self.pair_buf[1]
+        if self.graph is not None:
+            self.mod_cur.copy_(self.tr._mod_table[i:i + 1])
+            self.dt_cur.copy_(s.dts[i:i + 1])
+            self.graph.replay()
         else:
-            c, u = pred, None
-        ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=s.dts[i:i + 1])
-        s.cur, s.nxt = s.nxt, s.cur
+            self._step_body(self.tr._mod_table[i:i + 1], s.dts[i:i + 1])
 
     def close(self):
+        self.graph = None
         if self.sess is not None:
             self.sess.close()
             self.sess = None
