@@ -178,6 +178,12 @@ def main():
     K, Wm = args.steps, args.warmup
 
     den = ParallelDenoiser(cfg, dev, world, rank, seed=0, use_cuda_graph=not args.no_graph)
+    lay = den.layout
+    workload["config"]["parallelism"] = (
+        "single" if world == 1 else
+        (f"cfg{lay.cfg_degree}" if lay.cfg_degree > 1 else "cfg-sequential")
+        + (f" x ulysses{lay.sp_degree} ({'fused peer-memory scatter kernels' if den.exchange == 'peer' else 'NCCL all_to_all_single'})"
+           if lay.sp_degree > 1 else ""))
     # synthetic inputs: cond N(0,1) seed 1, uncond seed 2, latents seed 42
     g1, g2, g3 = (torch.Generator().manual_seed(s) for s in (1, 2, 42))
     cond_h = torch.randn(1, s_txt, cfg.joint_attention_dim, generator=g1).bfloat16().pin_memory()

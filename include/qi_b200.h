@@ -75,6 +75,9 @@ typedef struct {
 
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
                  qi_stream_t stream);
+/* Tile width of the persistent GEMM: 0 = automatic (cheapest wave schedule over 148 SMs), or one of
+ * 128 / 192 / 256 to pin it (tests and tile sweeps). */
+int qi_gemm_set_tile_n(int bn);
 
 /* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
  * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).
@@ -104,6 +107,50 @@ int qi_rmsnorm_affine(const void* x, void* y, int rows, int d, int ld_x, int ld_
 int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq, int s_txt,
                    const void* wq_img, const void* wk_img, const void* wq_txt, const void* wk_txt,
                    const void* freqs_cos_sin, float eps, qi_stream_t stream);
+
+/* ---- Fused Ulysses exchange over peer memory (NVLink / NVSwitch; one process per GPU).
+ * The reference has no parallelism; this is the head<->sequence all-to-all of
+ * SURVEY §8e folded into the kernels on either side of it.  `base[p]` is rank p's buffer mapped
+ * into this process (qi_peer_import, or any other peer mapping); rank p owns heads
+ * [p*heads/P, (p+1)*heads/P) and sequence rows [row_prefix[p], row_prefix[p+1]) of the rank-major
+ * joint sequence (ragged shards allowed). */
+typedef struct {
+  int n_peers;       /* P <= 8 */
+  int my_index;      /* this rank's position in the group */
+  void* base[8];
+  int row_prefix[9]; /* row_prefix[P] = total sequence length */
+  long long chunk_stride; /* attention scatter only: elements between head-group chunks at the destination */
+} qi_peer_scatter_t;
+
+/* K2 with scatter: qkv is this rank's [batch*seq, ld] row block ([q|k|v], all heads); normalised and
+ * rotated q/k vectors and untouched v vectors are stored to base[owner of the head], laid out
+ * [batch, row_prefix[P], 3, heads/P, head_dim], at sequence row row_prefix[my_index] + s. */
+int qi_qknorm_rope_scatter(const void* qkv, int rows, int ld, int heads, int head_dim, int seq, int s_txt,
+                           const void* wq_img, const void* wk_img, const void* wq_txt, const void* wk_txt,
+                           const void* freqs_cos_sin, float eps, const qi_peer_scatter_t* dst /* host */,
+                           qi_stream_t stream);
+
+/* K4 with scatter: attention over the full sequence for this rank's heads; output row r (owned by
+ * rank p) is stored to base[p] + my_index*chunk_stride + b*o_batch_stride + (r - row_prefix[p])*ld_o
+ * + head*head_dim, i.e. into the K-chunked A operand of p's out-projection GEMM. */
+int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int batch, int seq_q, int seq_kv,
+                             int heads, int head_dim, long long ld_q, long long ld_kv, long long ld_o,
+                             long long q_batch_stride, long long kv_batch_stride, long long o_batch_stride,
+                             float softmax_scale, const qi_peer_scatter_t* dst /* host */, qi_stream_t stream);
+
+/* Peer memory: device allocations that can be mapped by the other ranks of the node (CUDA IPC).
+ * handle64 is a 64-byte host blob to ship to the peers (e.g. torch.distributed.all_gather_object). */
+int qi_peer_alloc(void** ptr /* host out */, unsigned long long bytes); /* zero-filled */
+int qi_peer_free(void* ptr);
+int qi_peer_export(void* ptr, void* handle64 /* host */);
+int qi_peer_import(const void* handle64 /* host */, void** ptr /* host out */);
+int qi_peer_unmap(void* ptr);
+/* Flag barrier across the ranks of a group, enqueued on `stream` (graph-capturable): orders every
+ * peer store issued by earlier kernels of the stream before the flag, then waits for all peers.
+ * signal_ptrs_dev: DEVICE array of n_peers pointers, entry p = rank p's u32[n_peers] signal array
+ * (zero-initialised, peer-mapped).  state_dev: this rank's u32[2] {epoch, sticky timeout flag}. */
+int qi_peer_barrier(void* const* signal_ptrs_dev, int n_peers, int my_index, uint32_t* state_dev,
+                    unsigned int timeout_ms, qi_stream_t stream);
 
 /* ---- K5: true-CFG combine + per-token norm rescale + FlowMatch Euler update in one pass
  * (replaces QwenImagePipeline's comb_pred/cond_norm/noise_norm lines and

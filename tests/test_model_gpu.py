@@ -120,9 +120,26 @@ def test_block_at_20b_width(cuda_device):
     assert O.rel_l2(out.float().cpu(), ref) < TOL
 
 
-@pytest.mark.parametrize("n,graph", [(2, "0"), (2, "1"), (4, "1"), (8, "1")])
-def test_multi_gpu_parity(cuda_device, n, graph):
-    """CFG-parallel (n=2) and CFG x Ulysses (n=4, 8) runs must reproduce the oracle's latents."""
+_MGPU_CASES = [
+    # (gpus, env) — CFG-parallel at 2, CFG x Ulysses at 4/8, pure Ulysses (QI_CFG_PARALLEL=0), both exchanges,
+    # ragged shards (272x240 px -> 255 image tokens, 33 prompt tokens) and batch 2
+    (2, dict(QI_GRAPH="0")),
+    (2, dict(QI_GRAPH="1")),
+    (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer")),
+    (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="nccl")),
+    (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PAR_H="272", QI_PAR_W="240",
+             QI_PAR_TXT="33", QI_PAR_BATCH="2")),
+    (4, dict(QI_GRAPH="1", QI_SP_EXCHANGE="peer")),
+    (4, dict(QI_GRAPH="1", QI_SP_EXCHANGE="nccl")),
+    (4, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PAR_H="272", QI_PAR_W="240",
+             QI_PAR_TXT="33", QI_PAR_BATCH="2")),
+    (8, dict(QI_GRAPH="1", QI_SP_EXCHANGE="peer")),
+]
+
+
+@pytest.mark.parametrize("n,env", _MGPU_CASES)
+def test_multi_gpu_parity(cuda_device, n, env):
+    """CFG-parallel (n=2), CFG x Ulysses (n=4, 8) and pure-Ulysses runs must reproduce the oracle's latents."""
     import os
     import subprocess
     import sys
@@ -133,6 +150,6 @@ def test_multi_gpu_parity(cuda_device, n, graph):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
                         "--master-addr", "127.0.0.1", "--master-port", str(port),
                         os.path.join(root, "tools", "mgpu_parity.py")],
-                       capture_output=True, text=True, timeout=600, env=dict(os.environ, QI_GRAPH=graph))
+                       capture_output=True, text=True, timeout=600, env=dict(os.environ, **env))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "MGPU_PARITY" in r.stdout

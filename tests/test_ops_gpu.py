@@ -175,3 +175,108 @@ def test_attention(cuda_device, B, S, H, Dh):
         q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
     err = O.rel_l2(out.cpu(), ref.cpu())
     assert err < 1e-2, f"rel_l2={err}"
+
+
+@pytest.mark.parametrize("bn", [128, 192, 256])
+def test_gemm_tile_widths(cuda_device, bn):
+    """Every tile width of the persistent GEMM (auto-selected by wave count in production) is exact."""
+    ops = _ops()
+    ops.gemm_set_tile_n(bn)
+    try:
+        for (B, M, N, K, epi) in [(1, 1152, 3072, 3072, 2), (2, 200, 1024, 256, 1), (1, 257, 64, 128, 0)]:
+            a, w, bias = _rand((B, M, K), 60), _rand((N, K), 61, 0.05), _rand((N,), 62, 0.5)
+            out = torch.zeros(B, M, N, device="cuda", dtype=torch.bfloat16)
+            res = _rand((B, M, N), 63) if epi == 2 else None
+            gate = _rand((B, N), 64) if epi == 2 else None
+            ops.gemm([ops.gemm_problem(a, w, bias, out, epi, res, gate)])
+            y = torch.matmul(a.float(), w.float().t()) + bias.float()
+            if epi == 1:
+                y = torch.nn.functional.gelu(y, approximate="tanh")
+            elif epi == 2:
+                y = res.float() + gate.float()[:, None, :] * y
+            err = O.rel_l2(out.cpu(), y.cpu())
+            assert err < 5e-3, f"bn={bn} case {(B, M, N, K, epi)} rel_l2={err}"
+    finally:
+        ops.gemm_set_tile_n(0)
+
+
+def _peer_scatter(bases, prefix, me, chunk_stride=0):
+    from vllm_omni_draft_b200._lib import PeerScatter
+    d = PeerScatter()
+    d.n_peers, d.my_index, d.chunk_stride = len(bases), me, chunk_stride
+    for p, t in enumerate(bases):
+        d.base[p] = t.data_ptr()
+    for i, v in enumerate(prefix):
+        d.row_prefix[i] = v
+    return d
+
+
+@pytest.mark.parametrize("P,B,counts", [(2, 1, [40, 40]), (4, 2, [37, 36, 36, 36])])
+def test_ulysses_scatter_kernels_emulated_ranks(cuda_device, P, B, counts):
+    """The fused exchange (K2 scatter -> attention scatter -> K-chunked out-proj operand) with the P
+    ranks emulated on one GPU: every 'peer' buffer is a local tensor, so the layout arithmetic of both
+    scatter kernels (ragged shards, batch, head ownership) is checked against the unsharded path."""
+    ops = _ops()
+    from vllm_omni_draft_b200 import rope
+    H, Dh, axes = 4, 64, (8, 28, 28)
+    d = H * Dh
+    hs = H // P
+    pre = [0]
+    for c in counts:
+        pre.append(pre[-1] + c)
+    S = pre[-1]
+    s_max = max(counts)
+    s_txt_full = 2 * P + 1                       # ragged text split as well
+    from vllm_omni_draft_b200.peer import prefix as _prefix, shard_counts
+    txt_counts = shard_counts(s_txt_full, P)
+    img_counts = [c - t for c, t in zip(counts, txt_counts)]
+    s_img_full = sum(img_counts)
+    tpre, ipre = _prefix(txt_counts), _prefix(img_counts)
+    hh, ww = 1, s_img_full                       # one row of image tokens
+    qkv_full = _rand((B, s_txt_full + s_img_full, 3 * d), 70, 1.2)          # joint order [txt; img]
+    ws = [_rand((Dh,), 71 + i, 0.2) + 1 for i in range(4)]
+    freqs_full = rope.joint_cos_sin(axes, 10000.0, [(1, hh, ww)], s_txt_full).cuda()
+    # unsharded reference on the same kernels: K2 in place, then attention
+    ref_qkv = qkv_full.clone()
+    ops.qknorm_rope(ref_qkv.view(B * (s_txt_full + s_img_full), 3 * d), H, Dh, s_txt_full + s_img_full, s_txt_full,
+                    ws[0], ws[1], ws[2], ws[3], freqs_full)
+    rq, rk, rv = [ref_qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
+    ref_o = torch.zeros(B, s_txt_full + s_img_full, H, Dh, device="cuda", dtype=torch.bfloat16)
+    ops.attention(rq, rk, rv, ref_o)
+    # emulated ranks
+    recv = [torch.zeros(B, S, 3, hs, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    back = [torch.zeros(P, B, s_max, hs * Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    rows_of = []
+    for r in range(P):
+        rows = list(range(tpre[r], tpre[r + 1])) + [s_txt_full + i for i in range(ipre[r], ipre[r + 1])]
+        rows_of.append(rows)
+        local = qkv_full[:, rows].contiguous()                               # [B, S_loc, 3d]
+        fl = freqs_full[rows].contiguous()
+        ops.qknorm_rope_scatter(local.view(B * counts[r], 3 * d), H, Dh, counts[r], txt_counts[r],
+                                ws[0], ws[1], ws[2], ws[3], fl, _peer_scatter(recv, pre, r))
+    for r in range(P):
+        full = recv[r]
+        ops.attention_scatter(full[:, :, 0], full[:, :, 1], full[:, :, 2],
+                              _peer_scatter(back, pre, r, B * s_max * hs * Dh), hs * Dh, s_max * hs * Dh)
+    torch.cuda.synchronize()
+    for r in range(P):
+        got = back[r][:, :, :counts[r]].permute(1, 2, 0, 3).reshape(B, counts[r], H, Dh)   # chunk = head group
+        want = ref_o[:, rows_of[r]]
+        err = O.rel_l2(got.cpu(), want.cpu())
+        assert err < 4e-3, f"rank {r}: rel_l2={err}"
+        # the scattered q/k/v themselves are bit-identical to the in-place kernel's output
+        full_rows = [x for rr in rows_of for x in rr]
+        for j, t in enumerate((rq, rk, rv)):
+            assert torch.equal(recv[r][:, :, j], t[:, full_rows][:, :, r * hs:(r + 1) * hs])
+
+
+def test_peer_barrier_single_rank(cuda_device):
+    """n_peers = 1: the rank signals itself; the epoch advances and the timeout flag stays clear."""
+    ops = _ops()
+    sig = torch.zeros(8, dtype=torch.int32, device="cuda")
+    table = torch.tensor([sig.data_ptr()], dtype=torch.int64, device="cuda")
+    state = torch.zeros(2, dtype=torch.int32, device="cuda")
+    for _ in range(3):
+        ops.peer_barrier(table, 1, 0, state)
+    torch.cuda.synchronize()
+    assert state.tolist() == [3, 0] and int(sig[0]) == 3

@@ -23,8 +23,11 @@ def test_layout_and_shards():
     l4 = ParallelLayout.make(4, 2, do_cfg=False)
     assert (l4.cfg_degree, l4.sp_degree, l4.sp_rank) == (1, 4, 2)
     assert shard_bounds(4096, 4, 3) == (3072, 4096)
-    with pytest.raises(ValueError):
-        shard_bounds(6889, 4, 0)        # cfg-5's ragged length is not supported yet
+    # cfg-5's ragged length: 6889 = 1723 + 3 * 1722, shards tile the sequence without gaps
+    b = [shard_bounds(6889, 4, i) for i in range(4)]
+    assert b == [(0, 1723), (1723, 3445), (3445, 5167), (5167, 6889)]
+    from vllm_omni_draft_b200.peer import prefix, shard_counts
+    assert shard_counts(7401, 4) == [1851, 1850, 1850, 1850] and prefix([3, 2, 2]) == [0, 3, 5, 7]
     with pytest.raises(ValueError):
         ParallelLayout.make(2, 2)
 

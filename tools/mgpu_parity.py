@@ -18,13 +18,17 @@ def main():
     dev = torch.device("cuda", local_rank)
     ocfg = O.tiny_config()
     sd = O.init_state_dict(ocfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
-    lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, 256, 256, 32)
+    # shape knobs: QI_PAR_H/W (pixels), QI_PAR_TXT (prompt tokens), QI_PAR_BATCH; 272x240 with 33 prompt
+    # tokens gives ragged shards (255 image tokens)
+    env = lambda k, v: int(os.environ.get(k, v))
+    Hpx, Wpx, s_txt, batch = env("QI_PAR_H", 256), env("QI_PAR_W", 256), env("QI_PAR_TXT", 32), env("QI_PAR_BATCH", 1)
+    lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, Hpx, Wpx, s_txt, batch=batch)
     steps = 4
     den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=os.environ.get("QI_GRAPH", "0") == "1", state_dict=sd)
-    den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), 256, 256, steps, true_cfg_scale=4.0)
+    den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), Hpx, Wpx, steps, true_cfg_scale=4.0)
     for i in range(steps):
         den.step(i)
-    out = torch.zeros(1, lat.shape[1], 64, dtype=torch.bfloat16).pin_memory()
+    out = torch.zeros(batch, lat.shape[1], 64, dtype=torch.bfloat16).pin_memory()
     den.read_latents(out)
     torch.cuda.synchronize()
     full = out.to(dev)
@@ -34,12 +38,17 @@ def main():
             full.zero_()
         dist.all_reduce(full)
     graph_on = den.graph is not None
+    if den.exchange_timed_out():
+        print(f"rank {rank}: peer barrier timed out", flush=True)
+        sys.exit(3)
+    exch = den.exchange if den.layout.sp_degree > 1 else "-"
     den.close()
     if rank == 0:
         ref = O.denoise_loop(sd, ocfg, lat, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
         err = O.rel_l2(full.float().cpu(), ref)
         lay = den.layout
-        print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} graph={graph_on} rel_l2={err:.4e}", flush=True)
+        print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} exchange={exch} graph={graph_on} "
+              f"px={Hpx}x{Wpx} txt={s_txt} B={batch} rel_l2={err:.4e}", flush=True)
         if not err < 1e-2:
             sys.exit(1)
     if world > 1:

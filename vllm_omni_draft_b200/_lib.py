@@ -31,11 +31,28 @@ class GemmProblem(C.Structure):
     ]
 
 
+class PeerScatter(C.Structure):
+    """qi_peer_scatter_t"""
+    _fields_ = [("n_peers", _i), ("my_index", _i), ("base", _vp * 8), ("row_prefix", _i * 9),
+                ("chunk_stride", _ll)]
+
+
 _SIGNATURES = {
     "qi_version": (_i, []),
     "qi_last_cuda_error": (C.c_char_p, []),
     "qi_device_sm_count": (_i, []),
     "qi_gemm_bf16": (_i, [C.POINTER(GemmProblem), _i, _vp]),
+    "qi_gemm_set_tile_n": (_i, [_i]),
+    "qi_attention_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f,
+                                      C.POINTER(PeerScatter), _vp]),
+    "qi_qknorm_rope_scatter": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f,
+                                    C.POINTER(PeerScatter), _vp]),
+    "qi_peer_alloc": (_i, [C.POINTER(_vp), C.c_ulonglong]),
+    "qi_peer_free": (_i, [_vp]),
+    "qi_peer_export": (_i, [_vp, _vp]),
+    "qi_peer_import": (_i, [_vp, C.POINTER(_vp)]),
+    "qi_peer_unmap": (_i, [_vp]),
+    "qi_peer_barrier": (_i, [_vp, _i, _i, _vp, C.c_uint, _vp]),
     "qi_attention_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f, _vp]),
     "qi_adaln_modulate": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _ll, _i, _f, _vp]),
     "qi_rmsnorm_affine": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp]),

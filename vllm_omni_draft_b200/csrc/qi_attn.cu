@@ -39,6 +39,12 @@ struct AttParams {
   long long ld_o, o_bs;
   int seq_q, seq_kv, heads;
   float scale_log2;
+  // Ulysses scatter epilogue (n_peer > 0): query row r owned by rank p goes to
+  // o_peer[p] + o_chunk_off + b*o_bs + (r - o_prefix[p])*ld_o + head*DH   (peer-mapped HBM)
+  int n_peer;
+  int o_prefix[9];
+  long long o_chunk_off;
+  __nv_bfloat16* o_peer[8];
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -272,7 +278,15 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     tc_fence_after();
     const int row = q0 + t * ATT_BM + quad * 32 + lane;
     const float inv = 1.f / l_sum;
-    __nv_bfloat16* orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
+    __nv_bfloat16* orow;
+    if (P.n_peer > 0) {
+      int p = 0;
+      while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
+      orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
+             (size_t)head * DH;
+    } else {
+      orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
+    }
 #pragma unroll 1
     for (int c = 0; c < DH / 32; ++c) {
       uint32_t r[32];
@@ -308,9 +322,18 @@ template <int DH>
 static int launch_attention(const void* q, const void* k, const void* v, void* o, int batch,
                             int seq_q, int seq_kv, int heads, long long ld_q, long long ld_kv,
                             long long ld_o, long long q_bs, long long kv_bs, long long o_bs,
-                            float scale, cudaStream_t stream) {
+                            float scale, const qi_peer_scatter_t* dst, cudaStream_t stream) {
   AttParams P;
   memset(&P, 0, sizeof(P));
+  if (dst) {
+    P.n_peer = dst->n_peers;
+    for (int p = 0; p < dst->n_peers; ++p) {
+      P.o_peer[p] = (__nv_bfloat16*)dst->base[p];
+      P.o_prefix[p] = dst->row_prefix[p];
+    }
+    P.o_prefix[dst->n_peers] = dst->row_prefix[dst->n_peers];
+    P.o_chunk_off = (long long)dst->my_index * dst->chunk_stride;
+  }
   const uint32_t box[4] = {64, 1, ATT_BM, 1};
   {
     uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_q, (uint64_t)batch};
@@ -348,12 +371,12 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   return QI_OK;
 }
 
-extern "C" int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int batch,
-                                int seq_q, int seq_kv, int heads, int head_dim, long long ld_q,
-                                long long ld_kv, long long ld_o, long long q_batch_stride,
-                                long long kv_batch_stride, long long o_batch_stride,
-                                float softmax_scale, cudaStream_t stream) {
-  if (!q || !k || !v || !o) return QI_ERR_ARG;
+static int attention_entry(const void* q, const void* k, const void* v, void* o, int batch,
+                           int seq_q, int seq_kv, int heads, int head_dim, long long ld_q,
+                           long long ld_kv, long long ld_o, long long q_batch_stride,
+                           long long kv_batch_stride, long long o_batch_stride, float softmax_scale,
+                           const qi_peer_scatter_t* dst, cudaStream_t stream) {
+  if (!q || !k || !v || (!o && !dst)) return QI_ERR_ARG;
   if (batch <= 0 || seq_q <= 0 || seq_kv <= 0 || heads <= 0) return QI_ERR_ARG;
   if (ld_q % 8 || ld_kv % 8 || ld_o % 8 || q_batch_stride % 8 || kv_batch_stride % 8 ||
       o_batch_stride % 8)
@@ -361,14 +384,44 @@ extern "C" int qi_attention_fwd(const void* q, const void* k, const void* v, voi
   if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) |
        reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(o)) & 15)
     return QI_ERR_ARG;
+  if (dst) {
+    if (dst->n_peers < 1 || dst->n_peers > 8 || dst->my_index < 0 || dst->my_index >= dst->n_peers ||
+        dst->chunk_stride % 8 || dst->row_prefix[0] != 0 || dst->row_prefix[dst->n_peers] != seq_q)
+      return QI_ERR_ARG;
+    for (int p = 0; p < dst->n_peers; ++p)
+      if (!dst->base[p] || (reinterpret_cast<uintptr_t>(dst->base[p]) & 15) ||
+          dst->row_prefix[p + 1] < dst->row_prefix[p])
+        return QI_ERR_ARG;
+  }
   if (qi_num_sms() <= 0) return QI_ERR_CUDA;
   if (head_dim == 128)
     return launch_attention<128>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
                                  q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
-                                 stream);
+                                 dst, stream);
   if (head_dim == 64)
     return launch_attention<64>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
                                 q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
-                                stream);
+                                dst, stream);
   return QI_ERR_UNSUPPORTED;
+}
+
+extern "C" int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int batch,
+                                int seq_q, int seq_kv, int heads, int head_dim, long long ld_q,
+                                long long ld_kv, long long ld_o, long long q_batch_stride,
+                                long long kv_batch_stride, long long o_batch_stride,
+                                float softmax_scale, cudaStream_t stream) {
+  return attention_entry(q, k, v, o, batch, seq_q, seq_kv, heads, head_dim, ld_q, ld_kv, ld_o,
+                         q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale, nullptr,
+                         stream);
+}
+
+extern "C" int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int batch,
+                                        int seq_q, int seq_kv, int heads, int head_dim,
+                                        long long ld_q, long long ld_kv, long long ld_o,
+                                        long long q_batch_stride, long long kv_batch_stride,
+                                        long long o_batch_stride, float softmax_scale,
+                                        const qi_peer_scatter_t* dst, cudaStream_t stream) {
+  if (!dst) return QI_ERR_ARG;
+  return attention_entry(q, k, v, nullptr, batch, seq_q, seq_kv, heads, head_dim, ld_q, ld_kv, ld_o,
+                         q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale, dst, stream);
 }

@@ -8,6 +8,7 @@
 // All use 128-bit global accesses, one warp per row (or per group of heads/tokens), and
 // warp-shuffle reductions; no shared memory is needed because no datum is reused across warps.
 #include "qi_common.cuh"
+#include "../../include/qi_b200.h"
 
 namespace qi {
 
@@ -245,6 +246,87 @@ __global__ void __launch_bounds__(256) qknorm_rope_kernel(
 }
 
 // ---------------------------------------------------------------------------------------------
+// K2 + Ulysses scatter: same arithmetic, but the result is not written back in place: head vector
+// (row, j in {q,k,v}, head h) goes straight to the rank that owns head h, i.e. into that rank's
+// [batch, s_total, 3, heads/P, DH] attention input buffer (peer-mapped over NVLink), at sequence
+// row row_offset + s.  v vectors are moved untouched.  This IS the head<->sequence all-to-all.
+// ---------------------------------------------------------------------------------------------
+struct ScatterDst {
+  __nv_bfloat16* base[8];
+  int n;               // ranks
+  int heads_per_rank;
+  int s_total;         // rows per batch item in the destination buffers
+  int row_offset;      // first destination row of this rank's tokens
+};
+
+template <int DH>
+__global__ void __launch_bounds__(256) qknorm_rope_scatter_kernel(
+    const __nv_bfloat16* __restrict__ qkv, int rows, int ld, int heads, int seq, int s_txt,
+    const __nv_bfloat16* __restrict__ wq_img, const __nv_bfloat16* __restrict__ wk_img,
+    const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
+    const float2* __restrict__ freqs, float eps, const __grid_constant__ ScatterDst D) {
+  constexpr int LPH = DH / 8;
+  constexpr int VPW = 32 / LPH;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPH;
+  const int grp = lane / LPH;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
+  const int b = row / seq;
+  const int pos = row - b * seq;
+  const bool is_txt = pos < s_txt;
+  const float4* fp = reinterpret_cast<const float4*>(freqs + (size_t)pos * (DH / 2) + sub * 4);
+  const float4 f01 = fp[0], f23 = fp[1];
+  const float cs[4] = {f01.x, f01.z, f23.x, f23.z};
+  const float sn[4] = {f01.y, f01.w, f23.y, f23.w};
+  float wq[8], wk[8];
+  unpack8(ldg128((is_txt ? wq_txt : wq_img) + sub * 8), wq);
+  unpack8(ldg128((is_txt ? wk_txt : wk_img) + sub * 8), wk);
+  const __nv_bfloat16* src = qkv + (size_t)row * ld + sub * 8;
+  const int hs = D.heads_per_rank;
+  // destination row (in units of DH-vectors): ((b*s_total + row_offset + pos)*3 + j)*hs + hl
+  const size_t drow = ((size_t)b * D.s_total + D.row_offset + pos) * 3;
+  const int nvec = 3 * heads;
+  constexpr int UNROLL = 4;
+  for (int v0 = grp; v0 < nvec; v0 += VPW * UNROLL) {
+    uint4 raw[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int vi = v0 + u * VPW;
+      if (vi < nvec) raw[u] = ldg128_stream(src + (size_t)vi * DH);
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int vi = v0 + u * VPW;
+      float v[8];
+      unpack8(raw[u], v);
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss = fmaf(v[j], v[j], ss);
+      ss = group_sum<LPH>(ss);
+      const float rstd = rsqrtf(ss * (1.f / DH) + eps);
+      const int j3 = vi / heads;            // 0 q, 1 k, 2 v
+      const int h = vi - j3 * heads;
+      const bool is_k = j3 == 1;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a = bf16_round(bf16_round(v[2 * j] * rstd) * (is_k ? wk[2 * j] : wq[2 * j]));
+        const float bb = bf16_round(bf16_round(v[2 * j + 1] * rstd) * (is_k ? wk[2 * j + 1] : wq[2 * j + 1]));
+        o[2 * j] = a * cs[j] - bb * sn[j];
+        o[2 * j + 1] = a * sn[j] + bb * cs[j];
+      }
+      if (vi < nvec) {
+        const int p = h / hs;
+        const int hl = h - p * hs;
+        __nv_bfloat16* dst = D.base[p] + ((drow + j3) * hs + hl) * DH + sub * 8;
+        stg128(dst, j3 == 2 ? raw[u] : pack8(o));
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // K5: one group of 8 lanes per token (64 channels = 8 lanes x 8 bf16).  Rounding follows the
 // eager bf16 pipeline op by op: comb, the two norms, their ratio, the product,
 // dt*v (dt itself rounded to bf16 by type promotion), then the fp32 accumulate and final cast.
@@ -419,6 +501,46 @@ extern "C" int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_d
         (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps);
+  } else {
+    return QI_ERR_UNSUPPORTED;
+  }
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_qknorm_rope_scatter(const void* qkv, int rows, int ld, int heads, int head_dim,
+                                      int seq, int s_txt, const void* wq_img, const void* wk_img,
+                                      const void* wq_txt, const void* wk_txt,
+                                      const void* freqs_cos_sin, float eps,
+                                      const qi_peer_scatter_t* dst, cudaStream_t stream) {
+  if (!qkv || !wq_img || !wk_img || !wq_txt || !wk_txt || !freqs_cos_sin || !dst) return QI_ERR_ARG;
+  if (rows <= 0) return QI_OK;
+  if (ld % 8 != 0 || seq <= 0 || rows % seq != 0) return QI_ERR_ARG;
+  if (dst->n_peers < 1 || dst->n_peers > 8 || dst->my_index < 0 || dst->my_index >= dst->n_peers ||
+      heads % dst->n_peers != 0)
+    return QI_ERR_ARG;
+  ScatterDst D;
+  for (int p = 0; p < 8; ++p) {
+    D.base[p] = p < dst->n_peers ? (__nv_bfloat16*)dst->base[p] : nullptr;
+    if (p < dst->n_peers && (!dst->base[p] || (reinterpret_cast<uintptr_t>(dst->base[p]) & 15)))
+      return QI_ERR_ARG;
+  }
+  D.n = dst->n_peers;
+  D.heads_per_rank = heads / dst->n_peers;
+  D.s_total = dst->row_prefix[dst->n_peers];
+  D.row_offset = dst->row_prefix[dst->my_index];
+  if (dst->row_prefix[dst->my_index + 1] - D.row_offset != seq) return QI_ERR_ARG;
+  const int blocks = (rows + 7) / 8;
+  if (head_dim == 128) {
+    qknorm_rope_scatter_kernel<128><<<blocks, 256, 0, stream>>>(
+        (const __nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
+        (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
+        (const float2*)freqs_cos_sin, eps, D);
+  } else if (head_dim == 64) {
+    qknorm_rope_scatter_kernel<64><<<blocks, 256, 0, stream>>>(
+        (const __nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
+        (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
+        (const float2*)freqs_cos_sin, eps, D);
   } else {
     return QI_ERR_UNSUPPORTED;
   }

@@ -44,8 +44,9 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
-  static constexpr int TMEM_COLS = 2 * BN;  // 512 or 256: power of two
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 192 ? 5 : 6);
+  static constexpr int ACC_STRIDE = (BN == 192) ? 256 : BN;   // TMEM columns between the two accumulators
+  static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;   // power of two
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -147,7 +148,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
         const int kblocks = L.prob[tc.p].k / BK;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
+        const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -191,7 +192,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       const __nv_bfloat16* rrow =
           P.residual ? P.residual + (size_t)tc.b * P.res_bs + (size_t)row * P.ld_res : nullptr;
       const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)tc.b * P.gate_bs : nullptr;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
@@ -344,20 +345,41 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
   return QI_OK;
 }
 
+static int g_force_bn = 0;
+extern "C" int qi_gemm_set_tile_n(int bn) {
+  if (bn != 0 && bn != 128 && bn != 192 && bn != 256) return QI_ERR_ARG;
+  g_force_bn = bn;
+  return QI_OK;
+}
+
 extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
                             cudaStream_t stream) {
   if (!problems || num_problems < 1 || num_problems > 2) return QI_ERR_ARG;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
-  // Pick BN=256 when every problem's N is a multiple of 256 and the 256-wide tiling still gives at
-  // least one full wave; otherwise BN=128 (more, smaller tiles for the short text stream).
-  long long tiles256 = 0;
-  bool ok256 = true;
-  for (int i = 0; i < num_problems; ++i) {
-    const qi_gemm_problem_t& p = problems[i];
-    if (p.n % 256 != 0) ok256 = false;
-    tiles256 += (long long)((p.m + BM - 1) / BM) * p.batch * ((p.n + 255) / 256);
+  // Tile width: the persistent grid runs ceil(tiles / SMs) waves of 128 x BN tiles, each costing
+  // ~BN (+ a fixed per-tile overhead).  Pick the BN in {256, 192, 128} with the cheapest schedule:
+  // 256 for the full-size problems, 192 where it turns 1.46 / 2.19 waves into 0.97 / 2.92 (the
+  // token-sharded Ulysses shapes), 128 for narrow outputs.
+  int bn = g_force_bn;
+  if (bn == 0) {
+    long long best = -1;
+    const int cand[3] = {256, 192, 128};
+    for (int c = 0; c < 3; ++c) {
+      long long tiles = 0;
+      for (int i = 0; i < num_problems; ++i) {
+        const qi_gemm_problem_t& p = problems[i];
+        tiles += (long long)((p.m + BM - 1) / BM) * p.batch * ((p.n + cand[c] - 1) / cand[c]);
+      }
+      const long long waves = (tiles + sms - 1) / sms;
+      const long long cost = waves * (cand[c] + 24);
+      if (best < 0 || cost < best) {
+        best = cost;
+        bn = cand[c];
+      }
+    }
   }
-  if (ok256 && tiles256 >= sms) return launch_gemm<256>(problems, num_problems, stream);
+  if (bn == 256) return launch_gemm<256>(problems, num_problems, stream);
+  if (bn == 192) return launch_gemm<192>(problems, num_problems, stream);
   return launch_gemm<128>(problems, num_problems, stream);
 }

@@ -68,11 +68,11 @@ class ParallelLayout:
 
 
 def shard_bounds(n: int, parts: int, idx: int) -> Tuple[int, int]:
-    """Even split; Ulysses here requires divisibility (ragged shards are SURVEY §7 'hard part')."""
-    if n % parts != 0:
-        raise ValueError(f"sequence length {n} is not divisible by the sequence-parallel degree {parts}")
-    step = n // parts
-    return idx * step, (idx + 1) * step
+    """Rows [lo, hi) of rank idx when n rows are split over `parts` ranks; ragged splits give the
+    first n % parts ranks one extra row (cfg-5: 6889 image tokens over 4 ranks)."""
+    from .peer import prefix, shard_counts
+    pre = prefix(shard_counts(n, parts))
+    return pre[idx], pre[idx + 1]
 
 
 # ------------------------------------------------------------------ Ulysses exchanges (backend-agnostic)
@@ -81,6 +81,7 @@ class UlyssesContext:
 
     def __init__(self, group, size: int, rank: int):
         self.group, self.size, self.rank = group, size, rank
+        self.peer = None      # peer.PeerExchange: the fused peer-memory exchange replaces both all-to-alls
 
     def scatter_heads(self, qkv_local: torch.Tensor, heads: int, head_dim: int,
                       send: Optional[torch.Tensor] = None, recv: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -116,11 +117,20 @@ class ParallelDenoiser:
     the) latents by one scheduler step on every rank."""
 
     def __init__(self, cfg, device, world: int = 1, rank: int = 0, seed: int = 0, use_cuda_graph: bool = True,
-                 state_dict=None):
+                 state_dict=None, cfg_parallel: Optional[bool] = None, exchange: Optional[str] = None):
+        """cfg_parallel: split cond/uncond over two rank groups (default: yes when world is even; the env
+        QI_CFG_PARALLEL=0 gives pure Ulysses over all ranks).  exchange: "peer" (fused peer-memory
+        scatter kernels, default) or "nccl" (all_to_all_single), env QI_SP_EXCHANGE."""
         from .pipeline import B200QwenImagePipeline
         from .transformer import B200QwenImageTransformer2DModel
         self.cfg, self.device, self.world, self.rank = cfg, device, world, rank
-        self.layout = ParallelLayout.make(world, rank)
+        if cfg_parallel is None:
+            cfg_parallel = os.environ.get("QI_CFG_PARALLEL", "1") != "0"
+        self.exchange = (exchange or os.environ.get("QI_SP_EXCHANGE", "peer")).lower()
+        if self.exchange not in ("peer", "nccl"):
+            raise ValueError("exchange must be 'peer' or 'nccl'")
+        self.layout = ParallelLayout.make(world, rank, do_cfg=cfg_parallel)
+        self.peer = None
         self.tr = B200QwenImageTransformer2DModel(cfg, device=device)
         if state_dict is not None:
             self.tr.load_diffusers_state_dict(state_dict)
@@ -170,6 +180,18 @@ class ParallelDenoiser:
         if lay.sp_degree > 1:
             self.tr.set_sequence_shard((1, Hl // 2, Wl // 2), self.s_img, self.s_txt, (self.i0, self.i1),
                                        (self.t0, self.t1))
+            if self.exchange == "peer":
+                from .peer import PeerExchange, shard_counts
+                rows = [a + b for a, b in zip(shard_counts(self.s_txt, lay.sp_degree),
+                                              shard_counts(self.s_img, lay.sp_degree))]
+                if self.peer is not None:
+                    self.peer.close()
+                self.peer = PeerExchange(self.sp_group, lay.sp_degree, lay.sp_rank, dev,
+                                         self.cfg.num_attention_heads, self.cfg.attention_head_dim,
+                                         lat.shape[0], rows)
+                self.tr._sp.peer = self.peer
+            elif (self.s_img % lay.sp_degree) or (self.s_txt % lay.sp_degree):
+                raise NotImplementedError("ragged shards need the peer-memory exchange (exchange='peer')")
         if self.world == 1:
             n0 = ops.launch_count
             self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
@@ -178,7 +200,7 @@ class ParallelDenoiser:
                 # launches recorded while capturing one step (+2 refresh copies are torch memcpys)
                 self.launches_per_step = (ops.launch_count - n0 - 4) // 2
         else:
-            self.sess = DenoiseSession(self.pipe, cond, None, lat, Hl, Wl, num_inference_steps, self.scale,
+            self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
                                        use_cuda_graph=False, image_seq_len=self.s_img)
             self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
             if self.use_cuda_graph:
@@ -204,11 +226,13 @@ class ParallelDenoiser:
     def _step_body(self, mod, dt_dev) -> None:
         from . import ops
         s = self.sess
-        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, img_shapes=s.shapes,
-                       txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod)[0]
+        kw = dict(img_shapes=s.shapes, txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod)
+        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, **kw)[0]
         if self.layout.cfg_degree == 2:
             dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
             c, u = self.pair_buf[0], self.pair_buf[1]
+        elif s.uncond is not None:
+            c, u = pred, self.tr(hidden_states=s.cur, encoder_hidden_states=s.uncond, **kw)[0]
         else:
             c, u = pred, None
         ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
@@ -239,8 +263,17 @@ class ParallelDenoiser:
         else:
             self._step_body(self.tr._mod_table[i:i + 1], s.dts[i:i + 1])
 
+    def exchange_timed_out(self) -> bool:
+        """True if a peer barrier gave up waiting (a rank died or the launch sequences diverged)."""
+        return self.peer is not None and self.peer.timed_out()
+
     def close(self):
         self.graph = None
+        if self.peer is not None:
+            if self.tr._sp is not None:
+                self.tr._sp.peer = None
+            self.peer.close()
+            self.peer = None
         if self.sess is not None:
             self.sess.close()
             self.sess = None

@@ -44,9 +44,12 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
     _req_bf16(a, w, bias, out, residual, gate)
     chunk = None
     if a_k_chunked:
-        nch, M_, kc = a.shape
+        # [chunks, M, Kc] or [chunks, B, M, Kc]
+        nch, kc = a.shape[0], a.shape[-1]
         chunk = (kc, a.stride(0))
-        a = a[0].unsqueeze(0)
+        a = a[0]
+        if a.dim() == 2:
+            a = a.unsqueeze(0)
     if a.dim() == 2:
         a = a.unsqueeze(0)
     if out.dim() == 2:
@@ -110,6 +113,54 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tens
                                       out.stride(0), float(scale), _stream()), "qi_attention_fwd")
     launch_count += 1
     return out
+
+
+def attention_scatter(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, dst: "_lib.PeerScatter", ld_o: int,
+                      o_batch_stride: int, softmax_scale: Optional[float] = None) -> None:
+    """Attention whose epilogue stores each output row into the HBM of the rank that owns the token
+    (qi_attention_fwd_scatter): the gather half of the Ulysses exchange."""
+    global launch_count
+    _req_bf16(q, k, v)
+    B, Sq, H, Dh = q.shape
+    Skv = k.shape[1]
+    for t in (q, k, v):
+        if t.stride(2) != Dh:
+            raise ValueError("heads must be packed contiguously inside a token row")
+    if k.stride() != v.stride():
+        raise ValueError("k and v must share strides")
+    scale = softmax_scale if softmax_scale is not None else Dh ** -0.5
+    check(_lib.lib().qi_attention_fwd_scatter(q.data_ptr(), k.data_ptr(), v.data_ptr(), B, Sq, Skv, H, Dh,
+                                              q.stride(1), k.stride(1), ld_o, q.stride(0), k.stride(0),
+                                              o_batch_stride, float(scale), C.byref(dst), _stream()),
+          "qi_attention_fwd_scatter")
+    launch_count += 1
+
+
+def qknorm_rope_scatter(qkv: torch.Tensor, heads: int, head_dim: int, seq: int, s_txt: int,
+                        wq_img, wk_img, wq_txt, wk_txt, freqs: torch.Tensor, dst: "_lib.PeerScatter",
+                        eps: float = 1e-6) -> None:
+    """K2 whose stores go to the head owner's attention input buffer (qi_qknorm_rope_scatter): the
+    scatter half of the Ulysses exchange.  qkv: [rows=B*seq, ld] local rows, all heads."""
+    global launch_count
+    _req_bf16(qkv, wq_img, wk_img, wq_txt, wk_txt)
+    if freqs.dtype != torch.float32 or not freqs.is_contiguous() or tuple(freqs.shape) != (seq, head_dim // 2, 2):
+        raise ValueError("freqs must be contiguous fp32 [seq, head_dim/2, 2]")
+    check(_lib.lib().qi_qknorm_rope_scatter(qkv.data_ptr(), qkv.shape[0], qkv.stride(0), heads, head_dim, seq,
+                                            s_txt, wq_img.data_ptr(), wk_img.data_ptr(), wq_txt.data_ptr(),
+                                            wk_txt.data_ptr(), freqs.data_ptr(), float(eps), C.byref(dst),
+                                            _stream()), "qi_qknorm_rope_scatter")
+    launch_count += 1
+
+
+def peer_barrier(signal_table: torch.Tensor, n: int, me: int, state: torch.Tensor, timeout_ms: int = 2000) -> None:
+    global launch_count
+    check(_lib.lib().qi_peer_barrier(signal_table.data_ptr(), n, me, state.data_ptr(), timeout_ms, _stream()),
+          "qi_peer_barrier")
+    launch_count += 1
+
+
+def gemm_set_tile_n(bn: int) -> None:
+    check(_lib.lib().qi_gemm_set_tile_n(int(bn)), "qi_gemm_set_tile_n")
 
 
 def adaln_modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor, out: torch.Tensor,

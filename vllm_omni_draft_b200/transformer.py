@@ -62,7 +62,7 @@ class _Workspace:
         self.sp = None
 
     def alloc_sp(self, cfg: MMDiTConfig, P: int, device, dtype):
-        """Ulysses exchange buffers (B == 1): send/recv [P, S_loc, 3, H/P, Dh], attention output
+        """NCCL Ulysses exchange buffers (B == 1): send/recv [P, S_loc, 3, H/P, Dh], attention output
         [P*S_loc, H/P, Dh], and the head-gathered result [P, S_loc, (H/P)*Dh]."""
         s_loc = self.qkv.shape[1]
         hs, dh = cfg.num_attention_heads // P, cfg.attention_head_dim
@@ -293,9 +293,13 @@ class B200QwenImageTransformer2DModel(nn.Module):
         sp = self._sp
         if sp is None and sum(f * h * w for f, h, w in shapes) != s_img:
             raise ValueError("img_shapes does not match the number of image tokens")
+        peer = sp.peer if sp is not None else None
         if sp is not None:
-            if B != 1:
-                raise NotImplementedError("Ulysses sequence parallelism is implemented for batch 1")
+            if peer is None and B != 1:
+                raise NotImplementedError("the NCCL Ulysses exchange is implemented for batch 1; "
+                                          "use the peer-memory exchange for batched runs")
+            if peer is not None and (peer.batch != B or peer.s_loc != s_img + s_txt):
+                raise ValueError("peer exchange buffers were sized for a different batch / shard")
             if self._sp_freqs is None or self._sp_freqs.shape[0] != s_img + s_txt:
                 raise ValueError("call set_sequence_shard() before a sequence-parallel forward")
         max_txt = int(max(txt_seq_lens)) if txt_seq_lens is not None else s_txt
@@ -311,7 +315,7 @@ class B200QwenImageTransformer2DModel(nn.Module):
             ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
         if sp is not None:
             freqs = self._sp_freqs
-            if ws.sp != sp.size:
+            if peer is None and ws.sp != sp.size:
                 ws.alloc_sp(cfg, sp.size, dev, dt)
         else:
             fkey = (shapes, s_txt)
@@ -356,13 +360,29 @@ class B200QwenImageTransformer2DModel(nn.Module):
             ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
                       ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
             nw = self.qk_norm_w[l]
-            ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
             if sp is None:
+                ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
                 ops.attention(q, k, v, attn4)
                 ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
                           ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
+            elif peer is not None:
+                # Fused exchange over peer memory: K2 stores each head vector into the head owner's HBM,
+                # attention stores each output row into the token owner's HBM; two flag barriers.
+                ops.qknorm_rope_scatter(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3],
+                                        freqs, peer.dst_qkv)
+                peer.barrier()
+                full = peer.recv                       # [B, S_total, 3, H/P, Dh]
+                ops.attention_scatter(full[:, :, 0], full[:, :, 1], full[:, :, 2], peer.dst_o, peer.o_ld,
+                                      peer.o_batch_stride)
+                peer.barrier()
+                back = peer.back[:, :, :S]             # [P, B, S_loc, (H/P)*Dh]: K-chunked A operand
+                ops.gemm([ops.gemm_problem(back[:, :, s_txt:], self.out_w[l, 0], self.out_b[l, 0], h, G, h,
+                                           bview(g_i1), a_k_chunked=True),
+                          ops.gemm_problem(back[:, :, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
+                                           bview(g_t1), a_k_chunked=True)])
             else:
-                # head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
+                # NCCL head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
+                ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
                 full = sp.scatter_heads(ws.qkv.view(S, 3 * d), H, Dh, ws.a2a_send, ws.a2a_recv)
                 ops.attention(full[:, 0].unsqueeze(0), full[:, 1].unsqueeze(0), full[:, 2].unsqueeze(0),
                               ws.o_full.unsqueeze(0))
