@@ -78,6 +78,9 @@ int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems 
 /* Tile width of the persistent GEMM: 0 = automatic (cheapest wave schedule over 148 SMs), or one of
  * 128 / 192 / 256 to pin it (tests and tile sweeps). */
 int qi_gemm_set_tile_n(int bn);
+/* CTA-pair (tcgen05 cta_group::2, 256-row tiles on a 2-CTA cluster) vs single-CTA tiles:
+ * -1 = automatic, 0 = never, 1 = always. */
+int qi_gemm_set_cta_pair(int mode);
 
 /* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
  * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).
@@ -95,6 +98,21 @@ int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int b
 int qi_adaln_modulate(const void* x, void* y, int rows, int d, int ld_x, int ld_y, const void* shift,
                       const void* scale, long long mod_batch_stride, int rows_per_batch, float eps,
                       qi_stream_t stream);
+
+/* Same kernel over up to two row sets in ONE launch (the img and txt streams of a block). */
+typedef struct {
+  const void* x;
+  void* y;
+  int rows;
+  int ld_x;
+  int ld_y;
+  const void* shift;
+  const void* scale;
+  long long mod_batch_stride;
+  int rows_per_batch;
+} qi_norm_rows_t;
+int qi_adaln_modulate_multi(const qi_norm_rows_t* segs /* host */, int num_segs /* 1 or 2 */, int d, float eps,
+                            qi_stream_t stream);
 
 /* RMSNorm with learned weight (replaces txt_norm = RMSNorm(joint_attention_dim, eps=1e-6)). */
 int qi_rmsnorm_affine(const void* x, void* y, int rows, int d, int ld_x, int ld_y, const void* weight,

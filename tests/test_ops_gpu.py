@@ -280,3 +280,41 @@ def test_peer_barrier_single_rank(cuda_device):
         ops.peer_barrier(table, 1, 0, state)
     torch.cuda.synchronize()
     assert state.tolist() == [3, 0] and int(sig[0]) == 3
+
+
+@pytest.mark.parametrize("bn", [128, 192, 256])
+def test_gemm_cta_pair(cuda_device, bn):
+    """tcgen05 cta_group::2 kernel (256 x BN tile per 2-CTA cluster): ragged M, batch, both fused
+    epilogues, two problems in one launch and the K-chunked A operand."""
+    ops = _ops()
+    ops.gemm_set_tile_n(bn)
+    ops.gemm_set_cta_pair(1)
+    try:
+        for (B, M, N, K, epi) in [(1, 4608, 3072, 3072, 2), (2, 300, 1024, 256, 1), (1, 257, 64, 128, 0),
+                                  (1, 1152, 9216, 3072, 0)]:
+            a, w, bias = _rand((B, M, K), 80), _rand((N, K), 81, 0.05), _rand((N,), 82, 0.5)
+            out = torch.zeros(B, M, N, device="cuda", dtype=torch.bfloat16)
+            res = _rand((B, M, N), 83) if epi == 2 else None
+            gate = _rand((B, N), 84) if epi == 2 else None
+            ops.gemm([ops.gemm_problem(a, w, bias, out, epi, res, gate)])
+            y = torch.matmul(a.float(), w.float().t()) + bias.float()
+            if epi == 1:
+                y = torch.nn.functional.gelu(y, approximate="tanh")
+            elif epi == 2:
+                y = res.float() + gate.float()[:, None, :] * y
+            err = O.rel_l2(out.cpu(), y.cpu())
+            assert err < 5e-3, f"pair bn={bn} case {(B, M, N, K, epi)} rel_l2={err}"
+        # two problems + K-chunked A ([chunks, B, M, Kc])
+        P_, Bb, M1, M2, kc, N = 4, 2, 200, 56, 64, 512
+        a1, a2 = _rand((P_, Bb, M1, kc), 85), _rand((P_, Bb, M2, kc), 86)
+        w1, w2 = _rand((N, P_ * kc), 87, 0.05), _rand((N, P_ * kc), 88, 0.05)
+        o1 = torch.zeros(Bb, M1, N, device="cuda", dtype=torch.bfloat16)
+        o2 = torch.zeros(Bb, M2, N, device="cuda", dtype=torch.bfloat16)
+        ops.gemm([ops.gemm_problem(a1, w1, None, o1, 0, a_k_chunked=True),
+                  ops.gemm_problem(a2, w2, None, o2, 0, a_k_chunked=True)])
+        for a, w, o in ((a1, w1, o1), (a2, w2, o2)):
+            af = a.permute(1, 2, 0, 3).reshape(Bb, a.shape[2], P_ * kc).float()
+            assert O.rel_l2(o.cpu(), (af @ w.float().t()).cpu()) < 5e-3
+    finally:
+        ops.gemm_set_tile_n(0)
+        ops.gemm_set_cta_pair(-1)

@@ -31,6 +31,12 @@ class GemmProblem(C.Structure):
     ]
 
 
+class NormRows(C.Structure):
+    """qi_norm_rows_t"""
+    _fields_ = [("x", _vp), ("y", _vp), ("rows", _i), ("ld_x", _i), ("ld_y", _i), ("shift", _vp), ("scale", _vp),
+                ("mod_batch_stride", _ll), ("rows_per_batch", _i)]
+
+
 class PeerScatter(C.Structure):
     """qi_peer_scatter_t"""
     _fields_ = [("n_peers", _i), ("my_index", _i), ("base", _vp * 8), ("row_prefix", _i * 9),
@@ -43,6 +49,7 @@ _SIGNATURES = {
     "qi_device_sm_count": (_i, []),
     "qi_gemm_bf16": (_i, [C.POINTER(GemmProblem), _i, _vp]),
     "qi_gemm_set_tile_n": (_i, [_i]),
+    "qi_gemm_set_cta_pair": (_i, [_i]),
     "qi_attention_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f,
                                       C.POINTER(PeerScatter), _vp]),
     "qi_qknorm_rope_scatter": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f,
@@ -55,6 +62,7 @@ _SIGNATURES = {
     "qi_peer_barrier": (_i, [_vp, _i, _i, _vp, C.c_uint, _vp]),
     "qi_attention_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f, _vp]),
     "qi_adaln_modulate": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _ll, _i, _f, _vp]),
+    "qi_adaln_modulate_multi": (_i, [C.POINTER(NormRows), _i, _i, _f, _vp]),
     "qi_rmsnorm_affine": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp]),
     "qi_qknorm_rope": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp]),
     "qi_cfg_euler_step": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _f, _vp, _f, _vp]),

@@ -46,13 +46,31 @@ __device__ __forceinline__ float group_sum(float v) {
 // Block-per-row variant: 128 threads own one row, CPT 16-byte chunks per thread (d = CPT * 1024).
 // ~40 registers per thread, so an SM keeps 16 rows (~100 KB of loads) in flight; the two
 // reductions (mean, then centred variance) go warp shuffle -> 4 partials in shared memory.
+struct NormSeg {   // one set of rows sharing strides and modulation vectors
+  const __nv_bfloat16* x;
+  __nv_bfloat16* y;
+  const __nv_bfloat16* shift;
+  const __nv_bfloat16* scale;
+  long long mod_batch_stride;
+  int rows, ld_x, ld_y, rows_per_batch;
+};
+
+// Up to two segments per launch (the img and txt streams of a block): block b < seg0.rows works on
+// segment 0, the others on segment 1.
 template <int CPT, int MODE>
-__global__ void __launch_bounds__(128) norm_rows_kernel(
-    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int rows, int ld_x, int ld_y,
-    const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale,
-    long long mod_batch_stride, int rows_per_batch, float eps) {
+__global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ NormSeg s0,
+                                                        const __grid_constant__ NormSeg s1,
+                                                        float eps) {
   __shared__ float red[2][4];
-  const int row = blockIdx.x;
+  const bool second = blockIdx.x >= s0.rows;
+  const int row = second ? blockIdx.x - s0.rows : blockIdx.x;
+  const __nv_bfloat16* x = second ? s1.x : s0.x;
+  __nv_bfloat16* y = second ? s1.y : s0.y;
+  const __nv_bfloat16* shift = second ? s1.shift : s0.shift;
+  const __nv_bfloat16* scale = second ? s1.scale : s0.scale;
+  const long long mod_batch_stride = second ? s1.mod_batch_stride : s0.mod_batch_stride;
+  const int ld_x = second ? s1.ld_x : s0.ld_x, ld_y = second ? s1.ld_y : s0.ld_y;
+  const int rows_per_batch = second ? s1.rows_per_batch : s0.rows_per_batch;
   const int tid = threadIdx.x;
   const int lane = tid & 31, wid = tid >> 5;
   constexpr int D = CPT * 1024;
@@ -126,13 +144,21 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(
 // pass instead of being held in registers.  Only used for widths without a register instantiation
 // (e.g. the tiny test config's joint_attention_dim = 128).
 template <int MODE>
-__global__ void __launch_bounds__(128) norm_rows_generic_kernel(
-    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int rows, int d, int ld_x,
-    int ld_y, const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale,
-    long long mod_batch_stride, int rows_per_batch, float eps) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_constant__ NormSeg s0,
+                                                                const __grid_constant__ NormSeg s1,
+                                                                int d, float eps) {
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (warp >= rows) return;
+  if (warp >= s0.rows + s1.rows) return;
+  const bool second = warp >= s0.rows;
+  if (second) warp -= s0.rows;
+  const __nv_bfloat16* x = second ? s1.x : s0.x;
+  __nv_bfloat16* y = second ? s1.y : s0.y;
+  const __nv_bfloat16* shift = second ? s1.shift : s0.shift;
+  const __nv_bfloat16* scale = second ? s1.scale : s0.scale;
+  const long long mod_batch_stride = second ? s1.mod_batch_stride : s0.mod_batch_stride;
+  const int ld_x = second ? s1.ld_x : s0.ld_x, ld_y = second ? s1.ld_y : s0.ld_y;
+  const int rows_per_batch = second ? s1.rows_per_batch : s0.rows_per_batch;
   const __nv_bfloat16* xr = x + (size_t)warp * ld_x;
   float s = 0.f;
   for (int off = lane * 8; off < d; off += 256) {
@@ -444,43 +470,71 @@ using namespace qi;
   } while (0)
 
 template <int MODE>
-static int launch_norm_rows(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
-                            const void* shift, const void* scale, long long mod_stride,
-                            int rows_per_batch, float eps, cudaStream_t st) {
+static int launch_norm_rows(const NormSeg& a, const NormSeg& b, int d, float eps, cudaStream_t st) {
+  const int rows = a.rows + b.rows;
   if (rows <= 0) return QI_OK;
-  if (d % 8 != 0 || ld_x % 8 != 0 || ld_y % 8 != 0) return QI_ERR_ARG;
+  if (d % 8 != 0 || a.ld_x % 8 != 0 || a.ld_y % 8 != 0 || (b.rows > 0 && (b.ld_x % 8 != 0 || b.ld_y % 8 != 0)))
+    return QI_ERR_ARG;
   const int blocks_generic = (rows + 3) / 4;
-#define QI_NORM_CASE(NC)                                                                     \
-  case NC:                                                                                   \
-    norm_rows_kernel<NC, MODE><<<rows, 128, 0, st>>>(                                        \
-        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, ld_x, ld_y,                        \
-        (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, \
-        eps);                                                                                \
+#define QI_NORM_CASE(NC)                                            \
+  case NC:                                                          \
+    norm_rows_kernel<NC, MODE><<<rows, 128, 0, st>>>(a, b, eps);    \
     break;
   switch (d % 1024 == 0 ? d / 1024 : 0) {
     QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(3) QI_NORM_CASE(4)
     default:
-      norm_rows_generic_kernel<MODE><<<blocks_generic, 128, 0, st>>>(
-          (const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, d, ld_x, ld_y,
-          (const __nv_bfloat16*)shift, (const __nv_bfloat16*)scale, mod_stride, rows_per_batch, eps);
+      norm_rows_generic_kernel<MODE><<<blocks_generic, 128, 0, st>>>(a, b, d, eps);
   }
 #undef QI_NORM_CASE
   QI_CHECK_LAUNCH();
   return QI_OK;
 }
 
+static NormSeg make_seg(const void* x, void* y, int rows, int ld_x, int ld_y, const void* shift,
+                        const void* scale, long long mod_stride, int rows_per_batch) {
+  NormSeg s;
+  s.x = (const __nv_bfloat16*)x;
+  s.y = (__nv_bfloat16*)y;
+  s.shift = (const __nv_bfloat16*)shift;
+  s.scale = (const __nv_bfloat16*)scale;
+  s.mod_batch_stride = mod_stride;
+  s.rows = rows;
+  s.ld_x = ld_x;
+  s.ld_y = ld_y;
+  s.rows_per_batch = rows_per_batch;
+  return s;
+}
+
 extern "C" int qi_adaln_modulate(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
                                  const void* shift, const void* scale, long long mod_batch_stride,
                                  int rows_per_batch, float eps, cudaStream_t stream) {
   if (!x || !y || !shift || !scale || rows_per_batch <= 0) return QI_ERR_ARG;
-  return launch_norm_rows<0>(x, y, rows, d, ld_x, ld_y, shift, scale, mod_batch_stride,
-                             rows_per_batch, eps, stream);
+  NormSeg none;
+  memset(&none, 0, sizeof(none));
+  return launch_norm_rows<0>(make_seg(x, y, rows, ld_x, ld_y, shift, scale, mod_batch_stride, rows_per_batch),
+                             none, d, eps, stream);
+}
+
+extern "C" int qi_adaln_modulate_multi(const qi_norm_rows_t* segs, int num_segs, int d, float eps,
+                                       cudaStream_t stream) {
+  if (!segs || num_segs < 1 || num_segs > 2) return QI_ERR_ARG;
+  NormSeg s[2];
+  memset(s, 0, sizeof(s));
+  for (int i = 0; i < num_segs; ++i) {
+    const qi_norm_rows_t& g = segs[i];
+    if (!g.x || !g.y || !g.shift || !g.scale || g.rows_per_batch <= 0 || g.rows < 0) return QI_ERR_ARG;
+    s[i] = make_seg(g.x, g.y, g.rows, g.ld_x, g.ld_y, g.shift, g.scale, g.mod_batch_stride, g.rows_per_batch);
+  }
+  return launch_norm_rows<0>(s[0], s[1], d, eps, stream);
 }
 
 extern "C" int qi_rmsnorm_affine(const void* x, void* y, int rows, int d, int ld_x, int ld_y,
                                  const void* weight, float eps, cudaStream_t stream) {
   if (!x || !y || !weight) return QI_ERR_ARG;
-  return launch_norm_rows<1>(x, y, rows, d, ld_x, ld_y, nullptr, weight, 0, 1 << 30, eps, stream);
+  NormSeg none;
+  memset(&none, 0, sizeof(none));
+  return launch_norm_rows<1>(make_seg(x, y, rows, ld_x, ld_y, nullptr, weight, 0, 1 << 30), none, d, eps,
+                             stream);
 }
 
 extern "C" int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq,

@@ -7,8 +7,16 @@
 // Tile 128 x BN x 64, UMMA 128 x BN x 16, operands K-major in 128B-swizzled shared memory filled by
 // TMA, fp32 accumulators double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps
 // the main loop of tile i+1.  Up to two problems (img + txt stream) share one persistent launch.
+//
+// Two kernels share the tile scheduler and the epilogue:
+//   gemm_bf16_kernel<BN>       one CTA per SM, tcgen05.mma.cta_group::1, tile 128 x BN
+//   gemm_pair_bf16_kernel<BN>  one CTA pair (cluster of 2, one TPC) per tile 256 x BN,
+//                              tcgen05.mma.cta_group::2 issued by the leader CTA: each CTA stages its
+//                              own 128 rows of A and only HALF of the B tile, so shared-memory fill and
+//                              operand-read traffic per FLOP drop by a third.
 #include "qi_common.cuh"
 #include "../../include/qi_b200.h"
+#include <cstdlib>
 
 namespace qi {
 
@@ -53,7 +61,7 @@ struct GemmCfg {
 struct TileCoord {
   int p, b, m0, n0;
 };
-__device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int BN) {
+__device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int BN, int TM = BM) {
   TileCoord tc;
   tc.p = (L.num_problems > 1 && t >= L.prob[1].tile_begin) ? 1 : 0;
   const GemmProb& P = L.prob[tc.p];
@@ -61,7 +69,7 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int
   const int mt = lt % P.tiles_m_total;
   const int nt = lt / P.tiles_m_total;
   tc.b = mt / P.tiles_m;
-  tc.m0 = (mt % P.tiles_m) * BM;
+  tc.m0 = (mt % P.tiles_m) * TM;
   tc.n0 = nt * BN;
   return tc;
 }
@@ -71,6 +79,68 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   float t;
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
   return 0.5f * x * (1.f + t);
+}
+
+// One epilogue warp's share of a tile: 32 accumulator rows (one per lane) x BN columns, read from
+// TMEM 32 columns at a time; `release` runs right after the last TMEM read so the MMA warp can reuse
+// the accumulator while the math and the stores of the last chunk are still in flight.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row, int n0,
+                                              uint32_t taddr, Release release) {
+  const bool row_ok = row < P.m;
+  __nv_bfloat16* crow =
+      reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + (size_t)row * P.ldc;
+  const __nv_bfloat16* rrow =
+      P.residual ? P.residual + (size_t)b * P.res_bs + (size_t)row * P.ld_res : nullptr;
+  const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)b * P.gate_bs : nullptr;
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    uint32_t r[32];
+    tmem_ld32(taddr + c * 32, r);
+    tmem_ld_wait();
+    if (c == BN / 32 - 1) release();
+    const int n_base = n0 + c * 32;
+    if (n_base >= P.n) continue;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int n = n_base + g * 8;
+      if (n >= P.n) break;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+      if (P.bias) {
+        const uint4 bu = *reinterpret_cast<const uint4*>(P.bias + n);
+        const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y), b2 = unpack_bf16(bu.z),
+                     b3 = unpack_bf16(bu.w);
+        v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+        v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+      }
+      if (P.epilogue == QI_EPI_BIAS_GELU_TANH) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
+      } else if (P.epilogue == QI_EPI_GATED_RESIDUAL) {
+        const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
+        const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
+                     g3 = unpack_bf16(gu.w);
+        const float gt[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+        float rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (row_ok) {
+          const uint4 ru = *reinterpret_cast<const uint4*>(rrow + n);
+          const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
+                       r3 = unpack_bf16(ru.w);
+          rs[0] = r0.x; rs[1] = r0.y; rs[2] = r1.x; rs[3] = r1.y;
+          rs[4] = r2.x; rs[5] = r2.y; rs[6] = r3.x; rs[7] = r3.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = rs[j] + gt[j] * v[j];
+      }
+      if (row_ok) {
+        const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
+                                   pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+        *reinterpret_cast<uint4*>(crow + n) = o;
+      }
+    }
+  }
 }
 
 template <int BN>
@@ -185,67 +255,12 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       const GemmProb& P = L.prob[tc.p];
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row = tc.m0 + q * 32 + lane;
-      const bool row_ok = row < P.m;
-      __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)tc.b * P.c_bs +
-                            (size_t)row * P.ldc;
-      const __nv_bfloat16* rrow =
-          P.residual ? P.residual + (size_t)tc.b * P.res_bs + (size_t)row * P.ld_res : nullptr;
-      const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)tc.b * P.gate_bs : nullptr;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(taddr + c * 32, r);
-        tmem_ld_wait();
-        if (c == BN / 32 - 1) {
-          // all TMEM reads of this accumulator are done: hand it back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-        }
-        const int n_base = tc.n0 + c * 32;
-        if (n_base >= P.n) continue;
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int n = n_base + g * 8;
-          if (n >= P.n) break;
-          float v[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-          if (P.bias) {
-            const uint4 bu = *reinterpret_cast<const uint4*>(P.bias + n);
-            const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y), b2 = unpack_bf16(bu.z),
-                         b3 = unpack_bf16(bu.w);
-            v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
-            v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
-          }
-          if (P.epilogue == QI_EPI_BIAS_GELU_TANH) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-          } else if (P.epilogue == QI_EPI_GATED_RESIDUAL) {
-            const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
-            const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
-                         g3 = unpack_bf16(gu.w);
-            const float gt[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
-            float rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            if (row_ok) {
-              const uint4 ru = *reinterpret_cast<const uint4*>(rrow + n);
-              const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
-                           r3 = unpack_bf16(ru.w);
-              rs[0] = r0.x; rs[1] = r0.y; rs[2] = r1.x; rs[3] = r1.y;
-              rs[4] = r2.x; rs[5] = r2.y; rs[6] = r3.x; rs[7] = r3.y;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = rs[j] + gt[j] * v[j];
-          }
-          if (row_ok) {
-            const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
-                                       pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-            *reinterpret_cast<uint4*>(crow + n) = o;
-          }
-        }
-      }
+      epilogue_rows<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      });
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -261,11 +276,172 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// CTA-pair kernel: cluster of 2 CTAs (one TPC) per 256 x BN tile, tcgen05.mma.cta_group::2.
+//   CTA r of the pair stages A rows [m0 + 128 r, +128) and B rows [n0 + BN/2 r, +BN/2) per k-block;
+//   both CTAs' TMA transactions complete on the LEADER's full barrier; the leader's MMA thread issues
+//   the 256 x BN x 16 MMAs (each CTA's tensor core reads its A rows and both B halves) and commits
+//   with a multicast arrive to the empty / accumulator-full barriers of both CTAs; each CTA's epilogue
+//   warps drain their own 128 accumulator rows from their own TMEM and release the accumulator on the
+//   leader's tmem_empty barrier (count 8 = 4 warps x 2 CTAs).
+// ---------------------------------------------------------------------------------------------
+template <int BN>
+struct GemmPairCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 6 : (BN == 192 ? 7 : 8);
+  static constexpr int ACC_STRIDE = (BN == 192) ? 256 : BN;
+  static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
+  using Cfg = GemmPairCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full = empty_bar + Cfg::STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    for (int p = 0; p < L.num_problems; ++p) {
+      tma_prefetch_desc(&L.tmap_a[p]);
+      tma_prefetch_desc(&L.tmap_b[p]);
+    }
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);    // leader's producer: arrive.expect_tx for both CTAs' bytes
+      mbar_init(&empty_bar[s], 1);   // multicast commit from the leader's MMA thread
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);   // multicast commit
+      mbar_init(&tmem_empty[a], 8);  // 4 epilogue warps of each CTA (used in the leader only)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_pair<Cfg::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < L.total_tiles; t += num_pairs) {
+        const TileCoord tc = decode_tile(L, t, BN, 2 * BM);
+        const int kblocks = L.prob[tc.p].k / BK;
+        const int m0 = tc.m0 + (int)cta * BM;
+        const int n0 = tc.n0 + (int)cta * (BN / 2);
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* sb = sa + Cfg::A_BYTES;
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+          const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
+          const int kidx = kb * BK;
+          const int kc = L.prob[tc.p].k_chunk;
+          tma_load_4d_pair(sa, &L.tmap_a[tc.p], bar, kidx % kc, m0, kidx / kc, tc.b);
+          tma_load_2d_pair(sb, &L.tmap_b[tc.p], bar, kb * BK, n0);
+          if (++stage == Cfg::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = pair; t < L.total_tiles; t += num_pairs) {
+        const TileCoord tc = decode_tile(L, t, BN, 2 * BM);
+        const int kblocks = L.prob[tc.p].k / BK;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint32_t sb = sa + Cfg::A_BYTES;
+          const uint64_t da = make_smem_desc(sa, 0, 1024);
+          const uint64_t db = make_smem_desc(sb, 0, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            mma_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          tc_commit_pair(&empty_bar[stage], 3);
+          if (++stage == Cfg::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tc_commit_pair(&tmem_full[acc], 3);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue warps (both CTAs)
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const uint32_t empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
+    const uint32_t empty1 = mapa_shared(smem_u32(&tmem_empty[1]), 0);
+    for (int t = pair; t < L.total_tiles; t += num_pairs) {
+      const TileCoord tc = decode_tile(L, t, BN, 2 * BM);
+      const GemmProb& P = L.prob[tc.p];
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
+      epilogue_rows<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(acc == 0 ? empty0 : empty1);
+      });
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
 }  // namespace qi
 
 using namespace qi;
 
-static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int BN, int tile_begin) {
+static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int BN, int tile_begin,
+                        int tile_m = BM, int b_box_rows = 0) {
   if (!in.a || !in.w || !in.c) return QI_ERR_ARG;
   if (in.m <= 0 || in.batch <= 0 || in.n <= 0 || in.k <= 0) return QI_ERR_ARG;
   if (in.k % BK != 0 || in.n % 8 != 0) return QI_ERR_UNSUPPORTED;
@@ -288,7 +464,7 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.ld_res = in.ld_res; P.res_bs = in.res_batch_stride; P.gate_bs = in.gate_batch_stride;
   P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
   P.epilogue = in.epilogue;
-  P.tiles_m = (in.m + BM - 1) / BM;
+  P.tiles_m = (in.m + tile_m - 1) / tile_m;
   P.tiles_m_total = P.tiles_m * in.batch;
   P.tiles_n = (in.n + BN - 1) / BN;
   P.tile_begin = tile_begin;
@@ -311,7 +487,7 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   {
     uint64_t dims[2] = {(uint64_t)in.k, (uint64_t)in.n};
     uint64_t strides[1] = {(uint64_t)in.k * 2};
-    uint32_t box[2] = {BK, (uint32_t)BN};
+    uint32_t box[2] = {BK, (uint32_t)(b_box_rows ? b_box_rows : BN)};
     int rc = qi_encode_tmap_bf16(&L.tmap_b[i], in.w, 2, dims, strides, box);
     if (rc) return rc;
   }
@@ -345,10 +521,44 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
   return QI_OK;
 }
 
+template <int BN>
+static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
+  GemmLaunch L;
+  memset(&L, 0, sizeof(L));
+  L.num_problems = num;
+  int tiles = 0;
+  for (int i = 0; i < num; ++i) {
+    int rc = fill_problem(L, i, problems[i], BN, tiles, 2 * BM, BN / 2);
+    if (rc) return rc;
+    tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
+  }
+  L.total_tiles = tiles;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm_pair_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             GemmPairCfg<BN>::SMEM_BYTES) != cudaSuccess)
+      return QI_ERR_CUDA;
+    attr_set = true;
+  }
+  const int pairs_max = qi_num_sms() / 2;
+  if (pairs_max <= 0) return QI_ERR_CUDA;
+  const int pairs = tiles < pairs_max ? tiles : pairs_max;
+  gemm_pair_bf16_kernel<BN><<<2 * pairs, GEMM_THREADS, GemmPairCfg<BN>::SMEM_BYTES, stream>>>(L);
+  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  return QI_OK;
+}
+
 static int g_force_bn = 0;
 extern "C" int qi_gemm_set_tile_n(int bn) {
   if (bn != 0 && bn != 128 && bn != 192 && bn != 256) return QI_ERR_ARG;
   g_force_bn = bn;
+  return QI_OK;
+}
+
+static int g_pair_mode = -1;   // -1 auto, 0 never, 1 always
+extern "C" int qi_gemm_set_cta_pair(int mode) {
+  if (mode < -1 || mode > 1) return QI_ERR_ARG;
+  g_pair_mode = mode;
   return QI_OK;
 }
 
@@ -357,27 +567,47 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
   if (!problems || num_problems < 1 || num_problems > 2) return QI_ERR_ARG;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
-  // Tile width: the persistent grid runs ceil(tiles / SMs) waves of 128 x BN tiles, each costing
-  // ~BN (+ a fixed per-tile overhead).  Pick the BN in {256, 192, 128} with the cheapest schedule:
-  // 256 for the full-size problems, 192 where it turns 1.46 / 2.19 waves into 0.97 / 2.92 (the
-  // token-sharded Ulysses shapes), 128 for narrow outputs.
-  int bn = g_force_bn;
-  if (bn == 0) {
-    long long best = -1;
+  // Schedule choice.  A persistent grid runs ceil(tiles / workers) waves; a tile costs ~BN (+ a fixed
+  // per-tile overhead).  Candidates: single-CTA tiles 128 x {256,192,128} on 148 SMs and CTA-pair
+  // tiles 256 x {256,192,128} on 74 pairs; the pair kernel moves a third less operand data per FLOP
+  // (weight ~0.93 per unit of work) but quantises M in steps of 256.
+  static const int env_pair = [] {
+    const char* e = getenv("QI_GEMM_PAIR");   // debugging aid: "0" / "1" pins the kernel family
+    return e ? atoi(e) : -1;
+  }();
+  const int pair_mode = g_pair_mode >= 0 ? g_pair_mode : (env_pair == 0 || env_pair == 1 ? env_pair : -1);
+  int bn = g_force_bn, pair = pair_mode;
+  if (bn == 0 || pair < 0) {
+    double best = -1;
     const int cand[3] = {256, 192, 128};
-    for (int c = 0; c < 3; ++c) {
-      long long tiles = 0;
-      for (int i = 0; i < num_problems; ++i) {
-        const qi_gemm_problem_t& p = problems[i];
-        tiles += (long long)((p.m + BM - 1) / BM) * p.batch * ((p.n + cand[c] - 1) / cand[c]);
-      }
-      const long long waves = (tiles + sms - 1) / sms;
-      const long long cost = waves * (cand[c] + 24);
-      if (best < 0 || cost < best) {
-        best = cost;
-        bn = cand[c];
+    int best_bn = 256, best_pair = 0;
+    for (int pm = 0; pm < 2; ++pm) {
+      if (pair_mode >= 0 && pm != pair_mode) continue;
+      for (int c = 0; c < 3; ++c) {
+        if (g_force_bn && cand[c] != g_force_bn) continue;
+        const int tm = pm ? 2 * BM : BM;
+        long long tiles = 0;
+        for (int i = 0; i < num_problems; ++i) {
+          const qi_gemm_problem_t& p = problems[i];
+          tiles += (long long)((p.m + tm - 1) / tm) * p.batch * ((p.n + cand[c] - 1) / cand[c]);
+        }
+        const int workers = pm ? sms / 2 : sms;
+        const long long waves = (tiles + workers - 1) / workers;
+        const double cost = (double)waves * (cand[c] + 24) * (pm ? 0.93 : 1.0);
+        if (best < 0 || cost < best) {
+          best = cost;
+          best_bn = cand[c];
+          best_pair = pm;
+        }
       }
     }
+    bn = best_bn;
+    pair = best_pair;
+  }
+  if (pair) {
+    if (bn == 256) return launch_gemm_pair<256>(problems, num_problems, stream);
+    if (bn == 192) return launch_gemm_pair<192>(problems, num_problems, stream);
+    return launch_gemm_pair<128>(problems, num_problems, stream);
   }
   if (bn == 256) return launch_gemm<256>(problems, num_problems, stream);
   if (bn == 192) return launch_gemm<192>(problems, num_problems, stream);

@@ -177,6 +177,9 @@ class ParallelDenoiser:
         if uncond is not None:
             uncond = uncond[:, self.t0:self.t1].contiguous()
         lat = lat_h.to(dev, dt)[:, self.i0:self.i1].contiguous()
+        # stacked (cond, uncond) forward whenever both branches run on this rank; the NCCL exchange
+        # is batch-1 only, so it keeps two forwards
+        batched = not (lay.sp_degree > 1 and self.exchange == "nccl")
         if lay.sp_degree > 1:
             self.tr.set_sequence_shard((1, Hl // 2, Wl // 2), self.s_img, self.s_txt, (self.i0, self.i1),
                                        (self.t0, self.t1))
@@ -188,7 +191,8 @@ class ParallelDenoiser:
                     self.peer.close()
                 self.peer = PeerExchange(self.sp_group, lay.sp_degree, lay.sp_rank, dev,
                                          self.cfg.num_attention_heads, self.cfg.attention_head_dim,
-                                         lat.shape[0], rows)
+                                         lat.shape[0] * (2 if (batched and lay.cfg_degree == 1 and uncond is not None) else 1),
+                                         rows)
                 self.tr._sp.peer = self.peer
             elif (self.s_img % lay.sp_degree) or (self.s_txt % lay.sp_degree):
                 raise NotImplementedError("ragged shards need the peer-memory exchange (exchange='peer')")
@@ -201,7 +205,7 @@ class ParallelDenoiser:
                 self.launches_per_step = (ops.launch_count - n0 - 4) // 2
         else:
             self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
-                                       use_cuda_graph=False, image_seq_len=self.s_img)
+                                       use_cuda_graph=False, image_seq_len=self.s_img, batched_cfg=batched)
             self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
             if self.use_cuda_graph:
                 # One graph per rank = forward + pair all-gather + K5 (+ the Ulysses all-to-alls inside the
@@ -227,12 +231,15 @@ class ParallelDenoiser:
         from . import ops
         s = self.sess
         kw = dict(img_shapes=s.shapes, txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod)
+        if self.layout.cfg_degree == 1:
+            c, u = self.pipe._predict(s.cur, s.cond, s.uncond, kw, s.enc2, s.x2)
+            ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
+            s.cur.copy_(s.nxt)
+            return
         pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, **kw)[0]
         if self.layout.cfg_degree == 2:
             dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
             c, u = self.pair_buf[0], self.pair_buf[1]
-        elif s.uncond is not None:
-            c, u = pred, self.tr(hidden_states=s.cur, encoder_hidden_states=s.uncond, **kw)[0]
         else:
             c, u = pred, None
         ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)

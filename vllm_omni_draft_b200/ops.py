@@ -163,6 +163,10 @@ def gemm_set_tile_n(bn: int) -> None:
     check(_lib.lib().qi_gemm_set_tile_n(int(bn)), "qi_gemm_set_tile_n")
 
 
+def gemm_set_cta_pair(mode: int) -> None:
+    check(_lib.lib().qi_gemm_set_cta_pair(int(mode)), "qi_gemm_set_cta_pair")
+
+
 def adaln_modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor, out: torch.Tensor,
                    rows_per_batch: int, eps: float = 1e-6) -> torch.Tensor:
     """x/out: [rows, d] views; shift/scale: [B, d] views sharing one batch stride."""
@@ -176,6 +180,26 @@ def adaln_modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor, ou
                                        float(eps), _stream()), "qi_adaln_modulate")
     launch_count += 1
     return out
+
+
+def adaln_modulate_pair(segs: Sequence[Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, int]],
+                        eps: float = 1e-6) -> None:
+    """K1 over up to two row sets (x, shift, scale, out, rows_per_batch) in one launch — the img and
+    txt streams of a block share the kernel launch like they share the GEMM launch."""
+    global launch_count
+    arr = (_lib.NormRows * len(segs))()
+    d = segs[0][0].shape[1]
+    for i, (x, shift, scale, out, rpb) in enumerate(segs):
+        _req_bf16(x, shift, scale, out)
+        if x.shape[1] != d:
+            raise ValueError("all row sets must share the width")
+        if shift.stride(0) != scale.stride(0) and shift.shape[0] > 1:
+            raise ValueError("shift/scale must share the batch stride")
+        a = arr[i]
+        a.x, a.y, a.rows, a.ld_x, a.ld_y = x.data_ptr(), out.data_ptr(), x.shape[0], x.stride(0), out.stride(0)
+        a.shift, a.scale, a.mod_batch_stride, a.rows_per_batch = shift.data_ptr(), scale.data_ptr(), shift.stride(0), rpb
+    check(_lib.lib().qi_adaln_modulate_multi(arr, len(segs), d, float(eps), _stream()), "qi_adaln_modulate_multi")
+    launch_count += 1
 
 
 def rmsnorm_affine(x: torch.Tensor, weight: torch.Tensor, out: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:

@@ -355,8 +355,8 @@ class B200QwenImageTransformer2DModel(nn.Module):
             sh_i2, sc_i2, g_i2 = mod_slices(bi + 3 * d)
             sh_t1, sc_t1, g_t1 = mod_slices(bt)
             sh_t2, sc_t2, g_t2 = mod_slices(bt + 3 * d)
-            ops.adaln_modulate(h2, bview(sh_i1), bview(sc_i1), xi2, s_img)
-            ops.adaln_modulate(e2, bview(sh_t1), bview(sc_t1), xt2, s_txt)
+            ops.adaln_modulate_pair([(h2, bview(sh_i1), bview(sc_i1), xi2, s_img),
+                                     (e2, bview(sh_t1), bview(sc_t1), xt2, s_txt)])
             ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
                       ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
             nw = self.qk_norm_w[l]
@@ -391,8 +391,8 @@ class B200QwenImageTransformer2DModel(nn.Module):
                                            bview(g_i1), a_k_chunked=True),
                           ops.gemm_problem(back[:, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
                                            bview(g_t1), a_k_chunked=True)])
-            ops.adaln_modulate(h2, bview(sh_i2), bview(sc_i2), xi2, s_img)
-            ops.adaln_modulate(e2, bview(sh_t2), bview(sc_t2), xt2, s_txt)
+            ops.adaln_modulate_pair([(h2, bview(sh_i2), bview(sc_i2), xi2, s_img),
+                                     (e2, bview(sh_t2), bview(sc_t2), xt2, s_txt)])
             ops.gemm([ops.gemm_problem(ws.xn_img, self.mlp_up_w[l, 0], self.mlp_up_b[l, 0], ws.mlp_img,
                                        ops.EPI_BIAS_GELU_TANH),
                       ops.gemm_problem(ws.xn_txt, self.mlp_up_w[l, 1], self.mlp_up_b[l, 1], ws.mlp_txt,
