@@ -42,6 +42,11 @@ enum qi_epilogue {
 int qi_version(void);
 const char* qi_last_cuda_error(void); /* host string, valid until the next failing call */
 int qi_device_sm_count(void);
+/* Programmatic dependent launch (every kernel of the library is launched with the programmatic
+ * stream-serialization attribute and gates its global-memory work on griddepcontrol.wait, so a
+ * kernel's prologue overlaps its predecessor's tail; CUDA-graph capture keeps the edges).  On by
+ * default; 0 turns the attribute off (also: QI_PDL=0 in the environment). */
+int qi_set_pdl(int on);
 
 /* ---- K3: tcgen05 bf16 GEMM with fused epilogues (replaces nn.Linear + the elementwise ops after it).
  * Up to two independent problems (the img and txt streams of one MMDiT block) run in ONE persistent

@@ -27,8 +27,11 @@ for name, (N, K, epi) in shapes.items():
     gate = r(batch, N) if epi == 2 else None
     ws = [w.view(-1)[:2 * N * K].view(2, N, K) for w in W]
     fl = 2.0 * batch * (s_img + s_txt) * N * K
+    only = sys.argv[3] if len(sys.argv) > 3 else ""
     for pair in (0, 1):
         for bn in (256, 192, 128):
+            if only == "pair256" and not (pair == 1 and bn == 256):
+                continue
             ops.gemm_set_cta_pair(pair)
             ops.gemm_set_tile_n(bn)
             fn = lambda i: ops.gemm([ops.gemm_problem(xi, ws[i % nw][0], bias[0, :N], oi, epi, ri, gate),

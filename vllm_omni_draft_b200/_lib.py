@@ -47,6 +47,7 @@ _SIGNATURES = {
     "qi_version": (_i, []),
     "qi_last_cuda_error": (C.c_char_p, []),
     "qi_device_sm_count": (_i, []),
+    "qi_set_pdl": (_i, [_i]),
     "qi_gemm_bf16": (_i, [C.POINTER(GemmProblem), _i, _vp]),
     "qi_gemm_set_tile_n": (_i, [_i]),
     "qi_gemm_set_cta_pair": (_i, [_i]),

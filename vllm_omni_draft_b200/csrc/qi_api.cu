@@ -3,6 +3,7 @@
 #include "qi_common.cuh"
 #include "../../include/qi_b200.h"
 #include <cudaTypedefs.h>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 
@@ -33,6 +34,22 @@ int qi_num_sms() {
   return sms;
 }
 extern "C" int qi_device_sm_count(void) { return qi_num_sms(); }
+
+// Programmatic dependent launch switch: on by default, QI_PDL=0 in the environment or
+// qi_set_pdl(0) turns the launch attribute off (the device-side griddepcontrol instructions are
+// no-ops then).
+static int g_pdl = -1;
+int qi_pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("QI_PDL");
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl;
+}
+extern "C" int qi_set_pdl(int on) {
+  g_pdl = on ? 1 : 0;
+  return QI_OK;
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,

@@ -77,6 +77,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   const int head = blockIdx.y;
   const int b = blockIdx.z;
   const int n_kv = (P.seq_kv + ATT_BN - 1) / ATT_BN;
+  pdl_launch_dependents();
 
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&P.tmap_q);
@@ -99,6 +100,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
   // Register re-balance (setmaxnreg is per warpgroup and must sit inside each role's own branch so
   // that ptxas allocates every role against its own budget): warps 8-11 shrink, softmax warps grow.
@@ -366,8 +368,9 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     attr_set = true;
   }
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
-  attention_fwd_kernel<DH><<<grid, ATT_THREADS, AttCfg<DH>::SMEM_BYTES, stream>>>(P);
-  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  if (qi_launch(attention_fwd_kernel<DH>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream, P) !=
+      cudaSuccess)
+    return QI_ERR_CUDA;
   return QI_OK;
 }
 

@@ -294,8 +294,37 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
          | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// Every kernel calls pdl_launch_dependents() first (the next kernel of the stream may be scheduled
+// as soon as SMs free up, so its prologue overlaps this kernel's tail) and pdl_wait() before its
+// first access to global memory (blocks until the previous kernel has completed and flushed).
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------ host side helpers
 }  // namespace qi
+
+int qi_pdl_enabled();
+
+// Host: launch with the programmatic-stream-serialization attribute (captured into CUDA graphs as a
+// programmatic dependency edge).
+template <typename... KArgs, typename... Args>
+inline cudaError_t qi_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                             cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = qi_pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // Host: encode a bf16 tiled tensor map with 128B swizzle via the driver entry point (no -lcuda).
 int qi_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,

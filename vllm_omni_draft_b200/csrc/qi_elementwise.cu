@@ -61,6 +61,8 @@ template <int CPT, int MODE>
 __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ NormSeg s0,
                                                         const __grid_constant__ NormSeg s1,
                                                         float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[2][4];
   const bool second = blockIdx.x >= s0.rows;
   const int row = second ? blockIdx.x - s0.rows : blockIdx.x;
@@ -147,6 +149,8 @@ template <int MODE>
 __global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_constant__ NormSeg s0,
                                                                 const __grid_constant__ NormSeg s1,
                                                                 int d, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= s0.rows + s1.rows) return;
@@ -216,6 +220,8 @@ __global__ void __launch_bounds__(256) qknorm_rope_kernel(
     const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
     const float2* __restrict__ freqs /* [seq, DH/2] (cos, sin), joint order txt first */,
     float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   // One warp per token row.  A group of LPH = DH/8 lanes owns one head vector (8 bf16 per lane);
   // the warp walks the row's 2*heads head vectors (q heads then k heads, contiguous in memory)
   // VPW at a time.  The row's rotation table and the norm weights are loaded once per row.
@@ -291,6 +297,8 @@ __global__ void __launch_bounds__(256) qknorm_rope_scatter_kernel(
     const __nv_bfloat16* __restrict__ wq_img, const __nv_bfloat16* __restrict__ wk_img,
     const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
     const float2* __restrict__ freqs, float eps, const __grid_constant__ ScatterDst D) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int LPH = DH / 8;
   constexpr int VPW = 32 / LPH;
   const int lane = threadIdx.x & 31;
@@ -361,6 +369,8 @@ __global__ void __launch_bounds__(256) cfg_euler_kernel(
     const __nv_bfloat16* __restrict__ cond, const __nv_bfloat16* __restrict__ uncond,
     const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, long long tokens,
     float cfg_scale, const float* __restrict__ dt_ptr, float dt_scalar) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long tok = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
   const int sub = threadIdx.x & 7;
   const bool active = tok < tokens;
@@ -404,6 +414,8 @@ __global__ void __launch_bounds__(256) small_linear_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ W,
     const __nv_bfloat16* __restrict__ bias, __nv_bfloat16* __restrict__ y, int M, int N, int K,
     int ld_x, int ld_y, int silu_in, int silu_out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (n >= N) return;
@@ -447,6 +459,8 @@ __global__ void __launch_bounds__(256) small_linear_kernel(
 // t [M] fp32 (already rounded the way the caller wants) -> [M, 256] bf16 = [cos(1000 t f_k), sin]
 __global__ void timestep_sinusoid_kernel(const float* __restrict__ t, __nv_bfloat16* __restrict__ out,
                                          int M) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= M * 128) return;
   const int m = i / 128, k = i % 128;
@@ -478,12 +492,12 @@ static int launch_norm_rows(const NormSeg& a, const NormSeg& b, int d, float eps
   const int blocks_generic = (rows + 3) / 4;
 #define QI_NORM_CASE(NC)                                            \
   case NC:                                                          \
-    norm_rows_kernel<NC, MODE><<<rows, 128, 0, st>>>(a, b, eps);    \
+    qi_launch(norm_rows_kernel<NC, MODE>, dim3(rows), dim3(128), 0, st, a, b, eps); \
     break;
   switch (d % 1024 == 0 ? d / 1024 : 0) {
     QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(3) QI_NORM_CASE(4)
     default:
-      norm_rows_generic_kernel<MODE><<<blocks_generic, 128, 0, st>>>(a, b, d, eps);
+      qi_launch(norm_rows_generic_kernel<MODE>, dim3(blocks_generic), dim3(128), 0, st, a, b, d, eps);
   }
 #undef QI_NORM_CASE
   QI_CHECK_LAUNCH();
@@ -546,12 +560,12 @@ extern "C" int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_d
   if (ld % 8 != 0 || seq <= 0 || rows % seq != 0) return QI_ERR_ARG;
   const int blocks = (rows + 7) / 8;
   if (head_dim == 128) {
-    qknorm_rope_kernel<128><<<blocks, 256, 0, stream>>>(
+    qi_launch(qknorm_rope_kernel<128>, dim3(blocks), dim3(256), 0, stream,
         (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps);
   } else if (head_dim == 64) {
-    qknorm_rope_kernel<64><<<blocks, 256, 0, stream>>>(
+    qi_launch(qknorm_rope_kernel<64>, dim3(blocks), dim3(256), 0, stream,
         (__nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps);
@@ -586,12 +600,12 @@ extern "C" int qi_qknorm_rope_scatter(const void* qkv, int rows, int ld, int hea
   if (dst->row_prefix[dst->my_index + 1] - D.row_offset != seq) return QI_ERR_ARG;
   const int blocks = (rows + 7) / 8;
   if (head_dim == 128) {
-    qknorm_rope_scatter_kernel<128><<<blocks, 256, 0, stream>>>(
+    qi_launch(qknorm_rope_scatter_kernel<128>, dim3(blocks), dim3(256), 0, stream,
         (const __nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps, D);
   } else if (head_dim == 64) {
-    qknorm_rope_scatter_kernel<64><<<blocks, 256, 0, stream>>>(
+    qi_launch(qknorm_rope_scatter_kernel<64>, dim3(blocks), dim3(256), 0, stream,
         (const __nv_bfloat16*)qkv, rows, ld, heads, seq, s_txt, (const __nv_bfloat16*)wq_img,
         (const __nv_bfloat16*)wk_img, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt,
         (const float2*)freqs_cos_sin, eps, D);
@@ -610,7 +624,7 @@ extern "C" int qi_cfg_euler_step(const void* cond, const void* uncond, const voi
   if (tokens <= 0) return QI_OK;
   const long long threads = tokens * 8;
   const int blocks = (int)((threads + 255) / 256);
-  cfg_euler_kernel<<<blocks, 256, 0, stream>>>((const __nv_bfloat16*)cond,
+  qi_launch(cfg_euler_kernel, dim3(blocks), dim3(256), 0, stream, (const __nv_bfloat16*)cond,
                                                (const __nv_bfloat16*)uncond,
                                                (const __nv_bfloat16*)latents, (__nv_bfloat16*)out,
                                                tokens, true_cfg_scale, dt_dev, dt);
@@ -625,7 +639,7 @@ extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, v
   if (M <= 0 || N <= 0) return QI_OK;
   if (K % 8 != 0 || ld_x % 8 != 0) return QI_ERR_ARG;
   dim3 grid((N + 7) / 8, (M + 3) / 4);
-  small_linear_kernel<4><<<grid, 256, 0, stream>>>(
+  qi_launch(small_linear_kernel<4>, grid, dim3(256), 0, stream,
       (const __nv_bfloat16*)x, (const __nv_bfloat16*)W, (const __nv_bfloat16*)bias,
       (__nv_bfloat16*)y, M, N, K, ld_x, ld_y, silu_in, silu_out);
   QI_CHECK_LAUNCH();
@@ -635,7 +649,7 @@ extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, v
 extern "C" int qi_timestep_sinusoid(const float* t, void* out, int M, cudaStream_t stream) {
   if (!t || !out) return QI_ERR_ARG;
   if (M <= 0) return QI_OK;
-  timestep_sinusoid_kernel<<<(M * 128 + 127) / 128, 128, 0, stream>>>(t, (__nv_bfloat16*)out, M);
+  qi_launch(timestep_sinusoid_kernel, dim3((M * 128 + 127) / 128), dim3(128), 0, stream, t, (__nv_bfloat16*)out, M);
   QI_CHECK_LAUNCH();
   return QI_OK;
 }

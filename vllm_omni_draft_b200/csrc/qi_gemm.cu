@@ -158,6 +158,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     for (int p = 0; p < L.num_problems; ++p) {
@@ -179,6 +180,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();   // everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -285,21 +287,21 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 //   warps drain their own 128 accumulator rows from their own TMEM and release the accumulator on the
 //   leader's tmem_empty barrier (count 8 = 4 warps x 2 CTAs).
 // ---------------------------------------------------------------------------------------------
-template <int BN>
+template <int BN, int STG = 0>
 struct GemmPairCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = (BN / 2) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 6 : (BN == 192 ? 7 : 8);
+  static constexpr int STAGES = STG ? STG : ((BN == 256) ? 6 : (BN == 192 ? 7 : 8));
   static constexpr int ACC_STRIDE = (BN == 192) ? 256 : BN;
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 };
 
-template <int BN>
+template <int BN, int STG = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
-  using Cfg = GemmPairCfg<BN>;
+  using Cfg = GemmPairCfg<BN, STG>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -315,6 +317,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   const bool leader = cta == 0;
   const int pair = blockIdx.x >> 1;
   const int num_pairs = gridDim.x >> 1;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     for (int p = 0; p < L.num_problems; ++p) {
@@ -336,6 +339,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
@@ -516,12 +520,13 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
   const int grid = tiles < sms ? tiles : sms;
-  gemm_bf16_kernel<BN><<<grid, GEMM_THREADS, GemmCfg<BN>::SMEM_BYTES, stream>>>(L);
-  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  if (qi_launch(gemm_bf16_kernel<BN>, dim3(grid), dim3(GEMM_THREADS), GemmCfg<BN>::SMEM_BYTES, stream, L) !=
+      cudaSuccess)
+    return QI_ERR_CUDA;
   return QI_OK;
 }
 
-template <int BN>
+template <int BN, int STG = 0>
 static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
   GemmLaunch L;
   memset(&L, 0, sizeof(L));
@@ -535,16 +540,17 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
   L.total_tiles = tiles;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_pair_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             GemmPairCfg<BN>::SMEM_BYTES) != cudaSuccess)
+    if (cudaFuncSetAttribute(gemm_pair_bf16_kernel<BN, STG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             GemmPairCfg<BN, STG>::SMEM_BYTES) != cudaSuccess)
       return QI_ERR_CUDA;
     attr_set = true;
   }
   const int pairs_max = qi_num_sms() / 2;
   if (pairs_max <= 0) return QI_ERR_CUDA;
   const int pairs = tiles < pairs_max ? tiles : pairs_max;
-  gemm_pair_bf16_kernel<BN><<<2 * pairs, GEMM_THREADS, GemmPairCfg<BN>::SMEM_BYTES, stream>>>(L);
-  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  if (qi_launch(gemm_pair_bf16_kernel<BN, STG>, dim3(2 * pairs), dim3(GEMM_THREADS),
+                GemmPairCfg<BN, STG>::SMEM_BYTES, stream, L) != cudaSuccess)
+    return QI_ERR_CUDA;
   return QI_OK;
 }
 
@@ -605,6 +611,14 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
     pair = best_pair;
   }
   if (pair) {
+    static const int env_stg = [] {
+      const char* e = getenv("QI_GEMM_PAIR_STAGES");   // tuning aid (256-wide pair tile only)
+      return e ? atoi(e) : 0;
+    }();
+    if (bn == 256 && env_stg == 3) return launch_gemm_pair<256, 3>(problems, num_problems, stream);
+    if (bn == 256 && env_stg == 4) return launch_gemm_pair<256, 4>(problems, num_problems, stream);
+    if (bn == 256 && env_stg == 5) return launch_gemm_pair<256, 5>(problems, num_problems, stream);
+    if (bn == 256 && env_stg == 7) return launch_gemm_pair<256, 7>(problems, num_problems, stream);
     if (bn == 256) return launch_gemm_pair<256>(problems, num_problems, stream);
     if (bn == 192) return launch_gemm_pair<192>(problems, num_problems, stream);
     return launch_gemm_pair<128>(problems, num_problems, stream);

@@ -33,6 +33,8 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(uint32_t* const* __res
                                                           int me, uint32_t* __restrict__ state,
                                                           unsigned long long timeout_ns) {
   const int p = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();   // the flag must not overtake the stores of the kernels before it
   const uint32_t epoch = state[0] + 1;
   const uint32_t failed = state[1];
   __syncwarp();
@@ -114,8 +116,9 @@ extern "C" int qi_peer_barrier(void* const* signal_ptrs_dev, int n_peers, int my
     return QI_ERR_ARG;
   if (qi_num_sms() <= 0) return QI_ERR_CUDA;
   const unsigned long long ns = (unsigned long long)(timeout_ms ? timeout_ms : 2000) * 1000000ull;
-  peer_barrier_kernel<<<1, 32, 0, stream>>>(reinterpret_cast<uint32_t* const*>(signal_ptrs_dev),
-                                            n_peers, my_index, state_dev, ns);
-  if (cudaGetLastError() != cudaSuccess) return QI_ERR_CUDA;
+  if (qi_launch(peer_barrier_kernel, dim3(1), dim3(32), 0, stream,
+                reinterpret_cast<uint32_t* const*>(signal_ptrs_dev), n_peers, my_index, state_dev,
+                ns) != cudaSuccess)
+    return QI_ERR_CUDA;
   return QI_OK;
 }
