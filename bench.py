@@ -206,11 +206,13 @@ def main():
         sampler.start()
     launches0 = ops.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()     # no-op unless run under `ncu --profile-from-start off`
     ev0.record()
     for i in range(K):
         den.step((Wm + i) % n_steps_sched)
     ev1.record()
     barrier()
+    torch.cuda.profiler.stop()
     ms = ev0.elapsed_time(ev1)
     launches = den.launches_per_step * K if den.launches_per_step else ops.launch_count - launches0
     clocks = sampler.stop() if rank == 0 else None
