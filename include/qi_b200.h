@@ -160,6 +160,11 @@ int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int ba
                              int heads, int head_dim, long long ld_q, long long ld_kv, long long ld_o,
                              long long q_batch_stride, long long kv_batch_stride, long long o_batch_stride,
                              float softmax_scale, const qi_peer_scatter_t* dst /* host */, qi_stream_t stream);
+/* Softmax variant of the attention kernel (tuning / tests): -1 = default (env QI_ATTN_VARIANT, else 11),
+ * otherwise EMU + 8 * SPLIT with EMU in {0, 2, 3, 4} = how many of every 8 element pairs evaluate 2^x
+ * with the FMA-pipe polynomial instead of MUFU.EX2, SPLIT in {0, 1} = P published in two halves. */
+int qi_attention_set_variant(int variant);
+
 
 /* Peer memory: device allocations that can be mapped by the other ranks of the node (CUDA IPC).
  * handle64 is a 64-byte host blob to ship to the peers (e.g. torch.distributed.all_gather_object). */

@@ -177,6 +177,30 @@ def test_attention(cuda_device, B, S, H, Dh):
     assert err < 1e-2, f"rel_l2={err}"
 
 
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 10, 11, 12])
+def test_attention_softmax_variants(cuda_device, variant):
+    """Every softmax variant (MUFU only / 2-3-4 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
+    or in two halves) matches fp32 SDPA, on a ragged sequence (partial last K/V tile, partial Q tile) with
+    large-magnitude logits so the lazy rescale and the polynomial's range reduction are exercised."""
+    ops = _ops()
+    B, S, H, Dh = 2, 1000, 3, 128
+    d = H * Dh
+    qkv = _rand((B, S, 3 * d), 51, 1.0)
+    qkv[:, :, :d] *= 3.0                      # logits ~ N(0, 3*sqrt(128)*...) -> wide dynamic range
+    q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
+    out = torch.zeros(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
+    ops.attention_set_variant(variant)
+    try:
+        ops.attention(q, k, v, out)
+        torch.cuda.synchronize()
+    finally:
+        ops.attention_set_variant(-1)
+    ref = torch.nn.functional.scaled_dot_product_attention(
+        q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
+    err = O.rel_l2(out.cpu(), ref.cpu())
+    assert err < 6e-3, f"variant={variant} rel_l2={err}"
+
+
 @pytest.mark.parametrize("bn", [128, 192, 256])
 def test_gemm_tile_widths(cuda_device, bn):
     """Every tile width of the persistent GEMM (auto-selected by wave count in production) is exact."""

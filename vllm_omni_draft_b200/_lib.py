@@ -51,6 +51,7 @@ _SIGNATURES = {
     "qi_gemm_bf16": (_i, [C.POINTER(GemmProblem), _i, _vp]),
     "qi_gemm_set_tile_n": (_i, [_i]),
     "qi_gemm_set_cta_pair": (_i, [_i]),
+    "qi_attention_set_variant": (_i, [_i]),
     "qi_attention_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f,
                                       C.POINTER(PeerScatter), _vp]),
     "qi_qknorm_rope_scatter": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f,

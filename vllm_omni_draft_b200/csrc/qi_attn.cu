@@ -8,9 +8,23 @@
 // ping-pong so the tensor pipe works on one tile while the other tile's softmax runs.
 // O is rescaled lazily: only when a row's running max grows by more than 2^8.
 //
+// Softmax inner loop (the kernel is bound by the S -> P chain, not by the tensor pipe):
+//   * row max over 8 independent 3-input-max chains (a single chain is 64 dependent FMNMX3);
+//   * x = s*scale - m and the row sum use packed fma.rn.f32x2 / add.rn.f32x2 (half the FMA-pipe slots);
+//   * EMU of every 8 element pairs evaluate 2^x on the FMA pipe (round-to-nearest range reduction +
+//     degree-3 minimax polynomial, 7.5e-5 relative error, P is rounded to bf16 afterwards) instead of
+//     MUFU.EX2, whose 16/clk/SM rate otherwise bounds the softmax at the tensor pipe's own tile time;
+//   * SPLIT: P is published in two halves so the first four P*V MMAs overlap the second half's exps;
+//   * only the last (partial) K/V tile runs the masked variant of the loop body.
+//
 // Warps: 0-3 softmax tile 0, 4-7 softmax tile 1, 8 TMA producer, 9 MMA issuer / TMEM owner.
 #include "qi_common.cuh"
 #include "../../include/qi_b200.h"
+#include <cstdlib>
+
+#ifndef QI_ATTN_DEFAULT_VARIANT
+#define QI_ATTN_DEFAULT_VARIANT 11   // EMU = 3 of 8 pairs on the FMA pipe, split P
+#endif
 
 namespace qi {
 
@@ -39,6 +53,7 @@ struct AttParams {
   long long ld_o, o_bs;
   int seq_q, seq_kv, heads;
   float scale_log2;
+  int split_p;   // softmax publishes P in two 64-key halves (p_half, then p_full)
   // Ulysses scatter epilogue (n_peer > 0): query row r owned by rank p goes to
   // o_peer[p] + o_chunk_off + b*o_bs + (r - o_prefix[p])*ld_o + head*DH   (peer-mapped HBM)
   int n_peer;
@@ -53,7 +68,112 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-template <int DH>
+// 2^x for a pair on the FMA/ALU pipes: j = round(x), f = x - j in [-0.5, 0.5], degree-3 minimax
+// polynomial for 2^f (max relative error 7.5e-5), exponent added as an integer.  x is clamped to
+// >= -126 so the exponent field cannot wrap (masked columns, x = -inf, come out as 2^-126 ~ 0).
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 t = __fadd2_rn(x, make_float2(12582912.f, 12582912.f));          // 1.5 * 2^23 + j
+  const float2 jf = __fadd2_rn(t, make_float2(-12582912.f, -12582912.f));
+  const float2 f = __ffma2_rn(jf, make_float2(-1.f, -1.f), x);
+  float2 p = __ffma2_rn(make_float2(0.0551716648f, 0.0551716648f), f,
+                        make_float2(0.2426111251f, 0.2426111251f));
+  p = __ffma2_rn(p, f, make_float2(0.6932609677f, 0.6932609677f));
+  p = __ffma2_rn(p, f, make_float2(0.9999280572f, 0.9999280572f));
+  float2 r;
+  r.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(t.x) << 23));
+  r.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(t.y) << 23));
+  return r;
+}
+
+// One K/V tile of the online softmax for one query row (one thread): S row from TMEM -> running
+// max / lazy O rescale -> P (bf16, packed over S's first 64 columns) + row-sum update.
+template <int DH, bool MASK, int EMU, bool SPLIT>
+__device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, int kv_valid, bool first,
+                                             float scale_log2, float& m_ref, float& l_sum,
+                                             uint64_t* p_half, uint64_t* p_full, int lane) {
+  uint32_t r[ATT_BN / 32][32];
+#pragma unroll
+  for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
+  tmem_ld_wait();
+  if (MASK) {
+#pragma unroll
+    for (int c = 0; c < ATT_BN / 32; ++c)
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: contributes 0
+  }
+  float mxs[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) mxs[q] = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < ATT_BN / 32; ++c)
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      mxs[i & 7] = fmaxf(fmaxf(mxs[i & 7], __uint_as_float(r[c][2 * i])), __uint_as_float(r[c][2 * i + 1]));
+  const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                         fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+  const float m_new = fmaxf(m_ref, mx * scale_log2);
+  const bool need = (m_new - m_ref) > 8.0f;   // also true on the first tile (m_ref = -inf)
+  if (__any_sync(0xffffffffu, need)) {
+    const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on tile 0
+    if (need) {
+      l_sum *= f;
+      m_ref = m_new;
+    }
+    if (!first) {
+#pragma unroll 1
+      for (int c = 0; c < DH / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(o_addr + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+        tmem_st32(o_addr + c * 32, o);
+      }
+    }
+  }
+  // P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
+  const float2 sc2 = make_float2(scale_log2, scale_log2);
+  const float2 nm2 = make_float2(-m_ref, -m_ref);
+  float2 acc[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) acc[q] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < ATT_BN / 32; ++c) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float2 x = __ffma2_rn(make_float2(__uint_as_float(r[c][2 * i]), __uint_as_float(r[c][2 * i + 1])),
+                                  sc2, nm2);
+      float2 p;
+      if (((i % 8) * EMU) % 8 < EMU) {
+        p = exp2_poly2(x);
+      } else {
+        p.x = fast_exp2(x.x);
+        p.y = fast_exp2(x.y);
+      }
+      acc[i & 3] = __fadd2_rn(acc[i & 3], p);
+      pk[i] = pack_bf16(p.x, p.y);
+    }
+    tmem_st16(s_addr + c * 16, pk);
+    if (SPLIT && c == ATT_BN / 64 - 1) {
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_half);
+    }
+  }
+  const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
+  l_sum += (a01.x + a01.y) + (a23.x + a23.y);
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_full);
+}
+
+template <int DH, int EMU, bool SPLIT>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attention_fwd_kernel(const __grid_constant__ AttParams P) {
   using Cfg = AttCfg<DH>;
@@ -69,7 +189,8 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   uint64_t* s_full = bars + 9;    // [2]  per Q tile
   uint64_t* p_full = bars + 11;   // [2]
   uint64_t* o_done = bars + 13;   // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* p_half = bars + 15;   // [2]  first 64 keys of P written (SPLIT only)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -91,6 +212,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
+      mbar_init(&p_half[i], 4);
       mbar_init(&o_done[i], 1);
     }
     fence_barrier_init();
@@ -107,7 +229,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   if (warp == 8) {
     // ------------------------------------------------------------------ TMA producer
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
       for (int t = 0; t < 2; ++t)
         for (int s = 0; s < Cfg::NSUB; ++s)
@@ -132,7 +254,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   } else if (warp == 9) {
     // ------------------------------------------------------------------ MMA issuer
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas knows a single thread issues (no per-instruction elect loops)
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
       const uint32_t s_col[2] = {tmem_base + Cfg::S_COL0, tmem_base + Cfg::S_COL1};
@@ -151,9 +273,9 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
             mma_ss(s_col[t], da + 2 * k, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
         }
       };
-      auto issue_pv = [&](int t, int st, bool accumulate) {
+      auto issue_pv = [&](int t, int st, bool accumulate, int k0, int k1) {
 #pragma unroll
-        for (int k = 0; k < ATT_BN / 16; ++k) {
+        for (int k = k0; k < k1; ++k) {
           // V sub-tile rows are keys (128 B each): 16 keys per MMA = 2048 B; the second 64 columns
           // of the head dim live one sub-tile (LBO) further.
           const uint64_t db =
@@ -178,9 +300,18 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         const uint32_t phn = ((j + 1) >> 1) & 1;
         mbar_wait(&v_full[st], ph);
         for (int t = 0; t < 2; ++t) {
-          mbar_wait(&p_full[t], j & 1);
-          tc_fence_after();
-          issue_pv(t, st, j > 0);
+          if (SPLIT) {
+            mbar_wait(&p_half[t], j & 1);
+            tc_fence_after();
+            issue_pv(t, st, j > 0, 0, ATT_BN / 32);
+            mbar_wait(&p_full[t], j & 1);
+            tc_fence_after();
+            issue_pv(t, st, j > 0, ATT_BN / 32, ATT_BN / 16);
+          } else {
+            mbar_wait(&p_full[t], j & 1);
+            tc_fence_after();
+            issue_pv(t, st, j > 0, 0, ATT_BN / 16);
+          }
           if (t == 1) tc_commit(&v_empty[st]);
           if (has_next) {
             if (t == 0) {
@@ -209,71 +340,17 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     const uint32_t o_addr = tmem_base + lane_off + (t == 0 ? Cfg::O_COL0 : Cfg::O_COL1);
     float m_ref = -INFINITY;   // reference max (scaled, log2 domain) used for P and O
     float l_sum = 0.f;
+    const int n_full = P.seq_kv / ATT_BN;   // K/V tiles with all 128 keys valid
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
-      const int kv_valid = min(ATT_BN, P.seq_kv - j * ATT_BN);
-      // S row (128 fp32) into registers with one wait: four x32 loads in flight
-      uint32_t r[ATT_BN / 32][32];
-#pragma unroll
-      for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
-      tmem_ld_wait();
-      float mx = -INFINITY;
-      if (kv_valid == ATT_BN) {
-#pragma unroll
-        for (int c = 0; c < ATT_BN / 32; ++c)
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+      if (j < n_full) {
+        softmax_tile<DH, false, EMU, SPLIT>(s_addr, o_addr, ATT_BN, j == 0, P.scale_log2, m_ref, l_sum,
+                                            &p_half[t], &p_full[t], lane);
       } else {
-#pragma unroll
-        for (int c = 0; c < ATT_BN / 32; ++c)
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: exp2 -> 0
-            mx = fmaxf(mx, __uint_as_float(r[c][i]));
-          }
+        softmax_tile<DH, true, EMU, SPLIT>(s_addr, o_addr, P.seq_kv - j * ATT_BN, j == 0, P.scale_log2,
+                                           m_ref, l_sum, &p_half[t], &p_full[t], lane);
       }
-      const float m_new = fmaxf(m_ref, mx * P.scale_log2);
-      const bool need = (m_new - m_ref) > 8.0f;   // also true on the first tile (m_ref = -inf)
-      if (__any_sync(0xffffffffu, need)) {
-        const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on tile 0
-        if (need) {
-          l_sum *= f;
-          m_ref = m_new;
-        }
-        if (j > 0) {
-#pragma unroll 1
-          for (int c = 0; c < DH / 32; ++c) {
-            uint32_t o[32];
-            tmem_ld32(o_addr + c * 32, o);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-            tmem_st32(o_addr + c * 32, o);
-          }
-        }
-      }
-      // P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
-      const float neg_m = -m_ref;
-      float ls0 = 0.f, ls1 = 0.f;
-#pragma unroll
-      for (int c = 0; c < ATT_BN / 32; ++c) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(r[c][2 * i]), P.scale_log2, neg_m));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(r[c][2 * i + 1]), P.scale_log2, neg_m));
-          ls0 += p0;
-          ls1 += p1;
-          pk[i] = pack_bf16(p0, p1);
-        }
-        tmem_st16(s_addr + c * 16, pk);
-      }
-      l_sum += ls0 + ls1;
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_full[t]);
     }
     // final: O / l -> bf16 -> global
     mbar_wait(&o_done[t], 0);
@@ -320,6 +397,36 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
 using namespace qi;
 
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT
+extern "C" int qi_attention_set_variant(int v) {
+  if (v < -1 || v > 15) return QI_ERR_ARG;
+  g_attn_variant = v;
+  return QI_OK;
+}
+static int attn_variant() {
+  static const int env = [] {
+    const char* e = getenv("QI_ATTN_VARIANT");   // tuning aid: EMU (0,2,3,4) + 8 * SPLIT
+    return e ? atoi(e) : -1;
+  }();
+  const int v = g_attn_variant >= 0 ? g_attn_variant : env;
+  return v >= 0 ? v : QI_ATTN_DEFAULT_VARIANT;
+}
+
+template <int DH, int EMU, bool SPLIT>
+static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(attention_fwd_kernel<DH, EMU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             AttCfg<DH>::SMEM_BYTES) != cudaSuccess)
+      return QI_ERR_CUDA;
+    attr_set = true;
+  }
+  if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream,
+                P) != cudaSuccess)
+    return QI_ERR_CUDA;
+  return QI_OK;
+}
+
 template <int DH>
 static int launch_attention(const void* q, const void* k, const void* v, void* o, int batch,
                             int seq_q, int seq_kv, int heads, long long ld_q, long long ld_kv,
@@ -360,18 +467,20 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.seq_kv = seq_kv;
   P.heads = heads;
   P.scale_log2 = scale * 1.4426950408889634f;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(attention_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             AttCfg<DH>::SMEM_BYTES) != cudaSuccess)
-      return QI_ERR_CUDA;
-    attr_set = true;
-  }
+  const int variant = attn_variant();
+  P.split_p = (variant >> 3) & 1;
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
-  if (qi_launch(attention_fwd_kernel<DH>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream, P) !=
-      cudaSuccess)
-    return QI_ERR_CUDA;
-  return QI_OK;
+  switch (variant) {
+    case 0: return launch_attention_v<DH, 0, false>(P, grid, stream);
+    case 2: return launch_attention_v<DH, 2, false>(P, grid, stream);
+    case 3: return launch_attention_v<DH, 3, false>(P, grid, stream);
+    case 4: return launch_attention_v<DH, 4, false>(P, grid, stream);
+    case 8: return launch_attention_v<DH, 0, true>(P, grid, stream);
+    case 10: return launch_attention_v<DH, 2, true>(P, grid, stream);
+    case 11: return launch_attention_v<DH, 3, true>(P, grid, stream);
+    case 12: return launch_attention_v<DH, 4, true>(P, grid, stream);
+    default: return QI_ERR_ARG;
+  }
 }
 
 static int attention_entry(const void* q, const void* k, const void* v, void* o, int batch,

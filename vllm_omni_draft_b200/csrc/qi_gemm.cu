@@ -184,7 +184,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -209,7 +209,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -343,7 +343,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = pair; t < L.total_tiles; t += num_pairs) {
@@ -371,7 +371,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (leader && lane == 0) {
+    if (leader && elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;

@@ -163,6 +163,11 @@ def gemm_set_tile_n(bn: int) -> None:
     check(_lib.lib().qi_gemm_set_tile_n(int(bn)), "qi_gemm_set_tile_n")
 
 
+def attention_set_variant(variant: int) -> None:
+    """-1 default; else EMU (0/2/3/4 of 8 pairs on the FMA-pipe exp2 polynomial) + 8 * SPLIT."""
+    check(_lib.lib().qi_attention_set_variant(int(variant)), "qi_attention_set_variant")
+
+
 def gemm_set_cta_pair(mode: int) -> None:
     check(_lib.lib().qi_gemm_set_cta_pair(int(mode)), "qi_gemm_set_cta_pair")
 
