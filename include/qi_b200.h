@@ -36,7 +36,10 @@ enum qi_status {
 enum qi_epilogue {
   QI_EPI_BIAS = 0,           /* C = A W^T + b                         (to_q/k/v, add_*_proj, img_in, ...) */
   QI_EPI_BIAS_GELU_TANH = 1, /* C = gelu_tanh(A W^T + b)              (FeedForward net.0: GELU(approximate="tanh")) */
-  QI_EPI_GATED_RESIDUAL = 2  /* C = R + gate[batch] * (A W^T + b)     (x = x + gate * attn/mlp output) */
+  QI_EPI_GATED_RESIDUAL = 2, /* C = R + gate[batch] * (A W^T + b)     (x = x + gate * attn/mlp output) */
+  QI_EPI_QKV_NORM_ROPE = 3   /* C = [rope(rmsnorm(q)) | rope(rmsnorm(k)) | v] of A W_qkv^T + b: the fused to_q/k/v
+                              * projection with norm_q/norm_k (RMSNorm over head_dim) and the MSRoPE rotation
+                              * applied per head vector in the epilogue (QwenDoubleStreamAttnProcessor2_0) */
 };
 
 int qi_version(void);
@@ -53,6 +56,7 @@ int qi_set_pdl(int on);
  * launch.  A is [batch, m, k] (row stride lda, batch stride a_batch_stride), W is the nn.Linear
  * weight [n, k] contiguous, C is [batch, m, n] (ldc, c_batch_stride).  k % 64 == 0, n % 8 == 0.
  * A zero-initialised struct with a/w/c/m/batch/n/k set is a plain C = A W^T. */
+struct qi_peer_scatter; /* defined with the Ulysses exchange entry points below */
 typedef struct {
   const void* a;
   long long lda;
@@ -76,6 +80,19 @@ typedef struct {
    * element (row, kk) of chunk c lives at a + c*a_k_chunk_stride + row*lda + kk.  0 = A is plain [m, k]. */
   int a_k_chunk;
   long long a_k_chunk_stride;
+  /* QI_EPI_QKV_NORM_ROPE only: n == 3 * heads * head_dim, columns [q | k | v], head_dim in {64, 128}. */
+  const void* qk_norm_wq;    /* [head_dim] bf16 RMSNorm weight of the q heads */
+  const void* qk_norm_wk;    /* [head_dim] bf16 RMSNorm weight of the k heads */
+  const void* rope_cos_sin;  /* fp32 [>= rope_pos0 + m, head_dim/2, 2] (cos, sin); row r of every batch item uses
+                              * table row rope_pos0 + r (joint order, text rows first) */
+  int rope_pos0;
+  int heads;
+  int head_dim;
+  float qk_norm_eps;
+  /* Optional Ulysses scatter (NULL = store into c): head vector (b, row, j in {q,k,v}, head h) goes to
+   * base[h / (heads/P)], laid out [batch, row_prefix[P], 3, heads/P, head_dim], at sequence row
+   * row_prefix[my_index] + rope_pos0 + row.  c may be NULL then. */
+  const struct qi_peer_scatter* scatter;
 } qi_gemm_problem_t;
 
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
@@ -137,7 +154,7 @@ int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq
  * into this process (qi_peer_import, or any other peer mapping); rank p owns heads
  * [p*heads/P, (p+1)*heads/P) and sequence rows [row_prefix[p], row_prefix[p+1]) of the rank-major
  * joint sequence (ragged shards allowed). */
-typedef struct {
+typedef struct qi_peer_scatter {
   int n_peers;       /* P <= 8 */
   int my_index;      /* this rank's position in the group */
   void* base[8];

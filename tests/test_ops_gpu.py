@@ -294,6 +294,85 @@ def test_ulysses_scatter_kernels_emulated_ranks(cuda_device, P, B, counts):
             assert torch.equal(recv[r][:, :, j], t[:, full_rows][:, :, r * hs:(r + 1) * hs])
 
 
+@pytest.mark.parametrize("H,Dh,axes,bn,pair", [(4, 64, (8, 28, 28), 0, -1), (4, 64, (8, 28, 28), 192, 0),
+                                               (4, 128, (16, 56, 56), 128, 1), (6, 128, (16, 56, 56), 256, 0),
+                                               (6, 128, (16, 56, 56), 0, -1)])
+def test_gemm_qkv_norm_rope_epilogue(cuda_device, H, Dh, axes, bn, pair):
+    """K2 fused into K3: the QKV GEMM whose epilogue applies QK-RMSNorm + MSRoPE per head vector equals the
+    plain QKV GEMM followed by qi_qknorm_rope (same rounding points; only the fp32 order of the 128-term sum
+    of squares differs, so a few elements may move by one bf16 ulp), for both streams in one launch."""
+    ops = _ops()
+    from vllm_omni_draft_b200 import rope
+    B, s_txt, hh, ww = 2, 37, 9, 31
+    s_img = hh * ww
+    S, d, K = s_txt + s_img, H * Dh, 256
+    xi, xt = _rand((B, s_img, K), 80), _rand((B, s_txt, K), 81)
+    wi, wt = _rand((3 * d, K), 82, 0.08), _rand((3 * d, K), 83, 0.08)
+    bi, bt = _rand((3 * d,), 84, 0.3), _rand((3 * d,), 85, 0.3)
+    nw = [_rand((Dh,), 86 + i, 0.2) + 1 for i in range(4)]
+    freqs = rope.joint_cos_sin(axes, 10000.0, [(1, hh, ww)], s_txt).cuda()
+    ref = torch.zeros(B, S, 3 * d, device="cuda", dtype=torch.bfloat16)
+    ops.gemm([ops.gemm_problem(xi, wi, bi, ref[:, s_txt:]), ops.gemm_problem(xt, wt, bt, ref[:, :s_txt])])
+    ops.qknorm_rope(ref.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
+    out = torch.zeros_like(ref)
+    ops.gemm_set_tile_n(bn)
+    ops.gemm_set_cta_pair(pair)
+    try:
+        kw = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=freqs, heads=H, head_dim=Dh)
+        ops.gemm([ops.gemm_problem(xi, wi, bi, out[:, s_txt:], qk_norm=(nw[0], nw[1]), rope_pos0=s_txt, **kw),
+                  ops.gemm_problem(xt, wt, bt, out[:, :s_txt], qk_norm=(nw[2], nw[3]), rope_pos0=0, **kw)])
+        torch.cuda.synchronize()
+    finally:
+        ops.gemm_set_tile_n(0)
+        ops.gemm_set_cta_pair(-1)
+    assert torch.equal(out[:, :, 2 * d:], ref[:, :, 2 * d:])            # v columns: plain bias epilogue
+    err = O.rel_l2(out.float().cpu(), ref.float().cpu())
+    same = (out == ref).float().mean().item()
+    assert err < 2e-3 and same > 0.98, f"rel_l2={err} identical={same}"
+
+
+def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device):
+    """The QKV epilogue's Ulysses scatter (head vectors stored straight into the head owners' attention
+    input buffers) against the in-place epilogue, P ranks emulated on one GPU, ragged shards, batch 2."""
+    ops = _ops()
+    from vllm_omni_draft_b200 import rope
+    from vllm_omni_draft_b200.peer import prefix as _prefix, shard_counts
+    P, B, H, Dh, axes, K = 2, 2, 4, 64, (8, 28, 28), 128
+    d, hs = H * Dh, H // P
+    s_txt_full, s_img_full = 5, 71
+    tc, ic = shard_counts(s_txt_full, P), shard_counts(s_img_full, P)
+    counts = [a + b for a, b in zip(tc, ic)]
+    pre, tpre, ipre = _prefix(counts), _prefix(tc), _prefix(ic)
+    S = pre[-1]
+    x = _rand((B, S, K), 90)                     # joint order [txt; img]
+    wi, wt = _rand((3 * d, K), 91, 0.1), _rand((3 * d, K), 92, 0.1)
+    bi, bt = _rand((3 * d,), 93, 0.3), _rand((3 * d,), 94, 0.3)
+    nw = [_rand((Dh,), 95 + i, 0.2) + 1 for i in range(4)]
+    freqs_full = rope.joint_cos_sin(axes, 10000.0, [(1, 1, s_img_full)], s_txt_full).cuda()
+    kw = dict(epilogue=ops.EPI_QKV_NORM_ROPE, heads=H, head_dim=Dh)
+    ref = torch.zeros(B, S, 3 * d, device="cuda", dtype=torch.bfloat16)
+    ops.gemm([ops.gemm_problem(x[:, s_txt_full:], wi, bi, ref[:, s_txt_full:], qk_norm=(nw[0], nw[1]),
+                               rope_pos0=s_txt_full, freqs=freqs_full, **kw),
+              ops.gemm_problem(x[:, :s_txt_full], wt, bt, ref[:, :s_txt_full], qk_norm=(nw[2], nw[3]),
+                               rope_pos0=0, freqs=freqs_full, **kw)])
+    recv = [torch.zeros(B, S, 3, hs, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    order = []
+    for r in range(P):
+        rows = list(range(tpre[r], tpre[r + 1])) + [s_txt_full + i for i in range(ipre[r], ipre[r + 1])]
+        order += rows
+        xl = x[:, rows].contiguous()
+        fl = freqs_full[rows].contiguous()
+        sc = _peer_scatter(recv, pre, r)
+        ops.gemm([ops.gemm_problem(xl[:, tc[r]:], wi, bi, None, qk_norm=(nw[0], nw[1]), rope_pos0=tc[r], freqs=fl,
+                                   scatter=sc, **kw),
+                  ops.gemm_problem(xl[:, :tc[r]], wt, bt, None, qk_norm=(nw[2], nw[3]), rope_pos0=0, freqs=fl,
+                                   scatter=sc, **kw)])
+    torch.cuda.synchronize()
+    want = ref[:, order].view(B, S, 3, H, Dh)
+    for r in range(P):
+        assert torch.equal(recv[r], want[:, :, :, r * hs:(r + 1) * hs])
+
+
 def test_peer_barrier_single_rank(cuda_device):
     """n_peers = 1: the rank signals itself; the epoch advances and the timeout flag stays clear."""
     ops = _ops()

@@ -28,6 +28,9 @@ class GemmProblem(C.Structure):
         ("gate", _vp), ("gate_batch_stride", _ll),
         ("m", _i), ("batch", _i), ("n", _i), ("k", _i), ("epilogue", _i),
         ("a_k_chunk", _i), ("a_k_chunk_stride", _ll),
+        ("qk_norm_wq", _vp), ("qk_norm_wk", _vp), ("rope_cos_sin", _vp),
+        ("rope_pos0", _i), ("heads", _i), ("head_dim", _i), ("qk_norm_eps", C.c_float),
+        ("scatter", _vp),
     ]
 
 

@@ -2,8 +2,8 @@
 //
 //   C[b, m, n] = epi( sum_k A[b, m, k] * W[n, k] + bias[n] )
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (+ TMEM owner),
-// warps 2..5 = epilogue (TMEM -> registers -> bias/GELU/gated-residual -> bf16 -> global).
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (+ TMEM owner),
+// warps 2..9 = epilogue, two per TMEM lane quadrant, each taking half of the tile's columns (TMEM -> registers -> bias/GELU/gated-residual -> bf16 -> global).
 // Tile 128 x BN x 64, UMMA 128 x BN x 16, operands K-major in 128B-swizzled shared memory filled by
 // TMA, fp32 accumulators double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps
 // the main loop of tile i+1.  Up to two problems (img + txt stream) share one persistent launch.
@@ -22,7 +22,8 @@ namespace qi {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_EPI_WARPS = 8;   // two warps per TMEM lane quadrant, each takes half of the tile's columns
+constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 
 struct GemmProb {
   void* c;
@@ -37,6 +38,15 @@ struct GemmProb {
   int tiles_n;
   int tile_begin;    // first global tile index of this problem
   int k_chunk;       // A's K axis is split into chunks of this many elements (== k when unsplit)
+  // QI_EPI_QKV_NORM_ROPE: per-head RMSNorm + MSRoPE on the q and k column blocks, v passes through
+  const float2* freqs;          // [>= pos0 + m, head_dim/2] (cos, sin)
+  const __nv_bfloat16* wq;      // [head_dim]
+  const __nv_bfloat16* wk;
+  int pos0, heads, head_dim;
+  float qk_eps;
+  // optional Ulysses scatter of the head vectors (sc_n > 0): see qi_peer_scatter_t
+  int sc_n, sc_hs, sc_s_total, sc_row_offset;
+  __nv_bfloat16* sc_base[8];
 };
 
 struct GemmLaunch {
@@ -86,19 +96,20 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // the accumulator while the math and the stores of the last chunk are still in flight.
 template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row, int n0,
-                                              uint32_t taddr, Release release) {
+                                              uint32_t taddr, int half, Release release) {
   const bool row_ok = row < P.m;
   __nv_bfloat16* crow =
       reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + (size_t)row * P.ldc;
   const __nv_bfloat16* rrow =
       P.residual ? P.residual + (size_t)b * P.res_bs + (size_t)row * P.ld_res : nullptr;
   const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)b * P.gate_bs : nullptr;
+  constexpr int CH = BN / 32 / 2;   // 32-column chunks per warp (this warp: [half*CH, half*CH + CH))
 #pragma unroll 1
-  for (int c = 0; c < BN / 32; ++c) {
+  for (int c = half * CH; c < half * CH + CH; ++c) {
     uint32_t r[32];
     tmem_ld32(taddr + c * 32, r);
     tmem_ld_wait();
-    if (c == BN / 32 - 1) release();
+    if (c == half * CH + CH - 1) release();
     const int n_base = n0 + c * 32;
     if (n_base >= P.n) continue;
 #pragma unroll
@@ -143,6 +154,131 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
   }
 }
 
+// QKV epilogue: the tile's BN columns are BN/DH whole head vectors of q, k or v.  Per row (one thread):
+// y = bf16(acc + bias); for q/k heads: RMSNorm over the DH columns (two passes over TMEM: sum of
+// squares, then normalise), * norm weight, MSRoPE rotation of adjacent (even, odd) pairs with the row's
+// (cos, sin) table -- rounding points as in qknorm_rope_kernel (upstream's eager order).  The head
+// vector is stored in place into C, or (sc_n > 0) straight into the head owner's attention input buffer
+// over NVLink: the head<->sequence all-to-all happens tile by tile under the GEMM's main loop.
+template <int BN, int DH, typename Release>
+__device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int row, int n0,
+                                                  uint32_t taddr, int half, Release release) {
+  constexpr int HPT = BN / DH;   // head vectors per tile row
+  const bool row_ok = row < P.m;
+  const int d_model = P.heads * DH;
+  const float2* fr = P.freqs + (size_t)(P.pos0 + (row_ok ? row : 0)) * (DH / 2);
+  bool released = false;
+#pragma unroll 1
+  for (int hh = half; hh < HPT; hh += 2) {      // the quadrant's two warps alternate head vectors
+    const int nh = n0 + hh * DH;
+    if (nh >= P.n) break;
+    const int j3 = nh / d_model;                 // 0 q, 1 k, 2 v
+    const int h = (nh - j3 * d_model) / DH;
+    __nv_bfloat16* dst;
+    if (P.sc_n > 0) {
+      const int p = h / P.sc_hs;
+      const int hl = h - p * P.sc_hs;
+      dst = P.sc_base[p] +
+            ((((size_t)b * P.sc_s_total + P.sc_row_offset + P.pos0 + row) * 3 + j3) * P.sc_hs + hl) * DH;
+    } else {
+      dst = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + (size_t)row * P.ldc + nh;
+    }
+    const uint32_t th = taddr + hh * DH;
+    float rstd = 0.f;
+    if (j3 < 2) {
+      float ss = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < DH / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(th + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float bv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+          if (P.bias) {
+            const uint4 bu = *reinterpret_cast<const uint4*>(P.bias + nh + c * 32 + g * 8);
+            const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y), b2 = unpack_bf16(bu.z),
+                         b3 = unpack_bf16(bu.w);
+            bv[0] = b0.x; bv[1] = b0.y; bv[2] = b1.x; bv[3] = b1.y;
+            bv[4] = b2.x; bv[5] = b2.y; bv[6] = b3.x; bv[7] = b3.y;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float v = bf16_round(__uint_as_float(r[g * 8 + j]) + bv[j]);
+            ss = fmaf(v, v, ss);
+          }
+        }
+      }
+      rstd = rsqrtf(ss * (1.f / DH) + P.qk_eps);
+    }
+    const __nv_bfloat16* wn = (j3 == 0) ? P.wq : P.wk;
+#pragma unroll 1
+    for (int c = 0; c < DH / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld32(th + c * 32, r);
+      tmem_ld_wait();
+      if (hh + 2 >= HPT && c == DH / 32 - 1) {
+        release();
+        released = true;
+      }
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int col = c * 32 + g * 8;     // column inside the head vector
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+        if (P.bias) {
+          const uint4 bu = *reinterpret_cast<const uint4*>(P.bias + nh + col);
+          const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y), b2 = unpack_bf16(bu.z),
+                       b3 = unpack_bf16(bu.w);
+          v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+          v[4] += b2.x; v[5] += b2.y; v[6] += b3.x; v[7] += b3.y;
+        }
+        if (j3 < 2) {
+          const uint4 wu = *reinterpret_cast<const uint4*>(wn + col);
+          const float2 w0 = unpack_bf16(wu.x), w1 = unpack_bf16(wu.y), w2 = unpack_bf16(wu.z),
+                       w3 = unpack_bf16(wu.w);
+          const float w[8] = {w0.x, w0.y, w1.x, w1.y, w2.x, w2.y, w3.x, w3.y};
+          const float4 f01 = *reinterpret_cast<const float4*>(fr + col / 2);
+          const float4 f23 = *reinterpret_cast<const float4*>(fr + col / 2 + 2);
+          const float cs[4] = {f01.x, f01.z, f23.x, f23.z};
+          const float sn[4] = {f01.y, f01.w, f23.y, f23.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float a = bf16_round(bf16_round(bf16_round(v[2 * j]) * rstd) * w[2 * j]);
+            const float bb = bf16_round(bf16_round(bf16_round(v[2 * j + 1]) * rstd) * w[2 * j + 1]);
+            v[2 * j] = a * cs[j] - bb * sn[j];
+            v[2 * j + 1] = a * sn[j] + bb * cs[j];
+          }
+        }
+        if (row_ok) {
+          const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
+                                     pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+          *reinterpret_cast<uint4*>(dst + col) = o;
+        }
+      }
+    }
+  }
+  if (!released) release();
+}
+
+// Epilogue dispatch for one warp's 32 rows of a tile.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row, int n0, uint32_t taddr,
+                                              int half, Release release) {
+  if (P.epilogue == QI_EPI_QKV_NORM_ROPE) {
+    if constexpr (BN % 128 == 0) {
+      if (P.head_dim == 128) {
+        epilogue_rows_qkv<BN, 128>(P, b, row, n0, taddr, half, release);
+        return;
+      }
+    }
+    epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, release);   // host guarantees head_dim == 64 here
+    return;
+  }
+  epilogue_rows<BN>(P, b, row, n0, taddr, half, release);
+}
+
 template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
@@ -171,7 +307,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
-      mbar_init(&tmem_empty[a], 4);
+      mbar_init(&tmem_empty[a], GEMM_EPI_WARPS);
     }
     fence_barrier_init();
   }
@@ -248,7 +384,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue warps (2..5)
+    // ------------------------------------------------------------ epilogue warps (2..9)
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -258,7 +394,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
-      epilogue_rows<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, [&]() {
+      epilogue_tile<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -330,7 +466,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);   // multicast commit
-      mbar_init(&tmem_empty[a], 8);  // 4 epilogue warps of each CTA (used in the leader only)
+      mbar_init(&tmem_empty[a], 2 * GEMM_EPI_WARPS);  // the epilogue warps of both CTAs (used in the leader only)
     }
     fence_barrier_init();
   }
@@ -420,7 +556,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
-      epilogue_rows<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, [&]() {
+      epilogue_tile<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(acc == 0 ? empty0 : empty1);
@@ -446,12 +582,12 @@ using namespace qi;
 
 static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int BN, int tile_begin,
                         int tile_m = BM, int b_box_rows = 0) {
-  if (!in.a || !in.w || !in.c) return QI_ERR_ARG;
+  if (!in.a || !in.w || (!in.c && !(in.epilogue == QI_EPI_QKV_NORM_ROPE && in.scatter))) return QI_ERR_ARG;
   if (in.m <= 0 || in.batch <= 0 || in.n <= 0 || in.k <= 0) return QI_ERR_ARG;
   if (in.k % BK != 0 || in.n % 8 != 0) return QI_ERR_UNSUPPORTED;
   if (in.lda % 8 != 0 || in.ldc % 8 != 0 || in.a_batch_stride % 8 != 0 || in.c_batch_stride % 8 != 0)
     return QI_ERR_ARG;
-  if (in.epilogue < 0 || in.epilogue > 2) return QI_ERR_ARG;
+  if (in.epilogue < 0 || in.epilogue > 3) return QI_ERR_ARG;
   if (in.epilogue == QI_EPI_GATED_RESIDUAL &&
       (!in.residual || !in.gate || in.ld_res % 8 != 0 || in.res_batch_stride % 8 != 0 ||
        in.gate_batch_stride % 8 != 0))
@@ -468,6 +604,34 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.ld_res = in.ld_res; P.res_bs = in.res_batch_stride; P.gate_bs = in.gate_batch_stride;
   P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
   P.epilogue = in.epilogue;
+  P.freqs = nullptr; P.wq = P.wk = nullptr; P.sc_n = 0;
+  if (in.epilogue == QI_EPI_QKV_NORM_ROPE) {
+    if (!in.qk_norm_wq || !in.qk_norm_wk || !in.rope_cos_sin || in.rope_pos0 < 0) return QI_ERR_ARG;
+    if (in.head_dim != 64 && in.head_dim != 128) return QI_ERR_UNSUPPORTED;
+    if (in.heads <= 0 || (long long)in.heads * in.head_dim * 3 != in.n || BN % in.head_dim != 0) return QI_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(in.qk_norm_wq) | reinterpret_cast<uintptr_t>(in.qk_norm_wk) |
+         reinterpret_cast<uintptr_t>(in.rope_cos_sin)) & 15)
+      return QI_ERR_ARG;
+    P.freqs = (const float2*)in.rope_cos_sin;
+    P.wq = (const __nv_bfloat16*)in.qk_norm_wq;
+    P.wk = (const __nv_bfloat16*)in.qk_norm_wk;
+    P.pos0 = in.rope_pos0; P.heads = in.heads; P.head_dim = in.head_dim; P.qk_eps = in.qk_norm_eps;
+    if (in.scatter) {
+      const qi_peer_scatter_t& d = *in.scatter;
+      if (d.n_peers < 1 || d.n_peers > 8 || d.my_index < 0 || d.my_index >= d.n_peers ||
+          in.heads % d.n_peers != 0 || d.row_prefix[0] != 0)
+        return QI_ERR_ARG;
+      if (d.row_prefix[d.my_index] + in.rope_pos0 + in.m > d.row_prefix[d.my_index + 1]) return QI_ERR_ARG;
+      for (int p = 0; p < d.n_peers; ++p) {
+        if (!d.base[p] || (reinterpret_cast<uintptr_t>(d.base[p]) & 15)) return QI_ERR_ARG;
+        P.sc_base[p] = (__nv_bfloat16*)d.base[p];
+      }
+      P.sc_n = d.n_peers;
+      P.sc_hs = in.heads / d.n_peers;
+      P.sc_s_total = d.row_prefix[d.n_peers];
+      P.sc_row_offset = d.row_prefix[d.my_index];
+    }
+  }
   P.tiles_m = (in.m + tile_m - 1) / tile_m;
   P.tiles_m_total = P.tiles_m * in.batch;
   P.tiles_n = (in.n + BN - 1) / BN;
@@ -582,7 +746,11 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
     return e ? atoi(e) : -1;
   }();
   const int pair_mode = g_pair_mode >= 0 ? g_pair_mode : (env_pair == 0 || env_pair == 1 ? env_pair : -1);
+  int bn_multiple = 64;   // the QKV epilogue needs whole head vectors inside a tile
+  for (int i = 0; i < num_problems; ++i)
+    if (problems[i].epilogue == QI_EPI_QKV_NORM_ROPE && problems[i].head_dim == 128) bn_multiple = 128;
   int bn = g_force_bn, pair = pair_mode;
+  if (bn != 0 && bn % bn_multiple != 0) return QI_ERR_UNSUPPORTED;
   if (bn == 0 || pair < 0) {
     double best = -1;
     const int cand[3] = {256, 192, 128};
@@ -591,6 +759,7 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
       if (pair_mode >= 0 && pm != pair_mode) continue;
       for (int c = 0; c < 3; ++c) {
         if (g_force_bn && cand[c] != g_force_bn) continue;
+        if (cand[c] % bn_multiple != 0) continue;
         const int tm = pm ? 2 * BM : BM;
         long long tiles = 0;
         for (int i = 0; i < num_problems; ++i) {

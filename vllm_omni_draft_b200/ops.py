@@ -11,7 +11,7 @@ import torch
 from . import _lib
 from ._lib import GemmProblem, check
 
-EPI_BIAS, EPI_BIAS_GELU_TANH, EPI_GATED_RESIDUAL = 0, 1, 2
+EPI_BIAS, EPI_BIAS_GELU_TANH, EPI_GATED_RESIDUAL, EPI_QKV_NORM_ROPE = 0, 1, 2, 3
 
 # kernel launches issued through this module (bench.py reports it as gpu_launches)
 launch_count = 0
@@ -37,10 +37,16 @@ def _req_bf16(*ts: torch.Tensor) -> None:
 
 def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                  epilogue: int = EPI_BIAS, residual: Optional[torch.Tensor] = None,
-                 gate: Optional[torch.Tensor] = None, a_k_chunked: bool = False) -> GemmProblem:
+                 gate: Optional[torch.Tensor] = None, a_k_chunked: bool = False,
+                 qk_norm: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, freqs: Optional[torch.Tensor] = None,
+                 rope_pos0: int = 0, heads: int = 0, head_dim: int = 0, eps: float = 1e-6,
+                 scatter: Optional["_lib.PeerScatter"] = None) -> GemmProblem:
     """a_k_chunked: a is [chunks, M, Kc] and stands for the [M, chunks*Kc] matrix whose K axis is
     the concatenation of the chunks (batch 1).  Otherwise a: [B, M, K] or [M, K] view (row/batch strides arbitrary, K contiguous); w: [N, K] contiguous;
-    out: [B, M, N] / [M, N] view; residual like out; gate [B, N] view."""
+    out: [B, M, N] / [M, N] view; residual like out; gate [B, N] view.
+    EPI_QKV_NORM_ROPE: w is the stacked [3*heads*head_dim, K] q|k|v projection, qk_norm = (norm_q weight,
+    norm_k weight), freqs fp32 [rows, head_dim/2, 2]; row r uses table row rope_pos0 + r.  With `scatter`
+    the head vectors go to the head owners' attention input buffers and `out` may be None."""
     _req_bf16(a, w, bias, out, residual, gate)
     chunk = None
     if a_k_chunked:
@@ -52,18 +58,37 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
             a = a.unsqueeze(0)
     if a.dim() == 2:
         a = a.unsqueeze(0)
-    if out.dim() == 2:
+    if out is not None and out.dim() == 2:
         out = out.unsqueeze(0)
     B, M, K = a.shape
     if chunk is not None:
         K = nch * kc
     N = w.shape[0]
-    if w.shape[1] != K or not w.is_contiguous() or tuple(out.shape) != (B, M, N):
-        raise ValueError(f"gemm shape mismatch: a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
+    if w.shape[1] != K or not w.is_contiguous() or (out is not None and tuple(out.shape) != (B, M, N)):
+        raise ValueError(f"gemm shape mismatch: a{tuple(a.shape)} w{tuple(w.shape)} "
+                         f"out{tuple(out.shape) if out is not None else None}")
     p = GemmProblem()
     p.a, p.lda, p.a_batch_stride = a.data_ptr(), a.stride(1), a.stride(0)
     p.w, p.bias = w.data_ptr(), _ptr(bias)
-    p.c, p.ldc, p.c_batch_stride = out.data_ptr(), out.stride(1), out.stride(0)
+    if out is not None:
+        p.c, p.ldc, p.c_batch_stride = out.data_ptr(), out.stride(1), out.stride(0)
+    elif not (epilogue == EPI_QKV_NORM_ROPE and scatter is not None):
+        raise ValueError("out is required")
+    if epilogue == EPI_QKV_NORM_ROPE:
+        if qk_norm is None or freqs is None or heads <= 0 or head_dim <= 0:
+            raise ValueError("the QKV epilogue needs qk_norm weights, the rope table, heads and head_dim")
+        wq, wk = qk_norm
+        _req_bf16(wq, wk)
+        if freqs.dtype != torch.float32 or not freqs.is_contiguous() or freqs.dim() != 3 \
+                or tuple(freqs.shape[1:]) != (head_dim // 2, 2) or freqs.shape[0] < rope_pos0 + M:
+            raise ValueError("freqs must be contiguous fp32 [>= rope_pos0 + rows, head_dim/2, 2]")
+        if N != 3 * heads * head_dim:
+            raise ValueError("the QKV epilogue needs n == 3 * heads * head_dim")
+        p.qk_norm_wq, p.qk_norm_wk, p.rope_cos_sin = wq.data_ptr(), wk.data_ptr(), freqs.data_ptr()
+        p.rope_pos0, p.heads, p.head_dim, p.qk_norm_eps = int(rope_pos0), int(heads), int(head_dim), float(eps)
+        if scatter is not None:
+            p.scatter = C.addressof(scatter)
+            p._keep = scatter          # the struct must outlive the launch call
     if epilogue == EPI_GATED_RESIDUAL:
         if residual is None or gate is None:
             raise ValueError("gated-residual epilogue needs residual and gate")

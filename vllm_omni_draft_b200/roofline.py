@@ -44,7 +44,7 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
     fl_mlp = 2.0 * S * 4 * d * d
     t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(xi, w_up[i % nw][0], b_up[0], mi, ops.EPI_BIAS_GELU_TANH),
                                         ops.gemm_problem(xt, w_up[i % nw][1], b_up[1], mt, ops.EPI_BIAS_GELU_TANH)]), reps)
-    roof = {"bound": "tensor", "kernel": "gemm_bf16_kernel<256> (MLP-up + bias + GELU-tanh, img+txt streams in one launch)",
+    roof = {"bound": "tensor", "kernel": "gemm_pair_bf16_kernel<256> (MLP-up + bias + GELU-tanh, img+txt streams in one launch, cta_group::2)",
             "achieved": fl_mlp / t / 1e12, "peak": sustained_tf, "unit": "TFLOP/s", "frac": fl_mlp / t / 1e12 / sustained_tf,
             "traffic": None, "peak_source": f"{src}: cuBLAS bf16 sustained (kernel timed in a back-to-back loop)",
             "launch_us": t * 1e6, "flops_per_launch": fl_mlp, "frac_of_burst": fl_mlp / t / 1e12 / burst_tf,
@@ -56,9 +56,14 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
     kern["gemm_mlp_down_gated_residual"] = {"us": t * 1e6, "tflops": fl_mlp / t / 1e12}
     w_qkv = [w.view(2, 4 * d, d)[:, :3 * d].contiguous() for w in w_up[:4]]
     qkv = emp(1, S, 3 * d)
-    t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(xi, w_qkv[i % 4][0], b_up[0, :3 * d], qkv[:, s_txt:], 0),
-                                        ops.gemm_problem(xt, w_qkv[i % 4][1], b_up[1, :3 * d], qkv[:, :s_txt], 0)]), reps)
-    kern["gemm_qkv"] = {"us": t * 1e6, "tflops": 2.0 * S * 3 * d * d / t / 1e12}
+    fr = rope.joint_cos_sin((16, 56, 56), 10000.0, [(1, int(s_img ** 0.5), int(s_img ** 0.5))], s_txt).to(dev)
+    nwt = r(4, Dh) + 1
+    qk = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=fr, heads=H, head_dim=Dh)
+    t = _time_graph(lambda i: ops.gemm([
+        ops.gemm_problem(xi, w_qkv[i % 4][0], b_up[0, :3 * d], qkv[:, s_txt:], qk_norm=(nwt[0], nwt[1]), rope_pos0=s_txt, **qk),
+        ops.gemm_problem(xt, w_qkv[i % 4][1], b_up[1, :3 * d], qkv[:, :s_txt], qk_norm=(nwt[2], nwt[3]), rope_pos0=0, **qk)]), reps)
+    kern["gemm_qkv_qknorm_rope"] = {"us": t * 1e6, "tflops": 2.0 * S * 3 * d * d / t / 1e12,
+                                    "note": "QK-RMSNorm + MSRoPE fused into the QKV GEMM epilogue"}
     w_o = [w.view(2, 4 * d, d)[:, :d].contiguous() for w in w_up[:4]]
     att = r(1, S, d)
     t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(att[:, s_txt:], w_o[i % 4][0], b_up[0, :d], ho, 2, xi, gate),
@@ -76,19 +81,18 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
     by = 4.0 * s_img * d
     kern["adaln_modulate_img"] = {"us": t * 1e6, "gbs": by / t / 1e9, "frac_of_hbm": by / t / 1e9 / hbm_gbs,
                                   "bytes": by, "note": "50 MB working set, L2-resident as inside a step"}
-    fr = rope.joint_cos_sin((16, 56, 56), 10000.0, [(1, int(s_img ** 0.5), int(s_img ** 0.5))], s_txt).to(dev)
-    nwt = r(4, Dh) + 1
     q2 = qkv.view(S, 3 * d)
     t = _time_graph(lambda i: ops.qknorm_rope(q2, H, Dh, S, s_txt, nwt[0], nwt[1], nwt[2], nwt[3], fr), reps)
     by = 8.0 * S * d
-    kern["qknorm_rope"] = {"us": t * 1e6, "gbs": by / t / 1e9, "frac_of_hbm": by / t / 1e9 / hbm_gbs, "bytes": by}
+    kern["qknorm_rope_standalone"] = {"us": t * 1e6, "gbs": by / t / 1e9, "frac_of_hbm": by / t / 1e9 / hbm_gbs, "bytes": by,
+                                      "note": "C-ABI entry point kept; inside the step this work runs in the QKV GEMM epilogue"}
     lat = [r(1, s_img, 64) for _ in range(4)]
     t = _time_graph(lambda i: ops.cfg_euler_step(lat[0], lat[1], lat[2], lat[3], 4.0, dt=-0.02), reps)
     by = 4.0 * s_img * 64 * 2
     kern["cfg_euler_step"] = {"us": t * 1e6, "gbs": by / t / 1e9, "bytes": by, "note": "2.1 MB: launch-latency bound"}
-    blk = (kern["gemm_qkv"]["us"] + kern["gemm_out_proj_gated_residual"]["us"] + roof["launch_us"]
+    blk = (kern["gemm_qkv_qknorm_rope"]["us"] + kern["gemm_out_proj_gated_residual"]["us"] + roof["launch_us"]
            + kern["gemm_mlp_down_gated_residual"]["us"] + kern["attention_fwd"]["us"]
-           + 2 * kern["adaln_modulate_img"]["us"] * (S / s_img) + kern["qknorm_rope"]["us"])
+           + 2 * kern["adaln_modulate_img"]["us"] * (S / s_img))
     kern["block_sum_us"] = blk
     kern["step_from_kernel_sum_ms"] = blk * 120 / 1e3
     return {"roofline": roof, "kernels": kern}

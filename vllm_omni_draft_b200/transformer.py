@@ -9,9 +9,9 @@ src/qwen_image_gen/model.py:122-134 of the reference; the class it replaces is d
 PyTorch is the host layer only: parameter storage, workspace allocation, stream.  Every FLOP of the
 forward runs in libqi_b200.so (hand-written sm_100a kernels).  Per MMDiT block the launch sequence is
 
-    K1 x2  adaLN-LN-modulate (img, txt)            -> xn
-    K3     QKV GEMM, img+txt in one persistent launch -> joint qkv [B, S, 3d] (text rows first)
-    K2     QK-RMSNorm + MSRoPE in place on qkv
+    K1     adaLN-LN-modulate (img + txt in one launch) -> xn
+    K3+K2  QKV GEMM, img+txt in one persistent launch, QK-RMSNorm + MSRoPE applied per head vector in
+           the epilogue -> joint qkv [B, S, 3d] (text rows first)
     K4     joint flash attention                    -> attn [B, S, d]
     K3     out-proj GEMM + gated residual (in place on h / e)
     K1 x2  adaLN-LN-modulate with mod2
@@ -25,6 +25,7 @@ step of a schedule before the loop starts (temb depends only on t).
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from types import SimpleNamespace
 from typing import Dict, List, Optional, Tuple
@@ -89,6 +90,8 @@ class B200QwenImageTransformer2DModel(nn.Module):
                                       joint_attention_dim=cfg.joint_attention_dim,
                                       patch_size=cfg.patch_size, axes_dims_rope=cfg.axes_dims_rope)
         self._attention_backend = "qi_tcgen05_flash"
+        # QK-RMSNorm + MSRoPE inside the QKV GEMM epilogue (default) or as the separate K2 launch
+        self.fuse_qknorm_rope = os.environ.get("QI_FUSE_QKNORM", "1") != "0"
 
         def P(*shape):
             return nn.Parameter(torch.empty(*shape, device=device, dtype=dtype), requires_grad=False)
@@ -357,19 +360,34 @@ class B200QwenImageTransformer2DModel(nn.Module):
             sh_t2, sc_t2, g_t2 = mod_slices(bt + 3 * d)
             ops.adaln_modulate_pair([(h2, bview(sh_i1), bview(sc_i1), xi2, s_img),
                                      (e2, bview(sh_t1), bview(sc_t1), xt2, s_txt)])
-            ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
-                      ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
+            # QKV projection with QK-RMSNorm + MSRoPE applied per head vector in the GEMM epilogue (K2 fused
+            # into K3); text rows first in the joint sequence, so the img stream's row 0 sits at table row s_txt
             nw = self.qk_norm_w[l]
+            sc = peer.dst_qkv if peer is not None else None
+            if self.fuse_qknorm_rope:
+                qk = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=freqs, heads=H, head_dim=Dh)
+                ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0],
+                                           None if sc is not None else qkv_img, qk_norm=(nw[0], nw[1]),
+                                           rope_pos0=s_txt, scatter=sc, **qk),
+                          ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1],
+                                           None if sc is not None else qkv_txt, qk_norm=(nw[2], nw[3]),
+                                           rope_pos0=0, scatter=sc, **qk)])
+            else:   # separate K2 launch (QI_FUSE_QKNORM=0): same arithmetic, one more pass over qkv
+                ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
+                          ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
+                if sc is not None:
+                    ops.qknorm_rope_scatter(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3],
+                                            freqs, sc)
+                else:
+                    ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
             if sp is None:
-                ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
                 ops.attention(q, k, v, attn4)
                 ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
                           ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
             elif peer is not None:
-                # Fused exchange over peer memory: K2 stores each head vector into the head owner's HBM,
-                # attention stores each output row into the token owner's HBM; two flag barriers.
-                ops.qknorm_rope_scatter(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3],
-                                        freqs, peer.dst_qkv)
+                # Fused exchange over peer memory: the QKV GEMM's epilogue has stored each head vector into
+                # the head owner's HBM, attention stores each output row into the token owner's HBM; two
+                # flag barriers.
                 peer.barrier()
                 full = peer.recv                       # [B, S_total, 3, H/P, Dh]
                 ops.attention_scatter(full[:, :, 0], full[:, :, 1], full[:, :, 2], peer.dst_o, peer.o_ld,
@@ -382,7 +400,6 @@ class B200QwenImageTransformer2DModel(nn.Module):
                                            bview(g_t1), a_k_chunked=True)])
             else:
                 # NCCL head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
-                ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
                 full = sp.scatter_heads(ws.qkv.view(S, 3 * d), H, Dh, ws.a2a_send, ws.a2a_recv)
                 ops.attention(full[:, 0].unsqueeze(0), full[:, 1].unsqueeze(0), full[:, 2].unsqueeze(0),
                               ws.o_full.unsqueeze(0))
