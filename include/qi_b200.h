@@ -103,6 +103,11 @@ int qi_gemm_set_tile_n(int bn);
 /* CTA-pair (tcgen05 cta_group::2, 256-row tiles on a 2-CTA cluster) vs single-CTA tiles:
  * -1 = automatic, 0 = never, 1 = always. */
 int qi_gemm_set_cta_pair(int mode);
+/* Measured schedule for problems of exactly these dims (m, batch, n, k, epilogue of each problem): later
+ * qi_gemm_bf16 calls with matching dims use (pair, bn) instead of the wave-count heuristic.  The host
+ * layer's autotuner (ops.tune_gemm) times every candidate once per new shape, before graph capture. */
+int qi_gemm_set_schedule(const qi_gemm_problem_t* problems /* host */, int num_problems, int pair, int bn);
+int qi_gemm_clear_schedules(void);
 
 /* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
  * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).

@@ -201,7 +201,7 @@ def test_attention_softmax_variants(cuda_device, variant):
     assert err < 6e-3, f"variant={variant} rel_l2={err}"
 
 
-@pytest.mark.parametrize("bn", [128, 192, 256])
+@pytest.mark.parametrize("bn", [128, 160, 192, 224, 256])
 def test_gemm_tile_widths(cuda_device, bn):
     """Every tile width of the persistent GEMM (auto-selected by wave count in production) is exact."""
     ops = _ops()
@@ -385,7 +385,7 @@ def test_peer_barrier_single_rank(cuda_device):
     assert state.tolist() == [3, 0] and int(sig[0]) == 3
 
 
-@pytest.mark.parametrize("bn", [128, 192, 256])
+@pytest.mark.parametrize("bn", [128, 160, 192, 224, 256])
 def test_gemm_cta_pair(cuda_device, bn):
     """tcgen05 cta_group::2 kernel (256 x BN tile per 2-CTA cluster): ragged M, batch, both fused
     epilogues, two problems in one launch and the K-chunked A operand."""

@@ -28,8 +28,14 @@ for name, (N, K, epi) in shapes.items():
     ws = [w.view(-1)[:2 * N * K].view(2, N, K) for w in W]
     fl = 2.0 * batch * (s_img + s_txt) * N * K
     only = sys.argv[3] if len(sys.argv) > 3 else ""
+    ops.gemm_set_cta_pair(-1)
+    ops.gemm_set_tile_n(0)
+    fn0 = lambda i: ops.gemm([ops.gemm_problem(xi, ws[i % nw][0], bias[0, :N], oi, epi, ri, gate),
+                              ops.gemm_problem(xt, ws[i % nw][1], bias[1, :N], ot, epi, rt, gate)])
+    t = _time_graph(fn0, max(8, int(0.05 / _time_graph(fn0, 8))))
+    print(f"sp={sp} B={batch} {name:5s} AUTO           : {t * 1e6:8.1f} us  {fl / t / 1e12:7.1f} TF/s", flush=True)
     for pair in (0, 1):
-        for bn in (256, 192, 128):
+        for bn in (256, 224, 192, 160, 128):
             if only == "pair256" and not (pair == 1 and bn == 256):
                 continue
             ops.gemm_set_cta_pair(pair)
@@ -37,7 +43,7 @@ for name, (N, K, epi) in shapes.items():
             fn = lambda i: ops.gemm([ops.gemm_problem(xi, ws[i % nw][0], bias[0, :N], oi, epi, ri, gate),
                                      ops.gemm_problem(xt, ws[i % nw][1], bias[1, :N], ot, epi, rt, gate)])
             t_one = _time_graph(fn, 8)
-            reps = max(8, int(0.12 / t_one))
+            reps = max(8, int(0.05 / t_one))
             t = _time_graph(fn, reps)
             print(f"sp={sp} B={batch} {name:5s} pair={pair} bn={bn:3d}: {t * 1e6:8.1f} us  {fl / t / 1e12:7.1f} TF/s (burst {fl / t_one / 1e12:7.1f})", flush=True)
 ops.gemm_set_cta_pair(-1)

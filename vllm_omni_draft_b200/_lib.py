@@ -55,6 +55,8 @@ _SIGNATURES = {
     "qi_gemm_set_tile_n": (_i, [_i]),
     "qi_gemm_set_cta_pair": (_i, [_i]),
     "qi_attention_set_variant": (_i, [_i]),
+    "qi_gemm_set_schedule": (_i, [_vp, _i, _i, _i]),
+    "qi_gemm_clear_schedules": (_i, []),
     "qi_attention_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f,
                                       C.POINTER(PeerScatter), _vp]),
     "qi_qknorm_rope_scatter": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f,

@@ -355,32 +355,47 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     // final: O / l -> bf16 -> global
     mbar_wait(&o_done[t], 0);
     tc_fence_after();
-    const int row = q0 + t * ATT_BM + quad * 32 + lane;
     const float inv = 1.f / l_sum;
-    __nv_bfloat16* orow;
-    if (P.n_peer > 0) {
-      int p = 0;
-      while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
-      orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
-             (size_t)head * DH;
-    } else {
-      orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
-    }
+    // O / l -> bf16, staged through this tile's (now idle) Q shared memory so that global stores are
+    // coalesced: DH/8 lanes write one row's contiguous DH*2 bytes.  One 16-byte store per lane and row
+    // (a lane owns a row in TMEM) turns into one NVLink packet per lane when the row lives on a peer.
+    constexpr int PPR = DH / 8;          // 16-byte pieces per row
+    constexpr int RPI = 32 / PPR;        // rows per store instruction
+    uint8_t* stage = smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + quad * (32 * DH * 2);
 #pragma unroll 1
     for (int c = 0; c < DH / 32; ++c) {
       uint32_t r[32];
       tmem_ld32(o_addr + c * 32, r);
       tmem_ld_wait();
-      if (row < P.seq_q) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 o;
-          o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
-          o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
-          o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
-          o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
-          *reinterpret_cast<uint4*>(orow + c * 32 + g * 8) = o;
+      for (int g = 0; g < 4; ++g) {
+        uint4 o;
+        o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+        o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+        o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+        o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+        *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + (((c * 4 + g) ^ (lane & 7)) << 4)) = o;
+      }
+    }
+    __syncwarp();
+    const int row_base = q0 + t * ATT_BM + quad * 32;
+#pragma unroll 4
+    for (int it = 0; it < 32 / RPI; ++it) {
+      const int rr = it * RPI + lane / PPR;
+      const int piece = lane % PPR;
+      const int row = row_base + rr;
+      const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * (DH * 2) + ((piece ^ (rr & 7)) << 4));
+      if (row < P.seq_q) {
+        __nv_bfloat16* orow;
+        if (P.n_peer > 0) {
+          int p = 0;
+          while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
+          orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
+                 (size_t)head * DH;
+        } else {
+          orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
         }
+        *reinterpret_cast<uint4*>(orow + piece * 8) = o;
       }
     }
   }

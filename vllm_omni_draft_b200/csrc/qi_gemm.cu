@@ -62,10 +62,13 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 192 ? 5 : 6);
-  static constexpr int ACC_STRIDE = (BN == 192) ? 256 : BN;   // TMEM columns between the two accumulators
+  static constexpr int STAGES = (BN >= 224) ? 4 : (BN >= 160 ? 5 : 6);
+  static constexpr int ACC_STRIDE = (BN > 128) ? 256 : BN;    // TMEM columns between the two accumulators
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;   // power of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // per-warp 32 x 64 B staging tile of the epilogue (coalesced residual loads / result stores)
+  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * 2048;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + EPI_STAGE_BYTES;
+  static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB shared-memory limit");
 };
 
 struct TileCoord {
@@ -94,27 +97,56 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // One epilogue warp's share of a tile: 32 accumulator rows (one per lane) x BN columns, read from
 // TMEM 32 columns at a time; `release` runs right after the last TMEM read so the MMA warp can reuse
 // the accumulator while the math and the stores of the last chunk are still in flight.
+// A lane owns a ROW of the accumulator, so direct global accesses would be one 16-byte access per
+// lane and row (32 different lines per instruction).  Every 32 x 64 B chunk is therefore staged
+// through a per-warp shared-memory tile (XOR-swizzled, conflict-free both ways): residual rows are
+// loaded and result rows stored with 4 lanes per row (64 contiguous bytes, 8 rows per instruction),
+// and the residual of chunk c+1 is prefetched into registers while chunk c is computed.
 template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row, int n0,
-                                              uint32_t taddr, int half, Release release) {
-  const bool row_ok = row < P.m;
-  __nv_bfloat16* crow =
-      reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + (size_t)row * P.ldc;
-  const __nv_bfloat16* rrow =
-      P.residual ? P.residual + (size_t)b * P.res_bs + (size_t)row * P.ld_res : nullptr;
+                                              uint32_t taddr, int half, uint8_t* stage, Release release) {
+  const int lane = threadIdx.x & 31;
+  const int row0 = row - lane;
+  __nv_bfloat16* cbase = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs;
+  const __nv_bfloat16* rbase = P.residual ? P.residual + (size_t)b * P.res_bs : nullptr;
   const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)b * P.gate_bs : nullptr;
-  constexpr int CH = BN / 32 / 2;   // 32-column chunks per warp (this warp: [half*CH, half*CH + CH))
+  const bool gated = P.epilogue == QI_EPI_GATED_RESIDUAL;
+  constexpr int NCH = BN / 32, SPLIT = (NCH + 1) / 2;   // 32-column chunks: warp half 0 takes [0, SPLIT)
+  const int c_begin = half ? SPLIT : 0;
+  const int c_end = half ? NCH : SPLIT;
+  const int piece = lane & 3;          // cooperative pattern: row it*8 + lane/4, 16-byte piece lane%4
+  const int rsub = lane >> 2;
+  uint4 rbuf[4];
+  auto load_residual = [&](int c) {
+    const int n = n0 + c * 32 + piece * 8;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int rr = row0 + it * 8 + rsub;
+      rbuf[it] = (rr < P.m && n < P.n) ? *reinterpret_cast<const uint4*>(rbase + (size_t)rr * P.ld_res + n)
+                                       : make_uint4(0, 0, 0, 0);
+    }
+  };
+  if (gated) load_residual(c_begin);
 #pragma unroll 1
-  for (int c = half * CH; c < half * CH + CH; ++c) {
+  for (int c = c_begin; c < c_end; ++c) {
+    if (gated) {
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rr = it * 8 + rsub;
+        *reinterpret_cast<uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4)) = rbuf[it];
+      }
+      __syncwarp();
+      if (c + 1 < c_end) load_residual(c + 1);
+    }
     uint32_t r[32];
     tmem_ld32(taddr + c * 32, r);
     tmem_ld_wait();
-    if (c == half * CH + CH - 1) release();
+    if (c == c_end - 1) release();
     const int n_base = n0 + c * 32;
-    if (n_base >= P.n) continue;
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       const int n = n_base + g * 8;
+      uint4* slot = reinterpret_cast<uint4*>(stage + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4));
       if (n >= P.n) break;
       float v[8];
 #pragma unroll
@@ -129,28 +161,33 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
       if (P.epilogue == QI_EPI_BIAS_GELU_TANH) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-      } else if (P.epilogue == QI_EPI_GATED_RESIDUAL) {
+      } else if (gated) {
         const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
         const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
                      g3 = unpack_bf16(gu.w);
         const float gt[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
-        float rs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (row_ok) {
-          const uint4 ru = *reinterpret_cast<const uint4*>(rrow + n);
-          const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
-                       r3 = unpack_bf16(ru.w);
-          rs[0] = r0.x; rs[1] = r0.y; rs[2] = r1.x; rs[3] = r1.y;
-          rs[4] = r2.x; rs[5] = r2.y; rs[6] = r3.x; rs[7] = r3.y;
-        }
+        const uint4 ru = *slot;          // this row's residual piece (zero outside the matrix)
+        const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
+                     r3 = unpack_bf16(ru.w);
+        const float rs[8] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y, r3.x, r3.y};
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = rs[j] + gt[j] * v[j];
       }
-      if (row_ok) {
-        const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
-                                   pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-        *reinterpret_cast<uint4*>(crow + n) = o;
+      *slot = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                         pack_bf16(v[6], v[7]));
+    }
+    __syncwarp();
+    {
+      const int n = n_base + piece * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rr = it * 8 + rsub;
+        const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
+        if (row0 + rr < P.m && n < P.n)
+          *reinterpret_cast<uint4*>(cbase + (size_t)(row0 + rr) * P.ldc + n) = o;
       }
     }
+    __syncwarp();
   }
 }
 
@@ -162,9 +199,11 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
 // over NVLink: the head<->sequence all-to-all happens tile by tile under the GEMM's main loop.
 template <int BN, int DH, typename Release>
 __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int row, int n0,
-                                                  uint32_t taddr, int half, Release release) {
+                                                  uint32_t taddr, int half, uint8_t* stage, Release release) {
   constexpr int HPT = BN / DH;   // head vectors per tile row
   const bool row_ok = row < P.m;
+  const int lane = threadIdx.x & 31;
+  const int row0 = row - lane;   // first row of this warp's 32-row slab
   const int d_model = P.heads * DH;
   const float2* fr = P.freqs + (size_t)(P.pos0 + (row_ok ? row : 0)) * (DH / 2);
   bool released = false;
@@ -174,14 +213,19 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
     if (nh >= P.n) break;
     const int j3 = nh / d_model;                 // 0 q, 1 k, 2 v
     const int h = (nh - j3 * d_model) / DH;
-    __nv_bfloat16* dst;
+    // Destination of row r's head vector: dst_base + r * dst_ld (in place in C, or the head owner's
+    // [batch, s_total, 3, heads/P, DH] attention input buffer over NVLink)
+    __nv_bfloat16* dst_base;
+    size_t dst_ld;
     if (P.sc_n > 0) {
       const int p = h / P.sc_hs;
       const int hl = h - p * P.sc_hs;
-      dst = P.sc_base[p] +
-            ((((size_t)b * P.sc_s_total + P.sc_row_offset + P.pos0 + row) * 3 + j3) * P.sc_hs + hl) * DH;
+      dst_ld = (size_t)3 * P.sc_hs * DH;
+      dst_base = P.sc_base[p] + ((size_t)b * P.sc_s_total + P.sc_row_offset + P.pos0) * dst_ld +
+                 ((size_t)j3 * P.sc_hs + hl) * DH;
     } else {
-      dst = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + (size_t)row * P.ldc + nh;
+      dst_ld = (size_t)P.ldc;
+      dst_base = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + nh;
     }
     const uint32_t th = taddr + hh * DH;
     float rstd = 0.f;
@@ -251,12 +295,23 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
             v[2 * j + 1] = a * sn[j] + bb * cs[j];
           }
         }
-        if (row_ok) {
-          const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
-                                     pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-          *reinterpret_cast<uint4*>(dst + col) = o;
-        }
+        // stage: piece g (16 B) of this lane's row, XOR-swizzled so neither side has bank conflicts
+        const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
+                                   pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+        *reinterpret_cast<uint4*>(stage + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4)) = o;
       }
+      __syncwarp();
+      // coalesced stores: 4 lanes write one row's 64 contiguous bytes, 8 rows per instruction (peer
+      // writes over NVLink need this: one 16-byte store per lane and row is a packet per lane)
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rr = it * 8 + (lane >> 2);
+        const int piece = lane & 3;
+        const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
+        if (row0 + rr < P.m)
+          *reinterpret_cast<uint4*>(dst_base + (size_t)(row0 + rr) * dst_ld + c * 32 + piece * 8) = o;
+      }
+      __syncwarp();
     }
   }
   if (!released) release();
@@ -265,18 +320,19 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
 // Epilogue dispatch for one warp's 32 rows of a tile.
 template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row, int n0, uint32_t taddr,
-                                              int half, Release release) {
+                                              int half, uint8_t* stage, Release release) {
   if (P.epilogue == QI_EPI_QKV_NORM_ROPE) {
     if constexpr (BN % 128 == 0) {
       if (P.head_dim == 128) {
-        epilogue_rows_qkv<BN, 128>(P, b, row, n0, taddr, half, release);
+        epilogue_rows_qkv<BN, 128>(P, b, row, n0, taddr, half, stage, release);
         return;
       }
     }
-    epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, release);   // host guarantees head_dim == 64 here
+    if constexpr (BN % 64 == 0)
+      epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, stage, release);   // host guarantees head_dim == 64 here
     return;
   }
-  epilogue_rows<BN>(P, b, row, n0, taddr, half, release);
+  epilogue_rows<BN>(P, b, row, n0, taddr, half, stage, release);
 }
 
 template <int BN>
@@ -386,6 +442,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (2..9)
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * 2048;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -394,7 +451,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
-      epilogue_tile<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, [&]() {
+      epilogue_tile<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, epi_stage, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -428,10 +485,12 @@ struct GemmPairCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = (BN / 2) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = STG ? STG : ((BN == 256) ? 6 : (BN == 192 ? 7 : 8));
-  static constexpr int ACC_STRIDE = (BN == 192) ? 256 : BN;
+  static constexpr int STAGES = STG ? STG : ((BN >= 224) ? 6 : (BN >= 192 ? 7 : 8));
+  static constexpr int ACC_STRIDE = (BN > 128) ? 256 : BN;
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * 2048;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + EPI_STAGE_BYTES;
+  static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB shared-memory limit");
 };
 
 template <int BN, int STG = 0>
@@ -546,6 +605,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (both CTAs)
     const int q = warp & 3;
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * 2048;
     int acc = 0;
     uint32_t acc_phase = 0;
     const uint32_t empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
@@ -556,7 +616,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
-      epilogue_tile<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, [&]() {
+      epilogue_tile<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, epi_stage, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(acc == 0 ? empty0 : empty1);
@@ -720,8 +780,50 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
 
 static int g_force_bn = 0;
 extern "C" int qi_gemm_set_tile_n(int bn) {
-  if (bn != 0 && bn != 128 && bn != 192 && bn != 256) return QI_ERR_ARG;
+  if (bn != 0 && bn != 128 && bn != 160 && bn != 192 && bn != 224 && bn != 256) return QI_ERR_ARG;
   g_force_bn = bn;
+  return QI_OK;
+}
+
+// Measured schedules: (problem dims) -> (pair, bn), filled by the host layer's autotuner
+// (ops.tune_gemm: times every candidate once per new shape before the step is captured into a graph).
+struct TunedSchedule {
+  int num, m[2], batch[2], n[2], k[2], epi[2];
+  int pair, bn;
+};
+static TunedSchedule g_tuned[64];
+static int g_num_tuned = 0;
+static bool tuned_matches(const TunedSchedule& t, const qi_gemm_problem_t* p, int num) {
+  if (t.num != num) return false;
+  for (int i = 0; i < num; ++i)
+    if (t.m[i] != p[i].m || t.batch[i] != p[i].batch || t.n[i] != p[i].n || t.k[i] != p[i].k ||
+        t.epi[i] != p[i].epilogue)
+      return false;
+  return true;
+}
+extern "C" int qi_gemm_set_schedule(const qi_gemm_problem_t* problems, int num_problems, int pair, int bn) {
+  if (!problems || num_problems < 1 || num_problems > 2 || pair < 0 || pair > 1) return QI_ERR_ARG;
+  if (bn != 128 && bn != 160 && bn != 192 && bn != 224 && bn != 256) return QI_ERR_ARG;
+  int slot = -1;
+  for (int i = 0; i < g_num_tuned; ++i)
+    if (tuned_matches(g_tuned[i], problems, num_problems)) slot = i;
+  if (slot < 0) {
+    if (g_num_tuned == 64) return QI_ERR_UNSUPPORTED;
+    slot = g_num_tuned++;
+  }
+  TunedSchedule& t = g_tuned[slot];
+  memset(&t, 0, sizeof(t));
+  t.num = num_problems;
+  for (int i = 0; i < num_problems; ++i) {
+    t.m[i] = problems[i].m; t.batch[i] = problems[i].batch; t.n[i] = problems[i].n; t.k[i] = problems[i].k;
+    t.epi[i] = problems[i].epilogue;
+  }
+  t.pair = pair;
+  t.bn = bn;
+  return QI_OK;
+}
+extern "C" int qi_gemm_clear_schedules(void) {
+  g_num_tuned = 0;
   return QI_OK;
 }
 
@@ -746,18 +848,27 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
     return e ? atoi(e) : -1;
   }();
   const int pair_mode = g_pair_mode >= 0 ? g_pair_mode : (env_pair == 0 || env_pair == 1 ? env_pair : -1);
-  int bn_multiple = 64;   // the QKV epilogue needs whole head vectors inside a tile
+  int bn_multiple = 32;   // the QKV epilogue needs whole head vectors inside a tile
   for (int i = 0; i < num_problems; ++i)
-    if (problems[i].epilogue == QI_EPI_QKV_NORM_ROPE && problems[i].head_dim == 128) bn_multiple = 128;
+    if (problems[i].epilogue == QI_EPI_QKV_NORM_ROPE && problems[i].head_dim > bn_multiple)
+      bn_multiple = problems[i].head_dim;
   int bn = g_force_bn, pair = pair_mode;
   if (bn != 0 && bn % bn_multiple != 0) return QI_ERR_UNSUPPORTED;
+  if (bn == 0 && pair < 0) {
+    for (int i = 0; i < g_num_tuned; ++i)
+      if (tuned_matches(g_tuned[i], problems, num_problems) && g_tuned[i].bn % bn_multiple == 0) {
+        bn = g_tuned[i].bn;
+        pair = g_tuned[i].pair;
+        break;
+      }
+  }
   if (bn == 0 || pair < 0) {
     double best = -1;
-    const int cand[3] = {256, 192, 128};
+    const int cand[5] = {256, 224, 192, 160, 128};
     int best_bn = 256, best_pair = 0;
     for (int pm = 0; pm < 2; ++pm) {
       if (pair_mode >= 0 && pm != pair_mode) continue;
-      for (int c = 0; c < 3; ++c) {
+      for (int c = 0; c < 5; ++c) {
         if (g_force_bn && cand[c] != g_force_bn) continue;
         if (cand[c] % bn_multiple != 0) continue;
         const int tm = pm ? 2 * BM : BM;
@@ -787,12 +898,15 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
     if (bn == 256 && env_stg == 3) return launch_gemm_pair<256, 3>(problems, num_problems, stream);
     if (bn == 256 && env_stg == 4) return launch_gemm_pair<256, 4>(problems, num_problems, stream);
     if (bn == 256 && env_stg == 5) return launch_gemm_pair<256, 5>(problems, num_problems, stream);
-    if (bn == 256 && env_stg == 7) return launch_gemm_pair<256, 7>(problems, num_problems, stream);
     if (bn == 256) return launch_gemm_pair<256>(problems, num_problems, stream);
+    if (bn == 224) return launch_gemm_pair<224>(problems, num_problems, stream);
     if (bn == 192) return launch_gemm_pair<192>(problems, num_problems, stream);
+    if (bn == 160) return launch_gemm_pair<160>(problems, num_problems, stream);
     return launch_gemm_pair<128>(problems, num_problems, stream);
   }
   if (bn == 256) return launch_gemm<256>(problems, num_problems, stream);
+  if (bn == 224) return launch_gemm<224>(problems, num_problems, stream);
   if (bn == 192) return launch_gemm<192>(problems, num_problems, stream);
+  if (bn == 160) return launch_gemm<160>(problems, num_problems, stream);
   return launch_gemm<128>(problems, num_problems, stream);
 }

@@ -113,6 +113,61 @@ def gemm(problems: Sequence[GemmProblem]) -> None:
     launch_count += 1
 
 
+_GEMM_CANDIDATES = [(pair, bn) for pair in (1, 0) for bn in (256, 224, 192, 160, 128)]
+_tuned_keys = set()
+
+
+def _gemm_key(problems: Sequence[GemmProblem]):
+    return tuple((p.m, p.batch, p.n, p.k, p.epilogue) for p in problems)
+
+
+def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 3) -> Optional[Tuple[int, int]]:
+    """Autotune the schedule (single-CTA / CTA-pair, tile width) for problems of these dims: every
+    candidate is timed with CUDA events (best of `groups` groups of `launches` back-to-back launches) and
+    the fastest is registered with the library (qi_gemm_set_schedule).  The problems' outputs are
+    overwritten repeatedly, so pass scratch / per-forward temporaries.  Must not run under graph
+    capture.  Returns the chosen (pair, bn), or None if these dims were tuned before."""
+    key = _gemm_key(problems)
+    if key in _tuned_keys:
+        return None
+    n = len(problems)
+    arr = (GemmProblem * n)(*problems)
+    lib = _lib.lib()
+    best, best_t = None, None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    try:
+        for pair, bn in _GEMM_CANDIDATES:
+            check(lib.qi_gemm_set_cta_pair(pair), "qi_gemm_set_cta_pair")
+            check(lib.qi_gemm_set_tile_n(bn), "qi_gemm_set_tile_n")
+            if lib.qi_gemm_bf16(arr, n, _stream()) != 0:      # candidate not valid for this epilogue / shape
+                continue
+            lib.qi_gemm_bf16(arr, n, _stream())
+            t = None
+            for _ in range(groups):
+                e0.record()
+                for _ in range(launches):
+                    lib.qi_gemm_bf16(arr, n, _stream())
+                e1.record()
+                e1.synchronize()
+                dt = e0.elapsed_time(e1)
+                t = dt if t is None else min(t, dt)
+            if best_t is None or t < best_t:
+                best, best_t = (pair, bn), t
+    finally:
+        lib.qi_gemm_set_cta_pair(-1)
+        lib.qi_gemm_set_tile_n(0)
+    if best is None:
+        raise RuntimeError("tune_gemm: no valid schedule for these problems")
+    check(lib.qi_gemm_set_schedule(arr, n, best[0], best[1]), "qi_gemm_set_schedule")
+    _tuned_keys.add(key)
+    return best
+
+
+def clear_gemm_schedules() -> None:
+    _tuned_keys.clear()
+    check(_lib.lib().qi_gemm_clear_schedules(), "qi_gemm_clear_schedules")
+
+
 def linear(a, w, bias, out=None, epilogue=EPI_BIAS, residual=None, gate=None) -> torch.Tensor:
     if out is None:
         out = torch.empty(*a.shape[:-1], w.shape[0], device=a.device, dtype=a.dtype)

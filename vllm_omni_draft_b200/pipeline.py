@@ -106,6 +106,8 @@ class DenoiseSession:
         self.shapes = [[(1, Hl // 2, Wl // 2)]] * B
         self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img)
         tr.prepare_schedule(self.sched.transformer_timesteps(dt))
+        # measured GEMM schedules for this forward's shapes (before any graph capture)
+        self.gemm_schedules = tr.tune_schedules(self.x2.shape[0] if self.x2 is not None else B, s_img, self.s_txt)
         self.dts = self.sched.dts.to(dev)
         self.cur = latents.contiguous().clone()
         self.nxt = torch.empty_like(self.cur)

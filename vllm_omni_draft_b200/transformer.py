@@ -225,6 +225,54 @@ class B200QwenImageTransformer2DModel(nn.Module):
         self._mod_table = None
         return self
 
+    # ------------------------------------------------------------------ GEMM schedule autotuning
+    @torch.no_grad()
+    def tune_schedules(self, B: int, s_img: int, s_txt: int) -> dict:
+        """Time every GEMM schedule (single-CTA / CTA-pair x tile width) for the four block GEMMs at this
+        forward's shapes and register the fastest with the library (ops.tune_gemm).  Uses the forward's
+        own workspace as scratch (every buffer is rewritten by the next forward); call before the step is
+        captured into a CUDA graph.  Tile quantisation over 148 SMs makes the best schedule shape
+        dependent (sequence-parallel shards especially), which a static heuristic only approximates."""
+        if os.environ.get("QI_GEMM_TUNE", "1") == "0":
+            return {}
+        cfg, dev, dt = self.cfg, self.device, self.dtype
+        d, H, Dh = cfg.inner_dim, cfg.num_attention_heads, cfg.attention_head_dim
+        key = (B, s_img, s_txt)
+        ws = self._ws.get(key)
+        if ws is None:
+            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
+        for t in (ws.h, ws.e, ws.xn_img, ws.xn_txt, ws.attn, ws.mlp_img, ws.mlp_txt):
+            t.zero_()
+        S = s_img + s_txt
+        freqs = torch.zeros(S, Dh // 2, 2, device=dev, dtype=torch.float32)
+        gate = torch.zeros(B, d, device=dev, dtype=dt)
+        nw = self.qk_norm_w[0]
+        G = ops.EPI_GATED_RESIDUAL
+        qkv_img, qkv_txt = ws.qkv[:, s_txt:], ws.qkv[:, :s_txt]
+        att_img, att_txt = ws.attn[:, s_txt:], ws.attn[:, :s_txt]
+        chosen = {}
+        if self.fuse_qknorm_rope:
+            qk = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=freqs, heads=H, head_dim=Dh)
+            probs = [ops.gemm_problem(ws.xn_img, self.qkv_w[0, 0], self.qkv_b[0, 0], qkv_img, qk_norm=(nw[0], nw[1]),
+                                      rope_pos0=s_txt, **qk),
+                     ops.gemm_problem(ws.xn_txt, self.qkv_w[0, 1], self.qkv_b[0, 1], qkv_txt, qk_norm=(nw[2], nw[3]),
+                                      rope_pos0=0, **qk)]
+        else:
+            probs = [ops.gemm_problem(ws.xn_img, self.qkv_w[0, 0], self.qkv_b[0, 0], qkv_img),
+                     ops.gemm_problem(ws.xn_txt, self.qkv_w[0, 1], self.qkv_b[0, 1], qkv_txt)]
+        chosen["qkv"] = ops.tune_gemm(probs)
+        chosen["out"] = ops.tune_gemm([
+            ops.gemm_problem(att_img, self.out_w[0, 0], self.out_b[0, 0], ws.h, G, ws.h, gate),
+            ops.gemm_problem(att_txt, self.out_w[0, 1], self.out_b[0, 1], ws.e, G, ws.e, gate)])
+        chosen["mlp_up"] = ops.tune_gemm([
+            ops.gemm_problem(ws.xn_img, self.mlp_up_w[0, 0], self.mlp_up_b[0, 0], ws.mlp_img, ops.EPI_BIAS_GELU_TANH),
+            ops.gemm_problem(ws.xn_txt, self.mlp_up_w[0, 1], self.mlp_up_b[0, 1], ws.mlp_txt, ops.EPI_BIAS_GELU_TANH)])
+        chosen["mlp_down"] = ops.tune_gemm([
+            ops.gemm_problem(ws.mlp_img, self.mlp_down_w[0, 0], self.mlp_down_b[0, 0], ws.h, G, ws.h, gate),
+            ops.gemm_problem(ws.mlp_txt, self.mlp_down_w[0, 1], self.mlp_down_b[0, 1], ws.e, G, ws.e, gate)])
+        torch.cuda.synchronize(dev)
+        return chosen
+
     # ------------------------------------------------------------------ modulation
     def _time_embed(self, t32: torch.Tensor, ws_sinus, ws_t1, ws_temb) -> torch.Tensor:
         ops.timestep_sinusoid(t32, ws_sinus)
