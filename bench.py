@@ -264,6 +264,12 @@ def main():
     torch.cuda.empty_cache()
     from vllm_omni_draft_b200.roofline import kernel_rooflines
     line.update(kernel_rooflines(burst, sustained, hbm, src))
+    # DRAM traffic of the dominant kernel per launch, from the committed `ncu --set full` capture of the same
+    # launch (profiles/r01c_ncu_full_summary.csv rows 1-3: dram__bytes_read.sum + dram__bytes_write.sum);
+    # algorithmic bytes = A 28.3 MB + W(img+txt) 151.0 MB + C 113.2 MB = 292.5 MB
+    line["roofline"]["traffic"] = 287.6e6
+    line["roofline"]["traffic_unit"] = "bytes per launch (ncu, profiles/r01c_ncu_full_summary.csv)"
+    line["roofline"]["algorithmic_bytes"] = 2.0 * (s_img + s_txt) * D + 2 * 2.0 * 4 * D * D + 2.0 * (s_img + s_txt) * 4 * D
     if world == 1 and not args.no_cpu_baseline and args.workload == "cfg2":
         times, threads = cpu_reference_sample(s_img, s_txt, 2, repeats=2)
         t_sample = min(times)

@@ -7,5 +7,5 @@ timeout -s KILL 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench1.lo
 timeout -s KILL 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2>&1; echo "bench ref rc=$?"; tail -1 gpurun_out/bench_ref.log | cut -c1-600
 timeout -s KILL 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_step.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_step.log 2>&1; echo "ncu list rc=$?"; wc -l gpurun_out/launches_step.csv
 timeout -s KILL 300 python tools/prof_kernels.py all > gpurun_out/plain_prof.log 2>&1 &&
-timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k regex:"gemm_pair|gemm_bf16|attention_fwd|norm_rows|qknorm|cfg_euler" -c 24 -o gpurun_out/prof_r1b python tools/prof_kernels.py all > gpurun_out/ncu_prof.log 2>&1; echo "ncu full rc=$?"
+timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k regex:"gemm_pair|gemm_bf16|attention_fwd|norm_rows|qknorm|cfg_euler" -c 30 -o gpurun_out/prof_r1c python tools/prof_kernels.py all > gpurun_out/ncu_prof.log 2>&1; echo "ncu full rc=$?"
 ls -la gpurun_out | head -30

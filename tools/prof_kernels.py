@@ -27,6 +27,17 @@ if which in ("all", "gemm"):
     for i in range(reps):
         ops.gemm([ops.gemm_problem(mi, w_dn[i][0], b_up[0, :d], xi, ops.EPI_GATED_RESIDUAL, xi, gate),
                   ops.gemm_problem(mt, w_dn[i][1], b_up[1, :d], xt, ops.EPI_GATED_RESIDUAL, xt, gate)])
+if which in ("all", "gemm", "qkv"):
+    from vllm_omni_draft_b200 import rope as _rope
+    w_qkv = [r(2, 3 * d, d, sc=0.02) for _ in range(reps)]
+    b_qkv = r(2, 3 * d)
+    fr_ = _rope.joint_cos_sin((16, 56, 56), 10000.0, [(1, 64, 64)], s_txt).to(dev)
+    nw_ = r(4, Dh) + 1
+    qkv_o = torch.empty(1, S, 3 * d, device=dev, dtype=torch.bfloat16)
+    kw = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=fr_, heads=H, head_dim=Dh)
+    for i in range(reps):
+        ops.gemm([ops.gemm_problem(xi, w_qkv[i][0], b_qkv[0], qkv_o[:, s_txt:], qk_norm=(nw_[0], nw_[1]), rope_pos0=s_txt, **kw),
+                  ops.gemm_problem(xt, w_qkv[i][1], b_qkv[1], qkv_o[:, :s_txt], qk_norm=(nw_[2], nw_[3]), rope_pos0=0, **kw)])
 if which in ("all", "attn"):
     qkv = r(1, S, 3 * d)
     q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
