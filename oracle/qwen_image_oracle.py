@@ -411,6 +411,63 @@ def denoise_loop(sd, cfg: OracleConfig, latents, prompt_embeds, prompt_mask,
     return (latents, trace) if return_all else latents
 
 
+def edit_denoise_loop(sd, cfg: OracleConfig, latents, image_latents, prompt_embeds, prompt_mask,
+                      negative_prompt_embeds=None, negative_prompt_mask=None,
+                      num_inference_steps: int = 50, true_cfg_scale: float = 4.0,
+                      img_shapes=None, return_all: bool = False):
+    """QwenImageEditPipeline.__call__ denoising loop (what the reference's
+    test_performance.py:229-307 / test_pipeline.py:123-124 actually drive): the packed reference-image
+    latents ride behind the noise tokens on the sequence axis, ``img_shapes = [[(1,h,w), (1,h',w')]]``
+    (RoPE frame index = image index), and only the first S_noise rows of the prediction are kept.
+    mu / the sigma schedule use the noise sequence length."""
+    B, S_noise, _ = latents.shape
+    timesteps, sigmas = flowmatch_sigmas(num_inference_steps, S_noise)
+    do_cfg = true_cfg_scale > 1 and negative_prompt_embeds is not None
+    txt_lens = prompt_mask.sum(dim=1).tolist()
+    neg_lens = negative_prompt_mask.sum(dim=1).tolist() if do_cfg else None
+    trace = []
+    for i, t in enumerate(timesteps):
+        timestep = t.expand(B).to(latents.dtype)
+        x = torch.cat([latents, image_latents], dim=1)
+        c = transformer_forward(sd, cfg, x, prompt_embeds, prompt_mask, timestep / 1000,
+                                img_shapes=img_shapes, txt_seq_lens=txt_lens)[:, :S_noise]
+        if do_cfg:
+            u = transformer_forward(sd, cfg, x, negative_prompt_embeds, negative_prompt_mask,
+                                    timestep / 1000, img_shapes=img_shapes, txt_seq_lens=neg_lens)[:, :S_noise]
+            v = true_cfg_combine(c, u, true_cfg_scale)
+        else:
+            v = c
+        latents = scheduler_step(v, latents, sigmas[i], sigmas[i + 1])
+        if return_all:
+            trace.append(latents.clone())
+    return (latents, trace) if return_all else latents
+
+
+# --------------------------------------------------------------------------------------
+# The reference's OWN placeholder loops (these lines are in /root/reference, not upstream)
+# --------------------------------------------------------------------------------------
+def reference_adapter_loop(sd, cfg: OracleConfig, latents, prompt_embeds, prompt_mask, num_steps: int,
+                           img_shapes=None, txt_seq_lens=None, step_size: float = 1.0):
+    """src/qwen_image/runner_adapter.py:64-68, 127-141: int64 timesteps linspace(1,0,N)*1000 passed
+    straight to the transformer, ``latents - residual``.  latents [B,64,H,W] (or 5-D)."""
+    timesteps = (torch.linspace(1.0, 0.0, steps=max(int(num_steps), 1)) * 1000).to(torch.long)
+    return reference_gen_loop(sd, cfg, latents, prompt_embeds, prompt_mask, timesteps, step_size=step_size,
+                              img_shapes=img_shapes, txt_seq_lens=txt_seq_lens)
+
+
+def reference_gen_loop(sd, cfg: OracleConfig, latents, prompt_embeds, prompt_mask, timesteps,
+                       step_size: float = 0.1, img_shapes=None, txt_seq_lens=None):
+    """src/qwen_image_gen/model.py:117-135: same loop, no img_shapes / txt_seq_lens kwargs,
+    ``latents - residual * 0.1``."""
+    B = latents.shape[0]
+    for t in timesteps:
+        sample = transformer_forward(sd, cfg, latents.flatten(2).transpose(1, 2), prompt_embeds, prompt_mask,
+                                     t.expand(B), img_shapes=img_shapes, txt_seq_lens=txt_seq_lens)
+        residual = sample.transpose(1, 2).unflatten(2, latents.shape[2:])
+        latents = latents - residual * step_size if step_size != 1.0 else latents - residual
+    return latents
+
+
 # --------------------------------------------------------------------------------------
 # Synthetic inputs (SURVEY §8d)
 # --------------------------------------------------------------------------------------

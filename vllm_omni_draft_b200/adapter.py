@@ -144,5 +144,10 @@ class QwenImageRunnerAdapter:
         if inputs.output_mode == Mode.LATENTS or not decode_pixels:
             return latents
         if self.vae is None:
-            raise RuntimeError("output_mode requests pixels but no VAE was provided (SURVEY §8 row f1)")
-        return self.vae.decode(latents)
+            raise RuntimeError("output_mode requests pixels but no VAE was provided")
+        if schedule == "flowmatch":
+            # the real pipeline de-normalises with the VAE's channel statistics before decoding
+            lat5 = latents if latents.dim() == 5 else latents.unsqueeze(2)
+            return self._pipe.decode_latents(pack_latents(lat5[:, :, 0]), lat5.shape[-2], lat5.shape[-1])
+        pixels = self.vae.decode(latents)        # literal: runner_adapter.py:149-160
+        return getattr(pixels, "sample", pixels)

@@ -57,6 +57,21 @@ def calculate_shift(image_seq_len, base_seq_len=256, max_seq_len=8192, base_shif
     return image_seq_len * m + b
 
 
+def postprocess_image(image: torch.Tensor, output_type: str = "pil"):
+    """VaeImageProcessor.postprocess: [-1, 1] -> [0, 1]; 'pt' tensor [B,3,H,W], 'np' float32 [B,H,W,3],
+    'pil' list of PIL images."""
+    if output_type not in ("pt", "np", "pil"):
+        raise ValueError(f"unknown output_type {output_type!r}")
+    image = (image / 2 + 0.5).clamp(0, 1)
+    if output_type == "pt":
+        return image
+    arr = image.cpu().permute(0, 2, 3, 1).float().numpy()
+    if output_type == "np":
+        return arr
+    from PIL import Image
+    return [Image.fromarray((a * 255).round().astype("uint8")) for a in arr]
+
+
 class FlowMatchEulerSchedule:
     """FlowMatchEulerDiscreteScheduler.set_timesteps with the Qwen-Image scheduler config
     (dynamic exponential shift, terminal stretch to 0.02); the step itself is the K5 kernel."""
@@ -87,7 +102,11 @@ class DenoiseSession:
 
     def __init__(self, pipe: "B200QwenImagePipeline", cond: torch.Tensor, uncond: Optional[torch.Tensor],
                  latents: torch.Tensor, Hl: int, Wl: int, num_inference_steps: int, true_cfg_scale: float,
-                 use_cuda_graph: bool = False, image_seq_len: Optional[int] = None, batched_cfg: bool = True):
+                 use_cuda_graph: bool = False, image_seq_len: Optional[int] = None, batched_cfg: bool = True,
+                 ref_tokens: Optional[torch.Tensor] = None, ref_hw: Optional[Tuple[int, int]] = None):
+        """ref_tokens [B, S_ref, 64] + ref_hw (token grid of the reference image): edit mode.
+        The reference-image tokens sit behind the noise tokens in one resident input buffer, written once;
+        each step only refreshes the first S_noise rows."""
         tr = pipe.transformer
         dev, dt = tr.device, tr.dtype
         self.pipe, self.tr = pipe, tr
@@ -98,16 +117,27 @@ class DenoiseSession:
         # the SMs once per step instead of twice and the step is 605 launches instead of 1209.  cond /
         # uncond stay addressable as the two halves of the stacked prompt buffer.
         self.enc2 = self.x2 = None
+        s_ref = 0 if ref_tokens is None else ref_tokens.shape[1]
+        nb = B
         if uncond is not None and batched_cfg:
             self.enc2 = torch.cat([cond, uncond], dim=0).contiguous()
             cond, uncond = self.enc2[:B], self.enc2[B:]
-            self.x2 = torch.empty(2 * B, s_img, latents.shape[-1], device=dev, dtype=dt)
+            nb = 2 * B
+        if nb != B or s_ref:
+            self.x2 = torch.empty(nb, s_img + s_ref, latents.shape[-1], device=dev, dtype=dt)
         self.cond, self.uncond = cond, uncond
-        self.shapes = [[(1, Hl // 2, Wl // 2)]] * B
+        shapes = [(1, Hl // 2, Wl // 2)]
+        if s_ref:
+            if ref_hw is None or ref_hw[0] * ref_hw[1] != s_ref or ref_tokens.shape[0] != B:
+                raise ValueError("reference-image tokens do not match their (h, w) token grid / the batch")
+            shapes.append((1, int(ref_hw[0]), int(ref_hw[1])))
+            for j in range(nb // B):
+                self.x2[j * B:(j + 1) * B, s_img:].copy_(ref_tokens)
+        self.shapes = [shapes] * B
         self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img)
         tr.prepare_schedule(self.sched.transformer_timesteps(dt))
         # measured GEMM schedules for this forward's shapes (before any graph capture)
-        self.gemm_schedules = tr.tune_schedules(self.x2.shape[0] if self.x2 is not None else B, s_img, self.s_txt)
+        self.gemm_schedules = tr.tune_schedules(nb, s_img + s_ref, self.s_txt)
         self.dts = self.sched.dts.to(dev)
         self.cur = latents.contiguous().clone()
         self.nxt = torch.empty_like(self.cur)
@@ -176,23 +206,42 @@ class B200QwenImagePipeline:
     def device(self):
         return self.transformer.device
 
+    # -------------------------------------------------------------- VAE decode (row f1)
+    def decode_latents(self, packed: torch.Tensor, Hl: int, Wl: int) -> torch.Tensor:
+        """Upstream's tail of __call__: unpack, ``latents / (1/std) + mean`` with the VAE's own channel
+        statistics, ``vae.decode(...)[0][:, :, 0]`` -> image [B, 3, 8*Hl, 8*Wl] in [-1, 1]."""
+        vae = self.vae
+        lat = unpack_latents(packed, Hl, Wl).to(vae.dtype)
+        zc = vae.config
+        mean = torch.tensor(list(zc.latents_mean), device=lat.device, dtype=lat.dtype).view(1, zc.z_dim, 1, 1, 1)
+        inv_std = 1.0 / torch.tensor(list(zc.latents_std), device=lat.device, dtype=lat.dtype).view(1, zc.z_dim, 1, 1, 1)
+        lat = lat / inv_std + mean
+        return vae.decode(lat, return_dict=False)[0][:, :, 0]
+
     # -------------------------------------------------------------- one denoising step (device)
     def _predict(self, latents, cond, uncond, kw, enc2=None, x2=None):
-        """(cond prediction, uncond prediction or None).  With stacked buffers the two branches are one
-        forward of batch 2B; otherwise two forwards."""
+        """(cond prediction, uncond prediction or None).  `x2` is the resident transformer input buffer
+        [B or 2B, S_noise + S_ref, 64]: with stacked prompts (`enc2`) the two CFG branches are one forward of
+        batch 2B; in edit mode the reference-image rows behind the first S_noise rows are already in place
+        and only `noise_pred[:, :S_noise]` is projected."""
         tr = self.transformer
+        B, n = latents.shape[:2]
+        x = latents
+        if x2 is not None:
+            for j in range(x2.shape[0] // B):
+                x2[j * B:(j + 1) * B, :n].copy_(latents)
+            x = x2[:B]
+            if x2.shape[1] != n:
+                kw = dict(kw, _out_rows=n)
         if uncond is None:
-            return tr(hidden_states=latents, encoder_hidden_states=cond, **kw)[0], None
+            return tr(hidden_states=x, encoder_hidden_states=cond, **kw)[0], None
         if enc2 is not None:
-            B = latents.shape[0]
-            x2[:B].copy_(latents)
-            x2[B:].copy_(latents)
             if kw.get("img_shapes") is not None:
                 kw = dict(kw, img_shapes=list(kw["img_shapes"]) * 2)
             out = tr(hidden_states=x2, encoder_hidden_states=enc2, **kw)[0]
             return out[:B], out[B:]
-        c = tr(hidden_states=latents, encoder_hidden_states=cond, **kw)[0]
-        u = tr(hidden_states=latents, encoder_hidden_states=uncond, **kw)[0]
+        c = tr(hidden_states=x, encoder_hidden_states=cond, **kw)[0]
+        u = tr(hidden_states=x, encoder_hidden_states=uncond, **kw)[0]
         return c, u
 
     def _step(self, latents, out_latents, cond, uncond, shapes, s_txt, i, dt_dev, scale, mod=None,
@@ -214,8 +263,16 @@ class B200QwenImagePipeline:
                  negative_prompt_embeds: Optional[torch.Tensor] = None,
                  negative_prompt_embeds_mask: Optional[torch.Tensor] = None,
                  output_type: str = "latent", return_dict: bool = True, record_steps: bool = False):
+        # Edit mode (reference test_performance.py:229-307): `image` must already be VAE
+        # latents [B,16,Hl',Wl'] / [B,16,1,Hl',Wl'] — upstream's pipeline takes that branch when
+        # image.size(1) == latent_channels; pixel images need the VAE *encoder*, which is outside the path.
+        ref_tokens = ref_hw = None
         if image is not None:
-            raise NotImplementedError("edit mode (reference-image latents) is SURVEY §8 row f2, not built yet")
+            if not (isinstance(image, torch.Tensor) and image.dim() in (4, 5) and image.shape[1] == 16):
+                raise NotImplementedError("edit mode takes the reference image as VAE latents [B,16,(1,)Hl,Wl]; "
+                                          "encoding pixels needs the VAE encoder (outside the hot path)")
+            ref_tokens = pack_latents(image)
+            ref_hw = (image.shape[-2] // 2, image.shape[-1] // 2)
         if prompt_embeds is None:
             if prompt is None:
                 raise ValueError("Provide either `prompt` or `prompt_embeds`")
@@ -252,8 +309,15 @@ class B200QwenImagePipeline:
         s_img = latents.shape[1]
         if s_img != (Hl // 2) * (Wl // 2):
             raise ValueError("latents do not match height/width")
+        if ref_tokens is not None:
+            if ref_tokens.shape[0] != B:
+                if B % ref_tokens.shape[0] != 0:
+                    raise ValueError("Cannot duplicate `image` to the effective batch size")
+                ref_tokens = ref_tokens.repeat_interleave(B // ref_tokens.shape[0], dim=0)
+            ref_tokens = ref_tokens.to(dev, dt)
         sess = DenoiseSession(self, cond, uncond, latents.to(dev, dt), Hl, Wl, num_inference_steps,
-                              true_cfg_scale, use_cuda_graph=self.use_cuda_graph, batched_cfg=self.batched_cfg)
+                              true_cfg_scale, use_cuda_graph=self.use_cuda_graph, batched_cfg=self.batched_cfg,
+                              ref_tokens=ref_tokens, ref_hw=ref_hw)
         self.last_step_latents = []
         for i in range(num_inference_steps):
             sess.step(i)
@@ -269,8 +333,9 @@ class B200QwenImagePipeline:
         else:
             if self.vae is None:
                 raise NotImplementedError(
-                    "pixel output needs the VAE decoder (SURVEY §8 row f1); use output_type='latent'")
-            images = self.vae.decode(unpack_latents(final, Hl, Wl))
+                    "pixel output needs a VAE decoder (vllm_omni_draft_b200.vae.B200QwenImageVAEDecoder or a "
+                    "diffusers AutoencoderKLQwenImage); use output_type='latent'")
+            images = postprocess_image(self.decode_latents(final, Hl, Wl), output_type)
         if not return_dict:
             return (images,)
         return QwenImagePipelineOutput(images=images)

@@ -317,7 +317,11 @@ class B200QwenImageTransformer2DModel(nn.Module):
                 encoder_hidden_states_mask: torch.Tensor = None, timestep: torch.Tensor = None,
                 img_shapes=None, txt_seq_lens=None, guidance: torch.Tensor = None,
                 attention_kwargs=None, controlnet_block_samples=None, return_dict: bool = True,
-                _step_index: Optional[int] = None, _mod_override: Optional[torch.Tensor] = None):
+                _step_index: Optional[int] = None, _mod_override: Optional[torch.Tensor] = None,
+                _out_rows: Optional[int] = None):
+        """Private kwargs (host layer of this package only): `_step_index` / `_mod_override` select a row of
+        the hoisted modulation table; `_out_rows` = n computes `proj_out` for the first n image tokens of every
+        sample only (edit mode keeps `noise_pred[:, :S_noise]`, so the reference-image rows need no projection)."""
         cfg = self.cfg
         if hidden_states.dim() != 3 or hidden_states.shape[-1] != cfg.in_channels:
             raise ValueError(f"hidden_states must be [B, S_img, {cfg.in_channels}]")
@@ -469,8 +473,11 @@ class B200QwenImageTransformer2DModel(nn.Module):
         # norm_out (AdaLayerNormContinuous: chunk order is (scale, shift)) + proj_out
         r0 = L * 12 * d
         ops.adaln_modulate(h2, bview(mod[:, r0 + d:r0 + 2 * d]), bview(mod[:, r0:r0 + d]), xi2, s_img)
-        out = torch.empty(B, s_img, cfg.proj_out_dim, device=dev, dtype=dt)
-        ops.gemm([ops.gemm_problem(ws.xn_img, self.proj_out_w, self.proj_out_b, out)])
+        n_out = s_img if _out_rows is None else int(_out_rows)
+        if not 0 < n_out <= s_img:
+            raise ValueError("_out_rows must be in (0, S_img]")
+        out = torch.empty(B, n_out, cfg.proj_out_dim, device=dev, dtype=dt)
+        ops.gemm([ops.gemm_problem(ws.xn_img[:, :n_out], self.proj_out_w, self.proj_out_b, out)])
         if not return_dict:
             return (out,)
         return Transformer2DModelOutput(sample=out)
