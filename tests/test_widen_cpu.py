@@ -180,3 +180,143 @@ def test_pipeline_edit_mode_input_validation():
         pipe(image="cat.png", prompt_embeds=emb)
     with pytest.raises(ValueError, match="even"):
         pipe(image=torch.zeros(1, 16, 5, 6), prompt_embeds=emb)
+
+
+# ------------------------------------------------------------------ f4: prompt-embedding producer
+class _Tokens(dict):
+    def __getattr__(self, k):
+        return self[k]
+
+    def to(self, device):
+        return self
+
+
+class _StubTokenizer:
+    """whitespace tokenizer with right padding; ids = word lengths."""
+
+    def __call__(self, text, max_length=None, padding=True, truncation=True, return_tensors="pt"):
+        rows = [[len(w) for w in t.replace("\n", " ").split()][:max_length] for t in text]
+        n = max(len(r) for r in rows)
+        ids = torch.tensor([r + [0] * (n - len(r)) for r in rows])
+        mask = torch.tensor([[1] * len(r) + [0] * (n - len(r)) for r in rows])
+        return _Tokens(input_ids=ids, attention_mask=mask)
+
+
+class _StubEncoder:
+    def __call__(self, input_ids=None, attention_mask=None, output_hidden_states=True, **kw):
+        pos = torch.arange(input_ids.shape[1]).view(1, -1, 1).expand(input_ids.shape[0], -1, 1)
+        h = torch.cat([input_ids.unsqueeze(-1), pos], dim=-1).float()      # [B, T, 2] = (id, position)
+        from types import SimpleNamespace
+        return SimpleNamespace(hidden_states=[h * 0, h])
+
+
+def test_prompt_embeds_template_drop_and_padding():
+    from vllm_omni_draft_b200 import prompt as P
+    template, drop = "sys a b c {} end", 4                  # 4 template words in front of the prompt
+    emb, mask = P.get_qwen_prompt_embeds(_StubEncoder(), _StubTokenizer(), ["red cat", "a very long prompt here"],
+                                         prompt_template_encode=template, prompt_template_encode_start_idx=drop)
+    # rows: prompt words + "end"; the 4 template words are gone; right-padded with zeros
+    assert emb.shape == (2, 6, 2) and mask.tolist() == [[1, 1, 1, 0, 0, 0], [1, 1, 1, 1, 1, 1]]
+    assert emb[0, :, 0].tolist() == [3, 3, 3, 0, 0, 0] and emb[0, :3, 1].tolist() == [4, 5, 6]
+    assert emb[1, :, 0].tolist() == [1, 4, 4, 6, 4, 3]
+    one, m1 = P.get_qwen_prompt_embeds(_StubEncoder(), _StubTokenizer(), "red cat", prompt_template_encode=template,
+                                       prompt_template_encode_start_idx=drop)
+    assert one.shape == (1, 3, 2) and torch.equal(one[0], emb[0, :3]) and m1.dtype == torch.long
+    assert P.PROMPT_TEMPLATE_ENCODE_START_IDX == 34 and P.PROMPT_TEMPLATE_ENCODE.count("{}") == 1
+    built = P.build_custom_inputs_text_only(text_encoder=_StubEncoder(), tokenizer=_StubTokenizer(),
+                                            image_latents=torch.zeros(1, 16, 4, 4), device="cpu", dtype=torch.float32,
+                                            prompt="red cat", prompt_template_encode=template,
+                                            prompt_template_encode_start_idx=drop, num_inference_steps=7)
+    assert built.prompt_embeds.shape == (1, 3, 2) and built.num_inference_steps == 7
+    with pytest.raises(ValueError):
+        P.build_custom_inputs_text_only(text_encoder=_StubEncoder(), tokenizer=_StubTokenizer(),
+                                        image_latents=torch.zeros(16, 4, 4), device="cpu", dtype=torch.float32,
+                                        prompt="x", prompt_template_encode=template, prompt_template_encode_start_idx=drop)
+
+
+def test_adapter_inline_prompt_errors_match_reference():
+    from types import SimpleNamespace
+    from vllm_omni_draft_b200 import prompt as P
+    with pytest.raises(ValueError, match="Qwen2.5-VL not available on worker"):
+        P.encode_prompt_inline(None, "x", "cpu")
+    w = SimpleNamespace(qwen_text_encoder=_StubEncoder(), qwen_tokenizer=_StubTokenizer(), qwen_processor=None)
+    with pytest.raises(ValueError, match="raw_prompt required"):
+        P.encode_prompt_inline(w, None, "cpu")
+    with pytest.raises(ValueError, match="processor and raw_image required"):
+        P.encode_prompt_inline(w, "x", "cpu", edit=True)
+    h, m = P.encode_prompt_inline(w, "a bb ccc", "cpu")
+    assert h.shape == (1, 3, 2) and h[0, :, 0].tolist() == [1, 2, 3] and m.tolist() == [[1, 1, 1]]
+
+
+# ------------------------------------------------------------------ f3: serving glue
+def test_serving_request_detection_and_dispatch():
+    from types import SimpleNamespace
+    from vllm_omni_draft_b200 import serving as S
+    from vllm_omni_draft_b200.adapter import QwenImageInputs
+
+    calls = []
+
+    class Model:
+        transformer = vae = object()
+
+        def _generate_image(self, q):
+            calls.append(q)
+            return torch.full((1,), 7.0)
+
+    class Base:
+        def execute_model(self, scheduler_output, *a, **k):
+            return "llm"
+
+    class W(S.QwenImageGenWorkerMixin, Base):
+        model_runner = SimpleNamespace(model=Model())
+
+    w = W()
+    w.verify_qwen_components()
+    q = QwenImageInputs(prompt_embeds=torch.zeros(1, 2, 4), prompt_embeds_mask=torch.ones(1, 2),
+                        image_latents=torch.zeros(1, 64, 2, 2), timesteps=torch.zeros(2).long())
+    plain = SimpleNamespace(scheduled_multimodal_inputs=[])
+    other = SimpleNamespace(scheduled_multimodal_inputs=[SimpleNamespace(processing_info=SimpleNamespace(extras={"x": 1}))])
+    mm = SimpleNamespace(processing_info=SimpleNamespace(extras={"qwen_inputs": q}))
+    image = SimpleNamespace(scheduled_multimodal_inputs=[SimpleNamespace(processing_info=None), mm])
+    assert not w._is_image_generation_request(plain) and not w._is_image_generation_request(other)
+    assert not w._is_image_generation_request(SimpleNamespace())          # vLLM's real SchedulerOutput: no field
+    assert w._is_image_generation_request(image)
+    assert w.execute_model(plain) == "llm" and w.execute_model(other, True) == "llm"
+    out = w.execute_model(image)
+    assert float(out) == 7.0 and calls == [q] and mm.generated_output is out
+    W.model_runner = SimpleNamespace(model=object())
+    with pytest.raises(RuntimeError, match="transformer and vae are required"):
+        W().verify_qwen_components()
+    # executor side: inject the worker class unless the user chose one
+    cfg = SimpleNamespace(parallel_config=SimpleNamespace(worker_cls=""))
+    assert S.inject_worker_cls(cfg, S.QWEN_IMAGE_WORKER_CLS).parallel_config.worker_cls == S.QWEN_IMAGE_WORKER_CLS
+    cfg = SimpleNamespace(parallel_config=SimpleNamespace(worker_cls="my.Worker"))
+    assert S.inject_worker_cls(cfg, S.QWEN_IMAGE_WORKER_CLS).parallel_config.worker_cls == "my.Worker"
+    # adapter plumbing of qwen_image/v1's worker
+    class AW(S.QwenImageWorkerMixin):
+        device = torch.device("cpu")
+        model_runner = SimpleNamespace(qwen_transformer=None, qwen_vae=None)
+    a = AW()
+    assert a.get_qwen_image_adapter() is None
+    a.model_runner = SimpleNamespace(qwen_transformer=_StubTransformer(), qwen_vae=object(),
+                                     model=SimpleNamespace(dtype=torch.bfloat16))
+    ad = a.get_qwen_image_adapter()
+    assert ad is not None and ad is a.get_qwen_image_adapter() and ad.worker is a and ad.dtype == torch.bfloat16
+
+
+def test_serving_classes_bind_onto_installed_vllm():
+    """The lazily built classes subclass the installed vLLM's V1 Worker / UniProcExecutor (import only)."""
+    pytest.importorskip("vllm")
+    from vllm_omni_draft_b200 import serving as S
+    try:
+        classes = S.make_vllm_classes()
+    except ImportError as e:
+        pytest.skip(str(e))
+    from vllm.v1.executor.abstract import UniProcExecutor
+    from vllm.v1.worker.gpu_worker import Worker
+    assert issubclass(classes["QwenImageWorker"], Worker) and issubclass(classes["QwenImageGenWorker"], Worker)
+    assert issubclass(classes["QwenImageUniProcExecutor"], UniProcExecutor)
+    assert issubclass(classes["QwenImageGenExecutor"], UniProcExecutor)
+    assert S.QwenImageGenWorker is classes["QwenImageGenWorker"]          # dotted-name resolution for worker_cls
+    mro = [c.__name__ for c in classes["QwenImageGenWorker"].__mro__]
+    assert mro.index("QwenImageGenWorkerMixin") < mro.index("Worker")     # our execute_model wins

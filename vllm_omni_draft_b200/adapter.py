@@ -103,9 +103,14 @@ class QwenImageRunnerAdapter:
     def generate(self, inputs: QwenImageCustomInputs, *, decode_pixels: bool = True,
                  schedule: str = "flowmatch", negative_prompt_embeds: Optional[torch.Tensor] = None) -> torch.Tensor:
         if inputs.prompt_embeds is None:
-            # the reference computes embeddings on the fly with Qwen2.5-VL when a worker holds one
-            # (runner_adapter.py:70-108); the text encoder is outside this path
-            raise ValueError("prompt_embeds missing and Qwen2.5-VL not available on worker")
+            # embeddings on the fly when the worker holds a Qwen2.5-VL encoder (runner_adapter.py:70-108);
+            # same ValueErrors as the reference when it does not
+            from .prompt import encode_prompt_inline
+            hidden, mask = encode_prompt_inline(
+                self.worker, getattr(inputs, "raw_prompt", None), self.device,
+                raw_image=getattr(inputs, "raw_image", None),
+                edit=inputs.task == QwenImageCustomInputs.QwenImageTask.TI2I)
+            inputs.prompt_embeds, inputs.prompt_embeds_mask = hidden, mask
         validate_custom_inputs(inputs)
         latents = inputs.image_latents.to(device=self.device, dtype=self.dtype)
         bsz = latents.shape[0]

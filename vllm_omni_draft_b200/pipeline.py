@@ -119,7 +119,9 @@ class DenoiseSession:
         self.enc2 = self.x2 = None
         s_ref = 0 if ref_tokens is None else ref_tokens.shape[1]
         nb = B
-        if uncond is not None and batched_cfg:
+        # (prompts of different token counts keep two forwards: stacking would need padding tokens, which
+        # take part in attention — upstream runs each branch at its own length)
+        if uncond is not None and batched_cfg and uncond.shape == cond.shape:
             self.enc2 = torch.cat([cond, uncond], dim=0).contiguous()
             cond, uncond = self.enc2[:B], self.enc2[B:]
             nb = 2 * B
@@ -185,10 +187,11 @@ class DenoiseSession:
 
 class B200QwenImagePipeline:
     def __init__(self, transformer: B200QwenImageTransformer2DModel, vae: Optional[torch.nn.Module] = None,
-                 text_encoder=None, vae_scale_factor: int = 8):
+                 text_encoder=None, vae_scale_factor: int = 8, tokenizer=None):
         self.transformer = transformer
         self.vae = vae
         self.text_encoder = text_encoder
+        self.tokenizer = tokenizer
         self.vae_scale_factor = vae_scale_factor
         self.use_cuda_graph = False
         self.batched_cfg = True      # true CFG as one batch-2B forward (False: two forwards per step)
@@ -241,6 +244,8 @@ class B200QwenImagePipeline:
             out = tr(hidden_states=x2, encoder_hidden_states=enc2, **kw)[0]
             return out[:B], out[B:]
         c = tr(hidden_states=x, encoder_hidden_states=cond, **kw)[0]
+        if kw.get("txt_seq_lens") is not None and uncond.shape[1] != cond.shape[1]:
+            kw = dict(kw, txt_seq_lens=[uncond.shape[1]])
         u = tr(hidden_states=x, encoder_hidden_states=uncond, **kw)[0]
         return c, u
 
@@ -276,7 +281,15 @@ class B200QwenImagePipeline:
         if prompt_embeds is None:
             if prompt is None:
                 raise ValueError("Provide either `prompt` or `prompt_embeds`")
-            raise ValueError("prompt strings need the Qwen2.5-VL encoder (out of scope); pass prompt_embeds")
+            if getattr(self, "text_encoder", None) is None or getattr(self, "tokenizer", None) is None:
+                raise ValueError("prompt strings need a Qwen2.5-VL text_encoder and tokenizer on the pipeline; "
+                                 "pass prompt_embeds otherwise")
+            from .prompt import get_qwen_prompt_embeds
+            prompt_embeds, prompt_embeds_mask = get_qwen_prompt_embeds(self.text_encoder, self.tokenizer, prompt,
+                                                                       device=self.device)
+            if negative_prompt is not None and negative_prompt_embeds is None and true_cfg_scale > 1:
+                negative_prompt_embeds, negative_prompt_embeds_mask = get_qwen_prompt_embeds(
+                    self.text_encoder, self.tokenizer, negative_prompt, device=self.device)
         if prompt_embeds.dim() != 3:
             raise ValueError("prompt_embeds must be 3D [B, T_txt, D_txt]")
         if prompt_embeds_mask is not None and prompt_embeds_mask.dim() != 2:
@@ -297,8 +310,8 @@ class B200QwenImagePipeline:
             uncond = negative_prompt_embeds.to(dev, dt)
             if num_images_per_prompt > 1:
                 uncond = uncond.repeat_interleave(num_images_per_prompt, dim=0)
-            if uncond.shape != cond.shape:
-                raise ValueError("negative_prompt_embeds must match prompt_embeds in shape")
+            if uncond.shape[0] != cond.shape[0] or uncond.shape[2] != cond.shape[2]:
+                raise ValueError("negative_prompt_embeds must match prompt_embeds in batch and width")
         if latents is None:
             g = generator
             noise = torch.randn(B, 1, 16, Hl, Wl, generator=g, device=g.device if g is not None else "cpu",
