@@ -331,15 +331,27 @@ def test_gemm_qkv_norm_rope_epilogue(cuda_device, H, Dh, axes, bn, pair):
     assert err < 2e-3 and same > 0.98, f"rel_l2={err} identical={same}"
 
 
-def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device):
+@pytest.mark.parametrize("P,H,Dh,bn,pair,s_txt_full,s_img_full", [
+    (2, 4, 64, 0, -1, 5, 71),          # schedule left to the heuristic
+    (2, 4, 64, 128, 0, 5, 71),         # destination-ordered tiles: 1 column tile per (q|k|v, owner) group
+    (2, 4, 64, 128, 1, 5, 71),
+    (3, 6, 64, 128, 1, 7, 301),
+    (4, 8, 128, 256, 1, 33, 700),      # the 8-GPU layout's schedule (pair kernel, 256-wide tiles), ragged rows
+    (4, 8, 128, 128, 1, 33, 700),      # 2 column tiles per group
+    (4, 8, 128, 128, 0, 33, 300),
+    (4, 12, 128, 256, 1, 16, 520),     # 384 columns per group: not a multiple of 256 -> plain tile order
+])
+def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device, P, H, Dh, bn, pair, s_txt_full, s_img_full):
     """The QKV epilogue's Ulysses scatter (head vectors stored straight into the head owners' attention
-    input buffers) against the in-place epilogue, P ranks emulated on one GPU, ragged shards, batch 2."""
+    input buffers) against the in-place epilogue, P ranks emulated on one GPU, ragged shards, batch 2.
+    With the scatter the column tiles are visited owner by owner (own heads last); every tile must still be
+    produced exactly once, bit-identically."""
     ops = _ops()
     from vllm_omni_draft_b200 import rope
     from vllm_omni_draft_b200.peer import prefix as _prefix, shard_counts
-    P, B, H, Dh, axes, K = 2, 2, 4, 64, (8, 28, 28), 128
+    B, K = 2, 128
+    axes = (8, 28, 28) if Dh == 64 else (16, 56, 56)
     d, hs = H * Dh, H // P
-    s_txt_full, s_img_full = 5, 71
     tc, ic = shard_counts(s_txt_full, P), shard_counts(s_img_full, P)
     counts = [a + b for a, b in zip(tc, ic)]
     pre, tpre, ipre = _prefix(counts), _prefix(tc), _prefix(ic)
@@ -355,22 +367,28 @@ def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device):
                                rope_pos0=s_txt_full, freqs=freqs_full, **kw),
               ops.gemm_problem(x[:, :s_txt_full], wt, bt, ref[:, :s_txt_full], qk_norm=(nw[2], nw[3]),
                                rope_pos0=0, freqs=freqs_full, **kw)])
-    recv = [torch.zeros(B, S, 3, hs, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    recv = [torch.full((B, S, 3, hs, Dh), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
     order = []
-    for r in range(P):
-        rows = list(range(tpre[r], tpre[r + 1])) + [s_txt_full + i for i in range(ipre[r], ipre[r + 1])]
-        order += rows
-        xl = x[:, rows].contiguous()
-        fl = freqs_full[rows].contiguous()
-        sc = _peer_scatter(recv, pre, r)
-        ops.gemm([ops.gemm_problem(xl[:, tc[r]:], wi, bi, None, qk_norm=(nw[0], nw[1]), rope_pos0=tc[r], freqs=fl,
-                                   scatter=sc, **kw),
-                  ops.gemm_problem(xl[:, :tc[r]], wt, bt, None, qk_norm=(nw[2], nw[3]), rope_pos0=0, freqs=fl,
-                                   scatter=sc, **kw)])
-    torch.cuda.synchronize()
+    ops.gemm_set_tile_n(bn)
+    ops.gemm_set_cta_pair(pair)
+    try:
+        for r in range(P):
+            rows = list(range(tpre[r], tpre[r + 1])) + [s_txt_full + i for i in range(ipre[r], ipre[r + 1])]
+            order += rows
+            xl = x[:, rows].contiguous()
+            fl = freqs_full[rows].contiguous()
+            sc = _peer_scatter(recv, pre, r)
+            ops.gemm([ops.gemm_problem(xl[:, tc[r]:], wi, bi, None, qk_norm=(nw[0], nw[1]), rope_pos0=tc[r],
+                                       freqs=fl, scatter=sc, **kw),
+                      ops.gemm_problem(xl[:, :tc[r]], wt, bt, None, qk_norm=(nw[2], nw[3]), rope_pos0=0, freqs=fl,
+                                       scatter=sc, **kw)])
+        torch.cuda.synchronize()
+    finally:
+        ops.gemm_set_tile_n(0)
+        ops.gemm_set_cta_pair(-1)
     want = ref[:, order].view(B, S, 3, H, Dh)
     for r in range(P):
-        assert torch.equal(recv[r], want[:, :, :, r * hs:(r + 1) * hs])
+        assert torch.equal(recv[r], want[:, :, :, r * hs:(r + 1) * hs])      # NaN anywhere = a tile never written
 
 
 def test_peer_barrier_single_rank(cuda_device):

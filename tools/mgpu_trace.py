@@ -27,6 +27,8 @@ g1, g2, g3 = (torch.Generator().manual_seed(s) for s in (1, 2, 42))
 cond = torch.randn(1, s_txt, cfg.joint_attention_dim, generator=g1).bfloat16()
 uncond = torch.randn(1, s_txt, cfg.joint_attention_dim, generator=g2).bfloat16()
 lat = torch.randn(1, s_img, 64, generator=g3).bfloat16()
+if os.environ.get("QI_TRACE_NO_CFG", "0") == "1":     # one branch only: with QI_CFG_PARALLEL=0 on P GPUs this is one
+    uncond = None                                     # rank's share of the 2P-GPU cfg x ulysses-P layout
 den.setup(cond, uncond, lat, H, W, 50, true_cfg_scale=4.0)
 for i in range(3):
     den.step(i)

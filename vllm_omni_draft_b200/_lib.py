@@ -11,7 +11,8 @@ import os
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libqi_b200.so")
+# QI_LIB_PATH: A/B aid (a differently built copy of the same library); the default is the in-tree build
+LIB_PATH = os.environ.get("QI_LIB_PATH") or os.path.join(_HERE, "libqi_b200.so")
 
 _lib: Optional[C.CDLL] = None
 

@@ -24,6 +24,13 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int GEMM_EPI_WARPS = 8;   // two warps per TMEM lane quadrant, each takes half of the tile's columns
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
+// Per-warp epilogue staging tile: 32 rows x 64 B, or 32 rows x 128 B for the tile widths the QKV epilogue's
+// wide stores use (BN % 128 == 0; the other widths would not fit their smem ring beside it).
+template <int BN>
+#ifndef QI_QKV_WIDE_STORES
+#define QI_QKV_WIDE_STORES 1      // build-time A/B aid: 0 keeps 64-byte row segments everywhere
+#endif
+struct EpiWarpBytes { static constexpr int value = (QI_QKV_WIDE_STORES && BN % 128 == 0) ? 4096 : 2048; };
 
 struct GemmProb {
   void* c;
@@ -46,6 +53,9 @@ struct GemmProb {
   float qk_eps;
   // optional Ulysses scatter of the head vectors (sc_n > 0): see qi_peer_scatter_t
   int sc_n, sc_hs, sc_s_total, sc_row_offset;
+  // scatter tile order (sc_tpg > 0): column tiles are visited destination by destination, starting with
+  // the peer after this rank and ending with this rank's own heads (sc_tpg = column tiles per (q|k|v, owner))
+  int sc_me, sc_tpg;
   __nv_bfloat16* sc_base[8];
 };
 
@@ -66,7 +76,8 @@ struct GemmCfg {
   static constexpr int ACC_STRIDE = (BN > 128) ? 256 : BN;    // TMEM columns between the two accumulators
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;   // power of two
   // per-warp 32 x 64 B staging tile of the epilogue (coalesced residual loads / result stores)
-  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * 2048;
+  static constexpr int EPI_WARP_BYTES = EpiWarpBytes<BN>::value;
+  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * EPI_WARP_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + EPI_STAGE_BYTES;
   static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB shared-memory limit");
 };
@@ -80,7 +91,25 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int
   const GemmProb& P = L.prob[tc.p];
   const int lt = t - P.tile_begin;
   const int mt = lt % P.tiles_m_total;
-  const int nt = lt / P.tiles_m_total;
+  int nt = lt / P.tiles_m_total;
+  if (P.sc_tpg > 0) {
+    // Ulysses scatter: rank r visits owners r+1, r+2, ..., r-1 (every rank sends to a different peer at any
+    // moment, so no GPU's NVLink ingress is a hot spot), q, k and v of each; its own heads come last, so the
+    // final wave's epilogue stores are local while the NVLink writes of the earlier waves drain.
+    const int lg = nt / P.sc_tpg, w = nt - lg * P.sc_tpg;
+    const int R = P.sc_n - 1;
+    int j3, owner;
+    if (lg < 3 * R) {
+      const int k = lg / 3;
+      j3 = lg - 3 * k;
+      owner = P.sc_me + 1 + k;
+      if (owner >= P.sc_n) owner -= P.sc_n;
+    } else {
+      j3 = lg - 3 * R;
+      owner = P.sc_me;
+    }
+    nt = (j3 * P.sc_n + owner) * P.sc_tpg + w;
+  }
   tc.b = mt / P.tiles_m;
   tc.m0 = (mt % P.tiles_m) * TM;
   tc.n0 = nt * BN;
@@ -201,6 +230,7 @@ template <int BN, int DH, typename Release>
 __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int row, int n0,
                                                   uint32_t taddr, int half, uint8_t* stage, Release release) {
   constexpr int HPT = BN / DH;   // head vectors per tile row
+  constexpr bool WIDE = EpiWarpBytes<BN>::value >= 4096;   // 128-byte row segments (else 64-byte)
   const bool row_ok = row < P.m;
   const int lane = threadIdx.x & 31;
   const int row0 = row - lane;   // first row of this warp's 32-row slab
@@ -298,20 +328,43 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
         // stage: piece g (16 B) of this lane's row, XOR-swizzled so neither side has bank conflicts
         const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
                                    pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-        *reinterpret_cast<uint4*>(stage + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4)) = o;
+        if constexpr (WIDE) {
+          const int gp = (c & 1) * 4 + g;      // piece inside the 128-byte (two-chunk) row segment
+          *reinterpret_cast<uint4*>(stage + lane * 128 + ((gp ^ (lane & 7)) << 4)) = o;
+        } else {
+          *reinterpret_cast<uint4*>(stage + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4)) = o;
+        }
       }
-      __syncwarp();
-      // coalesced stores: 4 lanes write one row's 64 contiguous bytes, 8 rows per instruction (peer
-      // writes over NVLink need this: one 16-byte store per lane and row is a packet per lane)
+      if constexpr (WIDE) {
+        // Two chunks make one full 128-byte line per row: 8 lanes write a row's line, 4 rows per instruction.
+        // Over NVLink the packet count halves against 64-byte segments (the scatter is bound by the peer
+        // write rate, not by the tensor pipe, once the head vectors leave the GPU).
+        if (c & 1) {
+          __syncwarp();
+#pragma unroll 4
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3);
+            const int piece = lane & 7;
+            const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((piece ^ (rr & 7)) << 4));
+            if (row0 + rr < P.m)
+              *reinterpret_cast<uint4*>(dst_base + (size_t)(row0 + rr) * dst_ld + (c - 1) * 32 + piece * 8) = o;
+          }
+          __syncwarp();
+        }
+      } else {
+        __syncwarp();
+        // coalesced stores: 4 lanes write one row's 64 contiguous bytes, 8 rows per instruction (peer
+        // writes over NVLink need this: one 16-byte store per lane and row is a packet per lane)
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int rr = it * 8 + (lane >> 2);
-        const int piece = lane & 3;
-        const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
-        if (row0 + rr < P.m)
-          *reinterpret_cast<uint4*>(dst_base + (size_t)(row0 + rr) * dst_ld + c * 32 + piece * 8) = o;
+        for (int it = 0; it < 4; ++it) {
+          const int rr = it * 8 + (lane >> 2);
+          const int piece = lane & 3;
+          const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
+          if (row0 + rr < P.m)
+            *reinterpret_cast<uint4*>(dst_base + (size_t)(row0 + rr) * dst_ld + c * 32 + piece * 8) = o;
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   }
   if (!released) release();
@@ -442,7 +495,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (2..9)
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
-    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * 2048;
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * Cfg::EPI_WARP_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -488,7 +541,8 @@ struct GemmPairCfg {
   static constexpr int STAGES = STG ? STG : ((BN >= 224) ? 6 : (BN >= 192 ? 7 : 8));
   static constexpr int ACC_STRIDE = (BN > 128) ? 256 : BN;
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;
-  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * 2048;
+  static constexpr int EPI_WARP_BYTES = EpiWarpBytes<BN>::value;
+  static constexpr int EPI_STAGE_BYTES = GEMM_EPI_WARPS * EPI_WARP_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + EPI_STAGE_BYTES;
   static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB shared-memory limit");
 };
@@ -605,7 +659,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (both CTAs)
     const int q = warp & 3;
-    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * 2048;
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * Cfg::EPI_WARP_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
     const uint32_t empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
@@ -664,7 +718,7 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.ld_res = in.ld_res; P.res_bs = in.res_batch_stride; P.gate_bs = in.gate_batch_stride;
   P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
   P.epilogue = in.epilogue;
-  P.freqs = nullptr; P.wq = P.wk = nullptr; P.sc_n = 0;
+  P.freqs = nullptr; P.wq = P.wk = nullptr; P.sc_n = 0; P.sc_me = 0; P.sc_tpg = 0;
   if (in.epilogue == QI_EPI_QKV_NORM_ROPE) {
     if (!in.qk_norm_wq || !in.qk_norm_wk || !in.rope_cos_sin || in.rope_pos0 < 0) return QI_ERR_ARG;
     if (in.head_dim != 64 && in.head_dim != 128) return QI_ERR_UNSUPPORTED;
@@ -690,6 +744,13 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
       P.sc_hs = in.heads / d.n_peers;
       P.sc_s_total = d.row_prefix[d.n_peers];
       P.sc_row_offset = d.row_prefix[d.my_index];
+      P.sc_me = d.my_index;
+      static const bool remap = [] {
+        const char* e = getenv("QI_SCATTER_REMAP");   // A/B aid: "0" keeps the plain column-tile order
+        return !(e && e[0] == '0');
+      }();
+      const int owner_cols = P.sc_hs * in.head_dim;   // columns of one (q|k|v, owner) group
+      if (remap && d.n_peers > 1 && owner_cols % BN == 0) P.sc_tpg = owner_cols / BN;
     }
   }
   P.tiles_m = (in.m + tile_m - 1) / tile_m;
