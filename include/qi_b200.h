@@ -168,19 +168,26 @@ typedef struct qi_peer_scatter {
 } qi_peer_scatter_t;
 
 /* K2 with scatter: qkv is this rank's [batch*seq, ld] row block ([q|k|v], all heads); normalised and
- * rotated q/k vectors and untouched v vectors are stored to base[owner of the head], laid out
- * [batch, row_prefix[P], 3, heads/P, head_dim], at sequence row row_prefix[my_index] + s. */
+ * rotated q/k vectors and untouched v vectors are stored to base[owner of the head], laid out HEAD-MAJOR
+ * [batch, 3, heads/P, row_prefix[P], head_dim], at sequence row row_prefix[my_index] + s (one head's rows are
+ * adjacent at the destination: peer writes of 128-byte segments reach 574 GB/s at a 256-byte row stride
+ * against 324 GB/s at the 3*heads/P*head_dim*2-byte stride of a token-major buffer; tools/p2p_bw.py).
+ * qi_gemm_bf16's QI_EPI_QKV_NORM_ROPE epilogue with `scatter` writes the same layout. */
 int qi_qknorm_rope_scatter(const void* qkv, int rows, int ld, int heads, int head_dim, int seq, int s_txt,
                            const void* wq_img, const void* wk_img, const void* wq_txt, const void* wk_txt,
                            const void* freqs_cos_sin, float eps, const qi_peer_scatter_t* dst /* host */,
                            qi_stream_t stream);
 
-/* K4 with scatter: attention over the full sequence for this rank's heads; output row r (owned by
+/* K4 with scatter: attention over the full sequence for this rank's heads; q/k/v element (b, s, h, :) sits
+ * at b*batch_stride + s*ld + h*head_stride (so head-major buffers are read in place); output row r (owned by
  * rank p) is stored to base[p] + my_index*chunk_stride + b*o_batch_stride + (r - row_prefix[p])*ld_o
- * + head*head_dim, i.e. into the K-chunked A operand of p's out-projection GEMM. */
+ * + head*o_head_stride, i.e. into the K-chunked A operand of p's out-projection GEMM (with
+ * ld_o = head_dim and o_head_stride = batch*S_max*head_dim every (source rank, head) is one K-chunk of
+ * head_dim columns whose rows are contiguous). */
 int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int batch, int seq_q, int seq_kv,
                              int heads, int head_dim, long long ld_q, long long ld_kv, long long ld_o,
                              long long q_batch_stride, long long kv_batch_stride, long long o_batch_stride,
+                             long long q_head_stride, long long kv_head_stride, long long o_head_stride,
                              float softmax_scale, const qi_peer_scatter_t* dst /* host */, qi_stream_t stream);
 /* Softmax variant of the attention kernel (tuning / tests): -1 = default (env QI_ATTN_VARIANT, else 11),
  * otherwise EMU + 8 * SPLIT with EMU in {0, 2, 3, 4} = how many of every 8 element pairs evaluate 2^x

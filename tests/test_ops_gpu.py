@@ -267,9 +267,9 @@ def test_ulysses_scatter_kernels_emulated_ranks(cuda_device, P, B, counts):
     rq, rk, rv = [ref_qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
     ref_o = torch.zeros(B, s_txt_full + s_img_full, H, Dh, device="cuda", dtype=torch.bfloat16)
     ops.attention(rq, rk, rv, ref_o)
-    # emulated ranks
-    recv = [torch.zeros(B, S, 3, hs, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
-    back = [torch.zeros(P, B, s_max, hs * Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    # emulated ranks; exchange buffers are head-major: recv [B, 3, H/P, S, Dh], back [P*H/P, B, S_max, Dh]
+    recv = [torch.zeros(B, 3, hs, S, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    back = [torch.zeros(P * hs, B, s_max, Dh, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
     rows_of = []
     for r in range(P):
         rows = list(range(tpre[r], tpre[r + 1])) + [s_txt_full + i for i in range(ipre[r], ipre[r + 1])]
@@ -280,18 +280,26 @@ def test_ulysses_scatter_kernels_emulated_ranks(cuda_device, P, B, counts):
                                 ws[0], ws[1], ws[2], ws[3], fl, _peer_scatter(recv, pre, r))
     for r in range(P):
         full = recv[r]
-        ops.attention_scatter(full[:, :, 0], full[:, :, 1], full[:, :, 2],
-                              _peer_scatter(back, pre, r, B * s_max * hs * Dh), hs * Dh, s_max * hs * Dh)
+        ops.attention_scatter(full[:, 0].transpose(1, 2), full[:, 1].transpose(1, 2), full[:, 2].transpose(1, 2),
+                              _peer_scatter(back, pre, r, hs * B * s_max * Dh), Dh, s_max * Dh,
+                              o_head_stride=B * s_max * Dh)
     torch.cuda.synchronize()
     for r in range(P):
-        got = back[r][:, :, :counts[r]].permute(1, 2, 0, 3).reshape(B, counts[r], H, Dh)   # chunk = head group
+        got = back[r][:, :, :counts[r]].permute(1, 2, 0, 3)                  # [B, S_loc, H (chunk = head), Dh]
         want = ref_o[:, rows_of[r]]
         err = O.rel_l2(got.cpu(), want.cpu())
         assert err < 4e-3, f"rank {r}: rel_l2={err}"
         # the scattered q/k/v themselves are bit-identical to the in-place kernel's output
         full_rows = [x for rr in rows_of for x in rr]
         for j, t in enumerate((rq, rk, rv)):
-            assert torch.equal(recv[r][:, :, j], t[:, full_rows][:, :, r * hs:(r + 1) * hs])
+            assert torch.equal(recv[r][:, j].transpose(1, 2), t[:, full_rows][:, :, r * hs:(r + 1) * hs])
+    # the out-projection reads `back` in place as a K-chunked A operand (one chunk of Dh columns per head)
+    w = _rand((96, d), 77, 0.05)
+    for r in range(P):
+        out = torch.zeros(B, counts[r], 96, device="cuda", dtype=torch.bfloat16)
+        ops.gemm([ops.gemm_problem(back[r][:, :, :counts[r]], w, None, out, 0, a_k_chunked=True)])
+        a = back[r][:, :, :counts[r]].permute(1, 2, 0, 3).reshape(B, counts[r], d).float()
+        assert O.rel_l2(out.cpu(), (a @ w.float().t()).cpu()) < 5e-3
 
 
 @pytest.mark.parametrize("H,Dh,axes,bn,pair", [(4, 64, (8, 28, 28), 0, -1), (4, 64, (8, 28, 28), 192, 0),
@@ -367,7 +375,7 @@ def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device, P, H, Dh, bn, pai
                                rope_pos0=s_txt_full, freqs=freqs_full, **kw),
               ops.gemm_problem(x[:, :s_txt_full], wt, bt, ref[:, :s_txt_full], qk_norm=(nw[2], nw[3]),
                                rope_pos0=0, freqs=freqs_full, **kw)])
-    recv = [torch.full((B, S, 3, hs, Dh), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    recv = [torch.full((B, 3, hs, S, Dh), float("nan"), device="cuda", dtype=torch.bfloat16) for _ in range(P)]
     order = []
     ops.gemm_set_tile_n(bn)
     ops.gemm_set_cta_pair(pair)
@@ -387,8 +395,8 @@ def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device, P, H, Dh, bn, pai
         ops.gemm_set_tile_n(0)
         ops.gemm_set_cta_pair(-1)
     want = ref[:, order].view(B, S, 3, H, Dh)
-    for r in range(P):
-        assert torch.equal(recv[r], want[:, :, :, r * hs:(r + 1) * hs])      # NaN anywhere = a tile never written
+    for r in range(P):      # head-major destination [B, 3, H/P, S, Dh]; NaN anywhere = a tile never written
+        assert torch.equal(recv[r].permute(0, 3, 1, 2, 4), want[:, :, :, r * hs:(r + 1) * hs])
 
 
 def test_peer_barrier_single_rank(cuda_device):

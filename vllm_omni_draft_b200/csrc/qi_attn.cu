@@ -50,12 +50,12 @@ struct AttCfg {
 struct AttParams {
   CUtensorMap tmap_q, tmap_k, tmap_v;
   __nv_bfloat16* o;
-  long long ld_o, o_bs;
+  long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
   int seq_q, seq_kv, heads;
   float scale_log2;
   int split_p;   // softmax publishes P in two 64-key halves (p_half, then p_full)
   // Ulysses scatter epilogue (n_peer > 0): query row r owned by rank p goes to
-  // o_peer[p] + o_chunk_off + b*o_bs + (r - o_prefix[p])*ld_o + head*DH   (peer-mapped HBM)
+  // o_peer[p] + o_chunk_off + b*o_bs + (r - o_prefix[p])*ld_o + head*o_hs   (peer-mapped HBM)
   int n_peer;
   int o_prefix[9];
   long long o_chunk_off;
@@ -391,9 +391,9 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
           int p = 0;
           while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
           orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
-                 (size_t)head * DH;
+                 (size_t)head * P.o_hs;
         } else {
-          orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * DH;
+          orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * P.o_hs;
         }
         *reinterpret_cast<uint4*>(orow + piece * 8) = o;
       }
@@ -446,6 +446,7 @@ template <int DH>
 static int launch_attention(const void* q, const void* k, const void* v, void* o, int batch,
                             int seq_q, int seq_kv, int heads, long long ld_q, long long ld_kv,
                             long long ld_o, long long q_bs, long long kv_bs, long long o_bs,
+                            long long q_hs, long long kv_hs, long long o_hs,
                             float scale, const qi_peer_scatter_t* dst, cudaStream_t stream) {
   AttParams P;
   memset(&P, 0, sizeof(P));
@@ -461,14 +462,14 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   const uint32_t box[4] = {64, 1, ATT_BM, 1};
   {
     uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_q, (uint64_t)batch};
-    uint64_t str[3] = {(uint64_t)DH * 2, (uint64_t)ld_q * 2,
+    uint64_t str[3] = {(uint64_t)q_hs * 2, (uint64_t)ld_q * 2,
                        (uint64_t)(batch > 1 ? q_bs : ld_q * (long long)seq_q) * 2};
     int rc = qi_encode_tmap_bf16(&P.tmap_q, q, 4, dims, str, box);
     if (rc) return rc;
   }
   {
     uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_kv, (uint64_t)batch};
-    uint64_t str[3] = {(uint64_t)DH * 2, (uint64_t)ld_kv * 2,
+    uint64_t str[3] = {(uint64_t)kv_hs * 2, (uint64_t)ld_kv * 2,
                        (uint64_t)(batch > 1 ? kv_bs : ld_kv * (long long)seq_kv) * 2};
     int rc = qi_encode_tmap_bf16(&P.tmap_k, k, 4, dims, str, box);
     if (rc) return rc;
@@ -478,6 +479,7 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.o = (__nv_bfloat16*)o;
   P.ld_o = ld_o;
   P.o_bs = o_bs;
+  P.o_hs = o_hs;
   P.seq_q = seq_q;
   P.seq_kv = seq_kv;
   P.heads = heads;
@@ -501,9 +503,11 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
 static int attention_entry(const void* q, const void* k, const void* v, void* o, int batch,
                            int seq_q, int seq_kv, int heads, int head_dim, long long ld_q,
                            long long ld_kv, long long ld_o, long long q_batch_stride,
-                           long long kv_batch_stride, long long o_batch_stride, float softmax_scale,
+                           long long kv_batch_stride, long long o_batch_stride, long long q_hs,
+                           long long kv_hs, long long o_hs, float softmax_scale,
                            const qi_peer_scatter_t* dst, cudaStream_t stream) {
   if (!q || !k || !v || (!o && !dst)) return QI_ERR_ARG;
+  if (q_hs <= 0 || kv_hs <= 0 || o_hs <= 0 || q_hs % 8 || kv_hs % 8 || o_hs % 8) return QI_ERR_ARG;
   if (batch <= 0 || seq_q <= 0 || seq_kv <= 0 || heads <= 0) return QI_ERR_ARG;
   if (ld_q % 8 || ld_kv % 8 || ld_o % 8 || q_batch_stride % 8 || kv_batch_stride % 8 ||
       o_batch_stride % 8)
@@ -523,12 +527,12 @@ static int attention_entry(const void* q, const void* k, const void* v, void* o,
   if (qi_num_sms() <= 0) return QI_ERR_CUDA;
   if (head_dim == 128)
     return launch_attention<128>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
-                                 q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
-                                 dst, stream);
+                                 q_batch_stride, kv_batch_stride, o_batch_stride, q_hs, kv_hs, o_hs,
+                                 softmax_scale, dst, stream);
   if (head_dim == 64)
     return launch_attention<64>(q, k, v, o, batch, seq_q, seq_kv, heads, ld_q, ld_kv, ld_o,
-                                q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale,
-                                dst, stream);
+                                q_batch_stride, kv_batch_stride, o_batch_stride, q_hs, kv_hs, o_hs,
+                                softmax_scale, dst, stream);
   return QI_ERR_UNSUPPORTED;
 }
 
@@ -538,17 +542,20 @@ extern "C" int qi_attention_fwd(const void* q, const void* k, const void* v, voi
                                 long long kv_batch_stride, long long o_batch_stride,
                                 float softmax_scale, cudaStream_t stream) {
   return attention_entry(q, k, v, o, batch, seq_q, seq_kv, heads, head_dim, ld_q, ld_kv, ld_o,
-                         q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale, nullptr,
-                         stream);
+                         q_batch_stride, kv_batch_stride, o_batch_stride, head_dim, head_dim, head_dim,
+                         softmax_scale, nullptr, stream);
 }
 
 extern "C" int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int batch,
                                         int seq_q, int seq_kv, int heads, int head_dim,
                                         long long ld_q, long long ld_kv, long long ld_o,
                                         long long q_batch_stride, long long kv_batch_stride,
-                                        long long o_batch_stride, float softmax_scale,
-                                        const qi_peer_scatter_t* dst, cudaStream_t stream) {
+                                        long long o_batch_stride, long long q_head_stride,
+                                        long long kv_head_stride, long long o_head_stride,
+                                        float softmax_scale, const qi_peer_scatter_t* dst,
+                                        cudaStream_t stream) {
   if (!dst) return QI_ERR_ARG;
   return attention_entry(q, k, v, nullptr, batch, seq_q, seq_kv, heads, head_dim, ld_q, ld_kv, ld_o,
-                         q_batch_stride, kv_batch_stride, o_batch_stride, softmax_scale, dst, stream);
+                         q_batch_stride, kv_batch_stride, o_batch_stride, q_head_stride, kv_head_stride,
+                         o_head_stride, softmax_scale, dst, stream);
 }

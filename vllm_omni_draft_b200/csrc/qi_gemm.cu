@@ -244,15 +244,16 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
     const int j3 = nh / d_model;                 // 0 q, 1 k, 2 v
     const int h = (nh - j3 * d_model) / DH;
     // Destination of row r's head vector: dst_base + r * dst_ld (in place in C, or the head owner's
-    // [batch, s_total, 3, heads/P, DH] attention input buffer over NVLink)
+    // [batch, 3, heads/P, s_total, DH] attention input buffer over NVLink)
     __nv_bfloat16* dst_base;
     size_t dst_ld;
     if (P.sc_n > 0) {
       const int p = h / P.sc_hs;
       const int hl = h - p * P.sc_hs;
-      dst_ld = (size_t)3 * P.sc_hs * DH;
-      dst_base = P.sc_base[p] + ((size_t)b * P.sc_s_total + P.sc_row_offset + P.pos0) * dst_ld +
-                 ((size_t)j3 * P.sc_hs + hl) * DH;
+      // head-major destination [batch, 3, heads/P, s_total, DH]: one head's rows are adjacent
+      dst_ld = (size_t)DH;
+      dst_base = P.sc_base[p] +
+                 ((((size_t)b * 3 + j3) * P.sc_hs + hl) * P.sc_s_total + P.sc_row_offset + P.pos0) * DH;
     } else {
       dst_ld = (size_t)P.ldc;
       dst_base = reinterpret_cast<__nv_bfloat16*>(P.c) + (size_t)b * P.c_bs + nh;

@@ -196,22 +196,25 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tens
 
 
 def attention_scatter(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, dst: "_lib.PeerScatter", ld_o: int,
-                      o_batch_stride: int, softmax_scale: Optional[float] = None) -> None:
+                      o_batch_stride: int, softmax_scale: Optional[float] = None,
+                      o_head_stride: Optional[int] = None) -> None:
     """Attention whose epilogue stores each output row into the HBM of the rank that owns the token
-    (qi_attention_fwd_scatter): the gather half of the Ulysses exchange."""
+    (qi_attention_fwd_scatter): the gather half of the Ulysses exchange.  q, k, v: [B, S, H, Dh] views with
+    arbitrary batch / token / head strides (Dh contiguous), so head-major exchange buffers are read in place.
+    Output element (b, row, head) goes to ... + b*o_batch_stride + row*ld_o + head*o_head_stride
+    (o_head_stride defaults to Dh: heads packed inside a token row)."""
     global launch_count
     _req_bf16(q, k, v)
     B, Sq, H, Dh = q.shape
     Skv = k.shape[1]
-    for t in (q, k, v):
-        if t.stride(2) != Dh:
-            raise ValueError("heads must be packed contiguously inside a token row")
     if k.stride() != v.stride():
         raise ValueError("k and v must share strides")
     scale = softmax_scale if softmax_scale is not None else Dh ** -0.5
     check(_lib.lib().qi_attention_fwd_scatter(q.data_ptr(), k.data_ptr(), v.data_ptr(), B, Sq, Skv, H, Dh,
                                               q.stride(1), k.stride(1), ld_o, q.stride(0), k.stride(0),
-                                              o_batch_stride, float(scale), C.byref(dst), _stream()),
+                                              o_batch_stride, q.stride(2), k.stride(2),
+                                              Dh if o_head_stride is None else int(o_head_stride),
+                                              float(scale), C.byref(dst), _stream()),
           "qi_attention_fwd_scatter")
     launch_count += 1
 

@@ -3,11 +3,14 @@
 The reference has no parallelism.  SURVEY §8e asks for the head<->sequence
 all-to-all around attention; here that exchange is folded into the kernels on either side of it:
 
-* ``qi_qknorm_rope_scatter`` (K2) stores every q/k/v head vector straight into the HBM of the rank
-  that owns the head — into that rank's ``recv`` buffer ``[B, S_total, 3, H/P, Dh]``;
+* the QKV GEMM's epilogue (or ``qi_qknorm_rope_scatter``, K2) stores every q/k/v head vector straight into
+  the HBM of the rank that owns the head — into that rank's ``recv`` buffer ``[B, 3, H/P, S_total, Dh]``;
 * ``qi_attention_fwd_scatter`` (K4) stores every output row straight into the HBM of the rank that
-  owns the token — into that rank's ``back`` buffer ``[P, B, S_loc_max, (H/P)·Dh]``, which the
-  out-projection GEMM reads as a K-chunked A operand;
+  owns the token — into that rank's ``back`` buffer ``[P·H/P, B, S_loc_max, Dh]`` (one K-chunk of Dh columns
+  per (source rank, head)), which the out-projection GEMM reads as a K-chunked A operand;
+* both buffers are HEAD-MAJOR: the rows of one head are adjacent at the destination, because the peer
+  write rate depends on the destination stride (tools/p2p_bw.py: 128-byte segments 574 GB/s at a 256-byte
+  row stride, 324 GB/s at the 4608-byte stride of a token-major ``[.., 3, H/P, Dh]`` row);
 * between producer and consumer sits ``qi_peer_barrier`` (a 32-thread flag kernel), twice per block.
 
 Host layer only: allocate one peer-mappable region per rank (``qi_peer_alloc``), ship the 64-byte
@@ -99,9 +102,9 @@ class PeerExchange:
         raw = torch.as_tensor(_RawDeviceMemory(self._own, self.nbytes // 2), device=device).view(torch.bfloat16)
         self._raw = raw
         r0 = self._recv_off // 2
-        self.recv = raw[r0:r0 + recv_bytes // 2].view(batch, self.s_total, 3, self.hs, head_dim)
+        self.recv = raw[r0:r0 + recv_bytes // 2].view(batch, 3, self.hs, self.s_total, head_dim)
         b0 = self._back_off // 2
-        self.back = raw[b0:b0 + back_bytes // 2].view(size, batch, self.s_max, row)
+        self.back = raw[b0:b0 + back_bytes // 2].view(size * self.hs, batch, self.s_max, head_dim)
         # scatter descriptors
         self.dst_qkv = PeerScatter()
         self.dst_o = PeerScatter()
@@ -111,9 +114,10 @@ class PeerExchange:
                 d.base[r] = self.ptrs[r] + off
             for i, v in enumerate(self.pre):
                 d.row_prefix[i] = v
-        self.dst_o.chunk_stride = batch * self.s_max * row
-        self.o_ld = row
-        self.o_batch_stride = self.s_max * row
+        self.dst_o.chunk_stride = batch * self.s_max * row          # one source rank's H/P head chunks
+        self.o_ld = head_dim
+        self.o_batch_stride = self.s_max * head_dim
+        self.o_head_stride = batch * self.s_max * head_dim
         torch.cuda.synchronize(device)
         dist.barrier(group=group)      # every region is zeroed and mapped before the first flag is written
 

@@ -441,11 +441,12 @@ class B200QwenImageTransformer2DModel(nn.Module):
                 # the head owner's HBM, attention stores each output row into the token owner's HBM; two
                 # flag barriers.
                 peer.barrier()
-                full = peer.recv                       # [B, S_total, 3, H/P, Dh]
-                ops.attention_scatter(full[:, :, 0], full[:, :, 1], full[:, :, 2], peer.dst_o, peer.o_ld,
-                                      peer.o_batch_stride)
+                full = peer.recv                       # head-major [B, 3, H/P, S_total, Dh]
+                ops.attention_scatter(full[:, 0].transpose(1, 2), full[:, 1].transpose(1, 2),
+                                      full[:, 2].transpose(1, 2), peer.dst_o, peer.o_ld, peer.o_batch_stride,
+                                      o_head_stride=peer.o_head_stride)
                 peer.barrier()
-                back = peer.back[:, :, :S]             # [P, B, S_loc, (H/P)*Dh]: K-chunked A operand
+                back = peer.back[:, :, :S]             # [P*H/P, B, S_loc, Dh]: K-chunked A operand (chunk = head)
                 ops.gemm([ops.gemm_problem(back[:, :, s_txt:], self.out_w[l, 0], self.out_b[l, 0], h, G, h,
                                            bview(g_i1), a_k_chunked=True),
                           ops.gemm_problem(back[:, :, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
