@@ -31,15 +31,52 @@ def _time_ms(fn, warm=2, iters=4):
     return e0.elapsed_time(e1) / iters
 
 
-def test_full_size_blocks_parity_and_library_baseline(cuda_device):
+L = 2
+
+
+@pytest.fixture(scope="module")
+def full_width(cuda_device):
+    """Two blocks at the real width on the GPU: (oracle config, bf16 state dict on the GPU, CUDA model)."""
     from vllm_omni_draft_b200.config import MMDiTConfig
     from vllm_omni_draft_b200.transformer import B200QwenImageTransformer2DModel
-    L, B, s_img, s_txt = 2, 2, 4096, 512
     ocfg = O.OracleConfig(num_layers=L)
     sd = O.init_state_dict(ocfg, seed=3, bias_std=0.02, norm_weight_std=0.1)
     tr = B200QwenImageTransformer2DModel(MMDiTConfig(num_layers=L), device="cuda:0")
     tr.load_diffusers_state_dict(sd)
     sdg = {k: v.to("cuda:0", torch.bfloat16) for k, v in sd.items()}
+    del sd
+    return ocfg, sdg, tr
+
+
+@pytest.mark.parametrize("name,B,hh,ww,s_txt", [
+    ("cfg4_2048px", 1, 128, 128, 512),       # BASELINE configs[3]: 16384 image tokens (one CFG branch)
+    ("cfg5_1328px", 2, 83, 83, 512),         # configs[4]: 83x83 = 6889 tokens (odd grid, ragged tiles), batched
+    ("short_prompt", 2, 64, 64, 77),         # odd text length at 1024px
+])
+def test_other_configs_full_width_parity(full_width, name, B, hh, ww, s_txt):
+    """The other BASELINE.json configs as parity cases: real width, real sequence lengths, against the oracle
+    run in eager bf16 on the GPU."""
+    ocfg, sdg, tr = full_width
+    g = torch.Generator().manual_seed(hh * 1000 + s_txt)
+    lat = torch.randn(B, hh * ww, 64, generator=g).to("cuda:0", torch.bfloat16)
+    enc = torch.randn(B, s_txt, 3584, generator=g).to("cuda:0", torch.bfloat16)
+    mask = torch.ones(B, s_txt, dtype=torch.bool, device="cuda:0")
+    t = torch.full((B,), 0.35, device="cuda:0")
+    shapes = [[(1, hh, ww)]] * B
+    with torch.no_grad():
+        ref = O.transformer_forward(sdg, ocfg, lat, enc, mask, t.bfloat16(), shapes, [s_txt] * B)
+        out = tr(hidden_states=lat, encoder_hidden_states=enc, encoder_hidden_states_mask=mask, timestep=t,
+                 img_shapes=shapes, txt_seq_lens=[s_txt] * B, return_dict=False)[0]
+    torch.cuda.synchronize()
+    err = O.rel_l2(out.float().cpu(), ref.float().cpu())
+    print(f"FULL_WIDTH_PARITY {name}: B={B} S_img={hh * ww} S_txt={s_txt} rel_l2_vs_eager_bf16={err:.3e}")
+    assert err < 2e-2, f"{name}: rel-L2 {err}"
+    tr._ws.clear()                            # release this shape's workspace before the next case
+
+
+def test_full_size_blocks_parity_and_library_baseline(full_width):
+    B, s_img, s_txt = 2, 4096, 512
+    ocfg, sdg, tr = full_width
     g = torch.Generator().manual_seed(11)
     lat = torch.randn(1, s_img, 64, generator=g).expand(B, -1, -1).contiguous().to("cuda:0", torch.bfloat16)
     enc = torch.randn(B, s_txt, 3584, generator=g).to("cuda:0", torch.bfloat16)
