@@ -177,3 +177,28 @@ def test_config_and_input_validation():
                                                      prompt_embeds_mask=torch.ones(1, 4),
                                                      image_latents=torch.zeros(1, 16, 4, 4),
                                                      img_shapes=[(1, 2, 2)], txt_seq_lens=[4, 4]))
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the reference's CPU path = the oracle on the host cores) prints ONE JSON line
+    with the keys the driver reads; runs without a GPU and without the CUDA library."""
+    import json
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    j = json.loads(lines[0])
+    assert j["impl"] == "reference" and j["metric"] == "denoise steps/s" and j["unit"] == "steps/s"
+    assert j["higher_is_better"] is True and j["vs_baseline"] is None and j["n_gpus"] == 1 and j["steps"] == 1
+    assert j["value"] > 0 and abs(j["value"] - 1e3 / j["ms_per_step"]) < 1e-9
+    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["sample"]
+    assert j["cpu_baseline"]["value"] == j["value"]
+    assert j["e2e"] == {"value": j["value"], "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "4096 image tokens" in j["config"]["workload"] and "model" not in j["config"]
+    # under torchrun only rank 0 prints; the other ranks exit 0 without work
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                       capture_output=True, text=True, timeout=120, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
+    assert r.returncode == 0 and not [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
