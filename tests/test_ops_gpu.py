@@ -399,6 +399,49 @@ def test_gemm_qkv_epilogue_scatter_emulated_ranks(cuda_device, P, H, Dh, bn, pai
         assert torch.equal(recv[r].permute(0, 3, 1, 2, 4), want[:, :, :, r * hs:(r + 1) * hs])
 
 
+def test_gemm_split_launch_matches_combined(cuda_device):
+    """ops.gemm may issue one launch per problem when the autotuner measured that to be faster for these dims
+    (a sequence-parallel rank's 128-row text stream wastes half of every 256-row pair tile in a combined launch).
+    Same kernels, so the results must be bit-identical; the launch counter must see both launches."""
+    ops = _ops()
+    B, m1, m2, K, N = 1, 1024, 128, 256, 768
+    a1, a2 = _rand((B, m1, K), 60), _rand((B, m2, K), 61)
+    w1, w2 = _rand((N, K), 62, 0.05), _rand((N, K), 63, 0.05)
+    b1, b2 = _rand((N,), 64, 0.5), _rand((N,), 65, 0.5)
+    r1, r2 = _rand((B, m1, N), 66), _rand((B, m2, N), 67)
+    gate = _rand((B, N), 68)
+
+    def run():
+        o1, o2 = torch.zeros_like(r1), torch.zeros_like(r2)
+        probs = [ops.gemm_problem(a1, w1, b1, o1, ops.EPI_GATED_RESIDUAL, r1, gate),
+                 ops.gemm_problem(a2, w2, b2, o2, ops.EPI_GATED_RESIDUAL, r2, gate)]
+        n0 = ops.launch_count
+        ops.gemm(probs)
+        torch.cuda.synchronize()
+        return o1, o2, ops.launch_count - n0, ops._gemm_key(probs), probs
+
+    o1, o2, n, key, probs = run()
+    assert n == 1 and key not in ops._split_keys
+    ops._split_keys.add(key)
+    try:
+        s1, s2, n, _, _ = run()
+    finally:
+        ops._split_keys.discard(key)
+    assert n == 2 and torch.equal(s1, o1) and torch.equal(s2, o2)
+    y = r1.float() + gate.float()[:, None, :] * (a1.float() @ w1.float().t() + b1.float())
+    assert O.rel_l2(o1.cpu(), y.cpu()) < 5e-3
+    # the tuner runs on scratch outputs, registers single-problem schedules too, and keeps its books consistent
+    ops.clear_gemm_schedules()
+    chosen = ops.tune_gemm(probs, allow_split=True)
+    assert chosen is not None and ops.tune_gemm(probs, allow_split=True) is None
+    assert ops._gemm_key(probs[:1]) in ops._tuned_keys and ops._gemm_key(probs[1:]) in ops._tuned_keys
+    t1, t2, n, _, _ = run()
+    assert n == (2 if key in ops._split_keys else 1)
+    assert O.rel_l2(t1.cpu(), y.cpu()) < 5e-3
+    ops.clear_gemm_schedules()
+    assert not ops._split_keys and not ops._tuned_keys
+
+
 def test_peer_barrier_single_rank(cuda_device):
     """n_peers = 1: the rank signals itself; the epoch advances and the timeout flag stays clear."""
     ops = _ops()

@@ -853,7 +853,7 @@ struct TunedSchedule {
   int num, m[2], batch[2], n[2], k[2], epi[2];
   int pair, bn;
 };
-static TunedSchedule g_tuned[64];
+static TunedSchedule g_tuned[512];
 static int g_num_tuned = 0;
 static bool tuned_matches(const TunedSchedule& t, const qi_gemm_problem_t* p, int num) {
   if (t.num != num) return false;
@@ -870,7 +870,7 @@ extern "C" int qi_gemm_set_schedule(const qi_gemm_problem_t* problems, int num_p
   for (int i = 0; i < g_num_tuned; ++i)
     if (tuned_matches(g_tuned[i], problems, num_problems)) slot = i;
   if (slot < 0) {
-    if (g_num_tuned == 64) return QI_ERR_UNSUPPORTED;
+    if (g_num_tuned == 512) return QI_ERR_UNSUPPORTED;
     slot = g_num_tuned++;
   }
   TunedSchedule& t = g_tuned[slot];

@@ -4,6 +4,7 @@ raises RuntimeError if the library is missing or reports an error (no fallback).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -104,8 +105,7 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
     return p
 
 
-def gemm(problems: Sequence[GemmProblem]) -> None:
-    """One persistent tcgen05 launch for 1 or 2 problems (img + txt stream)."""
+def _launch_gemm(problems: Sequence[GemmProblem]) -> None:
     global launch_count
     n = len(problems)
     arr = (GemmProblem * n)(*problems)
@@ -113,28 +113,46 @@ def gemm(problems: Sequence[GemmProblem]) -> None:
     launch_count += 1
 
 
+def gemm(problems: Sequence[GemmProblem]) -> None:
+    """One persistent tcgen05 launch for 1 or 2 problems (img + txt stream) — or, where the autotuner measured
+    it to be faster for these dims (`tune_gemm`), one launch per problem, each with its own schedule."""
+    if _split_keys and len(problems) == 2 and _gemm_key(problems) in _split_keys:
+        _launch_gemm(problems[:1])
+        _launch_gemm(problems[1:])
+    else:
+        _launch_gemm(problems)
+
+
 _GEMM_CANDIDATES = [(pair, bn) for pair in (1, 0) for bn in (256, 224, 192, 160, 128)]
 _tuned_keys = set()
+_split_keys = set()          # two-problem dims for which two launches beat the combined launch
+_SPLIT_MARGIN = 0.97         # a split must win by 3 % (one more launch; keeps noise from flipping the choice)
 
 
 def _gemm_key(problems: Sequence[GemmProblem]):
     return tuple((p.m, p.batch, p.n, p.k, p.epilogue) for p in problems)
 
 
-def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 3) -> Optional[Tuple[int, int]]:
-    """Autotune the schedule (single-CTA / CTA-pair, tile width) for problems of these dims: every
-    candidate is timed with CUDA events (best of `groups` groups of `launches` back-to-back launches) and
-    the fastest is registered with the library (qi_gemm_set_schedule).  The problems' outputs are
-    overwritten repeatedly, so pass scratch / per-forward temporaries.  Must not run under graph
-    capture.  Returns the chosen (pair, bn), or None if these dims were tuned before."""
-    key = _gemm_key(problems)
-    if key in _tuned_keys:
-        return None
+def _time_launches(fn, launches: int, groups: int) -> float:
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = None
+    for _ in range(groups):
+        e0.record()
+        for _ in range(launches):
+            fn()
+        e1.record()
+        e1.synchronize()
+        dt = e0.elapsed_time(e1)
+        best = dt if best is None else min(best, dt)
+    return best
+
+
+def _tune_schedule(problems: Sequence[GemmProblem], launches: int, groups: int) -> Tuple[int, int]:
+    """Time every (pair, bn) candidate for ONE launch over `problems`; register and return the fastest."""
     n = len(problems)
     arr = (GemmProblem * n)(*problems)
     lib = _lib.lib()
     best, best_t = None, None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     try:
         for pair, bn in _GEMM_CANDIDATES:
             check(lib.qi_gemm_set_cta_pair(pair), "qi_gemm_set_cta_pair")
@@ -142,15 +160,7 @@ def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 
             if lib.qi_gemm_bf16(arr, n, _stream()) != 0:      # candidate not valid for this epilogue / shape
                 continue
             lib.qi_gemm_bf16(arr, n, _stream())
-            t = None
-            for _ in range(groups):
-                e0.record()
-                for _ in range(launches):
-                    lib.qi_gemm_bf16(arr, n, _stream())
-                e1.record()
-                e1.synchronize()
-                dt = e0.elapsed_time(e1)
-                t = dt if t is None else min(t, dt)
+            t = _time_launches(lambda: lib.qi_gemm_bf16(arr, n, _stream()), launches, groups)
             if best_t is None or t < best_t:
                 best, best_t = (pair, bn), t
     finally:
@@ -159,12 +169,52 @@ def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 
     if best is None:
         raise RuntimeError("tune_gemm: no valid schedule for these problems")
     check(lib.qi_gemm_set_schedule(arr, n, best[0], best[1]), "qi_gemm_set_schedule")
+    return best
+
+
+def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 3,
+              allow_split: Optional[bool] = None) -> Optional[Tuple[int, int]]:
+    """Autotune the schedule (single-CTA / CTA-pair, tile width) for problems of these dims: every
+    candidate is timed with CUDA events (best of `groups` groups of `launches` back-to-back launches) and
+    the fastest is registered with the library (qi_gemm_set_schedule).  With `allow_split` (default: env
+    QI_GEMM_SPLIT=1, off otherwise) the alternative "one launch per problem, each with its own tuned schedule"
+    is timed for two-problem sets as well and remembered when it wins.  Measured at one rank's cfg2 x ulysses4
+    shapes (1024 image + 128 text rows; tools/split_tune.py, profiles/r01d_split_tune_p4.txt) the combined
+    launch wins every GEMM of the block (231 vs 293 us in sum: a lone 128-row problem runs one sparse wave that
+    costs a whole tile time), so the option is off by default and kept as a measured tuning dimension.  The problems'
+    outputs are overwritten repeatedly, so pass scratch / per-forward temporaries.  Must not run under graph
+    capture.  Returns the chosen (pair, bn) of the combined launch, or None if these dims were tuned before."""
+    key = _gemm_key(problems)
+    if key in _tuned_keys:
+        return None
+    best = _tune_schedule(problems, launches, groups)
     _tuned_keys.add(key)
+    if allow_split is None:
+        allow_split = os.environ.get("QI_GEMM_SPLIT", "0") == "1"
+    if allow_split and len(problems) == 2:
+        for p in problems:
+            k1 = _gemm_key([p])
+            if k1 not in _tuned_keys:
+                _tune_schedule([p], launches, groups)
+                _tuned_keys.add(k1)
+        lib = _lib.lib()
+        arr2 = (GemmProblem * 2)(*problems)
+        a0, a1 = (GemmProblem * 1)(problems[0]), (GemmProblem * 1)(problems[1])
+
+        def split():
+            lib.qi_gemm_bf16(a0, 1, _stream())
+            lib.qi_gemm_bf16(a1, 1, _stream())
+
+        t_comb = _time_launches(lambda: lib.qi_gemm_bf16(arr2, 2, _stream()), launches, groups)
+        t_split = _time_launches(split, launches, groups)
+        if t_split < _SPLIT_MARGIN * t_comb:
+            _split_keys.add(key)
     return best
 
 
 def clear_gemm_schedules() -> None:
     _tuned_keys.clear()
+    _split_keys.clear()
     check(_lib.lib().qi_gemm_clear_schedules(), "qi_gemm_clear_schedules")
 
 

@@ -271,6 +271,7 @@ class B200QwenImageTransformer2DModel(nn.Module):
             ops.gemm_problem(ws.mlp_img, self.mlp_down_w[0, 0], self.mlp_down_b[0, 0], ws.h, G, ws.h, gate),
             ops.gemm_problem(ws.mlp_txt, self.mlp_down_w[0, 1], self.mlp_down_b[0, 1], ws.e, G, ws.e, gate)])
         torch.cuda.synchronize(dev)
+        chosen["split_launches"] = len(ops._split_keys)     # two-problem dims issued as one launch per problem
         return chosen
 
     # ------------------------------------------------------------------ modulation
