@@ -351,11 +351,13 @@ def calculate_shift(image_seq_len, base_seq_len=256, max_seq_len=8192, base_shif
     return image_seq_len * m + b
 
 
-def flowmatch_sigmas(num_inference_steps: int, image_seq_len: int, shift_terminal: float = 0.02):
+def flowmatch_sigmas(num_inference_steps: int, image_seq_len: int, shift_terminal: float = 0.02, sigmas=None):
     """FlowMatchEulerDiscreteScheduler.set_timesteps(sigmas=linspace(1,1/N,N), mu=...) with the
     Qwen-Image scheduler config (dynamic exponential shift + terminal stretch), numpy float32.
     Returns (timesteps [N] fp32, sigmas [N+1] fp32 with trailing 0)."""
-    sigmas = np.linspace(1.0, 1.0 / num_inference_steps, num_inference_steps).astype(np.float32)
+    if sigmas is None:
+        sigmas = np.linspace(1.0, 1.0 / num_inference_steps, num_inference_steps)
+    sigmas = np.array(sigmas).astype(np.float32)      # pipeline's default, or the caller's `sigmas=` list
     mu = calculate_shift(image_seq_len)
     sigmas = math.exp(mu) / (math.exp(mu) + (1 / sigmas - 1) ** 1.0)
     one_minus = 1 - sigmas

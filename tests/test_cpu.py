@@ -154,6 +154,13 @@ def test_schedule_matches_oracle():
     assert latent_hw(1024, 1024) == (128, 128) and latent_hw(1328, 1328) == (166, 166)
     with pytest.raises(ValueError):
         FlowMatchEulerSchedule(0, 256)
+    # caller-supplied pre-shift sigmas (upstream's `sigmas=` argument of the pipeline call)
+    custom = [1.0, 0.8, 0.55, 0.3, 0.1]
+    sch = FlowMatchEulerSchedule(5, 1024, sigmas=custom)
+    ts, sig = O.flowmatch_sigmas(5, 1024, sigmas=custom)
+    assert torch.equal(sch.sigmas, sig) and torch.equal(sch.timesteps, ts) and sig[0] == 1.0
+    with pytest.raises(ValueError):
+        FlowMatchEulerSchedule(4, 1024, sigmas=custom)
 
 
 def test_config_and_input_validation():

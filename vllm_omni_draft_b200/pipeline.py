@@ -76,10 +76,15 @@ class FlowMatchEulerSchedule:
     """FlowMatchEulerDiscreteScheduler.set_timesteps with the Qwen-Image scheduler config
     (dynamic exponential shift, terminal stretch to 0.02); the step itself is the K5 kernel."""
 
-    def __init__(self, num_inference_steps: int, image_seq_len: int, shift_terminal: float = 0.02):
+    def __init__(self, num_inference_steps: int, image_seq_len: int, shift_terminal: float = 0.02, sigmas=None):
         if num_inference_steps < 1:
             raise ValueError("num_inference_steps must be >= 1")
-        sig = np.linspace(1.0, 1.0 / num_inference_steps, num_inference_steps).astype(np.float32)
+        if sigmas is None:
+            sig = np.linspace(1.0, 1.0 / num_inference_steps, num_inference_steps).astype(np.float32)
+        else:       # caller-supplied pre-shift sigmas, as upstream's `sigmas=` argument
+            sig = np.asarray(sigmas, dtype=np.float32)
+            if sig.ndim != 1 or sig.shape[0] != num_inference_steps:
+                raise ValueError("`sigmas` must hold one value per inference step")
         mu = calculate_shift(image_seq_len)
         sig = math.exp(mu) / (math.exp(mu) + (1 / sig - 1) ** 1.0)
         one_minus = 1 - sig
@@ -103,7 +108,7 @@ class DenoiseSession:
     def __init__(self, pipe: "B200QwenImagePipeline", cond: torch.Tensor, uncond: Optional[torch.Tensor],
                  latents: torch.Tensor, Hl: int, Wl: int, num_inference_steps: int, true_cfg_scale: float,
                  use_cuda_graph: bool = False, image_seq_len: Optional[int] = None, batched_cfg: bool = True,
-                 ref_tokens: Optional[torch.Tensor] = None, ref_hw: Optional[Tuple[int, int]] = None):
+                 ref_tokens: Optional[torch.Tensor] = None, ref_hw: Optional[Tuple[int, int]] = None, sigmas=None):
         """ref_tokens [B, S_ref, 64] + ref_hw (token grid of the reference image): edit mode.
         The reference-image tokens sit behind the noise tokens in one resident input buffer, written once;
         each step only refreshes the first S_noise rows."""
@@ -136,7 +141,7 @@ class DenoiseSession:
             for j in range(nb // B):
                 self.x2[j * B:(j + 1) * B, s_img:].copy_(ref_tokens)
         self.shapes = [shapes] * B
-        self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img)
+        self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img, sigmas=sigmas)
         tr.prepare_schedule(self.sched.transformer_timesteps(dt))
         # measured GEMM schedules for this forward's shapes (before any graph capture)
         self.gemm_schedules = tr.tune_schedules(nb, s_img + s_ref, self.s_txt)
@@ -295,7 +300,7 @@ class B200QwenImagePipeline:
         if prompt_embeds_mask is not None and prompt_embeds_mask.dim() != 2:
             raise ValueError("prompt_embeds_mask must be 2D [B, T_txt]")
         if sigmas is not None:
-            raise NotImplementedError("custom sigmas are not supported; the default linspace(1, 1/N, N) is used")
+            num_inference_steps = len(sigmas)
         dev, dt = self.device, self.transformer.dtype
         height = height or 1024
         width = width or 1024
@@ -330,7 +335,7 @@ class B200QwenImagePipeline:
             ref_tokens = ref_tokens.to(dev, dt)
         sess = DenoiseSession(self, cond, uncond, latents.to(dev, dt), Hl, Wl, num_inference_steps,
                               true_cfg_scale, use_cuda_graph=self.use_cuda_graph, batched_cfg=self.batched_cfg,
-                              ref_tokens=ref_tokens, ref_hw=ref_hw)
+                              ref_tokens=ref_tokens, ref_hw=ref_hw, sigmas=sigmas)
         self.last_step_latents = []
         for i in range(num_inference_steps):
             sess.step(i)
