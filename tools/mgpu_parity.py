@@ -24,8 +24,16 @@ def main():
     Hpx, Wpx, s_txt, batch = env("QI_PAR_H", 256), env("QI_PAR_W", 256), env("QI_PAR_TXT", 32), env("QI_PAR_BATCH", 1)
     lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, Hpx, Wpx, s_txt, batch=batch)
     steps = 4
+    edit = os.environ.get("QI_PAR_EDIT", "0") == "1"     # edit mode: a 12x20-token reference image behind the noise tokens
+    ref_tokens = ref_hw = None
+    if edit:
+        gref = torch.Generator().manual_seed(43)
+        ref_tokens = O.pack_latents(torch.randn(batch, 16, 1, 24, 40, generator=gref))
+        ref_hw = (12, 20)
+        shapes = [[shapes[0][0], (1, 12, 20)]] * batch
     den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=os.environ.get("QI_GRAPH", "0") == "1", state_dict=sd)
-    den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), Hpx, Wpx, steps, true_cfg_scale=4.0)
+    den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), Hpx, Wpx, steps, true_cfg_scale=4.0,
+              ref_h=ref_tokens.bfloat16() if edit else None, ref_hw=ref_hw)
     for i in range(steps):
         den.step(i)
     out = torch.zeros(batch, lat.shape[1], 64, dtype=torch.bfloat16).pin_memory()
@@ -44,11 +52,14 @@ def main():
     exch = den.exchange if den.layout.sp_degree > 1 else "-"
     den.close()
     if rank == 0:
-        ref = O.denoise_loop(sd, ocfg, lat, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
+        if edit:
+            ref = O.edit_denoise_loop(sd, ocfg, lat, ref_tokens, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
+        else:
+            ref = O.denoise_loop(sd, ocfg, lat, cond, mask, uncond, mask, steps, 4.0, img_shapes=shapes)
         err = O.rel_l2(full.float().cpu(), ref)
         lay = den.layout
         print(f"MGPU_PARITY world={world} cfg={lay.cfg_degree} sp={lay.sp_degree} exchange={exch} graph={graph_on} "
-              f"px={Hpx}x{Wpx} txt={s_txt} B={batch} rel_l2={err:.4e}", flush=True)
+              f"px={Hpx}x{Wpx} txt={s_txt} B={batch} edit={int(edit)} rel_l2={err:.4e}", flush=True)
         if not err < 1e-2:
             sys.exit(1)
     if world > 1:

@@ -159,7 +159,11 @@ class ParallelDenoiser:
         self.launches_per_step = None
 
     # -------------------------------------------------------------- setup / IO
-    def setup(self, cond_h, uncond_h, lat_h, height, width, num_inference_steps, true_cfg_scale=4.0):
+    def setup(self, cond_h, uncond_h, lat_h, height, width, num_inference_steps, true_cfg_scale=4.0,
+              ref_h=None, ref_hw=None):
+        """ref_h [B, S_ref, 64] + ref_hw = (h, w) token grid: edit mode — the packed reference-image
+        latents ride behind the noise tokens; under sequence parallelism noise and reference tokens are sharded
+        separately, so every rank updates an equal share of the latents."""
         from . import ops
         from .pipeline import DenoiseSession, latent_hw
         lay, dev, dt = self.layout, self.device, self.tr.dtype
@@ -167,6 +171,12 @@ class ParallelDenoiser:
         self.s_img, self.s_txt = lat_h.shape[1], cond_h.shape[1]
         self.i0, self.i1 = shard_bounds(self.s_img, lay.sp_degree, lay.sp_rank)
         self.t0, self.t1 = shard_bounds(self.s_txt, lay.sp_degree, lay.sp_rank)
+        s_ref = 0 if ref_h is None else ref_h.shape[1]
+        if s_ref and (ref_hw is None or ref_hw[0] * ref_hw[1] != s_ref):
+            raise ValueError("reference-image tokens do not match their (h, w) token grid")
+        j0, j1 = shard_bounds(s_ref, lay.sp_degree, lay.sp_rank)
+        ref = ref_h.to(dev, dt)[:, j0:j1].contiguous() if s_ref else None
+        ref_kw = dict(ref_tokens=ref, ref_hw=ref_hw) if s_ref else {}
         self.scale = float(true_cfg_scale)
         if lay.cfg_degree == 1:
             cond, uncond = cond_h.to(dev, dt), (uncond_h.to(dev, dt) if uncond_h is not None else None)
@@ -182,11 +192,13 @@ class ParallelDenoiser:
         batched = not (lay.sp_degree > 1 and self.exchange == "nccl")
         if lay.sp_degree > 1:
             self.tr.set_sequence_shard((1, Hl // 2, Wl // 2), self.s_img, self.s_txt, (self.i0, self.i1),
-                                       (self.t0, self.t1))
+                                       (self.t0, self.t1), ref_shape=(1, ref_hw[0], ref_hw[1]) if s_ref else None,
+                                       ref_range=(j0, j1))
             if self.exchange == "peer":
                 from .peer import PeerExchange, shard_counts
-                rows = [a + b for a, b in zip(shard_counts(self.s_txt, lay.sp_degree),
-                                              shard_counts(self.s_img, lay.sp_degree))]
+                rows = [a + b + c for a, b, c in zip(shard_counts(self.s_txt, lay.sp_degree),
+                                                     shard_counts(self.s_img, lay.sp_degree),
+                                                     shard_counts(s_ref, lay.sp_degree))]
                 if self.peer is not None:
                     self.peer.close()
                 self.peer = PeerExchange(self.sp_group, lay.sp_degree, lay.sp_rank, dev,
@@ -194,18 +206,18 @@ class ParallelDenoiser:
                                          lat.shape[0] * (2 if (batched and lay.cfg_degree == 1 and uncond is not None) else 1),
                                          rows)
                 self.tr._sp.peer = self.peer
-            elif (self.s_img % lay.sp_degree) or (self.s_txt % lay.sp_degree):
+            elif (self.s_img % lay.sp_degree) or (self.s_txt % lay.sp_degree) or (s_ref % lay.sp_degree):
                 raise NotImplementedError("ragged shards need the peer-memory exchange (exchange='peer')")
         if self.world == 1:
             n0 = ops.launch_count
             self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
-                                       use_cuda_graph=self.use_cuda_graph)
+                                       use_cuda_graph=self.use_cuda_graph, **ref_kw)
             if self.use_cuda_graph:
                 # launches recorded while capturing one step (+2 refresh copies are torch memcpys)
                 self.launches_per_step = (ops.launch_count - n0 - 4) // 2
         else:
             self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
-                                       use_cuda_graph=False, image_seq_len=self.s_img, batched_cfg=batched)
+                                       use_cuda_graph=False, image_seq_len=self.s_img, batched_cfg=batched, **ref_kw)
             self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
             if self.use_cuda_graph:
                 # One graph per rank = forward + pair all-gather + K5 (+ the Ulysses all-to-alls inside the
@@ -236,7 +248,7 @@ class ParallelDenoiser:
             ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
             s.cur.copy_(s.nxt)
             return
-        pred = self.tr(hidden_states=s.cur, encoder_hidden_states=s.cond, **kw)[0]
+        pred, _ = self.pipe._predict(s.cur, s.cond, None, kw, None, s.x2)     # x2: [cur; reference-image shard]
         if self.layout.cfg_degree == 2:
             dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
             c, u = self.pair_buf[0], self.pair_buf[1]

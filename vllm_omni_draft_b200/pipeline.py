@@ -135,9 +135,14 @@ class DenoiseSession:
         self.cond, self.uncond = cond, uncond
         shapes = [(1, Hl // 2, Wl // 2)]
         if s_ref:
-            if ref_hw is None or ref_hw[0] * ref_hw[1] != s_ref or ref_tokens.shape[0] != B:
-                raise ValueError("reference-image tokens do not match their (h, w) token grid / the batch")
-            shapes.append((1, int(ref_hw[0]), int(ref_hw[1])))
+            if ref_tokens.shape[0] != B:
+                raise ValueError("reference-image tokens do not match the batch")
+            if tr._sp is None:
+                if ref_hw is None or ref_hw[0] * ref_hw[1] != s_ref:
+                    raise ValueError("reference-image tokens do not match their (h, w) token grid")
+                shapes.append((1, int(ref_hw[0]), int(ref_hw[1])))
+            # (sequence-parallel: ref_tokens is this rank's shard and the RoPE rows come from
+            #  transformer.set_sequence_shard; img_shapes is not consulted)
             for j in range(nb // B):
                 self.x2[j * B:(j + 1) * B, s_img:].copy_(ref_tokens)
         self.shapes = [shapes] * B

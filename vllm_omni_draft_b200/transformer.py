@@ -126,14 +126,22 @@ class B200QwenImageTransformer2DModel(nn.Module):
         self._sp = ctx
         self._ws.clear()
 
-    def set_sequence_shard(self, img_shape, s_img_full: int, s_txt_full: int, img_range, txt_range) -> None:
-        """This rank owns image tokens [i0, i1) and text tokens [t0, t1) of the full sequence; its
-        RoPE rows are the matching rows of the full joint table (text rows first)."""
-        shapes = (tuple(int(v) for v in img_shape),)
-        full = rope.joint_cos_sin(self.cfg.axes_dims_rope, self.cfg.rope_theta, shapes, s_txt_full)
+    def set_sequence_shard(self, img_shape, s_img_full: int, s_txt_full: int, img_range, txt_range,
+                           ref_shape=None, ref_range=None) -> None:
+        """This rank owns image tokens [i0, i1) and text tokens [t0, t1) of the full sequence — and, in edit
+        mode, tokens [j0, j1) of the reference image (second entry of img_shapes, RoPE frame index 1); its RoPE
+        rows are the matching rows of the full joint table (text rows first, then image 0, then image 1)."""
+        shapes = [tuple(int(v) for v in img_shape)]
+        if ref_shape is not None:
+            shapes.append(tuple(int(v) for v in ref_shape))
+        full = rope.joint_cos_sin(self.cfg.axes_dims_rope, self.cfg.rope_theta, tuple(shapes), s_txt_full)
         (i0, i1), (t0, t1) = img_range, txt_range
-        local = torch.cat([full[t0:t1], full[s_txt_full + i0:s_txt_full + i1]], dim=0).contiguous()
-        self._sp_freqs = local.to(self.device)
+        parts = [full[t0:t1], full[s_txt_full + i0:s_txt_full + i1]]
+        if ref_shape is not None:
+            j0, j1 = ref_range
+            r0 = s_txt_full + s_img_full
+            parts.append(full[r0 + j0:r0 + j1])
+        self._sp_freqs = torch.cat(parts, dim=0).contiguous().to(self.device)
 
     # ------------------------------------------------------------------ host-layer conveniences
     @property
