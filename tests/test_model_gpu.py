@@ -261,7 +261,6 @@ _MGPU_CASES = [
     # edit mode (reference-image tokens sharded beside the noise tokens): pure Ulysses and CFG-parallel
     (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PAR_EDIT="1", QI_PAR_TXT="33")),
     (2, dict(QI_GRAPH="1", QI_PAR_EDIT="1")),
-    (4, dict(QI_GRAPH="1", QI_SP_EXCHANGE="peer", QI_PAR_EDIT="1")),
     (4, dict(QI_GRAPH="1", QI_SP_EXCHANGE="peer")),
     (4, dict(QI_GRAPH="1", QI_SP_EXCHANGE="nccl")),
     (4, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PAR_H="272", QI_PAR_W="240",
