@@ -93,6 +93,11 @@ typedef struct {
    * base[h / (heads/P)], laid out [batch, row_prefix[P], 3, heads/P, head_dim], at sequence row
    * row_prefix[my_index] + rope_pos0 + row.  c may be NULL then. */
   const struct qi_peer_scatter* scatter;
+  /* C (and the residual R of QI_EPI_GATED_RESIDUAL) are fp32 instead of bf16; ldc / ld_res / batch strides stay in
+   * ELEMENTS.  QI_EPI_BIAS and QI_EPI_GATED_RESIDUAL only.  The MMDiT residual streams are kept in fp32 this way:
+   * 60 blocks x 2 in-place bf16 roundings otherwise accumulate to a relative error of 1.9e-2. */
+  int c_fp32;
+  int gate_fp32; /* QI_EPI_GATED_RESIDUAL: gate is fp32 [batch, n] (a row of the fp32 modulation table) */
 } qi_gemm_problem_t;
 
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
@@ -137,6 +142,8 @@ typedef struct {
   const void* scale;
   long long mod_batch_stride;
   int rows_per_batch;
+  int x_fp32; /* x rows are fp32 (the residual streams; ld_x still in elements); both row sets of a launch must agree */
+  int mod_fp32; /* shift / scale are fp32 vectors (rows of the fp32 modulation table); both row sets must agree */
 } qi_norm_rows_t;
 int qi_adaln_modulate_multi(const qi_norm_rows_t* segs /* host */, int num_segs /* 1 or 2 */, int d, float eps,
                             qi_stream_t stream);
@@ -217,13 +224,28 @@ int qi_cfg_euler_step(const void* cond, const void* uncond, const void* latents,
                       long long tokens, int channels, float true_cfg_scale, const float* dt_dev,
                       float dt, qi_stream_t stream);
 
+/* Same step with fp32 predictions, fp32 latents and fp32 arithmetic throughout (what the pipeline uses: true CFG
+ * amplifies the rounding of the two predictions by 2s-1, and a bf16 latent re-rounded every step drifts from the fp32
+ * trajectory like sqrt(steps) * 1.7e-3).  out: the fp32 master copy of the new latents; out_bf16 (may be NULL): the
+ * bf16 copy the next forward reads. */
+int qi_cfg_euler_step_f32(const float* cond, const float* uncond, const float* latents, float* out, void* out_bf16,
+                          long long tokens, int channels, float true_cfg_scale, const float* dt_dev, float dt,
+                          qi_stream_t stream);
+
 /* ---- small-M linear (M <= a few rows): y = act_out(act_in(x) W^T + b); used for the timestep
  * embedder, the per-block modulation Linear(SiLU(temb)) and norm_out.linear.  HBM-bound on W. */
 int qi_small_linear(const void* x, const void* w, const void* bias, void* y, int m, int n, int k,
                     int ld_x, int ld_y, int silu_in, int silu_out, qi_stream_t stream);
 
+/* Same with fp32 activations in and out and no intermediate rounding (weights stay bf16): the timestep embedder
+ * and the modulation Linear feed every block of every step, so their rounding error is coherent across the whole
+ * forward; the fp32 form is what the transformer uses by default. */
+int qi_small_linear_f32(const float* x, const void* w, const void* bias, float* y, int m, int n, int k,
+                        int ld_x, int ld_y, int silu_in, int silu_out, qi_stream_t stream);
+
 /* Timesteps(256, flip_sin_to_cos=True, downscale_freq_shift=0, scale=1000): t fp32 [m] -> bf16 [m,256]. */
 int qi_timestep_sinusoid(const float* t, void* out, int m, qi_stream_t stream);
+int qi_timestep_sinusoid_f32(const float* t, float* out, int m, qi_stream_t stream); /* fp32 [m,256] */
 
 /* ---- host-side integer tables (bit-exact parts of the path; no GPU needed).
  * MSRoPE position ids (QwenEmbedRope): img_pos [sum F*H*W, 3], txt_pos [txt_len, 3] (int32, host).

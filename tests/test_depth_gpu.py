@@ -1,0 +1,57 @@
+"""Parity at the depth and shapes bench.py times: all 60 MMDiT blocks at BASELINE.json configs[1] shapes, CUDA
+path vs the oracle in fp32 ON THE GPU over the same (bf16-rounded) weights.  Gate: north_star's relative-L2
+<= 1e-2 for `.sample` and for every per-step latent, PSNR >= 40 dB for the decoded image at the real
+AutoencoderKLQwenImage dimensions.  See tests/depth_parity.py for the mechanics."""
+import json
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOL = 1e-2          # BASELINE.json north_star: per-step latents within relative-L2 <= 1e-2
+
+
+@pytest.fixture(scope="module")
+def model60(cuda_device):
+    free, _ = torch.cuda.mem_get_info()
+    if free < 90e9:
+        pytest.skip("needs ~90 GB of free HBM (41 GB of weights + the fp32 oracle's activations)")
+    from depth_parity import build_model
+    return build_model(60)
+
+
+def _dump(name, res):
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, name), "w") as f:
+            json.dump(res, f, indent=1)
+
+
+def test_forward_60_blocks_vs_fp32_oracle(model60):
+    from depth_parity import forward_depth
+    tr, ocfg = model60
+    res = forward_depth(tr, ocfg, B=2, hh=64, ww=64, s_txt=512)
+    growth = [(r["block"], round(r["h"], 5), round(r["e"], 5)) for r in res["per_block"][::10]]
+    print(f"DEPTH_FORWARD rel_l2_sample={res['rel_l2_sample']:.3e} per-block (block, h, e) {growth} "
+          f"last={res['per_block'][-1]}")
+    _dump("depth_forward.json", res)
+    assert res["rel_l2_sample"] <= TOL
+    assert max(r["h"] for r in res["per_block"]) <= TOL
+    assert max(r["e"] for r in res["per_block"]) <= TOL
+
+
+def test_denoise_8_steps_60_blocks_vs_fp32_oracle(model60):
+    from depth_parity import _init_vae_, loop_depth
+    from vllm_omni_draft_b200.vae import B200QwenImageVAEDecoder
+    tr, ocfg = model60
+    vae = B200QwenImageVAEDecoder(device="cuda:0")          # real dims: base 96, mult (1,2,4,4), 2 res blocks
+    _init_vae_(vae)
+    res = loop_depth(tr, ocfg, steps=8, vae=vae, use_cuda_graph=True)
+    print("DEPTH_LOOP " + json.dumps(res))
+    _dump("depth_loop.json", res)
+    assert all(r["rel_l2"] <= TOL for r in res["per_step"]), res["per_step"]
+    assert res["image_std"] > 0.02
+    assert res["psnr_db"] >= 40.0

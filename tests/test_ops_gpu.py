@@ -490,3 +490,163 @@ def test_gemm_cta_pair(cuda_device, bn):
     finally:
         ops.gemm_set_tile_n(0)
         ops.gemm_set_cta_pair(-1)
+
+
+# ------------------------------------------------------------------ fp32 residual streams (c_fp32 / x_fp32)
+@pytest.mark.parametrize("bn,pair", [(0, -1), (128, 0), (160, 1), (192, 0), (224, 1), (256, 1)])
+@pytest.mark.parametrize("epi", [0, 2])
+def test_gemm_fp32_output_and_residual(cuda_device, bn, pair, epi):
+    """C (and R) in fp32: the residual-stream form of the bias and gated-residual epilogues, every tile width,
+    ragged M and N, two problems in one launch, in place (R aliases C)."""
+    ops = _ops()
+    B, K = 2, 512
+    shapes = [(333, 1096), (77, 1096)]
+    probs, refs, outs, keep = [], [], [], []          # `keep`: a GemmProblem holds raw pointers, not references
+    for i, (M, N) in enumerate(shapes):
+        a, w, bias = _rand((B, M, K), 60 + i), _rand((N, K), 62 + i, 0.05), _rand((N,), 64 + i, 0.5)
+        keep += [a, w, bias]
+        y = torch.matmul(a.float(), w.float().t()) + bias.float()
+        if epi == 2:
+            g = torch.Generator().manual_seed(70 + i)
+            res = torch.randn(B, M, N, generator=g).cuda()                  # fp32 stream, not bf16-representable
+            gate = _rand((B, N), 66 + i)
+            y = res + gate.float()[:, None, :] * y
+            out = res.clone()
+            keep.append(gate)
+            probs.append(ops.gemm_problem(a, w, bias, out, epi, out, gate))
+        else:
+            out = torch.zeros(B, M, N, device="cuda", dtype=torch.float32)
+            probs.append(ops.gemm_problem(a, w, bias, out, epi))
+        refs.append(y)
+        outs.append(out)
+    try:
+        ops.gemm_set_tile_n(bn)
+        ops.gemm_set_cta_pair(pair)
+        ops.gemm(probs)
+        torch.cuda.synchronize()
+    finally:
+        ops.gemm_set_tile_n(0)
+        ops.gemm_set_cta_pair(-1)
+    for out, y in zip(outs, refs):
+        # fp32 in, fp32 out: only the bf16 operands' products (exact in fp32) and summation order differ
+        assert O.rel_l2(out, y) < 1e-5
+
+
+@pytest.mark.parametrize("mod_f32", [False, True])
+@pytest.mark.parametrize("d", [128, 256, 3072])
+def test_adaln_modulate_fp32_rows(cuda_device, d, mod_f32):
+    ops = _ops()
+    B, S1, S2 = 2, 333, 41
+    g = torch.Generator().manual_seed(9)
+    x1, x2 = (torch.randn(B * S1, d, generator=g) * 2).cuda(), (torch.randn(B * S2, d, generator=g) * 2).cuda()
+    mod = _rand((B, 6 * d), 5, 0.3)
+    if mod_f32:
+        mod = (torch.randn(B, 6 * d, generator=g) * 0.3).cuda()
+    o1 = torch.empty(B * S1, d, device="cuda", dtype=torch.bfloat16)
+    o2 = torch.empty(B * S2, d, device="cuda", dtype=torch.bfloat16)
+    ops.adaln_modulate_pair([(x1, mod[:, 0:d], mod[:, d:2 * d], o1, S1), (x2, mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], o2, S2)])
+    m = mod.float()
+    for x, o, S, c0 in ((x1, o1, S1, 0), (x2, o2, S2, 3 * d)):
+        ref = O.layer_norm(x.view(B, S, d)) * (1 + m[:, None, c0 + d:c0 + 2 * d]) + m[:, None, c0:c0 + d]
+        assert O.rel_l2(o.view(B, S, d), ref) < 3e-3            # one bf16 rounding of the result
+
+
+def test_time_embed_and_modulation_fp32(cuda_device):
+    """qi_timestep_sinusoid_f32 + qi_small_linear_f32: the fp32 timestep-embedding / modulation chain vs PyTorch fp32."""
+    ops = _ops()
+    M, d, n = 5, 256, 1544
+    t = torch.tensor([1.0, 0.7446, 0.5, 0.1, 0.02], device="cuda")
+    w1, b1, w2, b2, wm, bm = (_rand((d, 256), 90, 0.05), _rand((d,), 91, 0.1), _rand((d, d), 92, 0.05), _rand((d,), 93, 0.1),
+                              _rand((n, d), 94, 0.05), _rand((n,), 95, 0.1))
+    sin = torch.empty(M, 256, device="cuda")
+    t1, temb, mod = torch.empty(M, d, device="cuda"), torch.empty(M, d, device="cuda"), torch.empty(M, n, device="cuda")
+    ops.timestep_sinusoid(t, sin)
+    ops.small_linear(sin, w1, b1, t1, silu_out=True)
+    ops.small_linear(t1, w2, b2, temb)
+    ops.small_linear(temb, wm, bm, mod, silu_in=True)
+    F = torch.nn.functional
+    ref_sin = O.timestep_sinusoid(t)
+    ref_temb = F.linear(F.silu(F.linear(ref_sin, w1.float(), b1.float())), w2.float(), b2.float())
+    ref_mod = F.linear(F.silu(ref_temb), wm.float(), bm.float())
+    # cos/sin of arguments up to 1000: one ulp of the frequency moves the argument by 6e-5
+    assert O.rel_l2(sin, ref_sin) < 2e-4
+    assert O.rel_l2(temb, ref_temb) < 2e-4
+    assert O.rel_l2(mod, ref_mod) < 2e-4
+    # given the same sinusoid the two Linears themselves are exact to fp32 summation order
+    ref2 = F.linear(F.silu(F.linear(F.silu(F.linear(sin, w1.float(), b1.float())), w2.float(), b2.float())), wm.float(), bm.float())
+    assert O.rel_l2(mod, ref2) < 5e-6
+
+
+# ------------------------------------------------------------------ torch.ops.qi (dispatcher-visible C ABI)
+def test_torch_ops_inference_mode_and_cuda_graph(cuda_device):
+    """the C ABI registered as torch.library ops — callable under inference_mode and capturable."""
+    import vllm_omni_draft_b200.torch_ops as T
+    Q = torch.ops.qi
+    assert set(T.OP_NAMES) >= {"gemm_bf16", "attention_fwd", "adaln_modulate", "qknorm_rope", "cfg_euler_step"}
+    B, S, H, Dh, d = 1, 256, 2, 128, 256
+    with torch.inference_mode():
+        a, w, bias = _rand((B, S, d), 80), _rand((3 * d, d), 81, 0.05), _rand((3 * d,), 82)
+        qkv = torch.zeros(B, S, 3 * d, device="cuda", dtype=torch.bfloat16)
+        o = torch.zeros(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
+        h = torch.randn(B, S, d, device="cuda")
+        gate, wo, bo = _rand((B, d), 83), _rand((d, d), 84, 0.05), _rand((d,), 85)
+        xn = torch.empty(B * S, d, device="cuda", dtype=torch.bfloat16)
+        mod = _rand((B, 2 * d), 86, 0.3)
+        c, u, x = _rand((B, S, 64), 87), _rand((B, S, 64), 88), _rand((B, S, 64), 89)
+        nxt = torch.empty_like(x)
+
+        def body():
+            Q.adaln_modulate([h.view(B * S, d)], [mod[:, :d]], [mod[:, d:]], [xn], [S])
+            Q.gemm_bf16([xn.view(B, S, d)], [w], [bias], [qkv], 0, [None], [None])
+            q, k, v = (qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3))
+            Q.attention_fwd(q, k, v, o)
+            Q.gemm_bf16([o.view(B, S, d)], [wo], [bo], [h], 2, [h], [gate])
+            Q.cfg_euler_step(c, u, x, nxt, 4.0, None, -0.05)
+
+        h0 = h.clone()
+        body()
+        torch.cuda.synchronize()
+        eager_h, eager_n = h.clone(), nxt.clone()
+        h.copy_(h0)
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            body()
+        torch.cuda.current_stream().wait_stream(side)
+        h.copy_(h0)
+        with torch.cuda.graph(g):
+            body()
+        h.copy_(h0)
+        nxt.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(h, eager_h) and torch.equal(nxt, eager_n)
+        # against fp32 PyTorch
+        xr = O.layer_norm(h0) * (1 + mod.float()[:, None, d:]) + mod.float()[:, None, :d]
+        qkv_r = xr.bfloat16().float() @ w.float().t() + bias.float()
+        qr, kr, vr = (qkv_r[:, :, i * d:(i + 1) * d].bfloat16().float().unflatten(-1, (H, Dh)).transpose(1, 2) for i in range(3))
+        orf = torch.nn.functional.scaled_dot_product_attention(qr, kr, vr).transpose(1, 2).flatten(2)
+        hr = h0 + gate.float()[:, None] * (orf.bfloat16().float() @ wo.float().t() + bo.float())
+        assert O.rel_l2(eager_h, hr) < 3e-3
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        Q.attention_fwd(torch.zeros(1, 8, 1, 64), torch.zeros(1, 8, 1, 64), torch.zeros(1, 8, 1, 64),
+                        torch.zeros(1, 8, 1, 64))          # CPU tensors: no such kernel, no fallback
+
+
+def test_cfg_euler_step_f32_matches_oracle(cuda_device):
+    """K5 in fp32 (the pipeline's form): fp32 predictions and latents, in place, + the bf16 copy for the next forward."""
+    ops = _ops()
+    B, S = 2, 4096 + 3
+    g = torch.Generator().manual_seed(4)
+    c, u, x = (torch.randn(B, S, 64, generator=g).cuda() for _ in range(3))
+    sig = torch.tensor([0.7446114, 0.4266735])
+    ref = O.scheduler_step(O.true_cfg_combine(c, u, 4.0), x, sig[0].cuda(), sig[1].cuda())
+    xb = torch.empty(B, S, 64, device="cuda", dtype=torch.bfloat16)
+    x1 = x.clone()
+    ops.cfg_euler_step_f32(c, u, x1, x1, xb, 4.0, dt=float(sig[1] - sig[0]))       # in place
+    assert O.rel_l2(x1, ref) < 1e-6
+    assert torch.equal(xb, x1.bfloat16())
+    out = torch.empty_like(x)
+    ops.cfg_euler_step_f32(c, None, x, out, None, 1.0, dt_dev=(sig[1] - sig[0]).reshape(1).cuda())
+    assert O.rel_l2(out, O.scheduler_step(c, x, sig[0].cuda(), sig[1].cuda())) < 1e-6

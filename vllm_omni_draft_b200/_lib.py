@@ -32,13 +32,14 @@ class GemmProblem(C.Structure):
         ("qk_norm_wq", _vp), ("qk_norm_wk", _vp), ("rope_cos_sin", _vp),
         ("rope_pos0", _i), ("heads", _i), ("head_dim", _i), ("qk_norm_eps", C.c_float),
         ("scatter", _vp),
+        ("c_fp32", _i), ("gate_fp32", _i),
     ]
 
 
 class NormRows(C.Structure):
     """qi_norm_rows_t"""
     _fields_ = [("x", _vp), ("y", _vp), ("rows", _i), ("ld_x", _i), ("ld_y", _i), ("shift", _vp), ("scale", _vp),
-                ("mod_batch_stride", _ll), ("rows_per_batch", _i)]
+                ("mod_batch_stride", _ll), ("rows_per_batch", _i), ("x_fp32", _i), ("mod_fp32", _i)]
 
 
 class PeerScatter(C.Structure):
@@ -74,8 +75,11 @@ _SIGNATURES = {
     "qi_rmsnorm_affine": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp]),
     "qi_qknorm_rope": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp]),
     "qi_cfg_euler_step": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _f, _vp, _f, _vp]),
+    "qi_cfg_euler_step_f32": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _vp, _f, _vp]),
     "qi_small_linear": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "qi_timestep_sinusoid": (_i, [_vp, _vp, _i, _vp]),
+    "qi_small_linear_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "qi_timestep_sinusoid_f32": (_i, [_vp, _vp, _i, _vp]),
     "qi_rope_position_ids": (_i, [C.POINTER(C.c_int), _i, _i, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "qi_pack_latents_index": (_i, [_i, _i, _i, C.POINTER(C.c_int64)]),
 }

@@ -23,6 +23,15 @@ __device__ __forceinline__ uint4 ldg128_stream(const void* p) {
   return r;
 }
 __device__ __forceinline__ void stg128(void* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }
+__device__ __forceinline__ uint2 ldg64(const void* p) { return *reinterpret_cast<const uint2*>(p); }
+__device__ __forceinline__ void stg64(void* p, uint2 v) { *reinterpret_cast<uint2*>(p) = v; }
+__device__ __forceinline__ float4 ldg_f4_stream(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
 
 __device__ __forceinline__ void unpack8(uint4 u, float (&f)[8]) {
   float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
@@ -47,17 +56,35 @@ __device__ __forceinline__ float group_sum(float v) {
 // ~40 registers per thread, so an SM keeps 16 rows (~100 KB of loads) in flight; the two
 // reductions (mean, then centred variance) go warp shuffle -> 4 partials in shared memory.
 struct NormSeg {   // one set of rows sharing strides and modulation vectors
-  const __nv_bfloat16* x;
+  const __nv_bfloat16* x;    // fp32 rows when the kernel is instantiated with XF32 (the fp32 residual streams)
   __nv_bfloat16* y;
   const __nv_bfloat16* shift;
   const __nv_bfloat16* scale;
   long long mod_batch_stride;
   int rows, ld_x, ld_y, rows_per_batch;
+  int mod_fp32;              // shift / scale are fp32 vectors (the fp32 modulation table), else bf16
 };
 
 // Up to two segments per launch (the img and txt streams of a block): block b < seg0.rows works on
 // segment 0, the others on segment 1.
-template <int CPT, int MODE>
+// XF32: x is fp32 (the residual streams h / e are kept in fp32).  A thread then owns, per 1024-element
+// chunk, elements [4 tid, +4) and [512 + 4 tid, +4): two fully coalesced 16-byte loads in, two 8-byte stores out.
+// 8 fp32 modulation values for the elements a thread owns in chunk c (same ownership as the x loads)
+template <bool XF32>
+__device__ __forceinline__ void load_mod_f32(const float* p, int c, int tid, float (&o)[8]) {
+  float4 a, b;
+  if constexpr (XF32) {
+    a = *reinterpret_cast<const float4*>(p + c * 1024 + tid * 4);
+    b = *reinterpret_cast<const float4*>(p + c * 1024 + 512 + tid * 4);
+  } else {
+    const float4* q = reinterpret_cast<const float4*>(p + (c * 128 + tid) * 8);
+    a = q[0];
+    b = q[1];
+  }
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+
+template <int CPT, int MODE, bool XF32>
 __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ NormSeg s0,
                                                         const __grid_constant__ NormSeg s1,
                                                         float eps) {
@@ -76,9 +103,22 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ 
   const int tid = threadIdx.x;
   const int lane = tid & 31, wid = tid >> 5;
   constexpr int D = CPT * 1024;
-  const __nv_bfloat16* xr = x + (size_t)row * ld_x;
   float v[CPT][8];
-  {
+  if constexpr (XF32) {
+    const float* xr = reinterpret_cast<const float*>(x) + (size_t)row * ld_x;
+    float4 raw[CPT][2];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      raw[c][0] = ldg_f4_stream(xr + c * 1024 + tid * 4);
+      raw[c][1] = ldg_f4_stream(xr + c * 1024 + 512 + tid * 4);
+    }
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      v[c][0] = raw[c][0].x; v[c][1] = raw[c][0].y; v[c][2] = raw[c][0].z; v[c][3] = raw[c][0].w;
+      v[c][4] = raw[c][1].x; v[c][5] = raw[c][1].y; v[c][6] = raw[c][1].z; v[c][7] = raw[c][1].w;
+    }
+  } else {
+    const __nv_bfloat16* xr = x + (size_t)row * ld_x;
     uint4 raw[CPT];
 #pragma unroll
     for (int c = 0; c < CPT; ++c) raw[c] = ldg128_stream(xr + (c * 128 + tid) * 8);
@@ -89,11 +129,26 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ 
   const int b = row / rows_per_batch;
   const __nv_bfloat16* sh = (MODE == 0) ? shift + (size_t)b * mod_batch_stride : nullptr;
   const __nv_bfloat16* sc = scale + ((MODE == 0) ? (size_t)b * mod_batch_stride : 0);
+  // fp32 modulation vectors (12 KB per batch item, L1/L2 resident) are read after the reductions instead, which
+  // keeps the register count (and with it the rows in flight per SM) where the bf16 variant has it
+  const bool mf32 = (MODE == 0) && s0.mod_fp32;
+  const float* sh32 = reinterpret_cast<const float*>(shift) + (size_t)b * mod_batch_stride;
+  const float* sc32 = reinterpret_cast<const float*>(scale) + (size_t)b * mod_batch_stride;
   uint4 wraw[CPT], hraw[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
-    wraw[c] = ldg128(sc + (c * 128 + tid) * 8);
-    if (MODE == 0) hraw[c] = ldg128(sh + (c * 128 + tid) * 8);
+    if (mf32) break;
+    if constexpr (XF32) {
+      const uint2 lo = ldg64(sc + c * 1024 + tid * 4), hi = ldg64(sc + c * 1024 + 512 + tid * 4);
+      wraw[c] = make_uint4(lo.x, lo.y, hi.x, hi.y);
+      if (MODE == 0) {
+        const uint2 l2 = ldg64(sh + c * 1024 + tid * 4), h2 = ldg64(sh + c * 1024 + 512 + tid * 4);
+        hraw[c] = make_uint4(l2.x, l2.y, h2.x, h2.y);
+      }
+    } else {
+      wraw[c] = ldg128(sc + (c * 128 + tid) * 8);
+      if (MODE == 0) hraw[c] = ldg128(sh + (c * 128 + tid) * 8);
+    }
   }
   float s = 0.f;
 #pragma unroll
@@ -127,17 +182,25 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ 
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     float w[8], o[8];
-    unpack8(wraw[c], w);
+    if (mf32) load_mod_f32<XF32>(sc32, c, tid, w);
+    else unpack8(wraw[c], w);
     if (MODE == 0) {
       float h[8];
-      unpack8(hraw[c], h);
+      if (mf32) load_mod_f32<XF32>(sh32, c, tid, h);
+      else unpack8(hraw[c], h);
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mean) * rstd * (1.f + w[j]) + h[j];
     } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = bf16_round(v[c][j] * rstd) * w[j];
     }
-    stg128(yr + (c * 128 + tid) * 8, pack8(o));
+    const uint4 pk = pack8(o);
+    if constexpr (XF32) {
+      stg64(yr + c * 1024 + tid * 4, make_uint2(pk.x, pk.y));
+      stg64(yr + c * 1024 + 512 + tid * 4, make_uint2(pk.z, pk.w));
+    } else {
+      stg128(yr + (c * 128 + tid) * 8, pk);
+    }
   }
 }
 
@@ -145,7 +208,18 @@ __global__ void __launch_bounds__(128) norm_rows_kernel(const __grid_constant__ 
 // Generic-width variant (any d % 8 == 0): the row is re-read from L1/L2 for the second and third
 // pass instead of being held in registers.  Only used for widths without a register instantiation
 // (e.g. the tiny test config's joint_attention_dim = 128).
-template <int MODE>
+template <bool XF32>
+__device__ __forceinline__ void load_row8(const __nv_bfloat16* xr, int off, float (&v)[8]) {
+  if constexpr (XF32) {
+    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xr) + off);
+    const float4 a = p[0], b = p[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+    unpack8(ldg128(xr + off), v);
+  }
+}
+
+template <int MODE, bool XF32>
 __global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_constant__ NormSeg s0,
                                                                 const __grid_constant__ NormSeg s1,
                                                                 int d, float eps) {
@@ -163,11 +237,13 @@ __global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_con
   const long long mod_batch_stride = second ? s1.mod_batch_stride : s0.mod_batch_stride;
   const int ld_x = second ? s1.ld_x : s0.ld_x, ld_y = second ? s1.ld_y : s0.ld_y;
   const int rows_per_batch = second ? s1.rows_per_batch : s0.rows_per_batch;
-  const __nv_bfloat16* xr = x + (size_t)warp * ld_x;
+  // (for XF32 the row pointer is kept in bf16 units of the fp32 row: load_row8 re-derives the float address)
+  const __nv_bfloat16* xr = XF32 ? reinterpret_cast<const __nv_bfloat16*>(reinterpret_cast<const float*>(x) + (size_t)warp * ld_x)
+                                 : x + (size_t)warp * ld_x;
   float s = 0.f;
   for (int off = lane * 8; off < d; off += 256) {
     float v[8];
-    unpack8(ldg128(xr + off), v);
+    load_row8<XF32>(xr, off, v);
 #pragma unroll
     for (int j = 0; j < 8; ++j) s += (MODE == 0) ? v[j] : v[j] * v[j];
   }
@@ -178,7 +254,7 @@ __global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_con
     float q = 0.f;
     for (int off = lane * 8; off < d; off += 256) {
       float v[8];
-      unpack8(ldg128(xr + off), v);
+      load_row8<XF32>(xr, off, v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
     }
@@ -193,11 +269,14 @@ __global__ void __launch_bounds__(128) norm_rows_generic_kernel(const __grid_con
   __nv_bfloat16* yr = y + (size_t)warp * ld_y;
   for (int off = lane * 8; off < d; off += 256) {
     float v[8], w[8], o[8];
-    unpack8(ldg128(xr + off), v);
-    unpack8(ldg128(sc + off), w);
+    load_row8<XF32>(xr, off, v);
+    const bool mf32 = (MODE == 0) && s0.mod_fp32;
+    if (mf32) load_row8<true>(reinterpret_cast<const __nv_bfloat16*>(reinterpret_cast<const float*>(scale) + (size_t)b * mod_batch_stride), off, w);
+    else unpack8(ldg128(sc + off), w);
     if (MODE == 0) {
       float h[8];
-      unpack8(ldg128(sh + off), h);
+      if (mf32) load_row8<true>(reinterpret_cast<const __nv_bfloat16*>(reinterpret_cast<const float*>(shift) + (size_t)b * mod_batch_stride), off, h);
+      else unpack8(ldg128(sh + off), h);
 #pragma unroll
       for (int j = 0; j < 8; ++j) o[j] = (v[j] - mean) * rstd * (1.f + w[j]) + h[j];
     } else {
@@ -406,16 +485,58 @@ __global__ void __launch_bounds__(256) cfg_euler_kernel(
   if (active) stg128(out + off, pack8(o));
 }
 
+// K5, fp32 form: predictions, latents and all arithmetic in fp32 (the form the pipeline uses).  True CFG amplifies
+// whatever error the two predictions carry by (2 s - 1) = 7 at s = 4 before the norm rescale, and a bf16 latent
+// re-rounded every step random-walks away from the fp32 trajectory (sqrt(50) * 1.7e-3 = 1.2e-2 over 50 steps),
+// so the loop state is an fp32 master copy; `out_bf16` is the copy the next forward's img_in GEMM reads.
+// 16 lanes per token (64 channels = 16 lanes x 4 fp32).
+__global__ void __launch_bounds__(256) cfg_euler_f32_kernel(
+    const float* __restrict__ cond, const float* __restrict__ uncond, const float* x /* may alias out */,
+    float* out, __nv_bfloat16* __restrict__ out_bf16, long long tokens, float cfg_scale,
+    const float* __restrict__ dt_ptr, float dt_scalar) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long tok = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+  const int sub = threadIdx.x & 15;
+  const bool active = tok < tokens;
+  const size_t off = (size_t)(active ? tok : tokens - 1) * 64 + sub * 4;
+  const float dt = dt_ptr ? *dt_ptr : dt_scalar;
+  const float4 c = *reinterpret_cast<const float4*>(cond + off);
+  const float4 xv = *reinterpret_cast<const float4*>(x + off);
+  float4 v = c;
+  if (uncond != nullptr) {
+    const float4 u = *reinterpret_cast<const float4*>(uncond + off);
+    const float4 comb = make_float4(fmaf(cfg_scale, c.x - u.x, u.x), fmaf(cfg_scale, c.y - u.y, u.y),
+                                    fmaf(cfg_scale, c.z - u.z, u.z), fmaf(cfg_scale, c.w - u.w, u.w));
+    float cn = c.x * c.x + c.y * c.y + c.z * c.z + c.w * c.w;
+    float nn = comb.x * comb.x + comb.y * comb.y + comb.z * comb.z + comb.w * comb.w;
+    cn = group_sum<16>(cn);
+    nn = group_sum<16>(nn);
+    const float ratio = sqrtf(cn) / sqrtf(nn);
+    v = make_float4(comb.x * ratio, comb.y * ratio, comb.z * ratio, comb.w * ratio);
+  }
+  const float4 o = make_float4(fmaf(dt, v.x, xv.x), fmaf(dt, v.y, xv.y), fmaf(dt, v.z, xv.z), fmaf(dt, v.w, xv.w));
+  if (active) {
+    *reinterpret_cast<float4*>(out + off) = o;
+    if (out_bf16 != nullptr) stg64(out_bf16 + off, make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w)));
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Small-M linear: y[m, n] = act_out( sum_k act_in(x[m,k]) * W[n,k] + bias[n] ), M <= 32.
 // One warp per output column n: the weight row is streamed once (128-bit loads) and reused for
 // every m from registers; x stays L1/L2 resident.  HBM-bound on the weight bytes.
 // ---------------------------------------------------------------------------------------------
-template <int MT>
+// F32: x and y are fp32 and nothing is rounded in between (the timestep embedder and the modulation Linear feed
+// every block of every step: their bf16 rounding is a coherent error, the largest single term of the path's
+// distance to the fp32 oracle — tools/rounding_ablation.py).  Weights stay bf16.
+template <int MT, bool F32>
 __global__ void __launch_bounds__(256) small_linear_kernel(
-    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ W,
-    const __nv_bfloat16* __restrict__ bias, __nv_bfloat16* __restrict__ y, int M, int N, int K,
+    const void* __restrict__ x_, const __nv_bfloat16* __restrict__ W,
+    const __nv_bfloat16* __restrict__ bias, void* __restrict__ y_, int M, int N, int K,
     int ld_x, int ld_y, int silu_in, int silu_out) {
+  const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(x_);
+  __nv_bfloat16* y = reinterpret_cast<__nv_bfloat16*>(y_);
   pdl_launch_dependents();
   pdl_wait();
   const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -433,11 +554,17 @@ __global__ void __launch_bounds__(256) small_linear_kernel(
     for (int m = 0; m < MT; ++m) {
       if (m0 + m < M) {
         float xv[8];
-        unpack8(ldg128(x + (size_t)(m0 + m) * ld_x + k), xv);
+        if constexpr (F32) {
+          const float4* xp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x_) + (size_t)(m0 + m) * ld_x + k);
+          const float4 a4 = xp[0], b4 = xp[1];
+          xv[0] = a4.x; xv[1] = a4.y; xv[2] = a4.z; xv[3] = a4.w; xv[4] = b4.x; xv[5] = b4.y; xv[6] = b4.z; xv[7] = b4.w;
+        } else {
+          unpack8(ldg128(x + (size_t)(m0 + m) * ld_x + k), xv);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           float a = xv[j];
-          if (silu_in) a = bf16_round(a / (1.f + __expf(-a)));
+          if (silu_in) a = F32 ? a / (1.f + expf(-a)) : bf16_round(a / (1.f + __expf(-a)));
           acc[m] = fmaf(a, w[j], acc[m]);
         }
       }
@@ -450,17 +577,18 @@ __global__ void __launch_bounds__(256) small_linear_kernel(
     if (lane == 0 && m0 + m < M) {
       s += bv;
       if (silu_out) {
-        s = bf16_round(s);
-        s = s / (1.f + __expf(-s));
+        if (!F32) s = bf16_round(s);
+        s = F32 ? s / (1.f + expf(-s)) : s / (1.f + __expf(-s));
       }
-      y[(size_t)(m0 + m) * ld_y + n] = __float2bfloat16_rn(s);
+      if constexpr (F32) reinterpret_cast<float*>(y_)[(size_t)(m0 + m) * ld_y + n] = s;
+      else y[(size_t)(m0 + m) * ld_y + n] = __float2bfloat16_rn(s);
     }
   }
 }
 
 // t [M] fp32 (already rounded the way the caller wants) -> [M, 256] bf16 = [cos(1000 t f_k), sin]
-__global__ void timestep_sinusoid_kernel(const float* __restrict__ t, __nv_bfloat16* __restrict__ out,
-                                         int M) {
+template <bool F32>
+__global__ void timestep_sinusoid_kernel(const float* __restrict__ t, void* __restrict__ out_, int M) {
   pdl_launch_dependents();
   pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -468,8 +596,15 @@ __global__ void timestep_sinusoid_kernel(const float* __restrict__ t, __nv_bfloa
   const int m = i / 128, k = i % 128;
   const float f = expf(-9.210340371976184f * (float)k / 128.f);
   const float a = 1000.f * (t[m] * f);
-  out[(size_t)m * 256 + k] = __float2bfloat16_rn(cosf(a));
-  out[(size_t)m * 256 + 128 + k] = __float2bfloat16_rn(sinf(a));
+  if constexpr (F32) {
+    float* out = reinterpret_cast<float*>(out_);
+    out[(size_t)m * 256 + k] = cosf(a);
+    out[(size_t)m * 256 + 128 + k] = sinf(a);
+  } else {
+    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(out_);
+    out[(size_t)m * 256 + k] = __float2bfloat16_rn(cosf(a));
+    out[(size_t)m * 256 + 128 + k] = __float2bfloat16_rn(sinf(a));
+  }
 }
 
 }  // namespace qi
@@ -485,7 +620,7 @@ using namespace qi;
     if (e__ != cudaSuccess) return QI_ERR_CUDA;        \
   } while (0)
 
-template <int MODE>
+template <int MODE, bool XF32 = false>
 static int launch_norm_rows(const NormSeg& a, const NormSeg& b, int d, float eps, cudaStream_t st) {
   const int rows = a.rows + b.rows;
   if (rows <= 0) return QI_OK;
@@ -494,12 +629,12 @@ static int launch_norm_rows(const NormSeg& a, const NormSeg& b, int d, float eps
   const int blocks_generic = (rows + 3) / 4;
 #define QI_NORM_CASE(NC)                                            \
   case NC:                                                          \
-    qi_launch(norm_rows_kernel<NC, MODE>, dim3(rows), dim3(128), 0, st, a, b, eps); \
+    qi_launch(norm_rows_kernel<NC, MODE, XF32>, dim3(rows), dim3(128), 0, st, a, b, eps); \
     break;
   switch (d % 1024 == 0 ? d / 1024 : 0) {
     QI_NORM_CASE(1) QI_NORM_CASE(2) QI_NORM_CASE(3) QI_NORM_CASE(4)
     default:
-      qi_launch(norm_rows_generic_kernel<MODE>, dim3(blocks_generic), dim3(128), 0, st, a, b, d, eps);
+      qi_launch(norm_rows_generic_kernel<MODE, XF32>, dim3(blocks_generic), dim3(128), 0, st, a, b, d, eps);
   }
 #undef QI_NORM_CASE
   QI_CHECK_LAUNCH();
@@ -518,6 +653,7 @@ static NormSeg make_seg(const void* x, void* y, int rows, int ld_x, int ld_y, co
   s.ld_x = ld_x;
   s.ld_y = ld_y;
   s.rows_per_batch = rows_per_batch;
+  s.mod_fp32 = 0;
   return s;
 }
 
@@ -536,11 +672,19 @@ extern "C" int qi_adaln_modulate_multi(const qi_norm_rows_t* segs, int num_segs,
   if (!segs || num_segs < 1 || num_segs > 2) return QI_ERR_ARG;
   NormSeg s[2];
   memset(s, 0, sizeof(s));
+  s[1].mod_fp32 = segs[0].mod_fp32 ? 1 : 0;
   for (int i = 0; i < num_segs; ++i) {
     const qi_norm_rows_t& g = segs[i];
     if (!g.x || !g.y || !g.shift || !g.scale || g.rows_per_batch <= 0 || g.rows < 0) return QI_ERR_ARG;
+    if ((g.x_fp32 != 0) != (segs[0].x_fp32 != 0) || (g.mod_fp32 != 0) != (segs[0].mod_fp32 != 0))
+      return QI_ERR_ARG;   // one input type and one modulation type per launch
+    if (g.mod_fp32 && ((reinterpret_cast<uintptr_t>(g.shift) | reinterpret_cast<uintptr_t>(g.scale)) & 15 ||
+                       g.mod_batch_stride % 4 != 0))
+      return QI_ERR_ARG;
     s[i] = make_seg(g.x, g.y, g.rows, g.ld_x, g.ld_y, g.shift, g.scale, g.mod_batch_stride, g.rows_per_batch);
+    s[i].mod_fp32 = g.mod_fp32 ? 1 : 0;
   }
+  if (segs[0].x_fp32) return launch_norm_rows<0, true>(s[0], s[1], d, eps, stream);
   return launch_norm_rows<0>(s[0], s[1], d, eps, stream);
 }
 
@@ -634,6 +778,23 @@ extern "C" int qi_cfg_euler_step(const void* cond, const void* uncond, const voi
   return QI_OK;
 }
 
+extern "C" int qi_cfg_euler_step_f32(const float* cond, const float* uncond, const float* latents, float* out,
+                                     void* out_bf16, long long tokens, int channels, float true_cfg_scale,
+                                     const float* dt_dev, float dt, cudaStream_t stream) {
+  if (!cond || !latents || !out) return QI_ERR_ARG;
+  if (channels != 64) return QI_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(cond) | reinterpret_cast<uintptr_t>(uncond) | reinterpret_cast<uintptr_t>(latents) |
+       reinterpret_cast<uintptr_t>(out)) & 15)
+    return QI_ERR_ARG;
+  if (tokens <= 0) return QI_OK;
+  const long long threads = tokens * 16;
+  const int blocks = (int)((threads + 255) / 256);
+  qi_launch(cfg_euler_f32_kernel, dim3(blocks), dim3(256), 0, stream, cond, uncond, latents, out,
+            (__nv_bfloat16*)out_bf16, tokens, true_cfg_scale, dt_dev, dt);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
 extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, void* y, int M,
                                int N, int K, int ld_x, int ld_y, int silu_in, int silu_out,
                                cudaStream_t stream) {
@@ -641,9 +802,20 @@ extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, v
   if (M <= 0 || N <= 0) return QI_OK;
   if (K % 8 != 0 || ld_x % 8 != 0) return QI_ERR_ARG;
   dim3 grid((N + 7) / 8, (M + 3) / 4);
-  qi_launch(small_linear_kernel<4>, grid, dim3(256), 0, stream,
-      (const __nv_bfloat16*)x, (const __nv_bfloat16*)W, (const __nv_bfloat16*)bias,
-      (__nv_bfloat16*)y, M, N, K, ld_x, ld_y, silu_in, silu_out);
+  qi_launch(small_linear_kernel<4, false>, grid, dim3(256), 0, stream, x, (const __nv_bfloat16*)W,
+            (const __nv_bfloat16*)bias, y, M, N, K, ld_x, ld_y, silu_in, silu_out);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_small_linear_f32(const float* x, const void* W, const void* bias, float* y, int M, int N, int K,
+                                   int ld_x, int ld_y, int silu_in, int silu_out, cudaStream_t stream) {
+  if (!x || !W || !y) return QI_ERR_ARG;
+  if (M <= 0 || N <= 0) return QI_OK;
+  if (K % 8 != 0 || ld_x % 4 != 0 || (reinterpret_cast<uintptr_t>(x) & 15)) return QI_ERR_ARG;
+  dim3 grid((N + 7) / 8, (M + 3) / 4);
+  qi_launch(small_linear_kernel<4, true>, grid, dim3(256), 0, stream, (const void*)x, (const __nv_bfloat16*)W,
+            (const __nv_bfloat16*)bias, (void*)y, M, N, K, ld_x, ld_y, silu_in, silu_out);
   QI_CHECK_LAUNCH();
   return QI_OK;
 }
@@ -651,7 +823,15 @@ extern "C" int qi_small_linear(const void* x, const void* W, const void* bias, v
 extern "C" int qi_timestep_sinusoid(const float* t, void* out, int M, cudaStream_t stream) {
   if (!t || !out) return QI_ERR_ARG;
   if (M <= 0) return QI_OK;
-  qi_launch(timestep_sinusoid_kernel, dim3((M * 128 + 127) / 128), dim3(128), 0, stream, t, (__nv_bfloat16*)out, M);
+  qi_launch(timestep_sinusoid_kernel<false>, dim3((M * 128 + 127) / 128), dim3(128), 0, stream, t, out, M);
+  QI_CHECK_LAUNCH();
+  return QI_OK;
+}
+
+extern "C" int qi_timestep_sinusoid_f32(const float* t, float* out, int M, cudaStream_t stream) {
+  if (!t || !out) return QI_ERR_ARG;
+  if (M <= 0) return QI_OK;
+  qi_launch(timestep_sinusoid_kernel<true>, dim3((M * 128 + 127) / 128), dim3(128), 0, stream, t, (void*)out, M);
   QI_CHECK_LAUNCH();
   return QI_OK;
 }

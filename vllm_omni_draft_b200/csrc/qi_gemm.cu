@@ -40,6 +40,8 @@ struct GemmProb {
   long long ldc, c_bs, ld_res, res_bs, gate_bs;
   int m, batch, n, k;
   int epilogue;
+  int c_fp32;        // C and the residual are fp32 (the residual streams), else bf16
+  int gate_fp32;     // gate vectors are fp32 (the fp32 modulation table), else bf16
   int tiles_m;       // per batch item
   int tiles_m_total; // tiles_m * batch
   int tiles_n;
@@ -191,10 +193,17 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
       } else if (gated) {
-        const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
-        const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
-                     g3 = unpack_bf16(gu.w);
-        const float gt[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+        float gt[8];
+        if (P.gate_fp32) {
+          const float4* gp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(P.gate) + (size_t)b * P.gate_bs + n);
+          const float4 ga = gp[0], gb = gp[1];
+          gt[0] = ga.x; gt[1] = ga.y; gt[2] = ga.z; gt[3] = ga.w; gt[4] = gb.x; gt[5] = gb.y; gt[6] = gb.z; gt[7] = gb.w;
+        } else {
+          const uint4 gu = *reinterpret_cast<const uint4*>(grow + n);
+          const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y), g2 = unpack_bf16(gu.z),
+                       g3 = unpack_bf16(gu.w);
+          gt[0] = g0.x; gt[1] = g0.y; gt[2] = g1.x; gt[3] = g1.y; gt[4] = g2.x; gt[5] = g2.y; gt[6] = g3.x; gt[7] = g3.y;
+        }
         const uint4 ru = *slot;          // this row's residual piece (zero outside the matrix)
         const float2 r0 = unpack_bf16(ru.x), r1 = unpack_bf16(ru.y), r2 = unpack_bf16(ru.z),
                      r3 = unpack_bf16(ru.w);
@@ -214,6 +223,94 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
         const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
         if (row0 + rr < P.m && n < P.n)
           *reinterpret_cast<uint4*>(cbase + (size_t)(row0 + rr) * P.ldc + n) = o;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// fp32 variant of epilogue_rows (P.c_fp32): C and the residual R are fp32 — the MMDiT residual streams h / e
+// (QI_EPI_BIAS for img_in / txt_in, QI_EPI_GATED_RESIDUAL for the out-projection and MLP-down).  Same staging scheme
+// with 16-column sub-chunks, so a staged row is again 64 bytes (16 fp32): residual rows are loaded and result rows
+// stored as 64 contiguous bytes per 4 lanes, 8 rows per instruction, the next sub-chunk's residual prefetched.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int row, int n0,
+                                                  uint32_t taddr, int half, uint8_t* stage, Release release) {
+  const int lane = threadIdx.x & 31;
+  const int row0 = row - lane;
+  float* cbase = reinterpret_cast<float*>(P.c) + (size_t)b * P.c_bs;
+  const float* rbase = P.residual ? reinterpret_cast<const float*>(P.residual) + (size_t)b * P.res_bs : nullptr;
+  const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)b * P.gate_bs : nullptr;
+  const bool gated = P.epilogue == QI_EPI_GATED_RESIDUAL;
+  constexpr int NCH = BN / 16, SPLIT = 2 * ((BN / 32 + 1) / 2);   // same column split between the two warps as bf16
+  const int c_begin = half ? SPLIT : 0;
+  const int c_end = half ? NCH : SPLIT;
+  const int piece = lane & 3;          // cooperative pattern: row it*8 + lane/4, 16-byte piece (4 fp32) lane%4
+  const int rsub = lane >> 2;
+  float4 rbuf[4];
+  auto load_residual = [&](int c) {
+    const int n = n0 + c * 16 + piece * 4;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int rr = row0 + it * 8 + rsub;
+      rbuf[it] = (rr < P.m && n < P.n) ? *reinterpret_cast<const float4*>(rbase + (size_t)rr * P.ld_res + n)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  if (gated) load_residual(c_begin);
+#pragma unroll 1
+  for (int c = c_begin; c < c_end; ++c) {
+    if (gated) {
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rr = it * 8 + rsub;
+        *reinterpret_cast<float4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4)) = rbuf[it];
+      }
+      __syncwarp();
+      if (c + 1 < c_end) load_residual(c + 1);
+    }
+    uint32_t r[16];
+    tmem_ld16(taddr + c * 16, r);
+    tmem_ld_wait();
+    if (c == c_end - 1) release();
+    const int n_base = n0 + c * 16;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int n = n_base + g * 4;
+      float4* slot = reinterpret_cast<float4*>(stage + lane * 64 + ((g ^ ((lane >> 1) & 3)) << 4));
+      if (n >= P.n) break;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = __uint_as_float(r[g * 4 + j]);
+      if (P.bias) {
+        const uint2 bu = *reinterpret_cast<const uint2*>(P.bias + n);
+        const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y);
+        v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
+      }
+      if (gated) {
+        float4 gt;
+        if (P.gate_fp32) {
+          gt = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(P.gate) + (size_t)b * P.gate_bs + n);
+        } else {
+          const uint2 gu = *reinterpret_cast<const uint2*>(grow + n);
+          const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y);
+          gt = make_float4(g0.x, g0.y, g1.x, g1.y);
+        }
+        const float4 rs = *slot;          // this row's residual piece (zero outside the matrix)
+        v[0] = fmaf(gt.x, v[0], rs.x); v[1] = fmaf(gt.y, v[1], rs.y);
+        v[2] = fmaf(gt.z, v[2], rs.z); v[3] = fmaf(gt.w, v[3], rs.w);
+      }
+      *slot = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    __syncwarp();
+    {
+      const int n = n_base + piece * 4;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rr = it * 8 + rsub;
+        const float4 o = *reinterpret_cast<const float4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
+        if (row0 + rr < P.m && n < P.n)
+          *reinterpret_cast<float4*>(cbase + (size_t)(row0 + rr) * P.ldc + n) = o;
       }
     }
     __syncwarp();
@@ -384,6 +481,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row,
     }
     if constexpr (BN % 64 == 0)
       epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, stage, release);   // host guarantees head_dim == 64 here
+    return;
+  }
+  if (P.c_fp32) {
+    epilogue_rows_f32<BN>(P, b, row, n0, taddr, half, stage, release);
     return;
   }
   epilogue_rows<BN>(P, b, row, n0, taddr, half, stage, release);
@@ -703,6 +804,9 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   if (in.lda % 8 != 0 || in.ldc % 8 != 0 || in.a_batch_stride % 8 != 0 || in.c_batch_stride % 8 != 0)
     return QI_ERR_ARG;
   if (in.epilogue < 0 || in.epilogue > 3) return QI_ERR_ARG;
+  if (in.c_fp32 && in.epilogue != QI_EPI_BIAS && in.epilogue != QI_EPI_GATED_RESIDUAL) return QI_ERR_UNSUPPORTED;
+  if (in.c_fp32 && in.epilogue == QI_EPI_GATED_RESIDUAL && (reinterpret_cast<uintptr_t>(in.residual) & 15))
+    return QI_ERR_ARG;
   if (in.epilogue == QI_EPI_GATED_RESIDUAL &&
       (!in.residual || !in.gate || in.ld_res % 8 != 0 || in.res_batch_stride % 8 != 0 ||
        in.gate_batch_stride % 8 != 0))
@@ -719,6 +823,9 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.ld_res = in.ld_res; P.res_bs = in.res_batch_stride; P.gate_bs = in.gate_batch_stride;
   P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
   P.epilogue = in.epilogue;
+  P.c_fp32 = in.c_fp32 ? 1 : 0;
+  P.gate_fp32 = (in.gate_fp32 && in.epilogue == QI_EPI_GATED_RESIDUAL) ? 1 : 0;
+  if (P.gate_fp32 && ((reinterpret_cast<uintptr_t>(in.gate) & 15) || in.gate_batch_stride % 4 != 0)) return QI_ERR_ARG;
   P.freqs = nullptr; P.wq = P.wk = nullptr; P.sc_n = 0; P.sc_me = 0; P.sc_tpg = 0;
   if (in.epilogue == QI_EPI_QKV_NORM_ROPE) {
     if (!in.qk_norm_wq || !in.qk_norm_wk || !in.rope_cos_sin || in.rope_pos0 < 0) return QI_ERR_ARG;
@@ -850,7 +957,7 @@ extern "C" int qi_gemm_set_tile_n(int bn) {
 // Measured schedules: (problem dims) -> (pair, bn), filled by the host layer's autotuner
 // (ops.tune_gemm: times every candidate once per new shape before the step is captured into a graph).
 struct TunedSchedule {
-  int num, m[2], batch[2], n[2], k[2], epi[2];
+  int num, m[2], batch[2], n[2], k[2], epi[2];   // epi = epilogue | c_fp32 << 8
   int pair, bn;
 };
 static TunedSchedule g_tuned[512];
@@ -859,7 +966,7 @@ static bool tuned_matches(const TunedSchedule& t, const qi_gemm_problem_t* p, in
   if (t.num != num) return false;
   for (int i = 0; i < num; ++i)
     if (t.m[i] != p[i].m || t.batch[i] != p[i].batch || t.n[i] != p[i].n || t.k[i] != p[i].k ||
-        t.epi[i] != p[i].epilogue)
+        t.epi[i] != (p[i].epilogue | (p[i].c_fp32 ? 256 : 0)))
       return false;
   return true;
 }
@@ -878,7 +985,7 @@ extern "C" int qi_gemm_set_schedule(const qi_gemm_problem_t* problems, int num_p
   t.num = num_problems;
   for (int i = 0; i < num_problems; ++i) {
     t.m[i] = problems[i].m; t.batch[i] = problems[i].batch; t.n[i] = problems[i].n; t.k[i] = problems[i].k;
-    t.epi[i] = problems[i].epilogue;
+    t.epi[i] = problems[i].epilogue | (problems[i].c_fp32 ? 256 : 0);
   }
   t.pair = pair;
   t.bn = bn;

@@ -137,7 +137,13 @@ class ParallelDenoiser:
         else:
             self.tr.init_random_(seed)            # same seed on every rank -> replicated weights
         self.pipe = B200QwenImagePipeline(self.tr)
+        if world > 1:
+            self.pipe.parallel = self        # pipe(...) on every rank = one sharded denoise (see `denoise`)
         self.use_cuda_graph = use_cuda_graph
+        # peer flag-barrier timeout: a rank that died or diverged must surface as an error, not as a hang; host
+        # skew at setup (per-rank autotuning, graph capture) is absorbed by explicit barriers, not by this
+        self.peer_timeout_ms = int(os.environ.get("QI_PEER_TIMEOUT_MS", "10000"))
+        self._setup_key = None
         self.graph = None
         self.sp_group = self.pair_group = None
         if world > 1:
@@ -167,6 +173,12 @@ class ParallelDenoiser:
         from . import ops
         from .pipeline import DenoiseSession, latent_hw
         lay, dev, dt = self.layout, self.device, self.tr.dtype
+        # a previous setup's graph and session hold pointers into the previous peer buffers: drop them first
+        self.graph = None
+        if self.sess is not None:
+            self.sess.close()
+            self.sess = None
+        self._setup_key = None
         Hl, Wl = latent_hw(height, width)
         self.s_img, self.s_txt = lat_h.shape[1], cond_h.shape[1]
         self.i0, self.i1 = shard_bounds(self.s_img, lay.sp_degree, lay.sp_rank)
@@ -175,6 +187,7 @@ class ParallelDenoiser:
         if s_ref and (ref_hw is None or ref_hw[0] * ref_hw[1] != s_ref):
             raise ValueError("reference-image tokens do not match their (h, w) token grid")
         j0, j1 = shard_bounds(s_ref, lay.sp_degree, lay.sp_rank)
+        self.j0, self.j1 = j0, j1
         ref = ref_h.to(dev, dt)[:, j0:j1].contiguous() if s_ref else None
         ref_kw = dict(ref_tokens=ref, ref_hw=ref_hw) if s_ref else {}
         self.scale = float(true_cfg_scale)
@@ -186,7 +199,7 @@ class ParallelDenoiser:
         cond = cond[:, self.t0:self.t1].contiguous()
         if uncond is not None:
             uncond = uncond[:, self.t0:self.t1].contiguous()
-        lat = lat_h.to(dev, dt)[:, self.i0:self.i1].contiguous()
+        lat = lat_h.to(dev)[:, self.i0:self.i1].contiguous()       # dtype kept: it seeds the fp32 master copy
         # stacked (cond, uncond) forward whenever both branches run on this rank; the NCCL exchange
         # is batch-1 only, so it keeps two forwards
         batched = not (lay.sp_degree > 1 and self.exchange == "nccl")
@@ -204,7 +217,7 @@ class ParallelDenoiser:
                 self.peer = PeerExchange(self.sp_group, lay.sp_degree, lay.sp_rank, dev,
                                          self.cfg.num_attention_heads, self.cfg.attention_head_dim,
                                          lat.shape[0] * (2 if (batched and lay.cfg_degree == 1 and uncond is not None) else 1),
-                                         rows)
+                                         rows, timeout_ms=self.peer_timeout_ms)
                 self.tr._sp.peer = self.peer
             elif (self.s_img % lay.sp_degree) or (self.s_txt % lay.sp_degree) or (s_ref % lay.sp_degree):
                 raise NotImplementedError("ragged shards need the peer-memory exchange (exchange='peer')")
@@ -218,17 +231,21 @@ class ParallelDenoiser:
         else:
             self.sess = DenoiseSession(self.pipe, cond, uncond, lat, Hl, Wl, num_inference_steps, self.scale,
                                        use_cuda_graph=False, image_seq_len=self.s_img, batched_cfg=batched, **ref_kw)
-            self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev, dtype=dt)
+            self.pair_buf = torch.empty(2, *lat.shape[:-1], 64, device=dev,
+                                        dtype=torch.float32 if self.sess.precise else dt)
             if self.use_cuda_graph:
                 # One graph per rank = forward + pair all-gather + K5 (+ the Ulysses all-to-alls inside the
                 # forward).  NCCL communicators are created by an eager warm-up step first; capture is
                 # thread-local so the NCCL watchdog thread cannot invalidate it.
                 tr, s = self.tr, self.sess
-                self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=dt)
+                self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=s.mod_table.dtype)
                 self.dt_cur = torch.empty(1, device=dev, dtype=torch.float32)
-                self.mod_cur.copy_(tr._mod_table[0:1])
+                self.mod_cur.copy_(s.mod_table[0:1])
                 self.dt_cur.copy_(s.dts[0:1])
-                keep = s.cur.clone()
+                keep = s.latents_master.clone()
+                # every rank has finished its own autotuning before anyone enters the first flag barrier
+                torch.cuda.synchronize()
+                dist.barrier()
                 self._step_body(self.mod_cur, self.dt_cur)
                 torch.cuda.synchronize()
                 dist.barrier()
@@ -237,36 +254,82 @@ class ParallelDenoiser:
                 with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
                     self._step_body(self.mod_cur, self.dt_cur)
                 self.launches_per_step = ops.launch_count - n0
-                s.cur.copy_(keep)
+                s._load(keep, None)
+            torch.cuda.synchronize()
+            dist.barrier()                  # nobody replays / steps before every rank is set up
+            self.check_exchange()
 
     def _step_body(self, mod, dt_dev) -> None:
-        from . import ops
         s = self.sess
-        kw = dict(img_shapes=s.shapes, txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod)
+        prec = s.precise
+        kw = dict(img_shapes=s.shapes, txt_seq_lens=[s.s_txt], return_dict=False, _mod_override=mod, _out_fp32=prec)
         if self.layout.cfg_degree == 1:
             c, u = self.pipe._predict(s.cur, s.cond, s.uncond, kw, s.enc2, s.x2)
-            ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
-            s.cur.copy_(s.nxt)
-            return
-        pred, _ = self.pipe._predict(s.cur, s.cond, None, kw, None, s.x2)     # x2: [cur; reference-image shard]
-        if self.layout.cfg_degree == 2:
+        else:
+            pred, _ = self.pipe._predict(s.cur, s.cond, None, kw, None, s.x2)     # x2: [cur; reference-image shard]
             dist.all_gather_into_tensor(self.pair_buf.view(-1), pred.reshape(-1), group=self.pair_group)
             c, u = self.pair_buf[0], self.pair_buf[1]
+        if prec:      # fp32 predictions, fp32 master latents updated in place, bf16 copy for the next forward
+            torch.ops.qi.cfg_euler_step_f32(c.contiguous(), None if u is None else u.contiguous(), s.cur32, s.cur32,
+                                            s.cur, self.scale, dt_dev)
         else:
-            c, u = pred, None
-        ops.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev=dt_dev)
-        s.cur.copy_(s.nxt)
+            torch.ops.qi.cfg_euler_step(c, u, s.cur, s.nxt, self.scale, dt_dev)
+            s.cur.copy_(s.nxt)
 
-    def load_inputs(self, cond_h, uncond_h, lat_h):
+    def load_inputs(self, cond_h, uncond_h, lat_h, ref_h=None):
         lay = self.layout
         mine = cond_h if (lay.cfg_degree == 1 or lay.branch == 0) else uncond_h
         self.sess.cond.copy_(mine[:, self.t0:self.t1], non_blocking=True)
         if self.sess.uncond is not None:
             self.sess.uncond.copy_(uncond_h[:, self.t0:self.t1], non_blocking=True)
-        self.sess.load_latents(lat_h[:, self.i0:self.i1])
+        ref = ref_h[:, self.j0:self.j1] if ref_h is not None else None
+        self.sess._load(lat_h[:, self.i0:self.i1], ref)
 
     def read_latents(self, out_h):
+        """This rank's shard of the current latents into its rows of a host buffer (no gather; see `gather_latents`)."""
         out_h[:, self.i0:self.i1].copy_(self.sess.latents, non_blocking=True)
+
+    def gather_latents(self) -> torch.Tensor:
+        """Complete current latents [B, S_img, 64] on every rank (device).  The shards of a sequence-parallel group
+        are ragged, so each rank drops its shard into a zero buffer and the group sums it (exact: x + 0)."""
+        lat = self.sess.latents_master       # fp32 loop state in precise mode
+        if self.layout.sp_degree == 1:
+            return lat.clone()
+        full = torch.zeros(lat.shape[0], self.s_img, lat.shape[2], device=lat.device, dtype=lat.dtype)
+        full[:, self.i0:self.i1] = lat
+        dist.all_reduce(full, group=self.sp_group)
+        return full
+
+    def check_exchange(self) -> None:
+        """Raise if a peer flag barrier timed out (a rank died or the launch sequences diverged): after a timeout
+        the barriers stop waiting, so every later step would silently read stale peer data."""
+        if self.peer is not None and self.peer.timed_out():
+            raise RuntimeError("peer-memory exchange: a flag barrier timed out; the latents of this run are invalid")
+
+    # -------------------------------------------------------------- the pipeline call, sharded
+    def denoise(self, cond, uncond, latents, height, width, num_inference_steps, true_cfg_scale=4.0,
+                ref_tokens=None, ref_hw=None, sigmas=None) -> torch.Tensor:
+        """What `B200QwenImagePipeline.__call__` runs when this denoiser is attached: every rank passes the same
+        full-size inputs (host or device), the ranks shard them, run the schedule and return the complete final
+        latents on every rank.  Setup (peer buffers, modulation table, tuning, graph) is kept across calls of the
+        same shapes."""
+        if sigmas is not None:
+            raise NotImplementedError("custom sigmas are not plumbed through the multi-GPU launcher")
+        if uncond is None and self.layout.cfg_degree == 2:
+            raise ValueError("CFG-parallel layout needs negative_prompt_embeds (or build with cfg_parallel=False)")
+        key = (tuple(cond.shape), None if uncond is None else tuple(uncond.shape), tuple(latents.shape), height, width,
+               num_inference_steps, float(true_cfg_scale), None if ref_tokens is None else (tuple(ref_tokens.shape), ref_hw))
+        if key != self._setup_key:
+            self.setup(cond, uncond, latents, height, width, num_inference_steps, true_cfg_scale,
+                       ref_h=ref_tokens, ref_hw=ref_hw)
+            self._setup_key = key
+        else:
+            self.load_inputs(cond, uncond, latents, ref_tokens)
+        for i in range(num_inference_steps):
+            self.step(i)
+        out = self.gather_latents()
+        self.check_exchange()
+        return out
 
     # -------------------------------------------------------------- one step
     def step(self, i: int) -> None:
@@ -276,11 +339,11 @@ class ParallelDenoiser:
             return
         s = self.sess
         if self.graph is not None:
-            self.mod_cur.copy_(self.tr._mod_table[i:i + 1])
+            self.mod_cur.copy_(s.mod_table[i:i + 1])
             self.dt_cur.copy_(s.dts[i:i + 1])
             self.graph.replay()
         else:
-            self._step_body(self.tr._mod_table[i:i + 1], s.dts[i:i + 1])
+            self._step_body(s.mod_table[i:i + 1], s.dts[i:i + 1])
 
     def exchange_timed_out(self) -> bool:
         """True if a peer barrier gave up waiting (a rank died or the launch sequences diverged)."""

@@ -36,6 +36,18 @@ def _req_bf16(*ts: torch.Tensor) -> None:
             raise ValueError("innermost dimension must be contiguous")
 
 
+def _req_bf16_or_f32(*ts: torch.Tensor) -> bool:
+    """Residual-stream operands (GEMM C / R, K1 input) may be fp32; all of them must agree.  Returns is_fp32."""
+    ts = [t for t in ts if t is not None]
+    f32 = bool(ts) and ts[0].dtype == torch.float32
+    for t in ts:
+        if t.dtype != (torch.float32 if f32 else torch.bfloat16) or not t.is_cuda:
+            raise ValueError("expected CUDA tensors, all bf16 or all fp32 (residual streams)")
+        if t.stride(-1) != 1:
+            raise ValueError("innermost dimension must be contiguous")
+    return f32
+
+
 def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                  epilogue: int = EPI_BIAS, residual: Optional[torch.Tensor] = None,
                  gate: Optional[torch.Tensor] = None, a_k_chunked: bool = False,
@@ -48,7 +60,11 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
     EPI_QKV_NORM_ROPE: w is the stacked [3*heads*head_dim, K] q|k|v projection, qk_norm = (norm_q weight,
     norm_k weight), freqs fp32 [rows, head_dim/2, 2]; row r uses table row rope_pos0 + r.  With `scatter`
     the head vectors go to the head owners' attention input buffers and `out` may be None."""
-    _req_bf16(a, w, bias, out, residual, gate)
+    _req_bf16(a, w, bias)
+    gate_fp32 = _req_bf16_or_f32(gate)
+    c_fp32 = _req_bf16_or_f32(out, residual)
+    if c_fp32 and epilogue not in (EPI_BIAS, EPI_GATED_RESIDUAL):
+        raise ValueError("fp32 outputs are supported by the bias and gated-residual epilogues only")
     chunk = None
     if a_k_chunked:
         # [chunks, M, Kc] or [chunks, B, M, Kc]
@@ -100,6 +116,7 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
         p.residual, p.ld_res, p.res_batch_stride = residual.data_ptr(), residual.stride(1), residual.stride(0)
         p.gate, p.gate_batch_stride = gate.data_ptr(), gate.stride(0)
     p.m, p.batch, p.n, p.k, p.epilogue = M, B, N, K, epilogue
+    p.c_fp32, p.gate_fp32 = int(c_fp32), int(gate_fp32)
     if chunk is not None:
         p.a_k_chunk, p.a_k_chunk_stride = chunk
     return p
@@ -130,7 +147,7 @@ _SPLIT_MARGIN = 0.97         # a split must win by 3 % (one more launch; keeps n
 
 
 def _gemm_key(problems: Sequence[GemmProblem]):
-    return tuple((p.m, p.batch, p.n, p.k, p.epilogue) for p in problems)
+    return tuple((p.m, p.batch, p.n, p.k, p.epilogue, p.c_fp32) for p in problems)
 
 
 def _time_launches(fn, launches: int, groups: int) -> float:
@@ -327,8 +344,10 @@ def adaln_modulate_pair(segs: Sequence[Tuple[torch.Tensor, torch.Tensor, torch.T
     global launch_count
     arr = (_lib.NormRows * len(segs))()
     d = segs[0][0].shape[1]
+    x_fp32 = _req_bf16_or_f32(*[seg[0] for seg in segs])
+    mod_fp32 = _req_bf16_or_f32(*[t for seg in segs for t in seg[1:3]])
     for i, (x, shift, scale, out, rpb) in enumerate(segs):
-        _req_bf16(x, shift, scale, out)
+        _req_bf16(out)
         if x.shape[1] != d:
             raise ValueError("all row sets must share the width")
         if shift.stride(0) != scale.stride(0) and shift.shape[0] > 1:
@@ -336,6 +355,7 @@ def adaln_modulate_pair(segs: Sequence[Tuple[torch.Tensor, torch.Tensor, torch.T
         a = arr[i]
         a.x, a.y, a.rows, a.ld_x, a.ld_y = x.data_ptr(), out.data_ptr(), x.shape[0], x.stride(0), out.stride(0)
         a.shift, a.scale, a.mod_batch_stride, a.rows_per_batch = shift.data_ptr(), scale.data_ptr(), shift.stride(0), rpb
+        a.x_fp32, a.mod_fp32 = int(x_fp32), int(mod_fp32)
     check(_lib.lib().qi_adaln_modulate_multi(arr, len(segs), d, float(eps), _stream()), "qi_adaln_modulate_multi")
     launch_count += 1
 
@@ -380,14 +400,37 @@ def cfg_euler_step(cond: torch.Tensor, uncond: Optional[torch.Tensor], latents: 
     return out
 
 
+def cfg_euler_step_f32(cond: torch.Tensor, uncond: Optional[torch.Tensor], latents: torch.Tensor, out: torch.Tensor,
+                       out_bf16: Optional[torch.Tensor], true_cfg_scale: float, dt: float = 0.0,
+                       dt_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """K5 in fp32: cond / uncond / latents / out fp32 [.., 64]; out_bf16 (optional) receives the rounded copy."""
+    global launch_count
+    for t in (cond, uncond, latents, out):
+        if t is not None and (t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous()):
+            raise ValueError("cfg_euler_step_f32 needs contiguous CUDA fp32 tensors")
+    if out_bf16 is not None:
+        _req_bf16(out_bf16)
+        if not out_bf16.is_contiguous() or out_bf16.numel() != out.numel():
+            raise ValueError("out_bf16 must be a contiguous bf16 tensor of the same size as out")
+    tokens = cond.numel() // cond.shape[-1]
+    check(_lib.lib().qi_cfg_euler_step_f32(cond.data_ptr(), _ptr(uncond), latents.data_ptr(), out.data_ptr(),
+                                           _ptr(out_bf16), tokens, cond.shape[-1], float(true_cfg_scale),
+                                           _ptr(dt_dev), float(dt), _stream()), "qi_cfg_euler_step_f32")
+    launch_count += 1
+    return out
+
+
 def small_linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                  silu_in: bool = False, silu_out: bool = False) -> torch.Tensor:
+    """x, out bf16 — or both fp32 (qi_small_linear_f32: no rounding between input and output); w, bias bf16."""
     global launch_count
-    _req_bf16(x, w, bias, out)
+    _req_bf16(w, bias)
+    f32 = _req_bf16_or_f32(x, out)
     M, K = x.shape
     N = w.shape[0]
-    check(_lib.lib().qi_small_linear(x.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), M, N, K, x.stride(0),
-                                     out.stride(0), int(silu_in), int(silu_out), _stream()), "qi_small_linear")
+    fn = _lib.lib().qi_small_linear_f32 if f32 else _lib.lib().qi_small_linear
+    check(fn(x.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), M, N, K, x.stride(0),
+             out.stride(0), int(silu_in), int(silu_out), _stream()), "qi_small_linear")
     launch_count += 1
     return out
 
@@ -396,7 +439,10 @@ def timestep_sinusoid(t: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     global launch_count
     if t.dtype != torch.float32 or not t.is_cuda:
         raise ValueError("timestep must be CUDA fp32")
-    check(_lib.lib().qi_timestep_sinusoid(t.data_ptr(), out.data_ptr(), t.numel(), _stream()), "qi_timestep_sinusoid")
+    if out.dtype not in (torch.bfloat16, torch.float32) or not out.is_contiguous() or out.shape[-1] != 256:
+        raise ValueError("out must be contiguous [m, 256] bf16 or fp32")
+    fn = _lib.lib().qi_timestep_sinusoid_f32 if out.dtype == torch.float32 else _lib.lib().qi_timestep_sinusoid
+    check(fn(t.data_ptr(), out.data_ptr(), t.numel(), _stream()), "qi_timestep_sinusoid")
     launch_count += 1
     return out
 

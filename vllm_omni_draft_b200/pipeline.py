@@ -103,7 +103,12 @@ class FlowMatchEulerSchedule:
 class DenoiseSession:
     """State of one denoising run: resident embeddings, ping-pong latent buffers, the hoisted
     modulation table and (optionally) one captured CUDA graph of a full step.  `step(i)` advances
-    the latents by one scheduler step; `load_latents` / `latents` are the host-facing ends."""
+    the latents by one scheduler step; `load_latents` / `latents` are the host-facing ends.
+
+    A session depends only on SHAPES and on the schedule (batch, token counts, steps, sigmas, CFG on/off), not
+    on the values of the prompt embeddings or latents: `rebind()` loads a new request into the resident buffers,
+    so the pipeline keeps sessions across calls and a second image of the same shape pays no schedule GEMM, no
+    GEMM autotuning and no graph capture."""
 
     def __init__(self, pipe: "B200QwenImagePipeline", cond: torch.Tensor, uncond: Optional[torch.Tensor],
                  latents: torch.Tensor, Hl: int, Wl: int, num_inference_steps: int, true_cfg_scale: float,
@@ -117,12 +122,14 @@ class DenoiseSession:
         self.pipe, self.tr = pipe, tr
         self.scale = float(true_cfg_scale)
         B, s_img, _ = latents.shape
+        self.B, self.s_img = B, s_img
         self.s_txt = cond.shape[1]
         # True CFG as ONE forward of batch 2B (cond rows, then uncond rows): the weights stream through
         # the SMs once per step instead of twice and the step is 605 launches instead of 1209.  cond /
         # uncond stay addressable as the two halves of the stacked prompt buffer.
         self.enc2 = self.x2 = None
         s_ref = 0 if ref_tokens is None else ref_tokens.shape[1]
+        self.s_ref = s_ref
         nb = B
         # (prompts of different token counts keep two forwards: stacking would need padding tokens, which
         # take part in attention — upstream runs each branch at its own length)
@@ -130,6 +137,10 @@ class DenoiseSession:
             self.enc2 = torch.cat([cond, uncond], dim=0).contiguous()
             cond, uncond = self.enc2[:B], self.enc2[B:]
             nb = 2 * B
+        else:
+            cond = cond.contiguous().clone()
+            uncond = uncond.contiguous().clone() if uncond is not None else None
+        self.nb = nb
         if nb != B or s_ref:
             self.x2 = torch.empty(nb, s_img + s_ref, latents.shape[-1], device=dev, dtype=dt)
         self.cond, self.uncond = cond, uncond
@@ -143,56 +154,93 @@ class DenoiseSession:
                 shapes.append((1, int(ref_hw[0]), int(ref_hw[1])))
             # (sequence-parallel: ref_tokens is this rank's shard and the RoPE rows come from
             #  transformer.set_sequence_shard; img_shapes is not consulted)
-            for j in range(nb // B):
-                self.x2[j * B:(j + 1) * B, s_img:].copy_(ref_tokens)
         self.shapes = [shapes] * B
         self.sched = FlowMatchEulerSchedule(num_inference_steps, image_seq_len or s_img, sigmas=sigmas)
-        tr.prepare_schedule(self.sched.transformer_timesteps(dt))
+        self.mod_table = tr.prepare_schedule(self.sched.transformer_timesteps(dt))     # [steps, n_mod]
         # measured GEMM schedules for this forward's shapes (before any graph capture)
         self.gemm_schedules = tr.tune_schedules(nb, s_img + s_ref, self.s_txt)
         self.dts = self.sched.dts.to(dev)
-        self.cur = latents.contiguous().clone()
-        self.nxt = torch.empty_like(self.cur)
+        # Loop state.  Precise mode (fp32 residual streams, the default): the latents live in an fp32 master copy
+        # `cur32`, updated in place by the fp32 CFG/Euler kernel, which also writes the bf16 copy `cur` the next
+        # forward reads.  Legacy mode (QI_RESIDUAL=bf16): upstream's bf16 latents, ping-pong `cur` / `nxt`.
+        self.precise = tr.residual_dtype == torch.float32
+        self.cur = torch.empty(latents.shape, device=dev, dtype=dt)
+        self.cur32 = torch.empty(latents.shape, device=dev, dtype=torch.float32) if self.precise else None
+        self.nxt = None if self.precise else torch.empty_like(self.cur)
+        self._load(latents, ref_tokens)
         self.graph = None
         if use_cuda_graph:
             # One graph = one full step on fixed buffers; per step only the modulation row and dt are
             # refreshed by two small device copies enqueued before the replay.
-            self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=dt)
+            self.mod_cur = torch.empty(1, tr.n_mod, device=dev, dtype=self.mod_table.dtype)
             self.dt_cur = torch.empty(1, device=dev, dtype=torch.float32)
-            self.mod_cur.copy_(tr._mod_table[0:1])
+            self.mod_cur.copy_(self.mod_table[0:1])
             self.dt_cur.copy_(self.dts[0:1])
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
+            keep = (self.cur32 if self.precise else self.cur).clone()
             with torch.cuda.stream(side):     # warm-up launch outside capture (sets func attributes)
-                pipe._step(self.cur, self.nxt, cond, uncond, self.shapes, self.s_txt, 0, self.dt_cur,
-                           self.scale, mod=self.mod_cur, enc2=self.enc2, x2=self.x2)
+                self._run_step(self.dt_cur, self.mod_cur)
             torch.cuda.current_stream().wait_stream(side)
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
-                pipe._step(self.cur, self.nxt, cond, uncond, self.shapes, self.s_txt, 0, self.dt_cur,
-                           self.scale, mod=self.mod_cur, enc2=self.enc2, x2=self.x2)
-                self.cur.copy_(self.nxt)
+                self._run_step(self.dt_cur, self.mod_cur)
+                if not self.precise:
+                    self.cur.copy_(self.nxt)
+            self._load(keep, None)           # the warm-up step advanced the state: restore the request's latents
+
+    def _run_step(self, dt_dev: torch.Tensor, mod: torch.Tensor) -> None:
+        self.pipe._step(self.cur, self.cur32 if self.precise else self.nxt, self.cond, self.uncond, self.shapes,
+                        self.s_txt, dt_dev, self.scale, mod=mod, enc2=self.enc2, x2=self.x2, precise=self.precise)
+
+    def _load(self, latents: torch.Tensor, ref_tokens: Optional[torch.Tensor]) -> None:
+        if self.precise:
+            self.cur32.copy_(latents, non_blocking=True)
+            self.cur.copy_(self.cur32)
+        else:
+            self.cur.copy_(latents, non_blocking=True)
+        if ref_tokens is None:
+            return
+        if self.s_ref:
+            for j in range(self.nb // self.B):
+                self.x2[j * self.B:(j + 1) * self.B, self.s_img:].copy_(ref_tokens, non_blocking=True)
+
+    def rebind(self, cond: torch.Tensor, uncond: Optional[torch.Tensor], latents: torch.Tensor,
+               ref_tokens: Optional[torch.Tensor] = None, true_cfg_scale: Optional[float] = None) -> None:
+        """Load another request of the same shapes into the resident buffers (host or device tensors)."""
+        if true_cfg_scale is not None and float(true_cfg_scale) != self.scale:
+            raise ValueError("a cached session is bound to its true_cfg_scale")
+        self.cond.copy_(cond, non_blocking=True)
+        if self.uncond is not None:
+            self.uncond.copy_(uncond, non_blocking=True)
+        self._load(latents, ref_tokens)
 
     @property
     def latents(self) -> torch.Tensor:
+        """Current latents in the transformer's dtype (bf16), as upstream's loop carries them."""
         return self.cur
 
+    @property
+    def latents_master(self) -> torch.Tensor:
+        """The loop state itself: the fp32 master copy in precise mode, else the bf16 latents."""
+        return self.cur32 if self.precise else self.cur
+
     def load_latents(self, host_or_dev: torch.Tensor) -> None:
-        self.cur.copy_(host_or_dev, non_blocking=True)
+        self._load(host_or_dev, None)
 
     def step(self, i: int) -> None:
         if self.graph is not None:
-            self.mod_cur.copy_(self.tr._mod_table[i:i + 1])
+            self.mod_cur.copy_(self.mod_table[i:i + 1])
             self.dt_cur.copy_(self.dts[i:i + 1])
             self.graph.replay()
         else:
-            self.pipe._step(self.cur, self.nxt, self.cond, self.uncond, self.shapes, self.s_txt, i,
-                            self.dts[i:i + 1], self.scale, enc2=self.enc2, x2=self.x2)
-            self.cur, self.nxt = self.nxt, self.cur
+            self._run_step(self.dts[i:i + 1], self.mod_table[i:i + 1])
+            if not self.precise:
+                self.cur, self.nxt = self.nxt, self.cur
 
     def close(self) -> None:
-        self.tr.clear_schedule()
         self.graph = None
+        self.mod_table = None
 
 
 class B200QwenImagePipeline:
@@ -205,8 +253,11 @@ class B200QwenImagePipeline:
         self.vae_scale_factor = vae_scale_factor
         self.use_cuda_graph = False
         self.batched_cfg = True      # true CFG as one batch-2B forward (False: two forwards per step)
-        self._graph = None
-        self._graph_key = None
+        self.parallel = None         # launcher.ParallelDenoiser when the call is sharded over several GPUs
+        # DenoiseSessions kept across calls, keyed by shapes + schedule: a repeated call re-uses the hoisted
+        # modulation table, the tuned GEMM schedules and the captured CUDA graph (0 disables the cache)
+        self.max_cached_sessions = 2
+        self._sessions = {}
         self.last_step_latents: List[torch.Tensor] = []
 
     def to(self, device):
@@ -218,6 +269,11 @@ class B200QwenImagePipeline:
     @property
     def device(self):
         return self.transformer.device
+
+    def clear_sessions(self) -> None:
+        for sess in self._sessions.values():
+            sess.close()
+        self._sessions.clear()
 
     # -------------------------------------------------------------- VAE decode (row f1)
     def decode_latents(self, packed: torch.Tensor, Hl: int, Wl: int) -> torch.Tensor:
@@ -259,15 +315,18 @@ class B200QwenImagePipeline:
         u = tr(hidden_states=x, encoder_hidden_states=uncond, **kw)[0]
         return c, u
 
-    def _step(self, latents, out_latents, cond, uncond, shapes, s_txt, i, dt_dev, scale, mod=None,
-              enc2=None, x2=None):
-        kw = dict(img_shapes=shapes, txt_seq_lens=[s_txt], return_dict=False)
-        if mod is not None:
-            kw["_mod_override"] = mod
-        else:
-            kw["_step_index"] = i
+    def _step(self, latents, state, cond, uncond, shapes, s_txt, dt_dev, scale, mod, enc2=None, x2=None,
+              precise: bool = False):
+        """mod: [1, n_mod] row of the session's hoisted modulation table for this step.  precise: `state` is the
+        fp32 master copy of the latents, updated in place from fp32 predictions while `latents` receives the bf16
+        copy for the next forward; else `state` is the bf16 output buffer of upstream's bf16 step."""
+        kw = dict(img_shapes=shapes, txt_seq_lens=[s_txt], return_dict=False, _mod_override=mod, _out_fp32=precise)
         c, u = self._predict(latents, cond, uncond, kw, enc2, x2)
-        ops.cfg_euler_step(c, u, latents, out_latents, scale, dt_dev=dt_dev)
+        if precise:
+            torch.ops.qi.cfg_euler_step_f32(c.contiguous(), None if u is None else u.contiguous(), state, state,
+                                            latents, scale, dt_dev)
+        else:
+            torch.ops.qi.cfg_euler_step(c, u, latents, state, scale, dt_dev)
 
     @torch.no_grad()
     def __call__(self, image=None, prompt=None, negative_prompt=None, true_cfg_scale: float = 4.0,
@@ -323,9 +382,10 @@ class B200QwenImagePipeline:
             if uncond.shape[0] != cond.shape[0] or uncond.shape[2] != cond.shape[2]:
                 raise ValueError("negative_prompt_embeds must match prompt_embeds in batch and width")
         if latents is None:
+            # upstream's randn_tensor draws in the prompt dtype (bf16) on the generator's device; a CPU bf16
+            # normal_ consumes the RNG differently from an fp32 one, so the dtype is part of seed parity
             g = generator
-            noise = torch.randn(B, 1, 16, Hl, Wl, generator=g, device=g.device if g is not None else "cpu",
-                                dtype=torch.float32)
+            noise = torch.randn(B, 1, 16, Hl, Wl, generator=g, device=g.device if g is not None else "cpu", dtype=dt)
             latents = pack_latents(noise)
         elif latents.dim() != 3:
             latents = pack_latents(latents)
@@ -338,16 +398,41 @@ class B200QwenImagePipeline:
                     raise ValueError("Cannot duplicate `image` to the effective batch size")
                 ref_tokens = ref_tokens.repeat_interleave(B // ref_tokens.shape[0], dim=0)
             ref_tokens = ref_tokens.to(dev, dt)
-        sess = DenoiseSession(self, cond, uncond, latents.to(dev, dt), Hl, Wl, num_inference_steps,
-                              true_cfg_scale, use_cuda_graph=self.use_cuda_graph, batched_cfg=self.batched_cfg,
-                              ref_tokens=ref_tokens, ref_hw=ref_hw, sigmas=sigmas)
-        self.last_step_latents = []
-        for i in range(num_inference_steps):
-            sess.step(i)
-            if record_steps:
-                self.last_step_latents.append(sess.latents.clone())
-        final = sess.latents
-        sess.close()
+        if self.parallel is not None:
+            # one process per GPU (launcher.ParallelDenoiser): every rank makes this same call with the same
+            # arguments; the ranks shard the work and every rank gets the complete final latents back
+            final = self.parallel.denoise(cond, uncond, latents, height, width, num_inference_steps,
+                                          true_cfg_scale, ref_tokens=ref_tokens, ref_hw=ref_hw, sigmas=sigmas)
+            if output_type == "latent":
+                final = final.to(dt)          # upstream returns latents in the prompt dtype
+            self.last_step_latents = []
+        else:
+            key = (B, s_img, s_txt, None if uncond is None else tuple(uncond.shape), Hl, Wl, num_inference_steps,
+                   None if sigmas is None else tuple(float(v) for v in sigmas), float(true_cfg_scale),
+                   None if ref_tokens is None else (ref_tokens.shape[1], ref_hw), self.use_cuda_graph,
+                   self.batched_cfg)
+            sess = self._sessions.get(key)
+            if sess is None:
+                while len(self._sessions) >= self.max_cached_sessions:      # each holds a workspace + a graph
+                    self._sessions.pop(next(iter(self._sessions))).close()
+                sess = DenoiseSession(self, cond, uncond, latents.to(dev), Hl, Wl, num_inference_steps,
+                                      true_cfg_scale, use_cuda_graph=self.use_cuda_graph,
+                                      batched_cfg=self.batched_cfg, ref_tokens=ref_tokens, ref_hw=ref_hw,
+                                      sigmas=sigmas)
+                if self.max_cached_sessions > 0:
+                    self._sessions[key] = sess
+            else:
+                sess.rebind(cond, uncond, latents, ref_tokens)
+            self.last_step_latents = []
+            for i in range(num_inference_steps):
+                sess.step(i)
+                if record_steps:
+                    self.last_step_latents.append(sess.latents_master.clone())
+            # the session's buffers are reused by the next call; "latent" output keeps upstream's dtype (bf16),
+            # the decode path starts from the loop state itself
+            final = (sess.latents if output_type == "latent" else sess.latents_master).clone()
+            if self.max_cached_sessions <= 0:
+                sess.close()
 
         if output_type == "latent":
             images = final

@@ -34,6 +34,9 @@ import torch
 import torch.nn as nn
 
 from . import ops, rope
+from . import torch_ops  # noqa: F401  (registers torch.ops.qi.*)
+
+Q = torch.ops.qi      # the C ABI as dispatcher-visible ops (torch_ops.py); `ops` is used directly only for the peer-scatter variants
 from .config import MMDiTConfig
 
 
@@ -43,12 +46,15 @@ class Transformer2DModelOutput:
 
 
 class _Workspace:
-    def __init__(self, cfg: MMDiTConfig, B: int, s_img: int, s_txt: int, device, dtype):
+    def __init__(self, cfg: MMDiTConfig, B: int, s_img: int, s_txt: int, device, dtype,
+                 residual_dtype=torch.float32):
         d = cfg.inner_dim
         S = s_img + s_txt
         e = lambda *shape: torch.empty(*shape, device=device, dtype=dtype)
-        self.h = e(B, s_img, d)
-        self.e = e(B, s_txt, d)
+        # residual streams: fp32 by default.  In bf16 the two in-place roundings per block accumulate like
+        # sqrt(2 L) * 1.7e-3 = 1.9e-2 relative error over 60 blocks (measured, profiles/r02_depth_parity_bf16_stream.json)
+        self.h = torch.empty(B, s_img, d, device=device, dtype=residual_dtype)
+        self.e = torch.empty(B, s_txt, d, device=device, dtype=residual_dtype)
         self.xn_img = e(B, s_img, d)
         self.xn_txt = e(B, s_txt, d)
         self.txt_normed = e(B, s_txt, cfg.joint_attention_dim)
@@ -56,9 +62,12 @@ class _Workspace:
         self.attn = e(B, S, d)
         self.mlp_img = e(B, s_img, 4 * d)
         self.mlp_txt = e(B, s_txt, 4 * d)
-        self.sinus = e(B, 256)
-        self.t1 = e(B, d)
-        self.temb = e(B, d)
+        # timestep embedding and modulation follow the residual streams' precision (fp32: no rounding between
+        # t and the shift / scale / gate vectors; they feed every block, so their error is coherent)
+        md = residual_dtype
+        self.sinus = torch.empty(B, 256, device=device, dtype=md)
+        self.t1 = torch.empty(B, d, device=device, dtype=md)
+        self.temb = torch.empty(B, d, device=device, dtype=md)
         self.t32 = torch.empty(B, device=device, dtype=torch.float32)
         self.sp = None
 
@@ -92,6 +101,8 @@ class B200QwenImageTransformer2DModel(nn.Module):
         self._attention_backend = "qi_tcgen05_flash"
         # QK-RMSNorm + MSRoPE inside the QKV GEMM epilogue (default) or as the separate K2 launch
         self.fuse_qknorm_rope = os.environ.get("QI_FUSE_QKNORM", "1") != "0"
+        # dtype of the residual streams h / e between blocks (QI_RESIDUAL=bf16 keeps upstream's bf16 storage: A/B aid)
+        self.residual_dtype = torch.bfloat16 if os.environ.get("QI_RESIDUAL", "fp32") == "bf16" else torch.float32
 
         def P(*shape):
             return nn.Parameter(torch.empty(*shape, device=device, dtype=dtype), requires_grad=False)
@@ -214,16 +225,67 @@ class B200QwenImageTransformer2DModel(nn.Module):
         cp(self.proj_out_w, sd["proj_out.weight"]); cp(self.proj_out_b, sd["proj_out.bias"])
         self._mod_table = None
 
+    def diffusers_param(self, name: str) -> torch.Tensor:
+        """Inverse of `load_diffusers_state_dict` for ONE diffusers-named tensor: a view
+        into the fused parameter that holds it.  Lets a checker (or an exporter) walk the 20B model block by
+        block without materialising a second copy of the weights."""
+        d = self.cfg.inner_dim
+        top = {"img_in.weight": self.img_in_w, "img_in.bias": self.img_in_b, "txt_norm.weight": self.txt_norm_w,
+               "txt_in.weight": self.txt_in_w, "txt_in.bias": self.txt_in_b,
+               "time_text_embed.timestep_embedder.linear_1.weight": self.time_w1,
+               "time_text_embed.timestep_embedder.linear_1.bias": self.time_b1,
+               "time_text_embed.timestep_embedder.linear_2.weight": self.time_w2,
+               "time_text_embed.timestep_embedder.linear_2.bias": self.time_b2,
+               "proj_out.weight": self.proj_out_w, "proj_out.bias": self.proj_out_b}
+        if name in top:
+            return top[name]
+        r0 = self.cfg.num_layers * 12 * d
+        if name == "norm_out.linear.weight":
+            return self.mod_w[r0:]
+        if name == "norm_out.linear.bias":
+            return self.mod_b[r0:]
+        parts = name.split(".")
+        if parts[0] != "transformer_blocks":
+            raise KeyError(name)
+        l, rest, kind = int(parts[1]), ".".join(parts[2:-1]), parts[-1]
+        wb = lambda w, b: w if kind == "weight" else b
+        if rest in ("img_mod.1", "txt_mod.1"):
+            m0 = (l * 2 + (rest == "txt_mod.1")) * 6 * d
+            return wb(self.mod_w, self.mod_b)[m0:m0 + 6 * d]
+        qkv = {"attn.to_q": (0, 0), "attn.to_k": (0, 1), "attn.to_v": (0, 2),
+               "attn.add_q_proj": (1, 0), "attn.add_k_proj": (1, 1), "attn.add_v_proj": (1, 2)}
+        if rest in qkv:
+            s, j = qkv[rest]
+            return wb(self.qkv_w, self.qkv_b)[l, s, j * d:(j + 1) * d]
+        norms = {"attn.norm_q": 0, "attn.norm_k": 1, "attn.norm_added_q": 2, "attn.norm_added_k": 3}
+        if rest in norms:
+            return self.qk_norm_w[l, norms[rest]]
+        outs = {"attn.to_out.0": 0, "attn.to_add_out": 1}
+        if rest in outs:
+            return wb(self.out_w, self.out_b)[l, outs[rest]]
+        mlps = {"img_mlp.net.0.proj": (0, 0), "txt_mlp.net.0.proj": (1, 0), "img_mlp.net.2": (0, 1),
+                "txt_mlp.net.2": (1, 1)}
+        if rest in mlps:
+            s, dn = mlps[rest]
+            return (wb(self.mlp_down_w, self.mlp_down_b) if dn else wb(self.mlp_up_w, self.mlp_up_b))[l, s]
+        raise KeyError(name)
+
     @torch.no_grad()
-    def init_random_(self, seed: int = 0, weight_std: float = 0.02) -> "B200QwenImageTransformer2DModel":
+    def init_random_(self, seed: int = 0, weight_std: float = 0.02, bias_std: float = 0.0,
+                     norm_weight_std: float = 0.0) -> "B200QwenImageTransformer2DModel":
         """Random-init on the device for benchmarking at 20B scale (Linear.weight
-        ~ N(0, 0.02^2), bias 0, norm weights 1).  Uses the device generator, not the CPU one."""
+        ~ N(0, 0.02^2), bias 0, norm weights 1).  Uses the device generator, not the CPU one.
+        bias_std / norm_weight_std > 0 (parity tests) exercise the bias and affine-norm paths."""
         g = torch.Generator(device=self.device).manual_seed(seed)
         for name, p in self.named_parameters():
             if name in ("txt_norm_w", "qk_norm_w"):
                 p.fill_(1.0)
+                if norm_weight_std > 0:
+                    p.add_((torch.randn(p.shape, device=self.device, generator=g) * norm_weight_std).to(p.dtype))
             elif name.endswith("_b"):
                 p.zero_()
+                if bias_std > 0:
+                    p.copy_((torch.randn(p.shape, device=self.device, generator=g) * bias_std).to(p.dtype))
             else:
                 flat = p.view(-1)
                 step = 1 << 28
@@ -248,12 +310,12 @@ class B200QwenImageTransformer2DModel(nn.Module):
         key = (B, s_img, s_txt)
         ws = self._ws.get(key)
         if ws is None:
-            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
+            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt, self.residual_dtype)
         for t in (ws.h, ws.e, ws.xn_img, ws.xn_txt, ws.attn, ws.mlp_img, ws.mlp_txt):
             t.zero_()
         S = s_img + s_txt
         freqs = torch.zeros(S, Dh // 2, 2, device=dev, dtype=torch.float32)
-        gate = torch.zeros(B, d, device=dev, dtype=dt)
+        gate = torch.zeros(B, d, device=dev, dtype=self.residual_dtype)   # same dtype as the modulation table
         nw = self.qk_norm_w[0]
         G = ops.EPI_GATED_RESIDUAL
         qkv_img, qkv_txt = ws.qkv[:, s_txt:], ws.qkv[:, :s_txt]
@@ -284,25 +346,31 @@ class B200QwenImageTransformer2DModel(nn.Module):
 
     # ------------------------------------------------------------------ modulation
     def _time_embed(self, t32: torch.Tensor, ws_sinus, ws_t1, ws_temb) -> torch.Tensor:
-        ops.timestep_sinusoid(t32, ws_sinus)
-        ops.small_linear(ws_sinus, self.time_w1, self.time_b1, ws_t1, silu_out=True)
-        ops.small_linear(ws_t1, self.time_w2, self.time_b2, ws_temb)
+        Q.timestep_sinusoid(t32, ws_sinus)
+        Q.small_linear(ws_sinus, self.time_w1, self.time_b1, ws_t1, False, True)
+        Q.small_linear(ws_t1, self.time_w2, self.time_b2, ws_temb)
         return ws_temb
 
     @torch.no_grad()
-    def prepare_schedule(self, timesteps_over_1000: torch.Tensor) -> None:
+    def prepare_schedule(self, timesteps_over_1000: torch.Tensor) -> torch.Tensor:
         """Hoist every modulation Linear out of the denoising loop: temb depends only on t, so the
         [steps, L*12d+2d] modulation table is one tcgen05 GEMM over all steps.  `timesteps_over_1000`
         holds the values the pipeline would pass as `timestep` (already rounded to bf16)."""
         t = timesteps_over_1000.to(self.device, torch.bfloat16).to(torch.float32).contiguous()
         n, d = t.numel(), self.cfg.inner_dim
-        e = lambda *s: torch.empty(*s, device=self.device, dtype=self.dtype)
+        md = self.residual_dtype
+        e = lambda *s: torch.empty(*s, device=self.device, dtype=md)
         sinus, t1, temb = e(n, 256), e(n, d), e(n, d)
         self._time_embed(t, sinus, t1, temb)
-        silu = torch.nn.functional.silu(temb)   # host-layer glue on [steps, d]; 0.3 MB, once per image
         table = e(n, self.n_mod)
-        ops.gemm([ops.gemm_problem(silu, self.mod_w, self.mod_b, table, ops.EPI_BIAS)])
+        if md == torch.float32:
+            # fp32 end to end (weights bf16): HBM-bound on the 6.8 GB of modulation weights, once per schedule
+            Q.small_linear(temb, self.mod_w, self.mod_b, table, True, False)
+        else:
+            silu = torch.nn.functional.silu(temb)   # host-layer glue on [steps, d]; 0.3 MB, once per image
+            Q.gemm_bf16([silu], [self.mod_w], [self.mod_b], [table], ops.EPI_BIAS, [None], [None])
         self._mod_table, self._mod_steps = table, t
+        return table
 
     def clear_schedule(self) -> None:
         self._mod_table = self._mod_steps = None
@@ -315,9 +383,9 @@ class B200QwenImageTransformer2DModel(nn.Module):
         temb = self._time_embed(ws.t32, ws.sinus, ws.t1, ws.temb)
         key = ("mod", B)
         if key not in self._freqs:
-            self._freqs[key] = torch.empty(B, self.n_mod, device=self.device, dtype=self.dtype)
+            self._freqs[key] = torch.empty(B, self.n_mod, device=self.device, dtype=self.residual_dtype)
         mod = self._freqs[key]
-        ops.small_linear(temb, self.mod_w, self.mod_b, mod, silu_in=True)
+        Q.small_linear(temb, self.mod_w, self.mod_b, mod, True, False)
         return mod, self.n_mod
 
     # ------------------------------------------------------------------ forward
@@ -327,10 +395,13 @@ class B200QwenImageTransformer2DModel(nn.Module):
                 img_shapes=None, txt_seq_lens=None, guidance: torch.Tensor = None,
                 attention_kwargs=None, controlnet_block_samples=None, return_dict: bool = True,
                 _step_index: Optional[int] = None, _mod_override: Optional[torch.Tensor] = None,
-                _out_rows: Optional[int] = None):
+                _out_rows: Optional[int] = None, _block_hook=None, _out_fp32: bool = False):
         """Private kwargs (host layer of this package only): `_step_index` / `_mod_override` select a row of
         the hoisted modulation table; `_out_rows` = n computes `proj_out` for the first n image tokens of every
-        sample only (edit mode keeps `noise_pred[:, :S_noise]`, so the reference-image rows need no projection)."""
+        sample only (edit mode keeps `noise_pred[:, :S_noise]`, so the reference-image rows need no projection);
+        `_out_fp32` returns `.sample` in fp32 (the pipeline's fp32 CFG / Euler step reads it unrounded);
+        `_block_hook(l, h, e)` is called after block l with the residual streams (parity tests log the error
+        growth over depth with it)."""
         cfg = self.cfg
         if hidden_states.dim() != 3 or hidden_states.shape[-1] != cfg.in_channels:
             raise ValueError(f"hidden_states must be [B, S_img, {cfg.in_channels}]")
@@ -376,7 +447,7 @@ class B200QwenImageTransformer2DModel(nn.Module):
         key = (B, s_img, s_txt)
         ws = self._ws.get(key)
         if ws is None:
-            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt)
+            ws = self._ws[key] = _Workspace(cfg, B, s_img, s_txt, dev, dt, self.residual_dtype)
         if sp is not None:
             freqs = self._sp_freqs
             if peer is None and ws.sp != sp.size:
@@ -400,9 +471,9 @@ class B200QwenImageTransformer2DModel(nn.Module):
             return t if mbs != 0 else t.expand(B, d)
 
         # input projections
-        ops.rmsnorm_affine(enc.view(B * s_txt, -1), self.txt_norm_w, ws.txt_normed.view(B * s_txt, -1))
-        ops.gemm([ops.gemm_problem(x_in, self.img_in_w, self.img_in_b, ws.h),
-                  ops.gemm_problem(ws.txt_normed, self.txt_in_w, self.txt_in_b, ws.e)])
+        Q.rmsnorm_affine(enc.view(B * s_txt, -1), self.txt_norm_w, ws.txt_normed.view(B * s_txt, -1))
+        Q.gemm_bf16([x_in, ws.txt_normed], [self.img_in_w, self.txt_in_w], [self.img_in_b, self.txt_in_b],
+                    [ws.h, ws.e], ops.EPI_BIAS, [None, None], [None, None])
         h, e = ws.h, ws.e
         h2, e2 = h.view(B * s_img, d), e.view(B * s_txt, d)
         xi2, xt2 = ws.xn_img.view(B * s_img, d), ws.xn_txt.view(B * s_txt, d)
@@ -413,38 +484,47 @@ class B200QwenImageTransformer2DModel(nn.Module):
         v = ws.qkv[:, :, 2 * d:3 * d].unflatten(-1, (H, Dh))
         attn4 = ws.attn.unflatten(-1, (H, Dh))
         G = ops.EPI_GATED_RESIDUAL
+        N2 = [None, None]
+
+        def gated(a_i, a_t, w, bias, g_i, g_t, chunked=False):
+            # out-projection / MLP-down of both streams: h, e updated in place by the gated-residual epilogue
+            Q.gemm_bf16([a_i, a_t], [w[0], w[1]], [bias[0], bias[1]], [h, e], G, [h, e],
+                        [bview(g_i), bview(g_t)], chunked)
+
         for l in range(L):
             bi, bt = (l * 2) * 6 * d, (l * 2 + 1) * 6 * d
             sh_i1, sc_i1, g_i1 = mod_slices(bi)
             sh_i2, sc_i2, g_i2 = mod_slices(bi + 3 * d)
             sh_t1, sc_t1, g_t1 = mod_slices(bt)
             sh_t2, sc_t2, g_t2 = mod_slices(bt + 3 * d)
-            ops.adaln_modulate_pair([(h2, bview(sh_i1), bview(sc_i1), xi2, s_img),
-                                     (e2, bview(sh_t1), bview(sc_t1), xt2, s_txt)])
+            Q.adaln_modulate([h2, e2], [bview(sh_i1), bview(sh_t1)], [bview(sc_i1), bview(sc_t1)], [xi2, xt2],
+                             [s_img, s_txt])
             # QKV projection with QK-RMSNorm + MSRoPE applied per head vector in the GEMM epilogue (K2 fused
             # into K3); text rows first in the joint sequence, so the img stream's row 0 sits at table row s_txt
             nw = self.qk_norm_w[l]
             sc = peer.dst_qkv if peer is not None else None
-            if self.fuse_qknorm_rope:
-                qk = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=freqs, heads=H, head_dim=Dh)
-                ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0],
-                                           None if sc is not None else qkv_img, qk_norm=(nw[0], nw[1]),
-                                           rope_pos0=s_txt, scatter=sc, **qk),
-                          ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1],
-                                           None if sc is not None else qkv_txt, qk_norm=(nw[2], nw[3]),
-                                           rope_pos0=0, scatter=sc, **qk)])
+            w_qkv, b_qkv = self.qkv_w[l], self.qkv_b[l]
+            if self.fuse_qknorm_rope and sc is not None:
+                # peer scatter: the head vectors leave through CUDA-IPC pointers (no tensor form) -> ctypes call
+                qk = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=freqs, heads=H, head_dim=Dh, scatter=sc)
+                ops.gemm([ops.gemm_problem(ws.xn_img, w_qkv[0], b_qkv[0], None, qk_norm=(nw[0], nw[1]),
+                                           rope_pos0=s_txt, **qk),
+                          ops.gemm_problem(ws.xn_txt, w_qkv[1], b_qkv[1], None, qk_norm=(nw[2], nw[3]),
+                                           rope_pos0=0, **qk)])
+            elif self.fuse_qknorm_rope:
+                Q.gemm_qkv_norm_rope([ws.xn_img, ws.xn_txt], [w_qkv[0], w_qkv[1]], [b_qkv[0], b_qkv[1]],
+                                     [qkv_img, qkv_txt], [nw[0], nw[2]], [nw[1], nw[3]], freqs, [s_txt, 0], H, Dh)
             else:   # separate K2 launch (QI_FUSE_QKNORM=0): same arithmetic, one more pass over qkv
-                ops.gemm([ops.gemm_problem(ws.xn_img, self.qkv_w[l, 0], self.qkv_b[l, 0], qkv_img),
-                          ops.gemm_problem(ws.xn_txt, self.qkv_w[l, 1], self.qkv_b[l, 1], qkv_txt)])
+                Q.gemm_bf16([ws.xn_img, ws.xn_txt], [w_qkv[0], w_qkv[1]], [b_qkv[0], b_qkv[1]], [qkv_img, qkv_txt],
+                            ops.EPI_BIAS, N2, N2)
                 if sc is not None:
                     ops.qknorm_rope_scatter(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3],
                                             freqs, sc)
                 else:
-                    ops.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
+                    Q.qknorm_rope(ws.qkv.view(B * S, 3 * d), H, Dh, S, s_txt, nw[0], nw[1], nw[2], nw[3], freqs)
             if sp is None:
-                ops.attention(q, k, v, attn4)
-                ops.gemm([ops.gemm_problem(att_img, self.out_w[l, 0], self.out_b[l, 0], h, G, h, bview(g_i1)),
-                          ops.gemm_problem(att_txt, self.out_w[l, 1], self.out_b[l, 1], e, G, e, bview(g_t1))])
+                Q.attention_fwd(q, k, v, attn4)
+                gated(att_img, att_txt, self.out_w[l], self.out_b[l], g_i1, g_t1)
             elif peer is not None:
                 # Fused exchange over peer memory: the QKV GEMM's epilogue has stored each head vector into
                 # the head owner's HBM, attention stores each output row into the token owner's HBM; two
@@ -456,38 +536,30 @@ class B200QwenImageTransformer2DModel(nn.Module):
                                       o_head_stride=peer.o_head_stride)
                 peer.barrier()
                 back = peer.back[:, :, :S]             # [P*H/P, B, S_loc, Dh]: K-chunked A operand (chunk = head)
-                ops.gemm([ops.gemm_problem(back[:, :, s_txt:], self.out_w[l, 0], self.out_b[l, 0], h, G, h,
-                                           bview(g_i1), a_k_chunked=True),
-                          ops.gemm_problem(back[:, :, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
-                                           bview(g_t1), a_k_chunked=True)])
+                gated(back[:, :, s_txt:], back[:, :, :s_txt], self.out_w[l], self.out_b[l], g_i1, g_t1, True)
             else:
                 # NCCL head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
                 full = sp.scatter_heads(ws.qkv.view(S, 3 * d), H, Dh, ws.a2a_send, ws.a2a_recv)
-                ops.attention(full[:, 0].unsqueeze(0), full[:, 1].unsqueeze(0), full[:, 2].unsqueeze(0),
-                              ws.o_full.unsqueeze(0))
+                Q.attention_fwd(full[:, 0].unsqueeze(0), full[:, 1].unsqueeze(0), full[:, 2].unsqueeze(0),
+                                ws.o_full.unsqueeze(0))
                 back = sp.gather_heads(ws.o_full, ws.a2a_back)
-                ops.gemm([ops.gemm_problem(back[:, s_txt:], self.out_w[l, 0], self.out_b[l, 0], h, G, h,
-                                           bview(g_i1), a_k_chunked=True),
-                          ops.gemm_problem(back[:, :s_txt], self.out_w[l, 1], self.out_b[l, 1], e, G, e,
-                                           bview(g_t1), a_k_chunked=True)])
-            ops.adaln_modulate_pair([(h2, bview(sh_i2), bview(sc_i2), xi2, s_img),
-                                     (e2, bview(sh_t2), bview(sc_t2), xt2, s_txt)])
-            ops.gemm([ops.gemm_problem(ws.xn_img, self.mlp_up_w[l, 0], self.mlp_up_b[l, 0], ws.mlp_img,
-                                       ops.EPI_BIAS_GELU_TANH),
-                      ops.gemm_problem(ws.xn_txt, self.mlp_up_w[l, 1], self.mlp_up_b[l, 1], ws.mlp_txt,
-                                       ops.EPI_BIAS_GELU_TANH)])
-            ops.gemm([ops.gemm_problem(ws.mlp_img, self.mlp_down_w[l, 0], self.mlp_down_b[l, 0], h, G, h,
-                                       bview(g_i2)),
-                      ops.gemm_problem(ws.mlp_txt, self.mlp_down_w[l, 1], self.mlp_down_b[l, 1], e, G, e,
-                                       bview(g_t2))])
+                gated(back[:, s_txt:], back[:, :s_txt], self.out_w[l], self.out_b[l], g_i1, g_t1, True)
+            Q.adaln_modulate([h2, e2], [bview(sh_i2), bview(sh_t2)], [bview(sc_i2), bview(sc_t2)], [xi2, xt2],
+                             [s_img, s_txt])
+            Q.gemm_bf16([ws.xn_img, ws.xn_txt], [self.mlp_up_w[l, 0], self.mlp_up_w[l, 1]],
+                        [self.mlp_up_b[l, 0], self.mlp_up_b[l, 1]], [ws.mlp_img, ws.mlp_txt],
+                        ops.EPI_BIAS_GELU_TANH, N2, N2)
+            gated(ws.mlp_img, ws.mlp_txt, self.mlp_down_w[l], self.mlp_down_b[l], g_i2, g_t2)
+            if _block_hook is not None:
+                _block_hook(l, h, e)
         # norm_out (AdaLayerNormContinuous: chunk order is (scale, shift)) + proj_out
         r0 = L * 12 * d
-        ops.adaln_modulate(h2, bview(mod[:, r0 + d:r0 + 2 * d]), bview(mod[:, r0:r0 + d]), xi2, s_img)
+        Q.adaln_modulate([h2], [bview(mod[:, r0 + d:r0 + 2 * d])], [bview(mod[:, r0:r0 + d])], [xi2], [s_img])
         n_out = s_img if _out_rows is None else int(_out_rows)
         if not 0 < n_out <= s_img:
             raise ValueError("_out_rows must be in (0, S_img]")
-        out = torch.empty(B, n_out, cfg.proj_out_dim, device=dev, dtype=dt)
-        ops.gemm([ops.gemm_problem(ws.xn_img[:, :n_out], self.proj_out_w, self.proj_out_b, out)])
+        out = torch.empty(B, n_out, cfg.proj_out_dim, device=dev, dtype=torch.float32 if _out_fp32 else dt)
+        Q.gemm_bf16([ws.xn_img[:, :n_out]], [self.proj_out_w], [self.proj_out_b], [out], ops.EPI_BIAS, [None], [None])
         if not return_dict:
             return (out,)
         return Transformer2DModelOutput(sample=out)
