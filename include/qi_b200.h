@@ -113,6 +113,11 @@ int qi_gemm_set_cta_pair(int mode);
  * layer's autotuner (ops.tune_gemm) times every candidate once per new shape, before graph capture. */
 int qi_gemm_set_schedule(const qi_gemm_problem_t* problems /* host */, int num_problems, int pair, int bn);
 int qi_gemm_clear_schedules(void);
+/* Tile rasterisation of the persistent GEMM: supertiles of `group_m` row tiles x all column tiles (a wave of
+ * concurrently running tiles is then a ~square patch of the tile grid); 0 = column-major order (row tile fastest),
+ * -1 = default (env QI_GEMM_GROUP_M, else round(sqrt(workers))).  Tuning knob; single-threaded setup call like the
+ * other qi_gemm_set_* functions (they write process-wide state read by later launches). */
+int qi_gemm_set_group_m(int group_m);
 
 /* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
  * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).

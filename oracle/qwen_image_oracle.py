@@ -116,6 +116,18 @@ def init_state_dict(cfg: OracleConfig, seed: int = 0, dtype=torch.float32,
     return sd
 
 
+class ParamView:
+    """State dict for the oracle that READS THE MODEL UNDER TEST: diffusers-named tensors fetched from any object
+    with `diffusers_param(name)` (the CUDA model's fused parameters) and upcast on access.  Lets the oracle check a
+    20B-parameter model on the GPU on the very same (bf16-rounded) weights without a second copy of them."""
+
+    def __init__(self, model, dtype=torch.float32):
+        self.model, self.dtype = model, dtype
+
+    def __getitem__(self, name: str) -> torch.Tensor:
+        return self.model.diffusers_param(name).to(self.dtype)
+
+
 # --------------------------------------------------------------------------------------
 # MSRoPE (Appendix A.5).  Integer position ids are the bit-exact part.
 # --------------------------------------------------------------------------------------

@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run by the driver with -m gpu)")
+    config.addinivalue_line("markers", "sanitizer: opt-in compute-sanitizer pass (QI_SANITIZER=1)")
 
 
 @pytest.fixture(scope="session")

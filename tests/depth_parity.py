@@ -30,14 +30,7 @@ if ROOT not in sys.path:
 from oracle import qwen_image_oracle as O  # noqa: E402
 
 
-class LazyStateDict:
-    """diffusers-named view of the CUDA model's fused parameters, upcast on access (checker side only)."""
-
-    def __init__(self, tr, dtype=torch.float32):
-        self.tr, self.dtype = tr, dtype
-
-    def __getitem__(self, name: str) -> torch.Tensor:
-        return self.tr.diffusers_param(name).to(self.dtype)
+LazyStateDict = O.ParamView      # diffusers-named view of the CUDA model's fused parameters, upcast on access
 
 
 def build_model(num_layers: int = 60, seed: int = 5, device: str = "cuda:0"):

@@ -14,24 +14,62 @@ static void set_err(const std::string& s) { g_last_error = s; }
 extern "C" int qi_version(void) { return 100; }
 extern "C" const char* qi_last_cuda_error(void) { return g_last_error.c_str(); }
 
+// Per-device caches (a process may drive several GPUs; the current device decides).  Guarded by one mutex: the
+// library's other process-wide knobs (qi_gemm_set_tile_n / _cta_pair / _schedule, qi_attention_set_variant) are
+// documented as single-threaded setup calls, but these two sit on every launch path.
+static std::mutex g_dev_mutex;
+static int g_sms[64];
+static bool g_sms_init = false;
+
 int qi_num_sms() {
-  static int sms = -2;
-  if (sms == -2) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_err(std::string("no CUDA device: ") + cudaGetErrorString(cudaGetLastError()));
+    return -1;
+  }
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  if (!g_sms_init) {
+    for (int i = 0; i < 64; ++i) g_sms[i] = -2;
+    g_sms_init = true;
+  }
+  if (g_sms[dev] == -2) {
+    int n = 0, major = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
       set_err(std::string("no CUDA device: ") + cudaGetErrorString(cudaGetLastError()));
       return -1;  // do not cache: a later call may run after a device appears
     }
-    int major = 0;
     cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
     if (major != 10) {
       set_err("libqi_b200 requires an sm_100 (B200) device; there is no fallback path");
       return -1;
     }
-    sms = n;
+    g_sms[dev] = n;
   }
-  return sms;
+  return g_sms[dev];
+}
+
+int qi_set_max_smem(const void* kernel, int bytes) {
+  struct Entry { const void* k; unsigned long long devmask; };
+  static Entry table[256];
+  static int n = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return QI_ERR_CUDA;
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  Entry* e = nullptr;
+  for (int i = 0; i < n; ++i)
+    if (table[i].k == kernel) e = &table[i];
+  if (e && (e->devmask >> dev) & 1ull) return QI_OK;
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) {
+    set_err(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(cudaGetLastError()));
+    return QI_ERR_CUDA;
+  }
+  if (!e && n < 256) {
+    table[n].k = kernel;
+    table[n].devmask = 0;
+    e = &table[n++];
+  }
+  if (e) e->devmask |= 1ull << dev;
+  return QI_OK;
 }
 extern "C" int qi_device_sm_count(void) { return qi_num_sms(); }
 

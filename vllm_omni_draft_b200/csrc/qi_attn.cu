@@ -429,13 +429,8 @@ static int attn_variant() {
 
 template <int DH, int EMU, bool SPLIT>
 static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(attention_fwd_kernel<DH, EMU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             AttCfg<DH>::SMEM_BYTES) != cudaSuccess)
-      return QI_ERR_CUDA;
-    attr_set = true;
-  }
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_fwd_kernel<DH, EMU, SPLIT>), AttCfg<DH>::SMEM_BYTES))
+    return rc;
   if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream,
                 P) != cudaSuccess)
     return QI_ERR_CUDA;

@@ -330,3 +330,6 @@ inline cudaError_t qi_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, si
 int qi_encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                         const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box);
 int qi_num_sms();
+// cudaFuncAttributeMaxDynamicSharedMemorySize, set once per (kernel, device): the attribute is per device, so a
+// process that drives several GPUs must set it on each.  Thread-safe.
+int qi_set_max_smem(const void* kernel, int bytes);

@@ -67,6 +67,7 @@ struct GemmLaunch {
   GemmProb prob[2];
   int num_problems;
   int total_tiles;
+  int group_m;   // tile rasterisation: supertiles of group_m row tiles x all column tiles (0: column-major order)
 };
 
 template <int BN>
@@ -92,8 +93,25 @@ __device__ __forceinline__ TileCoord decode_tile(const GemmLaunch& L, int t, int
   tc.p = (L.num_problems > 1 && t >= L.prob[1].tile_begin) ? 1 : 0;
   const GemmProb& P = L.prob[tc.p];
   const int lt = t - P.tile_begin;
-  const int mt = lt % P.tiles_m_total;
-  int nt = lt / P.tiles_m_total;
+  // L2-aware rasterisation.  The persistent workers take tiles in linear order, so ~`workers` consecutive tiles run
+  // together.  Column-major order makes such a wave span every row tile and 2-4 column tiles: the whole A panel
+  // is streamed from HBM once per wave (MLP-down at batch 2: 226 MB x 5.8 waves against 376 MB of operands).
+  // Supertiles of group_m row tiles x all column tiles make a wave a ~square group_m x workers/group_m patch of
+  // the tile grid: it touches group_m A panels and workers/group_m W panels, and successive waves of a supertile
+  // reuse its A rows from L2.
+  int mt, nt;
+  if (L.group_m > 0) {
+    const int gsz = L.group_m * P.tiles_n;
+    const int g = lt / gsz;
+    const int m_base = g * L.group_m;
+    const int gm = min(L.group_m, P.tiles_m_total - m_base);
+    const int r = lt - g * gsz;
+    nt = r / gm;
+    mt = m_base + (r - nt * gm);
+  } else {
+    mt = lt % P.tiles_m_total;
+    nt = lt / P.tiles_m_total;
+  }
   if (P.sc_tpg > 0) {
     // Ulysses scatter: rank r visits owners r+1, r+2, ..., r-1 (every rank sends to a different peer at any
     // moment, so no GPU's NVLink ingress is a hot spot), q, k and v of each; its own heads come last, so the
@@ -232,10 +250,15 @@ __device__ __forceinline__ void epilogue_rows(const GemmProb& P, int b, int row,
 // fp32 variant of epilogue_rows (P.c_fp32): C and the residual R are fp32 — the MMDiT residual streams h / e
 // (QI_EPI_BIAS for img_in / txt_in, QI_EPI_GATED_RESIDUAL for the out-projection and MLP-down).  Same staging scheme
 // with 16-column sub-chunks, so a staged row is again 64 bytes (16 fp32): residual rows are loaded and result rows
-// stored as 64 contiguous bytes per 4 lanes, 8 rows per instruction, the next sub-chunk's residual prefetched.
-template <int BN, typename Release>
+// stored as 64 contiguous bytes per 4 lanes, 8 rows per instruction.
+// The residual does not depend on the accumulator, and its loads are what the epilogue waits for (one sub-chunk
+// in flight per warp bounds an SM at ~16 KB / latency): the first PF sub-chunks are requested BEFORE the warp
+// waits for the accumulator (`wait`), and PF sub-chunks stay in flight after that.  With one sub-chunk in flight
+// the out-projection (K = 3072: 13 us of MMAs per 256 x 256 tile) ran at 941 TFLOP/s against 1 374 with bf16
+// streams — the epilogue, not the tensor pipe, set the tile time.
+template <int BN, typename Wait, typename Release>
 __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int row, int n0,
-                                                  uint32_t taddr, int half, uint8_t* stage, Release release) {
+                                                  uint32_t taddr, int half, uint8_t* stage, Wait wait, Release release) {
   const int lane = threadIdx.x & 31;
   const int row0 = row - lane;
   float* cbase = reinterpret_cast<float*>(P.c) + (size_t)b * P.c_bs;
@@ -243,36 +266,45 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
   const __nv_bfloat16* grow = P.gate ? P.gate + (size_t)b * P.gate_bs : nullptr;
   const bool gated = P.epilogue == QI_EPI_GATED_RESIDUAL;
   constexpr int NCH = BN / 16, SPLIT = 2 * ((BN / 32 + 1) / 2);   // same column split between the two warps as bf16
+  constexpr int MAXI = SPLIT > NCH - SPLIT ? SPLIT : NCH - SPLIT;
+  constexpr int PF = 3;                                            // residual sub-chunks in flight per warp
   const int c_begin = half ? SPLIT : 0;
-  const int c_end = half ? NCH : SPLIT;
+  const int cnt = half ? NCH - SPLIT : SPLIT;
   const int piece = lane & 3;          // cooperative pattern: row it*8 + lane/4, 16-byte piece (4 fp32) lane%4
   const int rsub = lane >> 2;
-  float4 rbuf[4];
-  auto load_residual = [&](int c) {
+  float4 rbuf[PF][4];
+  auto load_residual = [&](int c, float4 (&dst)[4]) {
     const int n = n0 + c * 16 + piece * 4;
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int rr = row0 + it * 8 + rsub;
-      rbuf[it] = (rr < P.m && n < P.n) ? *reinterpret_cast<const float4*>(rbase + (size_t)rr * P.ld_res + n)
-                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+      dst[it] = (rr < P.m && n < P.n) ? *reinterpret_cast<const float4*>(rbase + (size_t)rr * P.ld_res + n)
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
-  if (gated) load_residual(c_begin);
-#pragma unroll 1
-  for (int c = c_begin; c < c_end; ++c) {
+  if (gated) {
+#pragma unroll
+    for (int p = 0; p < PF; ++p)
+      if (p < cnt) load_residual(c_begin + p, rbuf[p]);
+  }
+  wait();
+#pragma unroll
+  for (int i = 0; i < MAXI; ++i) {
+    if (i >= cnt) break;
+    const int c = c_begin + i;
     if (gated) {
 #pragma unroll
       for (int it = 0; it < 4; ++it) {
         const int rr = it * 8 + rsub;
-        *reinterpret_cast<float4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4)) = rbuf[it];
+        *reinterpret_cast<float4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4)) = rbuf[i % PF][it];
       }
       __syncwarp();
-      if (c + 1 < c_end) load_residual(c + 1);
+      if (i + PF < cnt) load_residual(c + PF, rbuf[i % PF]);
     }
     uint32_t r[16];
     tmem_ld16(taddr + c * 16, r);
     tmem_ld_wait();
-    if (c == c_end - 1) release();
+    if (i == cnt - 1) release();
     const int n_base = n0 + c * 16;
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -468,10 +500,16 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
   if (!released) release();
 }
 
-// Epilogue dispatch for one warp's 32 rows of a tile.
-template <int BN, typename Release>
+// Epilogue dispatch for one warp's 32 rows of a tile.  `wait` blocks until the tile's accumulator is complete; the
+// variants that can start work earlier (fp32 residual prefetch) call it late, the others first thing.
+template <int BN, typename Wait, typename Release>
 __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row, int n0, uint32_t taddr,
-                                              int half, uint8_t* stage, Release release) {
+                                              int half, uint8_t* stage, Wait wait, Release release) {
+  if (P.c_fp32 && P.epilogue != QI_EPI_QKV_NORM_ROPE) {
+    epilogue_rows_f32<BN>(P, b, row, n0, taddr, half, stage, wait, release);
+    return;
+  }
+  wait();
   if (P.epilogue == QI_EPI_QKV_NORM_ROPE) {
     if constexpr (BN % 128 == 0) {
       if (P.head_dim == 128) {
@@ -481,10 +519,6 @@ __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row,
     }
     if constexpr (BN % 64 == 0)
       epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, stage, release);   // host guarantees head_dim == 64 here
-    return;
-  }
-  if (P.c_fp32) {
-    epilogue_rows_f32<BN>(P, b, row, n0, taddr, half, stage, release);
     return;
   }
   epilogue_rows<BN>(P, b, row, n0, taddr, half, stage, release);
@@ -603,10 +637,11 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
       const TileCoord tc = decode_tile(L, t, BN);
       const GemmProb& P = L.prob[tc.p];
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
       epilogue_tile<BN>(P, tc.b, tc.m0 + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, epi_stage, [&]() {
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+      }, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -769,10 +804,11 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
     for (int t = pair; t < L.total_tiles; t += num_pairs) {
       const TileCoord tc = decode_tile(L, t, BN, 2 * BM);
       const GemmProb& P = L.prob[tc.p];
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * Cfg::ACC_STRIDE;
       epilogue_tile<BN>(P, tc.b, tc.m0 + (int)cta * BM + q * 32 + lane, tc.n0, taddr, (warp - 2) >> 2, epi_stage, [&]() {
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+      }, [&]() {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(acc == 0 ? empty0 : empty1);
@@ -891,6 +927,26 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   return QI_OK;
 }
 
+// Row tiles per supertile: ~sqrt(workers), so that one wave of `workers` tiles is a square patch of the tile grid
+// (9 for 74 CTA pairs, 12 for 148 CTAs).  QI_GEMM_GROUP_M overrides (0 = column-major order, the round-1 schedule).
+static int g_group_m = -1;   // -1: env QI_GEMM_GROUP_M or the default below
+extern "C" int qi_gemm_set_group_m(int group_m) {
+  if (group_m < -1 || group_m > 4096) return QI_ERR_ARG;
+  g_group_m = group_m;
+  return QI_OK;
+}
+static int gemm_group_m(int workers) {
+  static const int env = [] {
+    const char* e = getenv("QI_GEMM_GROUP_M");
+    return e ? atoi(e) : -1;
+  }();
+  if (g_group_m >= 0) return g_group_m;
+  if (env >= 0) return env;
+  int g = 1;
+  while ((g + 1) * (g + 1) <= workers) ++g;
+  return g + ((g * (g + 1) <= workers) ? 1 : 0);   // round sqrt to nearest
+}
+
 template <int BN>
 static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
   GemmLaunch L;
@@ -903,15 +959,10 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
     tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
   }
   L.total_tiles = tiles;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             GemmCfg<BN>::SMEM_BYTES) != cudaSuccess)
-      return QI_ERR_CUDA;
-    attr_set = true;
-  }
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_kernel<BN>), GemmCfg<BN>::SMEM_BYTES)) return rc;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
+  L.group_m = gemm_group_m(sms);
   const int grid = tiles < sms ? tiles : sms;
   if (qi_launch(gemm_bf16_kernel<BN>, dim3(grid), dim3(GEMM_THREADS), GemmCfg<BN>::SMEM_BYTES, stream, L) !=
       cudaSuccess)
@@ -931,15 +982,11 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
     tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
   }
   L.total_tiles = tiles;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_pair_bf16_kernel<BN, STG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             GemmPairCfg<BN, STG>::SMEM_BYTES) != cudaSuccess)
-      return QI_ERR_CUDA;
-    attr_set = true;
-  }
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_pair_bf16_kernel<BN, STG>), GemmPairCfg<BN, STG>::SMEM_BYTES))
+    return rc;
   const int pairs_max = qi_num_sms() / 2;
   if (pairs_max <= 0) return QI_ERR_CUDA;
+  L.group_m = gemm_group_m(pairs_max);
   const int pairs = tiles < pairs_max ? tiles : pairs_max;
   if (qi_launch(gemm_pair_bf16_kernel<BN, STG>, dim3(2 * pairs), dim3(GEMM_THREADS),
                 GemmPairCfg<BN, STG>::SMEM_BYTES, stream, L) != cudaSuccess)

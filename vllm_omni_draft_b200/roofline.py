@@ -99,9 +99,11 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
         roof["cublas_note"] = "F.linear (cuBLASLt), no bias/GELU epilogue, two calls (img, txt)"
     # ---- MLP-down + gated residual
     w_dn = [w.view(2, d, 4 * d) for w in w_up]
-    gate, ho, eo = r(B, d), emp(B, s_img, d), emp(B, s_txt, d)
-    t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(mi, w_dn[i % nw][0], b_up[0, :d], ho, 2, xi, gate),
-                                        ops.gemm_problem(mt, w_dn[i % nw][1], b_up[1, :d], eo, 2, xt, gate)]), reps)
+    # gated-residual launches as the step issues them: fp32 residual streams updated in place, fp32 gate row
+    r32 = lambda *s, sc=1.0: torch.randn(*s, device=dev, generator=g) * sc
+    gate, ho, eo = r32(1, d, sc=0.1).expand(B, d), r32(B, s_img, d), r32(B, s_txt, d)
+    t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(mi, w_dn[i % nw][0], b_up[0, :d], ho, 2, ho, gate),
+                                        ops.gemm_problem(mt, w_dn[i % nw][1], b_up[1, :d], eo, 2, eo, gate)]), reps)
     kern["gemm_mlp_down_gated_residual"] = {"us": t * 1e6, "tflops": fl_mlp / t / 1e12}
     tl = lib_pair(mi, mt, w_dn, d)
     if tl:
@@ -124,8 +126,8 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
     # ---- out-projection + gated residual
     w_o = [w.view(2, 4 * d, d)[:, :d].contiguous() for w in w_up[:4]]
     att = r(B, S, d)
-    t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(att[:, s_txt:], w_o[i % 4][0], b_up[0, :d], ho, 2, xi, gate),
-                                        ops.gemm_problem(att[:, :s_txt], w_o[i % 4][1], b_up[1, :d], eo, 2, xt, gate)]), reps)
+    t = _time_graph(lambda i: ops.gemm([ops.gemm_problem(att[:, s_txt:], w_o[i % 4][0], b_up[0, :d], ho, 2, ho, gate),
+                                        ops.gemm_problem(att[:, :s_txt], w_o[i % 4][1], b_up[1, :d], eo, 2, eo, gate)]), reps)
     fl = 2.0 * B * S * d * d
     kern["gemm_out_proj_gated_residual"] = {"us": t * 1e6, "tflops": fl / t / 1e12}
     tl = lib_pair(att[:, s_txt:].contiguous(), att[:, :s_txt].contiguous(), w_o, d)
@@ -154,11 +156,12 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
                       "gbs_l2_resident": by / t_l2 / 1e9, "note": note}
 
     rows = B * s_img
-    nb = max(3, int(2.5 * L2_BYTES // (4.0 * rows * d)) + 1)
-    xs, ys = [r(rows, d) for _ in range(nb)], [emp(rows, d) for _ in range(nb)]
-    mod = r(1, 6 * d, sc=0.1)
-    hbm_entry("adaln_modulate_img", lambda j: ops.adaln_modulate(xs[j], mod[:, :d], mod[:, d:2 * d], ys[j], rows),
-              4.0 * rows * d, nb, f"K1, batch {B}; {nb} rotating in/out pairs")
+    nb = max(3, int(2.5 * L2_BYTES // (6.0 * rows * d)) + 1)
+    xs, ys = [r32(rows, d) for _ in range(nb)], [emp(rows, d) for _ in range(nb)]
+    mod = r32(1, 6 * d, sc=0.1)
+    sh, sc_ = mod[:, :d].expand(B, d), mod[:, d:2 * d].expand(B, d)
+    hbm_entry("adaln_modulate_img", lambda j: ops.adaln_modulate_pair([(xs[j], sh, sc_, ys[j], s_img)]),
+              6.0 * rows * d, nb, f"K1 as in the step: fp32 residual rows in, bf16 out, fp32 modulation; batch {B}; {nb} rotating in/out pairs")
     del xs, ys
     nb = max(3, int(2.5 * L2_BYTES // (8.0 * S * d)) + 1)
     qs = [r(S, 3 * d) for _ in range(nb)]
@@ -166,10 +169,10 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
               lambda j: ops.qknorm_rope(qs[j], H, Dh, S, s_txt, nwt[0], nwt[1], nwt[2], nwt[3], fr),
               8.0 * S * d, nb, "K2 C-ABI entry point (batch 1); inside the step this work runs in the QKV GEMM epilogue")
     del qs
-    nb = 80
-    lat = [[r(1, s_img, 64) for _ in range(4)] for _ in range(nb)]
-    hbm_entry("cfg_euler_step", lambda j: ops.cfg_euler_step(lat[j][0], lat[j][1], lat[j][2], lat[j][3], 4.0, dt=-0.02),
-              4.0 * s_img * 64 * 2, nb, "K5, 2.1 MB per launch: launch-latency bound")
+    nb = 48
+    lat = [[r32(1, s_img, 64) for _ in range(3)] + [emp(1, s_img, 64)] for _ in range(nb)]
+    hbm_entry("cfg_euler_step", lambda j: ops.cfg_euler_step_f32(lat[j][0], lat[j][1], lat[j][2], lat[j][2], lat[j][3], 4.0, dt=-0.02),
+              (4 * 4.0 + 2.0) * s_img * 64, nb, "K5 in fp32 (master latents in place + bf16 copy), 4.7 MB per launch: launch-latency bound")
     blk = (kern["gemm_qkv_qknorm_rope"]["us"] + kern["gemm_out_proj_gated_residual"]["us"] + roof["launch_us"]
            + kern["gemm_mlp_down_gated_residual"]["us"] + kern["attention_fwd"]["us"]
            + 2 * kern["adaln_modulate_img"]["us_l2_resident"] * (S / s_img))
