@@ -400,6 +400,10 @@ def main():
             dist.destroy_process_group()
         return
 
+    out_dir = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out_dir):      # every GEMM schedule measured or loaded by this process (feeds tuned_schedules.json)
+        with open(os.path.join(out_dir, f"tuned_schedules_n{world}.json"), "w") as f:
+            json.dump(ops.tuned_schedules(), f, indent=0, sort_keys=True)
     burst, sustained, hbm, src = load_peaks()
     ms_step = ms / K
     flops_step = 2 * algorithmic_flops_per_forward(s_img, s_txt, batch=B, layers=cfg.num_layers, d=cfg.inner_dim,

@@ -112,6 +112,9 @@ int qi_gemm_set_cta_pair(int mode);
  * qi_gemm_bf16 calls with matching dims use (pair, bn) instead of the wave-count heuristic.  The host
  * layer's autotuner (ops.tune_gemm) times every candidate once per new shape, before graph capture. */
 int qi_gemm_set_schedule(const qi_gemm_problem_t* problems /* host */, int num_problems, int pair, int bn);
+/* Same, with the tile rasterisation (see qi_gemm_set_group_m) as part of the measured schedule; -1 = default. */
+int qi_gemm_set_schedule_ex(const qi_gemm_problem_t* problems /* host */, int num_problems, int pair, int bn,
+                            int group_m);
 int qi_gemm_clear_schedules(void);
 /* Tile rasterisation of the persistent GEMM: supertiles of `group_m` row tiles x all column tiles (a wave of
  * concurrently running tiles is then a ~square patch of the tile grid); 0 = column-major order (row tile fastest),

@@ -21,7 +21,8 @@ def main():
     vals = [int(v) for v in sys.argv[2:]] or [0, 9]
     rounds, reps, nw = 7, 24, 6
     lib = _lib.lib()
-    setter = {"group_m": lib.qi_gemm_set_group_m, "pdl": lib.qi_set_pdl}[knob]
+    lib.qi_gemm_set_debug.argtypes, lib.qi_gemm_set_debug.restype = [_lib.C.c_int], _lib.C.c_int
+    setter = {"group_m": lib.qi_gemm_set_group_m, "pdl": lib.qi_set_pdl, "dbg": lib.qi_gemm_set_debug}[knob]
     d, H, Dh, s_img, s_txt, B = 3072, 24, 128, 4096, 512, 2
     S = s_img + s_txt
     dev = "cuda"
@@ -60,7 +61,7 @@ def main():
                 for i in range(reps):
                     fn(i)
             graphs[(name, v)] = gr
-    setter(-1 if knob == "group_m" else 1)
+    setter({"group_m": -1, "pdl": 1, "dbg": 0}[knob])
     times = {k: [] for k in graphs}
     for _ in range(rounds):
         for k, gr in graphs.items():

@@ -60,6 +60,7 @@ _SIGNATURES = {
     "qi_gemm_set_schedule": (_i, [_vp, _i, _i, _i]),
     "qi_gemm_clear_schedules": (_i, []),
     "qi_gemm_set_group_m": (_i, [_i]),
+    "qi_gemm_set_schedule_ex": (_i, [_vp, _i, _i, _i, _i]),
     "qi_attention_fwd_scatter": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _ll, _ll, _ll,
                                       _f, C.POINTER(PeerScatter), _vp]),
     "qi_qknorm_rope_scatter": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f,

@@ -30,7 +30,8 @@ template <int BN>
 #ifndef QI_QKV_WIDE_STORES
 #define QI_QKV_WIDE_STORES 1      // build-time A/B aid: 0 keeps 64-byte row segments everywhere
 #endif
-struct EpiWarpBytes { static constexpr int value = (QI_QKV_WIDE_STORES && BN % 128 == 0) ? 4096 : 2048; };
+// (+1 KB behind the 2 KB staging tile: the fp32 epilogue keeps its warp's gate and bias columns there)
+struct EpiWarpBytes { static constexpr int value = (QI_QKV_WIDE_STORES && BN % 128 == 0) ? 4096 : 3072; };
 
 struct GemmProb {
   void* c;
@@ -42,6 +43,7 @@ struct GemmProb {
   int epilogue;
   int c_fp32;        // C and the residual are fp32 (the residual streams), else bf16
   int gate_fp32;     // gate vectors are fp32 (the fp32 modulation table), else bf16
+  int dbg;           // profiling aid (qi_gemm_set_debug): 1 skip residual loads, 2 skip result stores, 4 skip bias/gate loads
   int tiles_m;       // per batch item
   int tiles_m_total; // tiles_m * batch
   int tiles_n;
@@ -278,8 +280,8 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int rr = row0 + it * 8 + rsub;
-      dst[it] = (rr < P.m && n < P.n) ? *reinterpret_cast<const float4*>(rbase + (size_t)rr * P.ld_res + n)
-                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+      dst[it] = (rr < P.m && n < P.n && !(P.dbg & 1)) ? *reinterpret_cast<const float4*>(rbase + (size_t)rr * P.ld_res + n)
+                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
   if (gated) {
@@ -287,6 +289,38 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
     for (int p = 0; p < PF; ++p)
       if (p < cnt) load_residual(c_begin + p, rbuf[p]);
   }
+  // This warp's gate and bias columns (<= 128 of each) go to shared memory once per tile; every lane then reads
+  // them as broadcasts.  Loaded per sub-chunk from global they were the single largest cost of this epilogue
+  // (out-projection 211 -> 160 us with them removed): the 2 KB-per-sub-chunk residual stream evicts them from the
+  // ~28 KB of L1 that the 200 KB operand ring leaves, so every sub-chunk waited on an L2 round trip.
+  float* gsm = reinterpret_cast<float*>(stage + 2048);
+  float* bsm = gsm + 128;
+  {
+    const int j = lane * 4;
+    const int n = n0 + c_begin * 16 + j;
+    if (j < cnt * 16) {
+      float4 gt = make_float4(0.f, 0.f, 0.f, 0.f), bb = gt;
+      if (n < P.n && !(P.dbg & 4)) {
+        if (gated) {
+          if (P.gate_fp32) {
+            gt = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(P.gate) + (size_t)b * P.gate_bs + n);
+          } else {
+            const uint2 gu = *reinterpret_cast<const uint2*>(grow + n);
+            const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y);
+            gt = make_float4(g0.x, g0.y, g1.x, g1.y);
+          }
+        }
+        if (P.bias) {
+          const uint2 bu = *reinterpret_cast<const uint2*>(P.bias + n);
+          const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y);
+          bb = make_float4(b0.x, b0.y, b1.x, b1.y);
+        }
+      }
+      *reinterpret_cast<float4*>(gsm + j) = gt;
+      *reinterpret_cast<float4*>(bsm + j) = bb;
+    }
+  }
+  __syncwarp();
   wait();
 #pragma unroll
   for (int i = 0; i < MAXI; ++i) {
@@ -314,20 +348,10 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) v[j] = __uint_as_float(r[g * 4 + j]);
-      if (P.bias) {
-        const uint2 bu = *reinterpret_cast<const uint2*>(P.bias + n);
-        const float2 b0 = unpack_bf16(bu.x), b1 = unpack_bf16(bu.y);
-        v[0] += b0.x; v[1] += b0.y; v[2] += b1.x; v[3] += b1.y;
-      }
+      const float4 bb = *reinterpret_cast<const float4*>(bsm + i * 16 + g * 4);
+      v[0] += bb.x; v[1] += bb.y; v[2] += bb.z; v[3] += bb.w;
       if (gated) {
-        float4 gt;
-        if (P.gate_fp32) {
-          gt = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(P.gate) + (size_t)b * P.gate_bs + n);
-        } else {
-          const uint2 gu = *reinterpret_cast<const uint2*>(grow + n);
-          const float2 g0 = unpack_bf16(gu.x), g1 = unpack_bf16(gu.y);
-          gt = make_float4(g0.x, g0.y, g1.x, g1.y);
-        }
+        const float4 gt = *reinterpret_cast<const float4*>(gsm + i * 16 + g * 4);
         const float4 rs = *slot;          // this row's residual piece (zero outside the matrix)
         v[0] = fmaf(gt.x, v[0], rs.x); v[1] = fmaf(gt.y, v[1], rs.y);
         v[2] = fmaf(gt.z, v[2], rs.z); v[3] = fmaf(gt.w, v[3], rs.w);
@@ -341,7 +365,7 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
       for (int it = 0; it < 4; ++it) {
         const int rr = it * 8 + rsub;
         const float4 o = *reinterpret_cast<const float4*>(stage + rr * 64 + ((piece ^ ((rr >> 1) & 3)) << 4));
-        if (row0 + rr < P.m && n < P.n)
+        if (row0 + rr < P.m && n < P.n && !(P.dbg & 2))
           *reinterpret_cast<float4*>(cbase + (size_t)(row0 + rr) * P.ldc + n) = o;
       }
     }
@@ -675,7 +699,7 @@ struct GemmPairCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = (BN / 2) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = STG ? STG : ((BN >= 224) ? 6 : (BN >= 192 ? 7 : 8));
+  static constexpr int STAGES = STG ? STG : ((BN >= 224) ? 6 : 7);
   static constexpr int ACC_STRIDE = (BN > 128) ? 256 : BN;
   static constexpr int TMEM_COLS = (BN == 128) ? 256 : 512;
   static constexpr int EPI_WARP_BYTES = EpiWarpBytes<BN>::value;
@@ -832,6 +856,12 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
 using namespace qi;
 
+static int g_epi_dbg = 0;
+extern "C" int qi_gemm_set_debug(int mask) {   // profiling aid, not part of the public header
+  g_epi_dbg = mask;
+  return QI_OK;
+}
+
 static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int BN, int tile_begin,
                         int tile_m = BM, int b_box_rows = 0) {
   if (!in.a || !in.w || (!in.c && !(in.epilogue == QI_EPI_QKV_NORM_ROPE && in.scatter))) return QI_ERR_ARG;
@@ -860,6 +890,7 @@ static int fill_problem(GemmLaunch& L, int i, const qi_gemm_problem_t& in, int B
   P.m = in.m; P.batch = in.batch; P.n = in.n; P.k = in.k;
   P.epilogue = in.epilogue;
   P.c_fp32 = in.c_fp32 ? 1 : 0;
+  P.dbg = g_epi_dbg;
   P.gate_fp32 = (in.gate_fp32 && in.epilogue == QI_EPI_GATED_RESIDUAL) ? 1 : 0;
   if (P.gate_fp32 && ((reinterpret_cast<uintptr_t>(in.gate) & 15) || in.gate_batch_stride % 4 != 0)) return QI_ERR_ARG;
   P.freqs = nullptr; P.wq = P.wk = nullptr; P.sc_n = 0; P.sc_me = 0; P.sc_tpg = 0;
@@ -935,12 +966,13 @@ extern "C" int qi_gemm_set_group_m(int group_m) {
   g_group_m = group_m;
   return QI_OK;
 }
-static int gemm_group_m(int workers) {
+static int gemm_group_m(int workers, int tuned = -1) {
   static const int env = [] {
     const char* e = getenv("QI_GEMM_GROUP_M");
     return e ? atoi(e) : -1;
   }();
   if (g_group_m >= 0) return g_group_m;
+  if (tuned >= 0) return tuned;   // this launch's measured schedule
   if (env >= 0) return env;
   int g = 1;
   while ((g + 1) * (g + 1) <= workers) ++g;
@@ -948,7 +980,7 @@ static int gemm_group_m(int workers) {
 }
 
 template <int BN>
-static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
+static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t stream, int tuned_gm = -1) {
   GemmLaunch L;
   memset(&L, 0, sizeof(L));
   L.num_problems = num;
@@ -962,7 +994,7 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
   if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_kernel<BN>), GemmCfg<BN>::SMEM_BYTES)) return rc;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
-  L.group_m = gemm_group_m(sms);
+  L.group_m = gemm_group_m(sms, tuned_gm);
   const int grid = tiles < sms ? tiles : sms;
   if (qi_launch(gemm_bf16_kernel<BN>, dim3(grid), dim3(GEMM_THREADS), GemmCfg<BN>::SMEM_BYTES, stream, L) !=
       cudaSuccess)
@@ -971,7 +1003,7 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
 }
 
 template <int BN, int STG = 0>
-static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStream_t stream) {
+static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStream_t stream, int tuned_gm = -1) {
   GemmLaunch L;
   memset(&L, 0, sizeof(L));
   L.num_problems = num;
@@ -986,7 +1018,7 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
     return rc;
   const int pairs_max = qi_num_sms() / 2;
   if (pairs_max <= 0) return QI_ERR_CUDA;
-  L.group_m = gemm_group_m(pairs_max);
+  L.group_m = gemm_group_m(pairs_max, tuned_gm);
   const int pairs = tiles < pairs_max ? tiles : pairs_max;
   if (qi_launch(gemm_pair_bf16_kernel<BN, STG>, dim3(2 * pairs), dim3(GEMM_THREADS),
                 GemmPairCfg<BN, STG>::SMEM_BYTES, stream, L) != cudaSuccess)
@@ -1005,7 +1037,7 @@ extern "C" int qi_gemm_set_tile_n(int bn) {
 // (ops.tune_gemm: times every candidate once per new shape before the step is captured into a graph).
 struct TunedSchedule {
   int num, m[2], batch[2], n[2], k[2], epi[2];   // epi = epilogue | c_fp32 << 8
-  int pair, bn;
+  int pair, bn, group_m;   // group_m < 0: default rasterisation
 };
 static TunedSchedule g_tuned[512];
 static int g_num_tuned = 0;
@@ -1017,7 +1049,14 @@ static bool tuned_matches(const TunedSchedule& t, const qi_gemm_problem_t* p, in
       return false;
   return true;
 }
+extern "C" int qi_gemm_set_schedule_ex(const qi_gemm_problem_t* problems, int num_problems, int pair, int bn,
+                                       int group_m);
 extern "C" int qi_gemm_set_schedule(const qi_gemm_problem_t* problems, int num_problems, int pair, int bn) {
+  return qi_gemm_set_schedule_ex(problems, num_problems, pair, bn, -1);
+}
+extern "C" int qi_gemm_set_schedule_ex(const qi_gemm_problem_t* problems, int num_problems, int pair, int bn,
+                                       int group_m) {
+  if (group_m < -1 || group_m > 4096) return QI_ERR_ARG;
   if (!problems || num_problems < 1 || num_problems > 2 || pair < 0 || pair > 1) return QI_ERR_ARG;
   if (bn != 128 && bn != 160 && bn != 192 && bn != 224 && bn != 256) return QI_ERR_ARG;
   int slot = -1;
@@ -1036,6 +1075,7 @@ extern "C" int qi_gemm_set_schedule(const qi_gemm_problem_t* problems, int num_p
   }
   t.pair = pair;
   t.bn = bn;
+  t.group_m = group_m;
   return QI_OK;
 }
 extern "C" int qi_gemm_clear_schedules(void) {
@@ -1068,13 +1108,14 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
   for (int i = 0; i < num_problems; ++i)
     if (problems[i].epilogue == QI_EPI_QKV_NORM_ROPE && problems[i].head_dim > bn_multiple)
       bn_multiple = problems[i].head_dim;
-  int bn = g_force_bn, pair = pair_mode;
+  int bn = g_force_bn, pair = pair_mode, tuned_gm = -1;
   if (bn != 0 && bn % bn_multiple != 0) return QI_ERR_UNSUPPORTED;
   if (bn == 0 && pair < 0) {
     for (int i = 0; i < g_num_tuned; ++i)
       if (tuned_matches(g_tuned[i], problems, num_problems) && g_tuned[i].bn % bn_multiple == 0) {
         bn = g_tuned[i].bn;
         pair = g_tuned[i].pair;
+        tuned_gm = g_tuned[i].group_m;
         break;
       }
   }
@@ -1111,18 +1152,18 @@ extern "C" int qi_gemm_bf16(const qi_gemm_problem_t* problems, int num_problems,
       const char* e = getenv("QI_GEMM_PAIR_STAGES");   // tuning aid (256-wide pair tile only)
       return e ? atoi(e) : 0;
     }();
-    if (bn == 256 && env_stg == 3) return launch_gemm_pair<256, 3>(problems, num_problems, stream);
-    if (bn == 256 && env_stg == 4) return launch_gemm_pair<256, 4>(problems, num_problems, stream);
-    if (bn == 256 && env_stg == 5) return launch_gemm_pair<256, 5>(problems, num_problems, stream);
-    if (bn == 256) return launch_gemm_pair<256>(problems, num_problems, stream);
-    if (bn == 224) return launch_gemm_pair<224>(problems, num_problems, stream);
-    if (bn == 192) return launch_gemm_pair<192>(problems, num_problems, stream);
-    if (bn == 160) return launch_gemm_pair<160>(problems, num_problems, stream);
-    return launch_gemm_pair<128>(problems, num_problems, stream);
+    if (bn == 256 && env_stg == 3) return launch_gemm_pair<256, 3>(problems, num_problems, stream, tuned_gm);
+    if (bn == 256 && env_stg == 4) return launch_gemm_pair<256, 4>(problems, num_problems, stream, tuned_gm);
+    if (bn == 256 && env_stg == 5) return launch_gemm_pair<256, 5>(problems, num_problems, stream, tuned_gm);
+    if (bn == 256) return launch_gemm_pair<256>(problems, num_problems, stream, tuned_gm);
+    if (bn == 224) return launch_gemm_pair<224>(problems, num_problems, stream, tuned_gm);
+    if (bn == 192) return launch_gemm_pair<192>(problems, num_problems, stream, tuned_gm);
+    if (bn == 160) return launch_gemm_pair<160>(problems, num_problems, stream, tuned_gm);
+    return launch_gemm_pair<128>(problems, num_problems, stream, tuned_gm);
   }
-  if (bn == 256) return launch_gemm<256>(problems, num_problems, stream);
-  if (bn == 224) return launch_gemm<224>(problems, num_problems, stream);
-  if (bn == 192) return launch_gemm<192>(problems, num_problems, stream);
-  if (bn == 160) return launch_gemm<160>(problems, num_problems, stream);
-  return launch_gemm<128>(problems, num_problems, stream);
+  if (bn == 256) return launch_gemm<256>(problems, num_problems, stream, tuned_gm);
+  if (bn == 224) return launch_gemm<224>(problems, num_problems, stream, tuned_gm);
+  if (bn == 192) return launch_gemm<192>(problems, num_problems, stream, tuned_gm);
+  if (bn == 160) return launch_gemm<160>(problems, num_problems, stream, tuned_gm);
+  return launch_gemm<128>(problems, num_problems, stream, tuned_gm);
 }

@@ -164,8 +164,12 @@ def _time_launches(fn, launches: int, groups: int) -> float:
     return best
 
 
-def _tune_schedule(problems: Sequence[GemmProblem], launches: int, groups: int) -> Tuple[int, int]:
-    """Time every (pair, bn) candidate for ONE launch over `problems`; register and return the fastest."""
+_GROUP_M_CANDIDATES = (0, -1, 18, 36)     # column-major, default (~sqrt(workers)), and two taller supertiles
+
+
+def _tune_schedule(problems: Sequence[GemmProblem], launches: int, groups: int) -> Tuple[int, int, int]:
+    """Time every (pair, bn) candidate for ONE launch over `problems`, then the tile rasterisation (group_m) for
+    the winner; register and return the fastest (pair, bn, group_m)."""
     n = len(problems)
     arr = (GemmProblem * n)(*problems)
     lib = _lib.lib()
@@ -180,17 +184,86 @@ def _tune_schedule(problems: Sequence[GemmProblem], launches: int, groups: int) 
             t = _time_launches(lambda: lib.qi_gemm_bf16(arr, n, _stream()), launches, groups)
             if best_t is None or t < best_t:
                 best, best_t = (pair, bn), t
+        if best is None:
+            raise RuntimeError("tune_gemm: no valid schedule for these problems")
+        check(lib.qi_gemm_set_cta_pair(best[0]), "qi_gemm_set_cta_pair")
+        check(lib.qi_gemm_set_tile_n(best[1]), "qi_gemm_set_tile_n")
+        best_gm, best_gt = -1, None
+        for gm in _GROUP_M_CANDIDATES:
+            check(lib.qi_gemm_set_group_m(gm), "qi_gemm_set_group_m")
+            lib.qi_gemm_bf16(arr, n, _stream())
+            t = _time_launches(lambda: lib.qi_gemm_bf16(arr, n, _stream()), launches, groups)
+            if best_gt is None or t < 0.99 * best_gt:       # a later candidate must win by 1 %
+                best_gm, best_gt = gm, t
     finally:
         lib.qi_gemm_set_cta_pair(-1)
         lib.qi_gemm_set_tile_n(0)
-    if best is None:
-        raise RuntimeError("tune_gemm: no valid schedule for these problems")
-    check(lib.qi_gemm_set_schedule(arr, n, best[0], best[1]), "qi_gemm_set_schedule")
-    return best
+        lib.qi_gemm_set_group_m(-1)
+    check(lib.qi_gemm_set_schedule_ex(arr, n, best[0], best[1], best_gm), "qi_gemm_set_schedule_ex")
+    return best[0], best[1], best_gm
+
+
+# ------------------------------------------------------------------ persisted schedules
+# Tuned schedules are keyed by (SM count, library version, problem dims) and kept in two JSON files: one shipped
+# in-tree with the benchmark shapes (read-only) and one in the user's cache directory (read/write), so a new
+# process — and a new session in it — does not re-tune shapes that were measured before.
+_SCHEDULE_FILES = [os.path.join(os.path.dirname(os.path.abspath(__file__)), "tuned_schedules.json"),
+                   os.path.join(os.environ.get("QI_CACHE_DIR") or os.path.join(os.path.expanduser("~"), ".cache",
+                                                                               "vllm_omni_draft_b200"),
+                                "tuned_schedules.json")]
+_persisted = None
+
+
+def _persist_key(key) -> str:
+    lib = _lib.lib()
+    return f"sm{lib.qi_device_sm_count()}/v{lib.qi_version()}/" + ";".join(",".join(str(int(v)) for v in p) for p in key)
+
+
+def _load_persisted() -> dict:
+    global _persisted
+    if _persisted is None:
+        import json
+        _persisted = {}
+        if os.environ.get("QI_GEMM_SCHEDULE_CACHE", "1") != "0":
+            for f in _SCHEDULE_FILES:
+                try:
+                    with open(f) as fh:
+                        _persisted.update(json.load(fh))
+                except (OSError, ValueError):
+                    pass
+    return _persisted
+
+
+def _save_persisted(pkey: str, sched) -> None:
+    import json
+    _load_persisted()[pkey] = list(sched)
+    if os.environ.get("QI_GEMM_SCHEDULE_CACHE", "1") == "0":
+        return
+    f = _SCHEDULE_FILES[1]
+    try:
+        os.makedirs(os.path.dirname(f), exist_ok=True)
+        cur = {}
+        try:
+            with open(f) as fh:
+                cur = json.load(fh)
+        except (OSError, ValueError):
+            pass
+        cur[pkey] = list(sched)
+        tmp = f + f".{os.getpid()}.tmp"
+        with open(tmp, "w") as fh:
+            json.dump(cur, fh, indent=0, sort_keys=True)
+        os.replace(tmp, f)
+    except OSError:
+        pass                      # a read-only home is not an error: the schedule lives for this process
+
+
+def tuned_schedules() -> dict:
+    """Every schedule known to this process (persisted + measured now), keyed like the cache files."""
+    return dict(_load_persisted())
 
 
 def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 3,
-              allow_split: Optional[bool] = None) -> Optional[Tuple[int, int]]:
+              allow_split: Optional[bool] = None) -> Optional[Tuple[int, int, int]]:
     """Autotune the schedule (single-CTA / CTA-pair, tile width) for problems of these dims: every
     candidate is timed with CUDA events (best of `groups` groups of `launches` back-to-back launches) and
     the fastest is registered with the library (qi_gemm_set_schedule).  With `allow_split` (default: env
@@ -204,7 +277,16 @@ def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 
     key = _gemm_key(problems)
     if key in _tuned_keys:
         return None
-    best = _tune_schedule(problems, launches, groups)
+    pkey = _persist_key(key)
+    hit = _load_persisted().get(pkey)
+    if hit is not None and len(hit) == 3:
+        n = len(problems)
+        arr = (GemmProblem * n)(*problems)
+        check(_lib.lib().qi_gemm_set_schedule_ex(arr, n, int(hit[0]), int(hit[1]), int(hit[2])), "qi_gemm_set_schedule_ex")
+        best = tuple(int(v) for v in hit)
+    else:
+        best = _tune_schedule(problems, launches, groups)
+        _save_persisted(pkey, best)
     _tuned_keys.add(key)
     if allow_split is None:
         allow_split = os.environ.get("QI_GEMM_SPLIT", "0") == "1"
