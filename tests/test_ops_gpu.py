@@ -177,13 +177,15 @@ def test_attention(cuda_device, B, S, H, Dh):
     assert err < 1e-2, f"rel_l2={err}"
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 10, 11, 12])
-def test_attention_softmax_variants(cuda_device, variant):
+@pytest.mark.parametrize("Dh", [128, 64])
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 10, 11, 12, 16, 18, 19, 20])
+def test_attention_softmax_variants(cuda_device, variant, Dh):
     """Every softmax variant (MUFU only / 2-3-4 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
-    or in two halves) matches fp32 SDPA, on a ragged sequence (partial last K/V tile, partial Q tile) with
-    large-magnitude logits so the lazy rescale and the polynomial's range reduction are exercised."""
+    or in two halves, one thread or two threads per query row) matches fp32 SDPA, on a ragged sequence (partial
+    last K/V tile, partial Q tile) with large-magnitude logits so the lazy rescale and the polynomial's range
+    reduction are exercised."""
     ops = _ops()
-    B, S, H, Dh = 2, 1000, 3, 128
+    B, S, H = 2, 1000, 3
     d = H * Dh
     qkv = _rand((B, S, 3 * d), 51, 1.0)
     qkv[:, :, :d] *= 3.0                      # logits ~ N(0, 3*sqrt(128)*...) -> wide dynamic range

@@ -31,6 +31,7 @@ namespace qi {
 constexpr int ATT_BM = 128;   // query rows per tile
 constexpr int ATT_BN = 128;   // keys per tile
 constexpr int ATT_THREADS = 384;   // 3 warpgroups: softmax 0, softmax 1, {TMA, MMA, 2 idle}
+constexpr int ATT_THREADS2 = 640;  // TWO: 2 softmax warpgroups per Q tile (64 keys of every row each) + the same 4 warps
 constexpr int ATT_KV_STAGES = 2;
 
 template <int DH>
@@ -42,7 +43,8 @@ struct AttCfg {
   static constexpr int K_OFF = 2 * TILE_BYTES;
   static constexpr int V_OFF = K_OFF + ATT_KV_STAGES * TILE_BYTES;
   static constexpr int BAR_OFF = V_OFF + ATT_KV_STAGES * TILE_BYTES;
-  static constexpr int SMEM_BYTES = BAR_OFF + 256 + 1024;
+  static constexpr int XCH_OFF = BAR_OFF + 256;        // TWO: float [2 parities][2 tiles][2 halves][128 rows]
+  static constexpr int SMEM_BYTES = XCH_OFF + 4096 + 1024;
   // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,256+DH) O1 [384,384+DH)
   static constexpr int S_COL0 = 0, S_COL1 = 128, O_COL0 = 256, O_COL1 = 384;
 };
@@ -173,10 +175,106 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
   if (lane == 0) mbar_arrive(p_full);
 }
 
-template <int DH, int EMU, bool SPLIT>
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+
+// Rendezvous of the two warps that share 32 query rows (TWO): named barrier `id`, 64 threads.
+__device__ __forceinline__ void pair_sync(int id) {
+  asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+}
+
+// TWO: the same update with a row split over two threads (same lane of two warps in different warpgroups, same
+// TMEM lane quadrant): this thread owns keys [64*half, 64*half+64) of the tile and columns [half*DH/2, +DH/2) of O.
+// The row maximum is combined through shared memory (`xch_mine` / `xch_other`, double-buffered by the caller) and a
+// 64-thread named barrier; both threads then take identical rescale decisions.  The row sum stays partial per
+// thread and is combined once, in the epilogue.  Half 1 writes P over columns that held half 0's S values: the
+// barrier orders that store after half 0's tcgen05.ld (which is waited for before the barrier).
+template <int DH, bool MASK, int EMU>
+__device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_addr, int half, int kv_valid,
+                                                  bool first, float scale_log2, float& m_ref, float& l_sum,
+                                                  float* xch_mine, const float* xch_other, int bar_id,
+                                                  uint64_t* p_done, int lane) {
+  uint32_t r[2][32];
+  tmem_ld32(s_addr + half * 64, r[0]);
+  tmem_ld32(s_addr + half * 64 + 32, r[1]);
+  tmem_ld_wait();
+  if (MASK) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (half * 64 + c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;
+  }
+  float mxs[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) mxs[q] = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      mxs[i & 7] = fmaxf(fmaxf(mxs[i & 7], __uint_as_float(r[c][2 * i])), __uint_as_float(r[c][2 * i + 1]));
+  float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                   fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+  *xch_mine = mx;
+  pair_sync(bar_id);
+  mx = fmaxf(mx, *xch_other);
+  const float m_new = fmaxf(m_ref, mx * scale_log2);
+  const bool need = (m_new - m_ref) > 8.0f;
+  if (__any_sync(0xffffffffu, need)) {
+    const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;
+    if (need) {
+      l_sum *= f;
+      m_ref = m_new;
+    }
+    if (!first) {
+#pragma unroll 1
+      for (int c = 0; c < DH / 64; ++c) {
+        uint32_t o[32];
+        tmem_ld32(o_addr + half * (DH / 2) + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+        tmem_st32(o_addr + half * (DH / 2) + c * 32, o);
+      }
+    }
+  }
+  const float2 sc2 = make_float2(scale_log2, scale_log2);
+  const float2 nm2 = make_float2(-m_ref, -m_ref);
+  float2 acc[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) acc[q] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float2 x = __ffma2_rn(make_float2(__uint_as_float(r[c][2 * i]), __uint_as_float(r[c][2 * i + 1])),
+                                  sc2, nm2);
+      float2 p;
+      if (((i % 8) * EMU) % 8 < EMU) {
+        p = exp2_poly2(x);
+      } else {
+        p.x = fast_exp2(x.x);
+        p.y = fast_exp2(x.y);
+      }
+      acc[i & 3] = __fadd2_rn(acc[i & 3], p);
+      pk[i] = pack_bf16(p.x, p.y);
+    }
+    tmem_st16(s_addr + half * 32 + c * 16, pk);
+  }
+  const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
+  l_sum += (a01.x + a01.y) + (a23.x + a23.y);
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_done);
+}
+
+template <int DH, int EMU, bool SPLIT, bool TWO>
+__global__ void __launch_bounds__(TWO ? ATT_THREADS2 : ATT_THREADS, 1)
 attention_fwd_kernel(const __grid_constant__ AttParams P) {
   using Cfg = AttCfg<DH>;
+  static_assert(!TWO || SPLIT, "two threads per row publish P in two halves by construction");
+  constexpr int W_TMA = TWO ? 16 : 8;   // first warp of the last warpgroup
+  constexpr int W_MMA = W_TMA + 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -200,7 +298,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   const int n_kv = (P.seq_kv + ATT_BN - 1) / ATT_BN;
   pdl_launch_dependents();
 
-  if (warp == 8 && lane == 0) {
+  if (warp == W_TMA && lane == 0) {
     tma_prefetch_desc(&P.tmap_q);
     tma_prefetch_desc(&P.tmap_k);
     tma_prefetch_desc(&P.tmap_v);
@@ -217,7 +315,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     }
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc<512>(tmem_slot);
+  if (warp == W_MMA) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -226,9 +324,10 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
   // Register re-balance (setmaxnreg is per warpgroup and must sit inside each role's own branch so
   // that ptxas allocates every role against its own budget): warps 8-11 shrink, softmax warps grow.
-  if (warp == 8) {
+  if (warp == W_TMA) {
     // ------------------------------------------------------------------ TMA producer
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (elect_one()) {
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
       for (int t = 0; t < 2; ++t)
@@ -251,9 +350,10 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
+  } else if (warp == W_MMA) {
     // ------------------------------------------------------------------ MMA issuer
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (elect_one()) {   // elect.sync: ptxas knows a single thread issues (no per-instruction elect loops)
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
@@ -328,8 +428,89 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else if (warp >= 10) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+  } else if (warp > W_MMA) {
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+  } else if (TWO) {
+    // ------------------------------------------------------------------ softmax, two threads per query row
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    const int t = warp >> 3;                 // Q tile
+    const int half = (warp >> 2) & 1;        // which 64 keys of every K/V tile, which half of O's columns
+    const int quad = warp & 3;               // TMEM lane quadrant (warp % 4)
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_off + (t == 0 ? Cfg::S_COL0 : Cfg::S_COL1);
+    const uint32_t o_addr = tmem_base + lane_off + (t == 0 ? Cfg::O_COL0 : Cfg::O_COL1);
+    float* xch = reinterpret_cast<float*>(smem + Cfg::XCH_OFF);
+    const int xrow = quad * 32 + lane;
+    const int bar_id = 1 + t * 4 + quad;
+    uint64_t* p_done = half ? &p_full[t] : &p_half[t];
+    float m_ref = -INFINITY;
+    float l_sum = 0.f;                       // this thread's 64 keys only
+    const int n_full = P.seq_kv / ATT_BN;
+    for (int j = 0; j < n_kv; ++j) {
+      float* xm = xch + (((j & 1) * 2 + t) * 2 + half) * 128 + xrow;
+      const float* xo = xch + (((j & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+      mbar_wait(&s_full[t], j & 1);
+      tc_fence_after();
+      if (j < n_full) {
+        softmax_half_tile<DH, false, EMU>(s_addr, o_addr, half, ATT_BN, j == 0, P.scale_log2, m_ref, l_sum, xm, xo,
+                                          bar_id, p_done, lane);
+      } else {
+        softmax_half_tile<DH, true, EMU>(s_addr, o_addr, half, P.seq_kv - j * ATT_BN, j == 0, P.scale_log2, m_ref,
+                                         l_sum, xm, xo, bar_id, p_done, lane);
+      }
+    }
+    {   // row sum = both halves
+      float* xm = xch + (((n_kv & 1) * 2 + t) * 2 + half) * 128 + xrow;
+      const float* xo = xch + (((n_kv & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+      *xm = l_sum;
+      pair_sync(bar_id);
+      l_sum += *xo;
+    }
+    mbar_wait(&o_done[t], 0);
+    tc_fence_after();
+    const float inv = 1.f / l_sum;
+    constexpr int PPR = DH / 8;
+    constexpr int RPI = 32 / PPR;
+    uint8_t* stage = smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + quad * (32 * DH * 2);
+#pragma unroll 1
+    for (int c = 0; c < DH / 64; ++c) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + half * (DH / 2) + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        uint4 o;
+        o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+        o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+        o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+        o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+        const int piece = half * (DH / 16) + c * 4 + g;
+        *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + ((piece ^ (lane & 7)) << 4)) = o;
+      }
+    }
+    pair_sync(bar_id);
+    const int row_base = q0 + t * ATT_BM + quad * 32;
+    constexpr int ITS = 32 / RPI / 2;        // each of the two warps stores half of the 32 rows
+#pragma unroll 4
+    for (int it = half * ITS; it < (half + 1) * ITS; ++it) {
+      const int rr = it * RPI + lane / PPR;
+      const int piece = lane % PPR;
+      const int row = row_base + rr;
+      const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * (DH * 2) + ((piece ^ (rr & 7)) << 4));
+      if (row < P.seq_q) {
+        __nv_bfloat16* orow;
+        if (P.n_peer > 0) {
+          int p = 0;
+          while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
+          orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
+                 (size_t)head * P.o_hs;
+        } else {
+          orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * P.o_hs;
+        }
+        *reinterpret_cast<uint4*>(orow + piece * 8) = o;
+      }
+    }
   } else {
     // ------------------------------------------------------------------ softmax warpgroups
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
@@ -402,7 +583,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
@@ -412,9 +593,9 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, or 16 + EMU = two threads per row
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 15) return QI_ERR_ARG;
+  if (v < -1 || v > 23) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
@@ -427,12 +608,12 @@ static int attn_variant() {
   return v >= 0 ? v : QI_ATTN_DEFAULT_VARIANT;
 }
 
-template <int DH, int EMU, bool SPLIT>
+template <int DH, int EMU, bool SPLIT, bool TWO = false>
 static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream) {
-  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_fwd_kernel<DH, EMU, SPLIT>), AttCfg<DH>::SMEM_BYTES))
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_fwd_kernel<DH, EMU, SPLIT, TWO>), AttCfg<DH>::SMEM_BYTES))
     return rc;
-  if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream,
-                P) != cudaSuccess)
+  if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT, TWO>, grid, dim3(TWO ? ATT_THREADS2 : ATT_THREADS),
+                AttCfg<DH>::SMEM_BYTES, stream, P) != cudaSuccess)
     return QI_ERR_CUDA;
   return QI_OK;
 }
@@ -491,6 +672,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 10: return launch_attention_v<DH, 2, true>(P, grid, stream);
     case 11: return launch_attention_v<DH, 3, true>(P, grid, stream);
     case 12: return launch_attention_v<DH, 4, true>(P, grid, stream);
+    case 16: return launch_attention_v<DH, 0, true, true>(P, grid, stream);
+    case 18: return launch_attention_v<DH, 2, true, true>(P, grid, stream);
+    case 19: return launch_attention_v<DH, 3, true, true>(P, grid, stream);
+    case 20: return launch_attention_v<DH, 4, true, true>(P, grid, stream);
     default: return QI_ERR_ARG;
   }
 }
