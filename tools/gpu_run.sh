@@ -47,6 +47,13 @@ case "$T" in
     ncu -i gpurun_out/ncu_$W.ncu-rep --page raw --csv --print-units base > gpurun_out/ncu_${W}_raw.csv 2>/dev/null
     python tools/ncu_summary.py gpurun_out/ncu_${W}_raw.csv gpurun_out/ncu_${W}_summary.csv "ncu --set full --clock-control none, tools/prof_kernels.py $W 2 (cfg-2 shapes, batch 2)"
     cat gpurun_out/ncu_${W}_summary.csv;;
+  ncu_attn)
+    timeout -s KILL 300 python tools/prof_attn.py > /dev/null 2>&1 || { echo "plain run failed"; exit 1; }
+    timeout -s KILL 900 $NCU_FULL -c 12 -f -o gpurun_out/ncu_attn python tools/prof_attn.py > gpurun_out/ncu_attn.log 2>&1; echo "ncu rc=$?"
+    ncu -i gpurun_out/ncu_attn.ncu-rep --page raw --csv --print-units base > gpurun_out/ncu_attn_raw.csv 2>/dev/null
+    ncu -i gpurun_out/ncu_attn.ncu-rep --page details --csv --print-units base > gpurun_out/ncu_attn_details.csv 2>/dev/null
+    python tools/ncu_summary.py gpurun_out/ncu_attn_raw.csv gpurun_out/ncu_attn_summary.csv "ncu --set full --clock-control none, tools/prof_attn.py (batch 2, 4608 tokens, 24x128 heads): ours then cuDNN SDPA"
+    cat gpurun_out/ncu_attn_summary.csv;;
   ncu_step)
     timeout -s KILL 900 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-kernels --no-parity --e2e-steps 4 > gpurun_out/step_plain.json 2>&1 || { echo "plain run failed"; exit 1; }
     timeout -s KILL 1500 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 1400 --csv \

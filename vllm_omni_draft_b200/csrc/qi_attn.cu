@@ -62,6 +62,11 @@ struct AttParams {
   int o_prefix[9];
   long long o_chunk_off;
   __nv_bfloat16* o_peer[8];
+  // tuning aid (qi_attention_set_debug, not part of the ABI): cycle counters summed over CTAs —
+  // [0] MMA warp total, [1] waiting v_full, [2] p_half, [3] p_full, [4] k_full, [5] q/k first,
+  // [8] softmax warp 0 total, [9] waiting s_full, [10] waiting o_done,
+  // [11..15] one-thread softmax phases: S load, row max, O rescale, first half of P, second half
+  unsigned long long* dbg;
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -94,11 +99,21 @@ __device__ __forceinline__ float2 exp2_poly2(float2 x) {
 template <int DH, bool MASK, int EMU, bool SPLIT>
 __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, int kv_valid, bool first,
                                              float scale_log2, float& m_ref, float& l_sum,
-                                             uint64_t* p_half, uint64_t* p_full, int lane) {
+                                             uint64_t* p_half, uint64_t* p_full, int lane,
+                                             unsigned long long* pc = nullptr) {
   uint32_t r[ATT_BN / 32][32];
+  long long c_prev = pc ? clock64() : 0;
+  auto phase = [&](int i) {   // tuning aid: cycles per phase, thread 0 of the CTA only
+    if (pc) {
+      const long long now = clock64();
+      pc[i] += now - c_prev;
+      c_prev = now;
+    }
+  };
 #pragma unroll
   for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
   tmem_ld_wait();
+  phase(0);
   if (MASK) {
 #pragma unroll
     for (int c = 0; c < ATT_BN / 32; ++c)
@@ -118,6 +133,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
                          fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
   const float m_new = fmaxf(m_ref, mx * scale_log2);
   const bool need = (m_new - m_ref) > 8.0f;   // also true on the first tile (m_ref = -inf)
+  phase(1);
   if (__any_sync(0xffffffffu, need)) {
     const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on tile 0
     if (need) {
@@ -136,6 +152,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
       }
     }
   }
+  phase(2);
   // P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
   const float2 sc2 = make_float2(scale_log2, scale_log2);
   const float2 nm2 = make_float2(-m_ref, -m_ref);
@@ -165,6 +182,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_half);
+      phase(3);
     }
   }
   const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
@@ -173,6 +191,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(p_full);
+  phase(4);
 }
 
 
@@ -191,11 +210,20 @@ template <int DH, bool MASK, int EMU>
 __device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_addr, int half, int kv_valid,
                                                   bool first, float scale_log2, float& m_ref, float& l_sum,
                                                   float* xch_mine, const float* xch_other, int bar_id,
-                                                  uint64_t* p_done, int lane) {
+                                                  uint64_t* p_done, int lane, unsigned long long* pc = nullptr) {
   uint32_t r[2][32];
+  long long c_prev = pc ? clock64() : 0;
+  auto phase = [&](int i) {
+    if (pc) {
+      const long long now = clock64();
+      pc[i] += now - c_prev;
+      c_prev = now;
+    }
+  };
   tmem_ld32(s_addr + half * 64, r[0]);
   tmem_ld32(s_addr + half * 64 + 32, r[1]);
   tmem_ld_wait();
+  phase(0);
   if (MASK) {
 #pragma unroll
     for (int c = 0; c < 2; ++c)
@@ -214,10 +242,12 @@ __device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_ad
   float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
                    fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
   *xch_mine = mx;
+  phase(1);
   pair_sync(bar_id);
   mx = fmaxf(mx, *xch_other);
   const float m_new = fmaxf(m_ref, mx * scale_log2);
   const bool need = (m_new - m_ref) > 8.0f;
+  phase(2);   // TWO: [2] = the exchange (barrier + partner's maximum); the rare O rescale is counted with P
   if (__any_sync(0xffffffffu, need)) {
     const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;
     if (need) {
@@ -259,6 +289,7 @@ __device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_ad
       pk[i] = pack_bf16(p.x, p.y);
     }
     tmem_st16(s_addr + half * 32 + c * 16, pk);
+    phase(3 + c);
   }
   const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
   l_sum += (a01.x + a01.y) + (a23.x + a23.y);
@@ -266,6 +297,7 @@ __device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_ad
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(p_done);
+  phase(4);
 }
 
 template <int DH, int EMU, bool SPLIT, bool TWO>
@@ -326,7 +358,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   // that ptxas allocates every role against its own budget): warps 8-11 shrink, softmax warps grow.
   if (warp == W_TMA) {
     // ------------------------------------------------------------------ TMA producer
-    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (elect_one()) {
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
@@ -352,7 +384,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     __syncwarp();
   } else if (warp == W_MMA) {
     // ------------------------------------------------------------------ MMA issuer
-    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (elect_one()) {   // elect.sync: ptxas knows a single thread issues (no per-instruction elect loops)
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
@@ -384,8 +416,19 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         }
       };
 
-      mbar_wait(q_full, 0);
-      mbar_wait(&k_full[0], 0);
+      unsigned long long w_v = 0, w_ph = 0, w_pf = 0, w_k = 0, w_q = 0;
+      const long long t_begin = clock64();
+      auto timed_wait = [&](uint64_t* bar, uint32_t parity, unsigned long long& acc) {
+        if (P.dbg) {
+          const long long c0 = clock64();
+          mbar_wait(bar, parity);
+          acc += clock64() - c0;
+        } else {
+          mbar_wait(bar, parity);
+        }
+      };
+      timed_wait(q_full, 0, w_q);
+      timed_wait(&k_full[0], 0, w_q);
       tc_fence_after();
       issue_qk(0, 0);
       tc_commit(&s_full[0]);
@@ -398,24 +441,24 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         const bool has_next = (j + 1) < n_kv;
         const int stn = (j + 1) & 1;
         const uint32_t phn = ((j + 1) >> 1) & 1;
-        mbar_wait(&v_full[st], ph);
+        timed_wait(&v_full[st], ph, w_v);
         for (int t = 0; t < 2; ++t) {
           if (SPLIT) {
-            mbar_wait(&p_half[t], j & 1);
+            timed_wait(&p_half[t], j & 1, w_ph);
             tc_fence_after();
             issue_pv(t, st, j > 0, 0, ATT_BN / 32);
-            mbar_wait(&p_full[t], j & 1);
+            timed_wait(&p_full[t], j & 1, w_pf);
             tc_fence_after();
             issue_pv(t, st, j > 0, ATT_BN / 32, ATT_BN / 16);
           } else {
-            mbar_wait(&p_full[t], j & 1);
+            timed_wait(&p_full[t], j & 1, w_pf);
             tc_fence_after();
             issue_pv(t, st, j > 0, 0, ATT_BN / 16);
           }
           if (t == 1) tc_commit(&v_empty[st]);
           if (has_next) {
             if (t == 0) {
-              mbar_wait(&k_full[stn], phn);
+              timed_wait(&k_full[stn], phn, w_k);
               tc_fence_after();
             }
             issue_qk(t, stn);
@@ -426,10 +469,18 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
           }
         }
       }
+      if (P.dbg) {
+        atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
+        atomicAdd(&P.dbg[1], w_v);
+        atomicAdd(&P.dbg[2], w_ph);
+        atomicAdd(&P.dbg[3], w_pf);
+        atomicAdd(&P.dbg[4], w_k);
+        atomicAdd(&P.dbg[5], w_q);
+      }
     }
     __syncwarp();
   } else if (warp > W_MMA) {
-    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+    if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   } else if (TWO) {
     // ------------------------------------------------------------------ softmax, two threads per query row
@@ -447,14 +498,20 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     float m_ref = -INFINITY;
     float l_sum = 0.f;                       // this thread's 64 keys only
     const int n_full = P.seq_kv / ATT_BN;
+    const bool prof = P.dbg != nullptr && threadIdx.x == 0;
+    unsigned long long w_s = 0;
+    unsigned long long pcs[5] = {0, 0, 0, 0, 0};
+    const long long t_begin = clock64();
     for (int j = 0; j < n_kv; ++j) {
       float* xm = xch + (((j & 1) * 2 + t) * 2 + half) * 128 + xrow;
       const float* xo = xch + (((j & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+      const long long c0 = prof ? clock64() : 0;
       mbar_wait(&s_full[t], j & 1);
+      if (prof) w_s += clock64() - c0;
       tc_fence_after();
       if (j < n_full) {
         softmax_half_tile<DH, false, EMU>(s_addr, o_addr, half, ATT_BN, j == 0, P.scale_log2, m_ref, l_sum, xm, xo,
-                                          bar_id, p_done, lane);
+                                          bar_id, p_done, lane, prof ? pcs : nullptr);
       } else {
         softmax_half_tile<DH, true, EMU>(s_addr, o_addr, half, P.seq_kv - j * ATT_BN, j == 0, P.scale_log2, m_ref,
                                          l_sum, xm, xo, bar_id, p_done, lane);
@@ -466,6 +523,14 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       *xm = l_sum;
       pair_sync(bar_id);
       l_sum += *xo;
+    }
+    if (prof) {
+      for (int i = 0; i < 5; ++i) atomicAdd(&P.dbg[11 + i], pcs[i]);
+      const long long c0 = clock64();
+      mbar_wait(&o_done[t], 0);
+      atomicAdd(&P.dbg[10], (unsigned long long)(clock64() - c0));
+      atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
+      atomicAdd(&P.dbg[9], w_s);
     }
     mbar_wait(&o_done[t], 0);
     tc_fence_after();
@@ -522,18 +587,32 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     float m_ref = -INFINITY;   // reference max (scaled, log2 domain) used for P and O
     float l_sum = 0.f;
     const int n_full = P.seq_kv / ATT_BN;   // K/V tiles with all 128 keys valid
+    const bool prof = P.dbg != nullptr && threadIdx.x == 0;
+    unsigned long long w_s = 0;
+    unsigned long long pcs[5] = {0, 0, 0, 0, 0};   // S load, row max, O rescale, first half of P, second half
+    const long long t_begin = clock64();
     for (int j = 0; j < n_kv; ++j) {
+      const long long c0 = prof ? clock64() : 0;
       mbar_wait(&s_full[t], j & 1);
+      if (prof) w_s += clock64() - c0;
       tc_fence_after();
       if (j < n_full) {
         softmax_tile<DH, false, EMU, SPLIT>(s_addr, o_addr, ATT_BN, j == 0, P.scale_log2, m_ref, l_sum,
-                                            &p_half[t], &p_full[t], lane);
+                                            &p_half[t], &p_full[t], lane, prof ? pcs : nullptr);
       } else {
         softmax_tile<DH, true, EMU, SPLIT>(s_addr, o_addr, P.seq_kv - j * ATT_BN, j == 0, P.scale_log2,
                                            m_ref, l_sum, &p_half[t], &p_full[t], lane);
       }
     }
     // final: O / l -> bf16 -> global
+    if (prof) {
+      for (int i = 0; i < 5; ++i) atomicAdd(&P.dbg[11 + i], pcs[i]);
+      const long long c0 = clock64();
+      mbar_wait(&o_done[t], 0);
+      atomicAdd(&P.dbg[10], (unsigned long long)(clock64() - c0));
+      atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
+      atomicAdd(&P.dbg[9], w_s);
+    }
     mbar_wait(&o_done[t], 0);
     tc_fence_after();
     const float inv = 1.f / l_sum;
@@ -599,6 +678,11 @@ extern "C" int qi_attention_set_variant(int v) {
   g_attn_variant = v;
   return QI_OK;
 }
+static unsigned long long* g_attn_dbg = nullptr;   // device buffer of >= 16 counters, or null
+extern "C" int qi_attention_set_debug(unsigned long long* buf) {
+  g_attn_dbg = buf;
+  return QI_OK;
+}
 static int attn_variant() {
   static const int env = [] {
     const char* e = getenv("QI_ATTN_VARIANT");   // tuning aid: EMU (0,2,3,4) + 8 * SPLIT
@@ -660,6 +744,7 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.seq_kv = seq_kv;
   P.heads = heads;
   P.scale_log2 = scale * 1.4426950408889634f;
+  P.dbg = g_attn_dbg;
   const int variant = attn_variant();
   P.split_p = (variant >> 3) & 1;
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
