@@ -57,6 +57,7 @@ int qi_set_pdl(int on);
  * weight [n, k] contiguous, C is [batch, m, n] (ldc, c_batch_stride).  k % 64 == 0, n % 8 == 0.
  * A zero-initialised struct with a/w/c/m/batch/n/k set is a plain C = A W^T. */
 struct qi_peer_scatter; /* defined with the Ulysses exchange entry points below */
+struct qi_peer_signal;
 typedef struct {
   const void* a;
   long long lda;
@@ -90,14 +91,18 @@ typedef struct {
   int head_dim;
   float qk_norm_eps;
   /* Optional Ulysses scatter (NULL = store into c): head vector (b, row, j in {q,k,v}, head h) goes to
-   * base[h / (heads/P)], laid out [batch, row_prefix[P], 3, heads/P, head_dim], at sequence row
-   * row_prefix[my_index] + rope_pos0 + row.  c may be NULL then. */
+   * base[h / (heads/P)], laid out HEAD-MAJOR [batch, 3, heads/P, row_prefix[P], head_dim] (the layout
+   * qi_qknorm_rope_scatter writes), at sequence row row_prefix[my_index] + rope_pos0 + row.  c may be NULL then.
+   * scatter->notify (problem 0's) is signalled by the launch's last CTA. */
   const struct qi_peer_scatter* scatter;
   /* C (and the residual R of QI_EPI_GATED_RESIDUAL) are fp32 instead of bf16; ldc / ld_res / batch strides stay in
    * ELEMENTS.  QI_EPI_BIAS and QI_EPI_GATED_RESIDUAL only.  The MMDiT residual streams are kept in fp32 this way:
    * 60 blocks x 2 in-place bf16 roundings otherwise accumulate to a relative error of 1.9e-2. */
   int c_fp32;
   int gate_fp32; /* QI_EPI_GATED_RESIDUAL: gate is fp32 [batch, n] (a row of the fp32 modulation table) */
+  /* Problem 0 only, host pointer or NULL: the A operands of this launch were stored by peers (the attention
+   * scatter); the TMA producers poll these flags before their first load (see qi_peer_signal_t). */
+  const struct qi_peer_signal* wait;
 } qi_gemm_problem_t;
 
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
@@ -174,12 +179,29 @@ int qi_qknorm_rope(void* qkv, int rows, int ld, int heads, int head_dim, int seq
  * into this process (qi_peer_import, or any other peer mapping); rank p owns heads
  * [p*heads/P, (p+1)*heads/P) and sequence rows [row_prefix[p], row_prefix[p+1]) of the rank-major
  * joint sequence (ragged shards allowed). */
+/* Flags of one exchange, folded into the kernels on either side of it (no qi_peer_barrier launch in between):
+ * as `notify`, the LAST CTA of the scattering kernel bumps state[0] and release-increments slots[p][my_index] on
+ * every peer once all of the kernel's peer stores are ordered before it; as `wait`, the consuming kernel's loader
+ * thread acquire-polls slots[my_index][p] >= state[0] for every p before its first load of exchanged data (so the
+ * consumer must follow, in stream order, the producer of the same exchange on the same rank, and every rank must
+ * run the same sequence of exchanges).  A poll that exceeds timeout_ms sets state[2] and returns; once set, later
+ * waits return immediately (the host checks it, PeerExchange.timed_out()). */
+typedef struct qi_peer_signal {
+  void* const* slots;   /* DEVICE array [n_peers]: slots[p] = rank p's uint32[n_peers] slot array (peer mapped) */
+  unsigned int* state;  /* local DEVICE words, zero-initialised: [0] epoch, [1] CTA arrival counter, [2] timeout flag */
+  int n_peers, my_index;
+  unsigned int timeout_ms; /* 0: 2000 */
+} qi_peer_signal_t;
+
 typedef struct qi_peer_scatter {
   int n_peers;       /* P <= 8 */
   int my_index;      /* this rank's position in the group */
   void* base[8];
   int row_prefix[9]; /* row_prefix[P] = total sequence length */
   long long chunk_stride; /* attention scatter only: elements between head-group chunks at the destination */
+  const qi_peer_signal_t* notify; /* host pointer or NULL: signal the peers when this kernel's stores are done */
+  const qi_peer_signal_t* wait;   /* host pointer or NULL (qi_attention_fwd_scatter): flags of the exchange that
+                                     delivered this kernel's q/k/v */
 } qi_peer_scatter_t;
 
 /* K2 with scatter: qkv is this rank's [batch*seq, ld] row block ([q|k|v], all heads); normalised and

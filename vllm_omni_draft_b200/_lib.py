@@ -33,6 +33,7 @@ class GemmProblem(C.Structure):
         ("rope_pos0", _i), ("heads", _i), ("head_dim", _i), ("qk_norm_eps", C.c_float),
         ("scatter", _vp),
         ("c_fp32", _i), ("gate_fp32", _i),
+        ("wait", _vp),
     ]
 
 
@@ -42,10 +43,15 @@ class NormRows(C.Structure):
                 ("mod_batch_stride", _ll), ("rows_per_batch", _i), ("x_fp32", _i), ("mod_fp32", _i)]
 
 
+class PeerSignal(C.Structure):
+    """qi_peer_signal_t"""
+    _fields_ = [("slots", _vp), ("state", _vp), ("n_peers", _i), ("my_index", _i), ("timeout_ms", C.c_uint)]
+
+
 class PeerScatter(C.Structure):
     """qi_peer_scatter_t"""
     _fields_ = [("n_peers", _i), ("my_index", _i), ("base", _vp * 8), ("row_prefix", _i * 9),
-                ("chunk_stride", _ll)]
+                ("chunk_stride", _ll), ("notify", _vp), ("wait", _vp)]
 
 
 _SIGNATURES = {

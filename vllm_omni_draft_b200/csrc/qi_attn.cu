@@ -62,6 +62,8 @@ struct AttParams {
   int o_prefix[9];
   long long o_chunk_off;
   __nv_bfloat16* o_peer[8];
+  PeerSignal wait;     // flags of the exchange that delivered q/k/v (polled by the TMA thread), or slots == null
+  PeerSignal notify;   // flags of the O scatter (signalled by the grid's last CTA), or slots == null
   // tuning aid (qi_attention_set_debug, not part of the ABI): cycle counters summed over CTAs —
   // [0] MMA warp total, [1] waiting v_full, [2] p_half, [3] p_full, [4] k_full, [5] q/k first,
   // [8] softmax warp 0 total, [9] waiting s_full, [10] waiting o_done,
@@ -361,6 +363,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     if (elect_one()) {
+      peer_wait_all(P.wait);
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
       for (int t = 0; t < 2; ++t)
         for (int s = 0; s < Cfg::NSUB; ++s)
@@ -662,6 +665,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) peer_notify_last_cta(P.notify, gridDim.x * gridDim.y * gridDim.z);
   if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
@@ -718,6 +722,18 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     }
     P.o_prefix[dst->n_peers] = dst->row_prefix[dst->n_peers];
     P.o_chunk_off = (long long)dst->my_index * dst->chunk_stride;
+    for (int i = 0; i < 2; ++i) {
+      const qi_peer_signal_t* s = i ? dst->notify : dst->wait;
+      PeerSignal& d = i ? P.notify : P.wait;
+      if (!s) continue;
+      if (!s->slots || !s->state || s->n_peers < 1 || s->n_peers > 8 || s->my_index < 0 || s->my_index >= s->n_peers)
+        return QI_ERR_ARG;
+      d.slots = reinterpret_cast<uint32_t* const*>(s->slots);
+      d.state = s->state;
+      d.n = s->n_peers;
+      d.me = s->my_index;
+      d.timeout_ns = (unsigned long long)(s->timeout_ms ? s->timeout_ms : 2000) * 1000000ull;
+    }
   }
   const uint32_t box[4] = {64, 1, ATT_BM, 1};
   {

@@ -303,6 +303,66 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// ------------------------------------------------------------------ folded peer flags (qi_peer_signal_t)
+// The Ulysses exchange needs "every peer's stores have landed" between the scattering producer kernel and
+// its consumer on the other GPUs.  Instead of a flag-barrier kernel in between, the producer's LAST CTA
+// release-increments this rank's slot on every peer, and the consumer's loader thread acquire-polls its own
+// slots before the first load of exchanged data.  Epochs are monotone (CUDA-graph replayable); the consumer
+// reads the expected epoch from `state[0]`, which the producer kernel of the SAME rank and the same exchange
+// bumped (every rank runs the same sequence of exchanges; griddepcontrol.wait orders the read).
+struct PeerSignal {
+  uint32_t* const* slots;   // device array [n]: slots[p] = rank p's slot array (uint32[n], peer mapped)
+  uint32_t* state;          // local: [0] epoch, [1] CTA arrival counter, [2] sticky timeout flag
+  int n, me;
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ unsigned long long peer_global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Producer: ONE thread per CTA, after a CTA-wide barrier that follows the CTA's last store to peer memory.
+__device__ __forceinline__ void peer_notify_last_cta(const PeerSignal& s, unsigned total_ctas) {
+  if (s.slots == nullptr) return;
+  __threadfence_system();   // cumulative: the CTA's stores (observed through the barrier) before the count
+  const unsigned old = atomicAdd(&s.state[1], 1u);
+  if (old + 1 == total_ctas) {
+    __threadfence_system();
+    s.state[1] = 0;   // for the next launch (which cannot count before this kernel has completed)
+    s.state[0] = s.state[0] + 1;
+    for (int p = 0; p < s.n; ++p) {
+      uint32_t* remote = s.slots[p] + s.me;
+      asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(remote) : "memory");
+    }
+  }
+}
+
+// Consumer: one thread (the one that issues the loads), after griddepcontrol.wait.  Followed by a proxy
+// fence because the data is read by TMA (async proxy).
+__device__ __forceinline__ void peer_wait_all(const PeerSignal& s) {
+  if (s.slots == nullptr) return;
+  const uint32_t epoch = *reinterpret_cast<volatile const uint32_t*>(&s.state[0]);
+  if (*reinterpret_cast<volatile const uint32_t*>(&s.state[2]) == 0) {
+    const uint32_t* mine = s.slots[s.me];
+    const unsigned long long t0 = peer_global_ns();
+    for (int p = 0; p < s.n; ++p) {
+      for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + p) : "memory");
+        if (static_cast<int32_t>(v - epoch) >= 0) break;
+        if (peer_global_ns() - t0 > s.timeout_ns) {
+          atomicExch(&s.state[2], 1u);
+          break;
+        }
+        __nanosleep(20);
+      }
+    }
+  }
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+
 // ------------------------------------------------------------------ host side helpers
 }  // namespace qi
 

@@ -70,7 +70,22 @@ struct GemmLaunch {
   int num_problems;
   int total_tiles;
   int group_m;   // tile rasterisation: supertiles of group_m row tiles x all column tiles (0: column-major order)
+  PeerSignal notify;   // slots != null: the launch's last CTA signals the peers (problem 0's scatter->notify)
+  PeerSignal wait;     // slots != null: the TMA producers poll before their first load (problem 0's wait)
 };
+
+// Host: qi_peer_signal_t -> the by-value device form.
+static int fill_signal(PeerSignal& d, const qi_peer_signal_t* s) {
+  if (!s) return QI_OK;
+  if (!s->slots || !s->state || s->n_peers < 1 || s->n_peers > 8 || s->my_index < 0 || s->my_index >= s->n_peers)
+    return QI_ERR_ARG;
+  d.slots = reinterpret_cast<uint32_t* const*>(s->slots);
+  d.state = s->state;
+  d.n = s->n_peers;
+  d.me = s->my_index;
+  d.timeout_ns = (unsigned long long)(s->timeout_ms ? s->timeout_ms : 2000) * 1000000ull;
+  return QI_OK;
+}
 
 template <int BN>
 struct GemmCfg {
@@ -590,6 +605,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
+      peer_wait_all(L.wait);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -679,6 +695,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) peer_notify_last_cta(L.notify, gridDim.x);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
@@ -754,6 +771,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
     if (elect_one()) {
+      peer_wait_all(L.wait);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = pair; t < L.total_tiles; t += num_pairs) {
@@ -846,6 +864,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   tc_fence_before();
   cluster_sync_all();
+  if (threadIdx.x == 0) peer_notify_last_cta(L.notify, gridDim.x);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc_pair<Cfg::TMEM_COLS>(tmem_base);
@@ -991,6 +1010,8 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
     tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
   }
   L.total_tiles = tiles;
+  if (int rc = fill_signal(L.notify, problems[0].scatter ? problems[0].scatter->notify : nullptr)) return rc;
+  if (int rc = fill_signal(L.wait, problems[0].wait)) return rc;
   if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_kernel<BN>), GemmCfg<BN>::SMEM_BYTES)) return rc;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
@@ -1014,6 +1035,8 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
     tiles += L.prob[i].tiles_m_total * L.prob[i].tiles_n;
   }
   L.total_tiles = tiles;
+  if (int rc = fill_signal(L.notify, problems[0].scatter ? problems[0].scatter->notify : nullptr)) return rc;
+  if (int rc = fill_signal(L.wait, problems[0].wait)) return rc;
   if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_pair_bf16_kernel<BN, STG>), GemmPairCfg<BN, STG>::SMEM_BYTES))
     return rc;
   const int pairs_max = qi_num_sms() / 2;

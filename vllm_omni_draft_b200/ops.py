@@ -5,7 +5,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-from typing import Optional, Sequence, Tuple
+from typing import List, Optional, Sequence, Tuple
 
 import torch
 
@@ -53,13 +53,15 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
                  gate: Optional[torch.Tensor] = None, a_k_chunked: bool = False,
                  qk_norm: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, freqs: Optional[torch.Tensor] = None,
                  rope_pos0: int = 0, heads: int = 0, head_dim: int = 0, eps: float = 1e-6,
-                 scatter: Optional["_lib.PeerScatter"] = None) -> GemmProblem:
+                 scatter: Optional["_lib.PeerScatter"] = None,
+                 wait: Optional["_lib.PeerSignal"] = None) -> GemmProblem:
     """a_k_chunked: a is [chunks, M, Kc] and stands for the [M, chunks*Kc] matrix whose K axis is
     the concatenation of the chunks (batch 1).  Otherwise a: [B, M, K] or [M, K] view (row/batch strides arbitrary, K contiguous); w: [N, K] contiguous;
     out: [B, M, N] / [M, N] view; residual like out; gate [B, N] view.
     EPI_QKV_NORM_ROPE: w is the stacked [3*heads*head_dim, K] q|k|v projection, qk_norm = (norm_q weight,
     norm_k weight), freqs fp32 [rows, head_dim/2, 2]; row r uses table row rope_pos0 + r.  With `scatter`
-    the head vectors go to the head owners' attention input buffers and `out` may be None."""
+    the head vectors go to the head owners' attention input buffers and `out` may be None.  `wait` (problem 0 of
+    a launch): flags of the peer exchange that stored this launch's A operands (qi_peer_signal_t)."""
     _req_bf16(a, w, bias)
     gate_fp32 = _req_bf16_or_f32(gate)
     c_fp32 = _req_bf16_or_f32(out, residual)
@@ -85,6 +87,9 @@ def gemm_problem(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor],
         raise ValueError(f"gemm shape mismatch: a{tuple(a.shape)} w{tuple(w.shape)} "
                          f"out{tuple(out.shape) if out is not None else None}")
     p = GemmProblem()
+    if wait is not None:
+        p.wait = C.addressof(wait)
+        p._keep_wait = wait
     p.a, p.lda, p.a_batch_stride = a.data_ptr(), a.stride(1), a.stride(0)
     p.w, p.bias = w.data_ptr(), _ptr(bias)
     if out is not None:
@@ -262,6 +267,22 @@ def tuned_schedules() -> dict:
     return dict(_load_persisted())
 
 
+def _without_signals(problems: Sequence[GemmProblem]) -> List[GemmProblem]:
+    """Copies of the problems with the folded peer flags removed (scatter->notify / wait): timing launches are not
+    part of the exchange protocol — every rank must signal each exchange exactly once per forward."""
+    out = []
+    for p in problems:
+        q = GemmProblem.from_buffer_copy(p)
+        q.wait = None
+        if p.scatter:
+            sc = _lib.PeerScatter.from_buffer_copy(_lib.PeerScatter.from_address(p.scatter))
+            sc.notify, sc.wait = None, None
+            q.scatter = C.addressof(sc)
+            q._keep = sc
+        out.append(q)
+    return out
+
+
 def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 3,
               allow_split: Optional[bool] = None) -> Optional[Tuple[int, int, int]]:
     """Autotune the schedule (single-CTA / CTA-pair, tile width) for problems of these dims: every
@@ -277,6 +298,7 @@ def tune_gemm(problems: Sequence[GemmProblem], launches: int = 6, groups: int = 
     key = _gemm_key(problems)
     if key in _tuned_keys:
         return None
+    problems = _without_signals(problems)
     pkey = _persist_key(key)
     hit = _load_persisted().get(pkey)
     if hit is not None and len(hit) == 3:

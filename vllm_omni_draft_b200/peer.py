@@ -11,7 +11,11 @@ all-to-all around attention; here that exchange is folded into the kernels on ei
 * both buffers are HEAD-MAJOR: the rows of one head are adjacent at the destination, because the peer
   write rate depends on the destination stride (tools/p2p_bw.py: 128-byte segments 574 GB/s at a 256-byte
   row stride, 324 GB/s at the 4608-byte stride of a token-major ``[.., 3, H/P, Dh]`` row);
-* between producer and consumer sits ``qi_peer_barrier`` (a 32-thread flag kernel), twice per block.
+* between producer and consumer there is no kernel: the producer's last CTA release-increments this rank's flag
+  on every peer, the consumer's loader thread acquire-polls its own flags before the first load
+  (``qi_peer_signal_t``: ``sig_qkv`` rides in ``dst_qkv.notify`` / ``dst_o.wait``, ``sig_o`` in ``dst_o.notify``
+  and the out-projection GEMM's ``wait``).  ``QI_PEER_FOLD=0`` goes back to ``qi_peer_barrier`` (a 32-thread
+  flag kernel) twice per block, which the unfused K2 path still uses.
 
 Host layer only: allocate one peer-mappable region per rank (``qi_peer_alloc``), ship the 64-byte
 CUDA-IPC handles over ``torch.distributed`` and map the peers' regions (``qi_peer_import``).  No
@@ -20,13 +24,14 @@ data moves through this module.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Sequence
 
 import torch
 import torch.distributed as dist
 
 from . import _lib, ops
-from ._lib import PeerScatter, check
+from ._lib import PeerScatter, PeerSignal, check
 
 _ALIGN = 1024
 _SIG_BYTES = 1024
@@ -98,6 +103,15 @@ class PeerExchange:
                     self._mapped.append(q.value)
         self.sig_table = torch.tensor(self.ptrs, dtype=torch.int64, device=device)   # signal array at offset 0
         self.state = torch.zeros(2, dtype=torch.int32, device=device)
+        # folded flags: slot arrays of the two exchanges at byte offsets 64 and 128 of every rank's region
+        self.fold = os.environ.get("QI_PEER_FOLD", "1") != "0"
+        self._slot_tables = [torch.tensor([q + off for q in self.ptrs], dtype=torch.int64, device=device)
+                             for off in (64, 128)]
+        self.sig_state = torch.zeros(2, 4, dtype=torch.int32, device=device)   # per exchange: epoch, CTA count, timeout
+        self.sig_qkv, self.sig_o = PeerSignal(), PeerSignal()
+        for i, sg in enumerate((self.sig_qkv, self.sig_o)):
+            sg.slots, sg.state = self._slot_tables[i].data_ptr(), self.sig_state[i].data_ptr()
+            sg.n_peers, sg.my_index, sg.timeout_ms = size, rank, int(timeout_ms)
         # local views (bf16) of this rank's own region
         raw = torch.as_tensor(_RawDeviceMemory(self._own, self.nbytes // 2), device=device).view(torch.bfloat16)
         self._raw = raw
@@ -115,6 +129,13 @@ class PeerExchange:
             for i, v in enumerate(self.pre):
                 d.row_prefix[i] = v
         self.dst_o.chunk_stride = batch * self.s_max * row          # one source rank's H/P head chunks
+        # the same descriptors without flags (barrier-kernel protocol)
+        self.dst_qkv_plain = PeerScatter.from_buffer_copy(self.dst_qkv)
+        self.dst_o_plain = PeerScatter.from_buffer_copy(self.dst_o)
+        if self.fold:
+            self.dst_qkv.notify = C.addressof(self.sig_qkv)
+            self.dst_o.wait = C.addressof(self.sig_qkv)
+            self.dst_o.notify = C.addressof(self.sig_o)
         self.o_ld = head_dim
         self.o_batch_stride = self.s_max * head_dim
         self.o_head_stride = batch * self.s_max * head_dim
@@ -125,7 +146,7 @@ class PeerExchange:
         ops.peer_barrier(self.sig_table, self.size, self.rank, self.state, self.timeout_ms)
 
     def timed_out(self) -> bool:
-        return bool(self.state[1].item() != 0)
+        return bool(self.state[1].item() != 0) or bool((self.sig_state[:, 2] != 0).any().item())
 
     def close(self) -> None:
         if getattr(self, "_own", None) is None:

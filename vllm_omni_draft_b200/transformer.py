@@ -486,8 +486,12 @@ class B200QwenImageTransformer2DModel(nn.Module):
         G = ops.EPI_GATED_RESIDUAL
         N2 = [None, None]
 
-        def gated(a_i, a_t, w, bias, g_i, g_t, chunked=False):
+        def gated(a_i, a_t, w, bias, g_i, g_t, chunked=False, wait=None):
             # out-projection / MLP-down of both streams: h, e updated in place by the gated-residual epilogue
+            if wait is not None:    # A was stored by peers: the flags ride in the problem struct (ctypes call)
+                ops.gemm([ops.gemm_problem(a_i, w[0], bias[0], h, G, h, bview(g_i), a_k_chunked=chunked, wait=wait),
+                          ops.gemm_problem(a_t, w[1], bias[1], e, G, e, bview(g_t), a_k_chunked=chunked)])
+                return
             Q.gemm_bf16([a_i, a_t], [w[0], w[1]], [bias[0], bias[1]], [h, e], G, [h, e],
                         [bview(g_i), bview(g_t)], chunked)
 
@@ -502,7 +506,9 @@ class B200QwenImageTransformer2DModel(nn.Module):
             # QKV projection with QK-RMSNorm + MSRoPE applied per head vector in the GEMM epilogue (K2 fused
             # into K3); text rows first in the joint sequence, so the img stream's row 0 sits at table row s_txt
             nw = self.qk_norm_w[l]
-            sc = peer.dst_qkv if peer is not None else None
+            sc = None
+            if peer is not None:
+                sc = peer.dst_qkv if (peer.fold and self.fuse_qknorm_rope) else peer.dst_qkv_plain
             w_qkv, b_qkv = self.qkv_w[l], self.qkv_b[l]
             if self.fuse_qknorm_rope and sc is not None:
                 # peer scatter: the head vectors leave through CUDA-IPC pointers (no tensor form) -> ctypes call
@@ -527,16 +533,23 @@ class B200QwenImageTransformer2DModel(nn.Module):
                 gated(att_img, att_txt, self.out_w[l], self.out_b[l], g_i1, g_t1)
             elif peer is not None:
                 # Fused exchange over peer memory: the QKV GEMM's epilogue has stored each head vector into
-                # the head owner's HBM, attention stores each output row into the token owner's HBM; two
-                # flag barriers.
-                peer.barrier()
+                # the head owner's HBM, attention stores each output row into the token owner's HBM.  The
+                # "all peers' stores have landed" flags are folded into the kernels (producer's last CTA
+                # signals, consumer's TMA thread polls: peer.sig_qkv / peer.sig_o inside the descriptors);
+                # without the fused QKV epilogue, or with QI_PEER_FOLD=0, two flag-barrier kernels instead.
+                folded = peer.fold and self.fuse_qknorm_rope
+                dst_o = peer.dst_o if folded else peer.dst_o_plain
+                if not folded:
+                    peer.barrier()
                 full = peer.recv                       # head-major [B, 3, H/P, S_total, Dh]
                 ops.attention_scatter(full[:, 0].transpose(1, 2), full[:, 1].transpose(1, 2),
-                                      full[:, 2].transpose(1, 2), peer.dst_o, peer.o_ld, peer.o_batch_stride,
+                                      full[:, 2].transpose(1, 2), dst_o, peer.o_ld, peer.o_batch_stride,
                                       o_head_stride=peer.o_head_stride)
-                peer.barrier()
+                if not folded:
+                    peer.barrier()
                 back = peer.back[:, :, :S]             # [P*H/P, B, S_loc, Dh]: K-chunked A operand (chunk = head)
-                gated(back[:, :, s_txt:], back[:, :, :s_txt], self.out_w[l], self.out_b[l], g_i1, g_t1, True)
+                gated(back[:, :, s_txt:], back[:, :, :s_txt], self.out_w[l], self.out_b[l], g_i1, g_t1, True,
+                      wait=peer.sig_o if folded else None)
             else:
                 # NCCL head<->sequence all-to-all: [S_loc, H] -> [S, H/P]; attention; back as K-chunked A
                 full = sp.scatter_heads(ws.qkv.view(S, 3 * d), H, Dh, ws.a2a_send, ws.a2a_recv)
