@@ -362,8 +362,8 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     // ------------------------------------------------------------------ TMA producer
     if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    peer_wait_all_warp(P.wait, lane);
     if (elect_one()) {
-      peer_wait_all(P.wait);
       mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
       for (int t = 0; t < 2; ++t)
         for (int s = 0; s < Cfg::NSUB; ++s)

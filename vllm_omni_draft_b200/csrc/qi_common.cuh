@@ -339,27 +339,28 @@ __device__ __forceinline__ void peer_notify_last_cta(const PeerSignal& s, unsign
   }
 }
 
-// Consumer: one thread (the one that issues the loads), after griddepcontrol.wait.  Followed by a proxy
-// fence because the data is read by TMA (async proxy).
-__device__ __forceinline__ void peer_wait_all(const PeerSignal& s) {
+// Consumer: the whole warp of the thread that issues the loads, after griddepcontrol.wait.  Lane p polls peer p's
+// flag (one round trip for all peers); the warp barrier + system fence order every lane's later loads after the
+// acquires, and the proxy fence covers the TMA (async proxy) reads that follow.
+__device__ __forceinline__ void peer_wait_all_warp(const PeerSignal& s, int lane) {
   if (s.slots == nullptr) return;
   const uint32_t epoch = *reinterpret_cast<volatile const uint32_t*>(&s.state[0]);
-  if (*reinterpret_cast<volatile const uint32_t*>(&s.state[2]) == 0) {
-    const uint32_t* mine = s.slots[s.me];
+  if (lane < s.n && *reinterpret_cast<volatile const uint32_t*>(&s.state[2]) == 0) {
+    const uint32_t* mine = s.slots[s.me] + lane;
     const unsigned long long t0 = peer_global_ns();
-    for (int p = 0; p < s.n; ++p) {
-      for (;;) {
-        uint32_t v;
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + p) : "memory");
-        if (static_cast<int32_t>(v - epoch) >= 0) break;
-        if (peer_global_ns() - t0 > s.timeout_ns) {
-          atomicExch(&s.state[2], 1u);
-          break;
-        }
-        __nanosleep(20);
+    for (;;) {
+      uint32_t v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      if (static_cast<int32_t>(v - epoch) >= 0) break;
+      if (peer_global_ns() - t0 > s.timeout_ns) {
+        atomicExch(&s.state[2], 1u);
+        break;
       }
+      __nanosleep(20);
     }
   }
+  __syncwarp();
+  __threadfence_system();
   asm volatile("fence.proxy.async;" ::: "memory");
 }
 

@@ -70,6 +70,8 @@ struct GemmLaunch {
   int num_problems;
   int total_tiles;
   int group_m;   // tile rasterisation: supertiles of group_m row tiles x all column tiles (0: column-major order)
+  CUtensorMap tmap_sc[8];   // sc_tma: rank p's attention input buffer as [batch*3*heads/P, s_total, head_dim] (TMA store)
+  int sc_tma;
   PeerSignal notify;   // slots != null: the launch's last CTA signals the peers (problem 0's scatter->notify)
   PeerSignal wait;     // slots != null: the TMA producers poll before their first load (problem 0's wait)
 };
@@ -396,7 +398,8 @@ __device__ __forceinline__ void epilogue_rows_f32(const GemmProb& P, int b, int 
 // over NVLink: the head<->sequence all-to-all happens tile by tile under the GEMM's main loop.
 template <int BN, int DH, typename Release>
 __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int row, int n0,
-                                                  uint32_t taddr, int half, uint8_t* stage, Release release) {
+                                                  uint32_t taddr, int half, uint8_t* stage, Release release,
+                                                  const CUtensorMap* sc_maps) {
   constexpr int HPT = BN / DH;   // head vectors per tile row
   constexpr bool WIDE = EpiWarpBytes<BN>::value >= 4096;   // 128-byte row segments (else 64-byte)
   const bool row_ok = row < P.m;
@@ -415,9 +418,15 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
     // [batch, 3, heads/P, s_total, DH] attention input buffer over NVLink)
     __nv_bfloat16* dst_base;
     size_t dst_ld;
+    const CUtensorMap* tmap = nullptr;   // TMA store of whole 32-row slabs (scatter, WIDE staging)
+    int tma_slab = 0;
     if (P.sc_n > 0) {
       const int p = h / P.sc_hs;
       const int hl = h - p * P.sc_hs;
+      if (WIDE && sc_maps != nullptr && row0 + 32 <= P.m) {
+        tmap = sc_maps + p;
+        tma_slab = (b * 3 + j3) * P.sc_hs + hl;
+      }
       // head-major destination [batch, 3, heads/P, s_total, DH]: one head's rows are adjacent
       dst_ld = (size_t)DH;
       dst_base = P.sc_base[p] +
@@ -498,6 +507,11 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
         const uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
                                    pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
         if constexpr (WIDE) {
+          if (sc_maps != nullptr && g == 0 && (c & 1) == 0) {
+            // the staging tile may still be the source of the previous bulk store
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+          }
           const int gp = (c & 1) * 4 + g;      // piece inside the 128-byte (two-chunk) row segment
           *reinterpret_cast<uint4*>(stage + lane * 128 + ((gp ^ (lane & 7)) << 4)) = o;
         } else {
@@ -508,7 +522,20 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
         // Two chunks make one full 128-byte line per row: 8 lanes write a row's line, 4 rows per instruction.
         // Over NVLink the packet count halves against 64-byte segments (the scatter is bound by the peer
         // write rate, not by the tensor pipe, once the head vectors leave the GPU).
-        if (c & 1) {
+        if ((c & 1) && tmap != nullptr) {
+          // The staging tile is [32 rows][128 B] with the 16-byte pieces XOR-swizzled by (row & 7): exactly TMA's
+          // SWIZZLE_128B.  One bulk tensor store moves the slab's 4 KB to the head owner's HBM (32 rows of one
+          // head are adjacent there), instead of 8 st.global.v4 per lane through the LSU and over NVLink.
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) {
+            asm volatile(
+                "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];\n"
+                "cp.async.bulk.commit_group;" ::"l"(reinterpret_cast<uint64_t>(tmap)),
+                "r"((c - 1) * 32), "r"(P.sc_row_offset + P.pos0 + row0), "r"(tma_slab), "r"(smem_u32(stage))
+                : "memory");
+          }
+        } else if (c & 1) {
           __syncwarp();
 #pragma unroll 4
           for (int it = 0; it < 8; ++it) {
@@ -543,7 +570,8 @@ __device__ __forceinline__ void epilogue_rows_qkv(const GemmProb& P, int b, int 
 // variants that can start work earlier (fp32 residual prefetch) call it late, the others first thing.
 template <int BN, typename Wait, typename Release>
 __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row, int n0, uint32_t taddr,
-                                              int half, uint8_t* stage, Wait wait, Release release) {
+                                              int half, uint8_t* stage, Wait wait, Release release,
+                                              const CUtensorMap* sc_maps = nullptr) {
   if (P.c_fp32 && P.epilogue != QI_EPI_QKV_NORM_ROPE) {
     epilogue_rows_f32<BN>(P, b, row, n0, taddr, half, stage, wait, release);
     return;
@@ -552,12 +580,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmProb& P, int b, int row,
   if (P.epilogue == QI_EPI_QKV_NORM_ROPE) {
     if constexpr (BN % 128 == 0) {
       if (P.head_dim == 128) {
-        epilogue_rows_qkv<BN, 128>(P, b, row, n0, taddr, half, stage, release);
+        epilogue_rows_qkv<BN, 128>(P, b, row, n0, taddr, half, stage, release, sc_maps);
         return;
       }
     }
     if constexpr (BN % 64 == 0)
-      epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, stage, release);   // host guarantees head_dim == 64 here
+      epilogue_rows_qkv<BN, 64>(P, b, row, n0, taddr, half, stage, release, nullptr);   // host guarantees head_dim == 64 here
     return;
   }
   epilogue_rows<BN>(P, b, row, n0, taddr, half, stage, release);
@@ -570,7 +598,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::EPI_STAGE_BYTES);
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full = empty_bar + Cfg::STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -604,8 +632,8 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
+    peer_wait_all_warp(L.wait, lane);
     if (elect_one()) {
-      peer_wait_all(L.wait);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -671,7 +699,7 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (2..9)
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
-    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * Cfg::EPI_WARP_BYTES;
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + (warp - 2) * Cfg::EPI_WARP_BYTES;   // 1024-aligned
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < L.total_tiles; t += gridDim.x) {
@@ -685,11 +713,15 @@ gemm_bf16_kernel(const __grid_constant__ GemmLaunch L) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-      });
+      }, L.sc_tma ? L.tmap_sc : nullptr);
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
+    }
+    if (L.sc_tma && lane == 0) {   // this lane's bulk stores have been written before the CTA signals / exits
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      asm volatile("fence.proxy.async;" ::: "memory");
     }
   }
 
@@ -732,7 +764,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::EPI_STAGE_BYTES);
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full = empty_bar + Cfg::STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -770,8 +802,8 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
+    peer_wait_all_warp(L.wait, lane);
     if (elect_one()) {
-      peer_wait_all(L.wait);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = pair; t < L.total_tiles; t += num_pairs) {
@@ -838,7 +870,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
   } else {
     // ------------------------------------------------------------ epilogue warps (both CTAs)
     const int q = warp & 3;
-    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256 + (warp - 2) * Cfg::EPI_WARP_BYTES;
+    uint8_t* epi_stage = smem + Cfg::STAGES * Cfg::STAGE_BYTES + (warp - 2) * Cfg::EPI_WARP_BYTES;   // 1024-aligned
     int acc = 0;
     uint32_t acc_phase = 0;
     const uint32_t empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
@@ -854,11 +886,15 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(acc == 0 ? empty0 : empty1);
-      });
+      }, L.sc_tma ? L.tmap_sc : nullptr);
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
+    }
+    if (L.sc_tma && lane == 0) {
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      asm volatile("fence.proxy.async;" ::: "memory");
     }
   }
 
@@ -998,6 +1034,34 @@ static int gemm_group_m(int workers, int tuned = -1) {
   return g + ((g * (g + 1) <= workers) ? 1 : 0);   // round sqrt to nearest
 }
 
+// Scatter destinations as TMA-store tensors (QI_SCATTER_TMA=0: 16-byte st.global per lane instead).  Every problem
+// of the launch must scatter into the same buffers (the img and txt streams of one block do).
+static int fill_scatter_maps(GemmLaunch& L, const qi_gemm_problem_t* problems, int num) {
+  static const bool on = [] {
+    const char* e = getenv("QI_SCATTER_TMA");
+    return !(e && e[0] == '0');
+  }();
+  const qi_peer_scatter_t* d = problems[0].scatter;
+  if (!on || !d || problems[0].epilogue != QI_EPI_QKV_NORM_ROPE || problems[0].head_dim != 128) return QI_OK;
+  for (int i = 1; i < num; ++i) {
+    const qi_peer_scatter_t* e = problems[i].scatter;
+    if (!e || e->n_peers != d->n_peers || problems[i].batch != problems[0].batch ||
+        problems[i].heads != problems[0].heads || problems[i].head_dim != 128)
+      return QI_OK;
+    for (int p = 0; p < d->n_peers; ++p)
+      if (e->base[p] != d->base[p]) return QI_OK;
+  }
+  const int hs = problems[0].heads / d->n_peers;
+  const uint64_t s_total = (uint64_t)d->row_prefix[d->n_peers];
+  const uint64_t dims[3] = {128, s_total, (uint64_t)problems[0].batch * 3 * hs};
+  const uint64_t str[2] = {128 * 2, s_total * 128 * 2};
+  const uint32_t box[3] = {64, 32, 1};
+  for (int p = 0; p < d->n_peers; ++p)
+    if (int rc = qi_encode_tmap_bf16(&L.tmap_sc[p], d->base[p], 3, dims, str, box)) return rc;
+  L.sc_tma = 1;
+  return QI_OK;
+}
+
 template <int BN>
 static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t stream, int tuned_gm = -1) {
   GemmLaunch L;
@@ -1012,6 +1076,7 @@ static int launch_gemm(const qi_gemm_problem_t* problems, int num, cudaStream_t 
   L.total_tiles = tiles;
   if (int rc = fill_signal(L.notify, problems[0].scatter ? problems[0].scatter->notify : nullptr)) return rc;
   if (int rc = fill_signal(L.wait, problems[0].wait)) return rc;
+  if (int rc = fill_scatter_maps(L, problems, num)) return rc;
   if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_bf16_kernel<BN>), GemmCfg<BN>::SMEM_BYTES)) return rc;
   const int sms = qi_num_sms();
   if (sms <= 0) return QI_ERR_CUDA;
@@ -1037,6 +1102,7 @@ static int launch_gemm_pair(const qi_gemm_problem_t* problems, int num, cudaStre
   L.total_tiles = tiles;
   if (int rc = fill_signal(L.notify, problems[0].scatter ? problems[0].scatter->notify : nullptr)) return rc;
   if (int rc = fill_signal(L.wait, problems[0].wait)) return rc;
+  if (int rc = fill_scatter_maps(L, problems, num)) return rc;
   if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(gemm_pair_bf16_kernel<BN, STG>), GemmPairCfg<BN, STG>::SMEM_BYTES))
     return rc;
   const int pairs_max = qi_num_sms() / 2;
