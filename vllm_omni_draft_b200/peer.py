@@ -11,11 +11,14 @@ all-to-all around attention; here that exchange is folded into the kernels on ei
 * both buffers are HEAD-MAJOR: the rows of one head are adjacent at the destination, because the peer
   write rate depends on the destination stride (tools/p2p_bw.py: 128-byte segments 574 GB/s at a 256-byte
   row stride, 324 GB/s at the 4608-byte stride of a token-major ``[.., 3, H/P, Dh]`` row);
-* between producer and consumer there is no kernel: the producer's last CTA release-increments this rank's flag
-  on every peer, the consumer's loader thread acquire-polls its own flags before the first load
-  (``qi_peer_signal_t``: ``sig_qkv`` rides in ``dst_qkv.notify`` / ``dst_o.wait``, ``sig_o`` in ``dst_o.notify``
-  and the out-projection GEMM's ``wait``).  ``QI_PEER_FOLD=0`` goes back to ``qi_peer_barrier`` (a 32-thread
-  flag kernel) twice per block, which the unfused K2 path still uses.
+* between producer and consumer sits ``qi_peer_barrier`` (a 32-thread flag kernel, overlapped with its
+  neighbours' tails by programmatic dependent launch), twice per block.  ``QI_PEER_FOLD=1`` folds the flags into
+  the kernels instead (``qi_peer_signal_t``: the producer's last CTA release-increments this rank's flag on every
+  peer, the consumer's loader warp acquire-polls its own flags before the first load; ``sig_qkv`` rides in
+  ``dst_qkv.notify`` / ``dst_o.wait``, ``sig_o`` in ``dst_o.notify`` and the out-projection GEMM's ``wait``).
+  Measured on 4 GPUs (cfg-2, CFG x Ulysses-2, interleaved runs on one box) the folded form is 1.7 % SLOWER
+  (39.97 vs 39.27 ms/step): with PDL the barrier launches cost nothing that the in-kernel poll does not also
+  cost, and 216 attention CTAs polling system-scope flags is not free.  It stays as a tested option.
 
 Host layer only: allocate one peer-mappable region per rank (``qi_peer_alloc``), ship the 64-byte
 CUDA-IPC handles over ``torch.distributed`` and map the peers' regions (``qi_peer_import``).  No
@@ -104,7 +107,7 @@ class PeerExchange:
         self.sig_table = torch.tensor(self.ptrs, dtype=torch.int64, device=device)   # signal array at offset 0
         self.state = torch.zeros(2, dtype=torch.int32, device=device)
         # folded flags: slot arrays of the two exchanges at byte offsets 64 and 128 of every rank's region
-        self.fold = os.environ.get("QI_PEER_FOLD", "1") != "0"
+        self.fold = os.environ.get("QI_PEER_FOLD", "0") == "1"
         self._slot_tables = [torch.tensor([q + off for q in self.ptrs], dtype=torch.int64, device=device)
                              for off in (64, 128)]
         self.sig_state = torch.zeros(2, 4, dtype=torch.int32, device=device)   # per exchange: epoch, CTA count, timeout
