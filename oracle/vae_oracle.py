@@ -54,13 +54,28 @@ class VAEOracleConfig:
         return dims[0], out
 
 
+def encoder_dims(cfg: VAEOracleConfig):
+    """[(in_dim, out_dim, downsample_mode or None)] per encoder stage (QwenImageEncoder3d.__init__:
+    dims = base_dim * [1] + dim_mult; 'downsample3d' where temperal_downsample says so)."""
+    dims = [cfg.base_dim * u for u in (1,) + tuple(cfg.dim_mult)]
+    out = []
+    for i, (a, b) in enumerate(zip(dims[:-1], dims[1:])):
+        mode = None
+        if i != len(cfg.dim_mult) - 1:
+            mode = "downsample3d" if cfg.temperal_downsample[i] else "downsample2d"
+        out.append((a, b, mode))
+    return out
+
+
 def tiny_vae_config() -> VAEOracleConfig:
     return VAEOracleConfig(base_dim=8, dim_mult=(1, 2, 4, 4), num_res_blocks=1)
 
 
 def init_vae_state_dict(cfg: VAEOracleConfig, seed: int = 0, weight_std: float = 0.05,
-                        bias_std: float = 0.02, gamma_std: float = 0.1) -> Dict[str, torch.Tensor]:
-    """Random decoder weights under diffusers parameter names (fp32)."""
+                        bias_std: float = 0.02, gamma_std: float = 0.1,
+                        with_encoder: bool = True) -> Dict[str, torch.Tensor]:
+    """Random decoder (+ encoder) weights under diffusers parameter names (fp32).  The encoder entries are drawn
+    AFTER the decoder's, so the decoder weights of a seed do not depend on `with_encoder` (golden fixtures)."""
     g = torch.Generator().manual_seed(seed)
     sd: Dict[str, torch.Tensor] = {}
 
@@ -105,6 +120,31 @@ def init_vae_state_dict(cfg: VAEOracleConfig, seed: int = 0, weight_std: float =
         last = o
     gamma("decoder.norm_out", last, False)
     conv3("decoder.conv_out", 3, last, (3, 3, 3))
+    if with_encoder:
+        # QwenImageEncoder3d: down_blocks is ONE flat ModuleList (residual blocks and resamples interleaved)
+        stages = encoder_dims(cfg)
+        conv3("encoder.conv_in", stages[0][0], 3, (3, 3, 3))
+        k = 0
+        for (i, o, mode) in stages:
+            cur = i
+            for _ in range(cfg.num_res_blocks):
+                resblock(f"encoder.down_blocks.{k}.", cur, o)
+                cur = o
+                k += 1
+            if mode is not None:
+                conv2(f"encoder.down_blocks.{k}.resample.1", o, o, 3)
+                if mode == "downsample3d":
+                    conv3(f"encoder.down_blocks.{k}.time_conv", o, o, (3, 1, 1))
+                k += 1
+        top = stages[-1][1]
+        resblock("encoder.mid_block.resnets.0.", top, top)
+        gamma("encoder.mid_block.attentions.0.norm", top, True)
+        conv2("encoder.mid_block.attentions.0.to_qkv", 3 * top, top, 1)
+        conv2("encoder.mid_block.attentions.0.proj", top, top, 1)
+        resblock("encoder.mid_block.resnets.1.", top, top)
+        gamma("encoder.norm_out", top, False)
+        conv3("encoder.conv_out", 2 * z, top, (3, 3, 3))
+        conv3("quant_conv", 2 * z, 2 * z, (1, 1, 1))
     return sd
 
 
@@ -182,6 +222,64 @@ def decode(sd, cfg: VAEOracleConfig, z: torch.Tensor) -> torch.Tensor:
     x = F.silu(rms_norm_channels(x, sd["decoder.norm_out.gamma"]))
     x = causal_conv3d(x, sd["decoder.conv_out.weight"], sd["decoder.conv_out.bias"])
     return torch.clamp(x, min=-1.0, max=1.0)
+
+
+def resample_down(sd, p: str, x: torch.Tensor) -> torch.Tensor:
+    """QwenImageResample 'downsample2d'/'downsample3d' on the FIRST chunk of a clip: per frame ZeroPad2d((0,1,0,1))
+    then a 3x3 stride-2 conv; the temporal stride-2 conv of 'downsample3d' only runs from the second chunk on
+    (upstream stores the first chunk in its feature cache and returns), so an image never meets it."""
+    b, c, t, h, w = x.shape
+    x = x.permute(0, 2, 1, 3, 4).reshape(b * t, c, h, w)
+    x = F.pad(x, (0, 1, 0, 1))
+    x = F.conv2d(x, sd[p + "resample.1.weight"], sd[p + "resample.1.bias"], stride=2)
+    return x.view(b, t, x.shape[1], x.shape[2], x.shape[3]).permute(0, 2, 1, 3, 4)
+
+
+def encode(sd, cfg: VAEOracleConfig, x: torch.Tensor) -> torch.Tensor:
+    """AutoencoderKLQwenImage._encode on ONE frame [B, 3, 1, H, W] in [-1, 1] -> posterior moments
+    [B, 2*z, 1, H/8, W/8] (mean | logvar): encoder (conv_in, flat down_blocks, mid block, norm/SiLU/conv_out) then
+    quant_conv.  H and W must be multiples of 8."""
+    if x.dim() == 4:
+        x = x.unsqueeze(2)
+    if x.shape[2] != 1:
+        raise ValueError("the image pipeline encodes exactly one frame")
+    x = causal_conv3d(x, sd["encoder.conv_in.weight"], sd["encoder.conv_in.bias"])
+    k = 0
+    for (_, _, mode) in encoder_dims(cfg):
+        for _ in range(cfg.num_res_blocks):
+            x = residual_block(sd, f"encoder.down_blocks.{k}.", x)
+            k += 1
+        if mode is not None:
+            x = resample_down(sd, f"encoder.down_blocks.{k}.", x)
+            k += 1
+    x = residual_block(sd, "encoder.mid_block.resnets.0.", x)
+    x = attention_block(sd, "encoder.mid_block.attentions.0.", x)
+    x = residual_block(sd, "encoder.mid_block.resnets.1.", x)
+    x = F.silu(rms_norm_channels(x, sd["encoder.norm_out.gamma"]))
+    x = causal_conv3d(x, sd["encoder.conv_out.weight"], sd["encoder.conv_out.bias"])
+    return causal_conv3d(x, sd["quant_conv.weight"], sd["quant_conv.bias"])
+
+
+def encode_mode(sd, cfg: VAEOracleConfig, x: torch.Tensor) -> torch.Tensor:
+    """``retrieve_latents(vae.encode(image), sample_mode="argmax")``: the posterior's mode = its mean."""
+    return encode(sd, cfg, x)[:, :cfg.z_dim]
+
+
+def normalize_latents(latents: torch.Tensor, cfg: VAEOracleConfig) -> torch.Tensor:
+    """QwenImageEditPipeline._encode_vae_image after the encode: ``(latents - mean) / std`` per latent channel."""
+    shape = [1, cfg.z_dim] + [1] * (latents.dim() - 2)
+    mean = torch.tensor(cfg.latents_mean).view(shape).to(latents.device, latents.dtype)
+    std = torch.tensor(cfg.latents_std).view(shape).to(latents.device, latents.dtype)
+    return (latents - mean) / std
+
+
+def calculate_dimensions(target_area: int, ratio: float):
+    """QwenImageEditPipeline's output size for an input image of aspect ratio width/height: the area is
+    target_area, both sides rounded to multiples of 32.  Returns (width, height)."""
+    import math
+    width = math.sqrt(target_area * ratio)
+    height = width / ratio
+    return int(round(width / 32) * 32), int(round(height / 32) * 32)
 
 
 def denormalize_latents(latents: torch.Tensor, cfg: VAEOracleConfig) -> torch.Tensor:

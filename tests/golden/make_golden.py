@@ -82,8 +82,22 @@ def widen():
     out["vae_decode"] = V.decode(vsd, vcfg, z)
     out["vae_image_from_edit_final_s4"] = V.decode_packed(vsd, vcfg, final, 32, 32)[:, :, ::4, ::4].clone()
     torch.save(out, os.path.join(HERE, "tiny_widen.pt"))
+    vae_encode_golden()
     print("wrote", os.listdir(HERE))
 
 
+def vae_encode_golden():
+    """The encoder half (row b2: pixel images in), its own small file so the older fixtures stay byte-identical."""
+    vcfg = V.tiny_vae_config()
+    vsd = V.init_vae_state_dict(vcfg, seed=0)
+    x = torch.rand(2, 3, 1, 48, 80, generator=torch.Generator().manual_seed(8)) * 2 - 1
+    out = {"vae_encode_moments": V.encode(vsd, vcfg, x),
+           "vae_encode_normalized_mode": V.normalize_latents(V.encode_mode(vsd, vcfg, x), vcfg)}
+    torch.save(out, os.path.join(HERE, "tiny_vae_encode.pt"))
+
+
 if __name__ == "__main__":
-    main()
+    if "--vae-encode-only" in sys.argv:
+        vae_encode_golden()
+    else:
+        main()

@@ -249,6 +249,91 @@ def test_decoded_image_psnr(tiny):
     assert V.psnr(same.float().cpu(), ref_img) >= 40.0
 
 
+def test_vae_encoder_decoder_at_real_dimensions(cuda_device):
+    """Rows b2 / f1 at the real AutoencoderKLQwenImage dimensions (base 96, mult (1,2,4,4), 2 residual blocks,
+    z = 16; random-init): the one-frame bf16 encoder and decoder on the GPU against the 5-D causal fp32 restatement
+    (oracle/vae_oracle.py) run on the same GPU, on a non-square 384 x 512 image."""
+    from oracle import vae_oracle as V
+    from vllm_omni_draft_b200.vae import B200QwenImageVAE
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    vcfg = V.VAEOracleConfig()
+    vsd = {k: v.bfloat16().float().cuda() for k, v in V.init_vae_state_dict(vcfg, seed=1, weight_std=0.03).items()}
+    vae = B200QwenImageVAE(device="cuda:0")
+    vae.load_diffusers_state_dict(vsd)
+    g = torch.Generator().manual_seed(12)
+    x = (torch.rand(1, 3, 1, 384, 512, generator=g) * 2 - 1).bfloat16().float().cuda()
+    want = V.encode(vsd, vcfg, x)
+    dist = vae.encode(x).latent_dist
+    got = torch.cat([dist.mean, dist.logvar], 1).float()
+    assert got.shape == want.shape == (1, 32, 1, 48, 64)
+    err_mean = O.rel_l2(dist.mean.float(), want[:, :16])
+    err_all = O.rel_l2(got, want)
+    z = want[:, :16].contiguous()
+    img_want = V.decode(vsd, vcfg, z)
+    img = vae.decode(z).sample.float()
+    db = V.psnr(img, img_want)
+    print(f"VAE real dims: encode mean rel-L2 {err_mean:.3e}, moments {err_all:.3e}; decode PSNR {db:.1f} dB "
+          f"(image std {float(img_want.std()):.3f})")
+    assert err_mean < 2e-2 and err_all < 2e-2          # bf16 activations through 11 residual blocks
+    assert float(img_want.std()) > 0.02 and db >= 40.0
+
+
+def test_pipeline_takes_pixel_images_like_the_reference(tiny):
+    """The reference's literal call (src/performance_enhancement/test_performance.py:244-251, 277):
+    `pipe(image=<list of PIL images>, prompt_embeds=, prompt_embeds_mask=, generator=, num_inference_steps=,
+    true_cfg_scale=1.0, num_images_per_prompt=1).images` -> PIL images at the edit pipeline's working size
+    (~1024^2 at the input's aspect ratio), checked against the oracle: Lanczos resize, VAE encode (mode),
+    normalise, pack, edit loop, decode."""
+    import numpy as np
+    from PIL import Image
+    from oracle import vae_oracle as V
+    from vllm_omni_draft_b200.pipeline import B200QwenImagePipeline
+    from vllm_omni_draft_b200.vae import B200QwenImageVAE
+    ocfg, sd, tr = tiny
+    vcfg = V.tiny_vae_config()
+    vsd = V.init_vae_state_dict(vcfg, seed=0)
+    vae = B200QwenImageVAE(base_dim=vcfg.base_dim, num_res_blocks=vcfg.num_res_blocks, device="cuda:0")
+    vae.load_diffusers_state_dict(vsd)
+    pipe = B200QwenImagePipeline(tr, vae=vae)
+    rng = np.random.default_rng(3)
+    yy, xx = np.mgrid[0:480, 0:640]
+    images = []
+    for k in range(2):      # smooth synthetic photographs, 640 x 480
+        base = np.stack([np.sin(xx / (40.0 + 10 * k) + c) * np.cos(yy / (55.0 - 5 * k) - c) for c in range(3)], -1)
+        images.append(Image.fromarray(((base * 0.4 + 0.5 + rng.normal(0, 0.02, base.shape)).clip(0, 1) * 255).astype(np.uint8)))
+    batch_size, mock_seq_len, steps = 2, 40, 3
+    g = torch.Generator().manual_seed(4)
+    prompt_embeds = torch.randn(batch_size, mock_seq_len, ocfg.joint_attention_dim, generator=g).to("cuda:0", torch.bfloat16)
+    prompt_embeds_mask = torch.ones(batch_size, mock_seq_len, device="cuda:0", dtype=torch.bool)
+    generator = torch.Generator(device="cuda:0").manual_seed(42)
+    gen_kwargs = {"image": images, "prompt_embeds": prompt_embeds, "prompt_embeds_mask": prompt_embeds_mask,
+                  "generator": generator, "num_inference_steps": steps, "true_cfg_scale": 1.0,
+                  "num_images_per_prompt": 1}
+    out = pipe(**gen_kwargs).images
+    W, H = 1184, 896                                   # calculate_dimensions(1024*1024, 640/480)
+    assert isinstance(out, list) and len(out) == 2 and all(im.size == (W, H) for im in out)
+    # oracle side, fp32 on the GPU
+    dev = "cuda:0"
+    px = torch.stack([torch.from_numpy(np.asarray(im.resize((W, H), resample=Image.LANCZOS), dtype=np.float32) / 255.0)
+                      for im in images]).permute(0, 3, 1, 2) * 2 - 1
+    vsd_d = {k: v.to(dev) for k, v in vsd.items()}
+    sd_d = {k: v.to(dev) for k, v in sd.items()}
+    ref_lat = V.normalize_latents(V.encode_mode(vsd_d, vcfg, px.to(dev).unsqueeze(2)), vcfg)
+    Hl, Wl = H // 8, W // 8
+    noise = torch.randn(batch_size, 1, 16, Hl, Wl, generator=torch.Generator(device=dev).manual_seed(42),
+                        device=dev, dtype=torch.bfloat16)
+    lat = O.pack_latents(noise.float())
+    shapes = [[(1, Hl // 2, Wl // 2), (1, Hl // 2, Wl // 2)]] * batch_size
+    final = O.edit_denoise_loop(sd_d, ocfg, lat, O.pack_latents(ref_lat), prompt_embeds.float(),
+                                prompt_embeds_mask, None, None, steps, 1.0, img_shapes=shapes)
+    want = (V.decode_packed(vsd_d, vcfg, final, Hl, Wl) / 2 + 0.5).clamp(0, 1).cpu()
+    got = torch.stack([torch.from_numpy(np.asarray(im, dtype=np.float32) / 255.0) for im in out]).permute(0, 3, 1, 2)
+    db = V.psnr(got, want, data_range=1.0)
+    print(f"pixel-image edit call vs oracle: PSNR {db:.1f} dB (image std {float(want.std()):.3f})")
+    assert float(want.std()) > 0.02 and db >= 40.0
+
+
 _MGPU_CASES = [
     # (gpus, env) — CFG-parallel at 2, CFG x Ulysses at 4/8, pure Ulysses (QI_CFG_PARALLEL=0), both exchanges,
     # ragged shards (272x240 px -> 255 image tokens, 33 prompt tokens) and batch 2

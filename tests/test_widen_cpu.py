@@ -174,9 +174,9 @@ def test_pipeline_edit_mode_input_validation():
     pipe = B200QwenImagePipeline.__new__(B200QwenImagePipeline)
     pipe.transformer, pipe.vae = _StubTransformer(), None
     emb = torch.zeros(1, 4, 8)
-    with pytest.raises(NotImplementedError, match="VAE latents"):
+    with pytest.raises(NotImplementedError, match="VAE with an encoder"):
         pipe(image=torch.zeros(1, 3, 64, 64), prompt_embeds=emb)            # pixels: needs the encoder
-    with pytest.raises(NotImplementedError, match="VAE latents"):
+    with pytest.raises(NotImplementedError, match="VAE with an encoder"):
         pipe(image="cat.png", prompt_embeds=emb)
     with pytest.raises(ValueError, match="even"):
         pipe(image=torch.zeros(1, 16, 5, 6), prompt_embeds=emb)
@@ -320,3 +320,84 @@ def test_serving_classes_bind_onto_installed_vllm():
     assert S.QwenImageGenWorker is classes["QwenImageGenWorker"]          # dotted-name resolution for worker_cls
     mro = [c.__name__ for c in classes["QwenImageGenWorker"].__mro__]
     assert mro.index("QwenImageGenWorkerMixin") < mro.index("Worker")     # our execute_model wins
+
+
+# ------------------------------------------------------------------ b2 / f1: pixel images in (VAE encoder half)
+def test_oracle_vae_encoder_golden_and_causal_reduction():
+    import os
+    vcfg = V.tiny_vae_config()
+    vsd = V.init_vae_state_dict(vcfg, seed=0)
+    # the decoder weights of a seed do not depend on the encoder being drawn (older golden fixtures stay valid)
+    dec_only = V.init_vae_state_dict(vcfg, seed=0, with_encoder=False)
+    assert all(torch.equal(vsd[k], v) for k, v in dec_only.items())
+    x = torch.rand(2, 3, 1, 48, 80, generator=torch.Generator().manual_seed(8)) * 2 - 1
+    h = V.encode(vsd, vcfg, x)
+    assert h.shape == (2, 32, 1, 6, 10)
+    gold = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiny_vae_encode.pt"))
+    assert O.rel_l2(h, gold["vae_encode_moments"]) < 1e-5
+    assert O.rel_l2(V.normalize_latents(V.encode_mode(vsd, vcfg, x), vcfg), gold["vae_encode_normalized_mode"]) < 1e-5
+    # one frame never meets the first two temporal slices of a causal 3x3x3 kernel, nor any time_conv
+    cut = dict(vsd)
+    for k, w in vsd.items():
+        if k.endswith(".weight") and w.dim() == 5 and w.shape[2] == 3:
+            w = w.clone()
+            if "time_conv" in k:
+                w.zero_()
+            else:
+                w[:, :, :2] = 0
+            cut[k] = w
+    assert torch.equal(V.encode(cut, vcfg, x), h)
+    with pytest.raises(ValueError):
+        V.encode(vsd, vcfg, torch.zeros(1, 3, 2, 48, 80))
+    # architecture facts of the full-size encoder (AutoencoderKLQwenImage config): flat down_blocks 0..10
+    full = V.init_vae_state_dict(V.VAEOracleConfig(), seed=0, weight_std=0.0)
+    assert full["encoder.conv_in.weight"].shape == (96, 3, 3, 3, 3)
+    assert full["encoder.down_blocks.2.resample.1.weight"].shape == (96, 96, 3, 3)
+    assert "encoder.down_blocks.2.time_conv.weight" not in full          # temperal_downsample[0] is False
+    assert full["encoder.down_blocks.5.time_conv.weight"].shape == (192, 192, 3, 1, 1)
+    assert full["encoder.down_blocks.3.conv_shortcut.weight"].shape == (192, 96, 1, 1, 1)
+    assert full["encoder.down_blocks.10.conv2.weight"].shape == (384, 384, 3, 3, 3)
+    assert full["encoder.conv_out.weight"].shape == (32, 384, 3, 3, 3) and full["quant_conv.weight"].shape == (32, 32, 1, 1, 1)
+
+
+def test_vae_encoder_module_matches_oracle_cpu():
+    """The 2-D one-frame encoder/decoder module (host layer, plain torch) against the 5-D causal restatement."""
+    from vllm_omni_draft_b200.vae import B200QwenImageVAE
+    vcfg = V.tiny_vae_config()
+    vsd = V.init_vae_state_dict(vcfg, seed=3)
+    vae = B200QwenImageVAE(base_dim=vcfg.base_dim, num_res_blocks=vcfg.num_res_blocks, device="cpu", dtype=torch.float32)
+    vae.load_diffusers_state_dict(vsd)
+    x = torch.rand(2, 3, 1, 40, 56, generator=torch.Generator().manual_seed(9)) * 2 - 1
+    dist = vae.encode(x).latent_dist
+    want = V.encode(vsd, vcfg, x)
+    assert O.rel_l2(torch.cat([dist.mean, dist.logvar], 1), want) < 1e-5
+    assert torch.equal(dist.mode(), dist.mean)
+    assert O.rel_l2(vae.normalize(dist.mode()), V.normalize_latents(V.encode_mode(vsd, vcfg, x), vcfg)) < 1e-5
+    assert vae.encode(x[:, :, 0], return_dict=False)[0].mean.shape == (2, 16, 5, 7)
+    z = torch.randn(1, 16, 1, 5, 7, generator=torch.Generator().manual_seed(10))
+    assert O.rel_l2(vae.decode(z).sample, V.decode(vsd, vcfg, z)) < 1e-5
+    with pytest.raises(ValueError):
+        vae.encode(torch.zeros(1, 3, 1, 41, 56))
+
+
+def test_image_preprocessing_matches_edit_pipeline_rules():
+    import numpy as np
+    from PIL import Image
+    from vllm_omni_draft_b200.pipeline import calculate_dimensions, image_size, preprocess_image
+    # QwenImageEditPipeline.calculate_dimensions(1024*1024, w/h): sides rounded to multiples of 32
+    assert calculate_dimensions(1024 * 1024, 1.0) == (1024, 1024)
+    assert calculate_dimensions(1024 * 1024, 640 / 480) == (1184, 896)
+    assert calculate_dimensions(1024 * 1024, 16 / 9) == V.calculate_dimensions(1024 * 1024, 16 / 9) == (1376, 768)
+    rng = np.random.default_rng(0)
+    im = Image.fromarray(rng.integers(0, 256, (48, 64, 3), dtype=np.uint8))
+    assert image_size([im, im]) == (64, 48) and image_size(torch.zeros(2, 3, 48, 64)) == (64, 48)
+    t = preprocess_image([im, im], 96, 128)
+    assert t.shape == (2, 3, 96, 128) and t.dtype == torch.float32 and -1.0 <= float(t.min()) and float(t.max()) <= 1.0
+    want = np.asarray(im.resize((128, 96), resample=Image.LANCZOS), dtype=np.float32) / 255.0 * 2 - 1
+    assert np.allclose(t[0].permute(1, 2, 0).numpy(), want, atol=1e-6)
+    same = preprocess_image(im, 48, 64)                                   # no resize: exact 8-bit values
+    assert np.array_equal(((same[0].permute(1, 2, 0).numpy() + 1) * 127.5).round().astype(np.uint8), np.asarray(im))
+    tt = torch.rand(1, 3, 48, 64)
+    assert torch.allclose(preprocess_image(tt, 48, 64), tt * 2 - 1)
+    assert torch.equal(preprocess_image(tt * 2 - 1, 48, 64), tt * 2 - 1)  # already in [-1, 1]
+    assert preprocess_image(np.asarray(im, dtype=np.float32) / 255.0, 48, 64).shape == (1, 3, 48, 64)

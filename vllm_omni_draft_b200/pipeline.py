@@ -57,6 +57,70 @@ def calculate_shift(image_seq_len, base_seq_len=256, max_seq_len=8192, base_shif
     return image_seq_len * m + b
 
 
+def calculate_dimensions(target_area: int, ratio: float) -> Tuple[int, int]:
+    """QwenImageEditPipeline's working size for an input of aspect ratio width / height: area ~ target_area, both
+    sides rounded to multiples of 32.  Returns (width, height)."""
+    width = math.sqrt(target_area * ratio)
+    height = width / ratio
+    return int(round(width / 32) * 32), int(round(height / 32) * 32)
+
+
+def image_size(image) -> Tuple[int, int]:
+    """(width, height) of what `pipe(image=...)` was given: a PIL image, a list of them, an [H, W, 3] / [B, H, W, 3]
+    array or a [B, 3, H, W] / [3, H, W] tensor."""
+    if isinstance(image, (list, tuple)):
+        image = image[0]
+    if isinstance(image, torch.Tensor):
+        return int(image.shape[-1]), int(image.shape[-2])
+    if hasattr(image, "size") and not hasattr(image, "shape"):        # PIL
+        return int(image.size[0]), int(image.size[1])
+    if hasattr(image, "shape"):                                        # numpy, channels last
+        return int(image.shape[-2]), int(image.shape[-3])
+    raise ValueError(f"unsupported image type {type(image).__name__}")
+
+
+def preprocess_image(image, height: int, width: int) -> torch.Tensor:
+    """VaeImageProcessor.resize + preprocess as the edit pipeline drives them: PIL images (Lanczos resize), arrays
+    in [0, 1] or tensors [B, 3, H, W] in [0, 1] (already in [-1, 1] if they hold negative values) -> fp32
+    [B, 3, height, width] in [-1, 1]."""
+    if not isinstance(image, (list, tuple)):
+        image = [image]
+    out = []
+    for im in image:
+        if isinstance(im, torch.Tensor):
+            t = im.float()
+            if t.dim() == 3:
+                t = t.unsqueeze(0)
+            if t.dim() != 4 or t.shape[1] != 3:
+                raise ValueError("image tensors must be [B, 3, H, W] or [3, H, W]")
+            if tuple(t.shape[-2:]) != (height, width):
+                t = torch.nn.functional.interpolate(t, size=(height, width))
+        elif hasattr(im, "resize") and not hasattr(im, "shape"):     # PIL
+            import numpy as np
+            from PIL import Image
+            arr = np.asarray(im.convert("RGB").resize((width, height), resample=Image.LANCZOS), dtype=np.float32)
+            t = torch.from_numpy(arr / 255.0).permute(2, 0, 1).unsqueeze(0)
+        elif hasattr(im, "shape"):                                   # numpy [H, W, 3] / [B, H, W, 3] in [0, 1]
+            t = torch.as_tensor(im).float()
+            if t.dim() == 3:
+                t = t.unsqueeze(0)
+            t = t.permute(0, 3, 1, 2)
+            if tuple(t.shape[-2:]) != (height, width):
+                t = torch.nn.functional.interpolate(t, size=(height, width))
+        else:
+            raise ValueError(f"unsupported image type {type(im).__name__}")
+        out.append(t if float(t.min()) < 0 else 2.0 * t - 1.0)
+    return torch.cat(out, dim=0)
+
+
+def _normalize_latents(latents: torch.Tensor, cfg) -> torch.Tensor:
+    """(latents - mean) / std with a diffusers AutoencoderKLQwenImage config (a VAE object without .normalize)."""
+    shape = [1, len(cfg.latents_mean)] + [1] * (latents.dim() - 2)
+    mean = torch.tensor(cfg.latents_mean, device=latents.device, dtype=latents.dtype).view(shape)
+    std = torch.tensor(cfg.latents_std, device=latents.device, dtype=latents.dtype).view(shape)
+    return (latents - mean) / std
+
+
 def postprocess_image(image: torch.Tensor, output_type: str = "pil"):
     """VaeImageProcessor.postprocess: [-1, 1] -> [0, 1]; 'pt' tensor [B,3,H,W], 'np' float32 [B,H,W,3],
     'pil' list of PIL images."""
@@ -336,17 +400,32 @@ class B200QwenImagePipeline:
                  prompt_embeds: Optional[torch.Tensor] = None, prompt_embeds_mask: Optional[torch.Tensor] = None,
                  negative_prompt_embeds: Optional[torch.Tensor] = None,
                  negative_prompt_embeds_mask: Optional[torch.Tensor] = None,
-                 output_type: str = "latent", return_dict: bool = True, record_steps: bool = False):
-        # Edit mode (reference test_performance.py:229-307): `image` must already be VAE
-        # latents [B,16,Hl',Wl'] / [B,16,1,Hl',Wl'] — upstream's pipeline takes that branch when
-        # image.size(1) == latent_channels; pixel images need the VAE *encoder*, which is outside the path.
+                 output_type: str = "pil", return_dict: bool = True, record_steps: bool = False):
+        # Edit mode (reference test_performance.py:229-307 passes `image=<list of PIL images>`):
+        # VAE latents [B,16,Hl',Wl'] / [B,16,1,Hl',Wl'] go straight in (upstream takes that branch when
+        # image.size(1) == latent_channels); pixels are resized to ~1024^2 at the input's aspect ratio, encoded by
+        # the VAE (posterior mode), normalised and packed, as QwenImageEditPipeline does, and the output size
+        # defaults to that working size.
         ref_tokens = ref_hw = None
         if image is not None:
-            if not (isinstance(image, torch.Tensor) and image.dim() in (4, 5) and image.shape[1] == 16):
-                raise NotImplementedError("edit mode takes the reference image as VAE latents [B,16,(1,)Hl,Wl]; "
-                                          "encoding pixels needs the VAE encoder (outside the hot path)")
-            ref_tokens = pack_latents(image)
-            ref_hw = (image.shape[-2] // 2, image.shape[-1] // 2)
+            if isinstance(image, torch.Tensor) and image.dim() in (4, 5) and image.shape[1] == 16:
+                ref_lat = image
+            else:
+                if self.vae is None or not hasattr(self.vae, "encode"):
+                    raise NotImplementedError(
+                        "pixel images need a VAE with an encoder on the pipeline (vllm_omni_draft_b200.vae."
+                        "B200QwenImageVAE or a diffusers AutoencoderKLQwenImage); without one, edit mode takes "
+                        "the reference image as VAE latents [B,16,(1,)Hl,Wl]")
+                iw, ih = image_size(image)
+                cw, ch = calculate_dimensions(1024 * 1024, iw / ih)
+                height, width = height or ch, width or cw
+                pixels = preprocess_image(image, ch, cw).unsqueeze(2)
+                enc = self.vae.encode(pixels.to(self.device, self.vae.dtype))
+                dist = enc.latent_dist if hasattr(enc, "latent_dist") else enc[0]
+                ref_lat = self.vae.normalize(dist.mode()) if hasattr(self.vae, "normalize") else \
+                    _normalize_latents(dist.mode(), self.vae.config)
+            ref_tokens = pack_latents(ref_lat)
+            ref_hw = (ref_lat.shape[-2] // 2, ref_lat.shape[-1] // 2)
         if prompt_embeds is None:
             if prompt is None:
                 raise ValueError("Provide either `prompt` or `prompt_embeds`")
@@ -441,8 +520,9 @@ class B200QwenImagePipeline:
         else:
             if self.vae is None:
                 raise NotImplementedError(
-                    "pixel output needs a VAE decoder (vllm_omni_draft_b200.vae.B200QwenImageVAEDecoder or a "
-                    "diffusers AutoencoderKLQwenImage); use output_type='latent'")
+                    "pixel output (output_type='pil' is the default, as upstream) needs a VAE on the pipeline "
+                    "(vllm_omni_draft_b200.vae.B200QwenImageVAE or a diffusers AutoencoderKLQwenImage); "
+                    "use output_type='latent' without one")
             images = postprocess_image(self.decode_latents(final, Hl, Wl), output_type)
         if not return_dict:
             return (images,)

@@ -1,4 +1,4 @@
-"""VAE decode for the image pipeline — host layer.
+"""VAE decode and encode for the image pipeline — host layer.
 
 What the reference reaches through ``self.vae.decode(latents)`` (src/qwen_image/runner_adapter.py:149-160,
 src/qwen_image_gen/model.py:138-141) and ``pipe(...).images`` (test_performance.py:277): diffusers'
@@ -14,6 +14,12 @@ So this module stores 2-D weights (a third of the checkpoint's conv bytes), keep
 in bf16, and runs as ordinary library convolutions: it is 0.05 % of an image's FLOPs (≈4 TF against 7 830 TF
 for 50 true-CFG steps at 1024²) and sits outside the MMDiT block, whose kernels are the hand-written part
 of this package.  tests/ check it against the 5-D causal restatement in oracle/vae_oracle.py.
+
+The ENCODER (``B200QwenImageVAE.encode``; the edit pipeline's ``vae.encode(image)`` upstream, reached by the reference
+through ``pipe(image=<PIL images>, ...)``, src/performance_enhancement/test_performance.py:244-251) reduces the same
+way for one frame: every causal conv keeps its last temporal slice, and the stride-2 temporal conv of
+'downsample3d' only runs from a clip's second chunk on, so both resample modes are ZeroPad2d((0,1,0,1)) + a 3x3
+stride-2 conv.
 """
 from __future__ import annotations
 
@@ -93,6 +99,35 @@ class _Up2x(nn.Module):
         return self.conv(x)
 
 
+class _Down2x(nn.Module):
+    def __init__(self, dim: int):
+        super().__init__()
+        self.conv = nn.Conv2d(dim, dim, 3, stride=2)
+
+    def forward(self, x):
+        return self.conv(F.pad(x, (0, 1, 0, 1)))
+
+
+class DiagonalGaussian:
+    """The slice of diffusers' DiagonalGaussianDistribution the pipelines use (mode / mean / sample)."""
+
+    def __init__(self, moments: torch.Tensor):
+        self.mean, self.logvar = moments.chunk(2, dim=1)
+        self.logvar = self.logvar.clamp(-30.0, 20.0)
+
+    def mode(self) -> torch.Tensor:
+        return self.mean
+
+    def sample(self, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+        noise = torch.randn(self.mean.shape, generator=generator, device=self.mean.device, dtype=self.mean.dtype)
+        return self.mean + torch.exp(0.5 * self.logvar) * noise
+
+
+@dataclass
+class EncoderOutput:
+    latent_dist: DiagonalGaussian
+
+
 class B200QwenImageVAEDecoder(nn.Module):
     def __init__(self, base_dim: int = 96, z_dim: int = 16, dim_mult: Tuple[int, ...] = (1, 2, 4, 4),
                  num_res_blocks: int = 2, latents_mean=LATENTS_MEAN, latents_std=LATENTS_STD,
@@ -135,6 +170,10 @@ class B200QwenImageVAEDecoder(nn.Module):
     def load_diffusers_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
         """AutoencoderKLQwenImage names -> 2-D weights.  3-D kernels keep only their last temporal slice
         (the only one that meets real data for a single frame); encoder / time_conv entries are unused."""
+        self._load_decoder(sd)
+
+    @staticmethod
+    def _loaders(sd):
         def conv(m: nn.Conv2d, name: str):
             w = sd[name + ".weight"]
             if w.dim() == 5:
@@ -151,6 +190,11 @@ class B200QwenImageVAEDecoder(nn.Module):
             if m.conv_shortcut is not None:
                 conv(m.conv_shortcut, p + "conv_shortcut")
 
+        return conv, gamma, res
+
+    @torch.no_grad()
+    def _load_decoder(self, sd: Dict[str, torch.Tensor]) -> None:
+        conv, gamma, res = self._loaders(sd)
         conv(self.post_quant_conv, "post_quant_conv")
         conv(self.conv_in, "decoder.conv_in")
         res(self.mid[0], "decoder.mid_block.resnets.0.")
@@ -180,6 +224,13 @@ class B200QwenImageVAEDecoder(nn.Module):
         m = cls(device=device, dtype=torch_dtype)
         m.load_diffusers_state_dict(sd)
         return m
+
+    def normalize(self, latents: torch.Tensor) -> torch.Tensor:
+        """The edit pipeline's ``(latents - mean) / std`` (per latent channel) after encode."""
+        shape = [1, self.config.z_dim] + [1] * (latents.dim() - 2)
+        mean = torch.tensor(self.config.latents_mean, device=latents.device, dtype=latents.dtype).view(shape)
+        std = torch.tensor(self.config.latents_std, device=latents.device, dtype=latents.dtype).view(shape)
+        return (latents - mean) / std
 
     # ------------------------------------------------------------------ decode
     def denormalize(self, latents: torch.Tensor) -> torch.Tensor:
@@ -214,3 +265,72 @@ class B200QwenImageVAEDecoder(nn.Module):
         if not return_dict:
             return (x,)
         return DecoderOutput(sample=x)
+
+
+class B200QwenImageVAE(B200QwenImageVAEDecoder):
+    """Decoder + one-frame encoder (``AutoencoderKLQwenImage.encode`` / ``.decode`` for images)."""
+
+    def __init__(self, base_dim: int = 96, z_dim: int = 16, dim_mult: Tuple[int, ...] = (1, 2, 4, 4),
+                 num_res_blocks: int = 2, latents_mean=LATENTS_MEAN, latents_std=LATENTS_STD,
+                 device="cuda", dtype=torch.bfloat16):
+        super().__init__(base_dim, z_dim, dim_mult, num_res_blocks, latents_mean, latents_std, device, dtype)
+        dims = [base_dim * u for u in (1,) + tuple(dim_mult)]
+        self.enc_conv_in = nn.Conv2d(3, dims[0], 3, padding=1)
+        self.enc_down = nn.ModuleList()         # flat, like upstream's down_blocks: residual blocks and resamples
+        for i, (cin, cout) in enumerate(zip(dims[:-1], dims[1:])):
+            for _ in range(num_res_blocks):
+                self.enc_down.append(_ResBlock(cin, cout))
+                cin = cout
+            if i != len(dim_mult) - 1:
+                self.enc_down.append(_Down2x(cout))
+        top = dims[-1]
+        self.enc_mid = nn.ModuleList([_ResBlock(top, top), _SpatialAttention(top), _ResBlock(top, top)])
+        self.enc_norm_out = _ChannelNorm(top)
+        self.enc_conv_out = nn.Conv2d(top, 2 * z_dim, 3, padding=1)
+        self.quant_conv = nn.Conv2d(2 * z_dim, 2 * z_dim, 1)
+        self.requires_grad_(False)
+        self.to(device=device, dtype=dtype, memory_format=torch.channels_last)
+
+    @torch.no_grad()
+    def load_diffusers_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        self._load_decoder(sd)
+        conv, gamma, res = self._loaders(sd)
+        conv(self.enc_conv_in, "encoder.conv_in")
+        for k, m in enumerate(self.enc_down):
+            if isinstance(m, _ResBlock):
+                res(m, f"encoder.down_blocks.{k}.")
+            else:
+                conv(m.conv, f"encoder.down_blocks.{k}.resample.1")     # time_conv: never met by a single frame
+        res(self.enc_mid[0], "encoder.mid_block.resnets.0.")
+        a = "encoder.mid_block.attentions.0."
+        gamma(self.enc_mid[1].norm, a + "norm"); conv(self.enc_mid[1].to_qkv, a + "to_qkv")
+        conv(self.enc_mid[1].proj, a + "proj")
+        res(self.enc_mid[2], "encoder.mid_block.resnets.1.")
+        gamma(self.enc_norm_out, "encoder.norm_out")
+        conv(self.enc_conv_out, "encoder.conv_out")
+        conv(self.quant_conv, "quant_conv")
+
+    @torch.no_grad()
+    def encode(self, x: torch.Tensor, return_dict: bool = True):
+        """x: [B, 3, 1, H, W] (or [B, 3, H, W]) in [-1, 1], H and W multiples of 8 -> posterior over
+        [B, z_dim, 1, H/8, W/8] (``.latent_dist.mode()`` is what the edit pipeline takes)."""
+        five_d = x.dim() == 5
+        if five_d:
+            if x.shape[2] != 1:
+                raise ValueError("the image pipeline encodes exactly one frame")
+            x = x[:, :, 0]
+        if x.dim() != 4 or x.shape[1] != 3 or x.shape[2] % 8 or x.shape[3] % 8:
+            raise ValueError("images must be [B, 3, (1,) H, W] with H and W multiples of 8")
+        x = x.to(self.device, self.dtype).contiguous(memory_format=torch.channels_last)
+        x = self.enc_conv_in(x)
+        for m in self.enc_down:
+            x = m(x)
+        for m in self.enc_mid:
+            x = m(x)
+        x = self.quant_conv(self.enc_conv_out(F.silu(self.enc_norm_out(x))))
+        if five_d:
+            x = x.unsqueeze(2)
+        dist = DiagonalGaussian(x)
+        if not return_dict:
+            return (dist,)
+        return EncoderOutput(latent_dist=dist)
