@@ -220,12 +220,13 @@ def make_workload(name: str, gpus: int):
 
 def layout_parity(world, rank, dev, wl, use_graph, tiny):
     """Correctness of the layout being timed: a 2-block model of the SAME width run through the SAME host path
-    (pipeline call -> ParallelDenoiser -> peer exchange kernels -> CUDA graph) at the SAME shapes for 2 true-CFG
-    steps, against the oracle's loop in fp32 on rank 0's GPU (weights read from rank 0's replica)."""
+    (pipeline call -> ParallelDenoiser -> peer exchange kernels -> CUDA graph) at the SAME shapes for 4 true-CFG
+    steps, against the oracle's loop in fp32 on rank 0's GPU (weights read from rank 0's replica); with more than
+    one GPU also against the same call on rank 0 alone (what the sharding itself changes)."""
     from oracle import qwen_image_oracle as O
     from vllm_omni_draft_b200.config import MMDiTConfig
     from vllm_omni_draft_b200.launcher import ParallelDenoiser
-    steps = 2
+    steps = 4
     cfg = MMDiTConfig.tiny() if tiny else MMDiTConfig(num_layers=2)
     ocfg = O.tiny_config() if tiny else O.OracleConfig(num_layers=2)
     den = ParallelDenoiser(cfg, dev, world, rank, seed=7, use_cuda_graph=use_graph)
@@ -260,6 +261,16 @@ def layout_parity(world, rank, dev, wl, use_graph, tiny):
                "shapes": f"batch {B}, {s_img} image + {s_txt} text tokens (the timed workload's)",
                "path": "B200QwenImagePipeline.__call__" + (" -> ParallelDenoiser (same groups layout, exchange, graph capture)" if world > 1 else ""),
                "against": "oracle loop in fp32 on rank 0's GPU, same weights"}
+        if world > 1:
+            from vllm_omni_draft_b200.pipeline import B200QwenImagePipeline
+            solo = B200QwenImagePipeline(den.tr)
+            solo.use_cuda_graph = use_graph
+            one = solo(prompt_embeds=cond, prompt_embeds_mask=mask, negative_prompt_embeds=uncond,
+                       negative_prompt_embeds_mask=mask, true_cfg_scale=4.0, num_inference_steps=steps, latents=lat,
+                       height=wl["H"], width=wl["W"], output_type="latent").images
+            torch.cuda.synchronize()
+            res["rel_l2_vs_single_gpu_cuda_path"] = O.rel_l2(out.float(), one.float())
+            solo.clear_sessions()
     den.close()
     den.pipe.clear_sessions()
     del den

@@ -26,11 +26,11 @@ extern "C" {
 typedef struct CUstream_st* qi_stream_t; /* == cudaStream_t */
 
 enum qi_status {
-  QI_STATUS_OK = 0,
-  QI_STATUS_ERR_ARG = -1,         /* malformed argument (null pointer, bad alignment/shape) */
-  QI_STATUS_ERR_CUDA = -2,        /* CUDA runtime error at launch (see qi_last_cuda_error) */
-  QI_STATUS_ERR_DRIVER = -3,      /* tensor-map encode failed */
-  QI_STATUS_ERR_UNSUPPORTED = -4  /* shape outside the compiled instantiations */
+  QI_OK = 0,
+  QI_ERR_ARG = -1,         /* malformed argument (null pointer, bad alignment/shape) */
+  QI_ERR_CUDA = -2,        /* CUDA runtime error at launch (see qi_last_cuda_error) */
+  QI_ERR_DRIVER = -3,      /* tensor-map encode failed */
+  QI_ERR_UNSUPPORTED = -4  /* shape outside the compiled instantiations */
 };
 
 enum qi_epilogue {
@@ -108,7 +108,9 @@ typedef struct {
 int qi_gemm_bf16(const qi_gemm_problem_t* problems /* host */, int num_problems /* 1 or 2 */,
                  qi_stream_t stream);
 /* Tile width of the persistent GEMM: 0 = automatic (cheapest wave schedule over 148 SMs), or one of
- * 128 / 192 / 256 to pin it (tests and tile sweeps). */
+ * 128 / 160 / 192 / 224 / 256 to pin it (tests and tile sweeps; QI_EPI_QKV_NORM_ROPE needs a multiple of head_dim).
+ * The qi_gemm_set_* / qi_attention_set_variant functions write process-wide state that later launches read without
+ * a lock: call them from the thread that launches, before the launches they are meant for (setup / tuning time). */
 int qi_gemm_set_tile_n(int bn);
 /* CTA-pair (tcgen05 cta_group::2, 256-row tiles on a 2-CTA cluster) vs single-CTA tiles:
  * -1 = automatic, 0 = never, 1 = always. */
@@ -130,8 +132,8 @@ int qi_gemm_set_group_m(int group_m);
 /* ---- K4: joint text+image attention, non-causal, no mask, softmax scale 1/sqrt(head_dim)
  * (replaces dispatch_attention_fn / F.scaled_dot_product_attention in QwenDoubleStreamAttnProcessor2_0).
  * q, k, v, o are [batch, seq, heads, head_dim] views with a common row stride ld (elements between
- * consecutive tokens) and batch stride; head_dim in {64, 128}.  Keys kv_start..kv_start+kv_len of the
- * k/v views are attended by queries 0..seq_q (Ulysses passes full-sequence K/V of its local heads). */
+ * consecutive tokens) and batch stride; head_dim in {64, 128}.  Queries 0..seq_q attend keys 0..seq_kv of the
+ * k/v views (Ulysses passes the full-sequence K/V of its local heads); partial last tiles are masked in-kernel. */
 int qi_attention_fwd(const void* q, const void* k, const void* v, void* o, int batch, int seq_q,
                      int seq_kv, int heads, int head_dim, long long ld_q, long long ld_kv,
                      long long ld_o, long long q_batch_stride, long long kv_batch_stride,
@@ -279,7 +281,7 @@ int qi_timestep_sinusoid_f32(const float* t, float* out, int m, qi_stream_t stre
 
 /* ---- host-side integer tables (bit-exact parts of the path; no GPU needed).
  * MSRoPE position ids (QwenEmbedRope): img_pos [sum F*H*W, 3], txt_pos [txt_len, 3] (int32, host).
- * shapes: num_images triples (F,H,W).  Returns 0, or QI_STATUS_ERR_ARG if a text position would
+ * shapes: num_images triples (F,H,W).  Returns 0, or QI_ERR_ARG if a text position would
  * exceed the 4096-entry table. */
 int qi_rope_position_ids(const int* shapes /* host */, int num_images, int txt_len,
                          int32_t* img_pos /* host */, int32_t* txt_pos /* host */);

@@ -6,11 +6,7 @@
 #include <cuda.h>
 #include <stdint.h>
 
-#define QI_OK 0
-#define QI_ERR_ARG -1
-#define QI_ERR_CUDA -2
-#define QI_ERR_DRIVER -3
-#define QI_ERR_UNSUPPORTED -4
+#include "../../include/qi_b200.h"   // status codes (enum qi_status) and the C ABI the kernels implement
 
 namespace qi {
 

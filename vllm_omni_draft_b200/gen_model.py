@@ -1,9 +1,10 @@
 """Drop-in for the reference's vLLM-facing model wrapper.
 
-Mirrors ``QwenImageGenModel`` (reference src/qwen_image_gen/model.py:17-165), ``QwenImageConfig`` /
-``create_qwen_image_config`` (src/qwen_image_gen/config.py:10-66) and ``QwenImageOutputs``
+Mirrors ``QwenImageGenModel`` (reference src/qwen_image_gen/model.py:17-165) and ``QwenImageOutputs``
 (src/qwen_image_gen/types.py:35-39): same names, argument meaning and error behaviour, with the B200
-transformer behind them.  Host layer only — the loop body is the reference's own three tensor ops
+transformer behind them.  The reference's ``QwenImageConfig`` / ``create_qwen_image_config`` (config.py) are
+out of scope (the model reads ``model_id`` / subfolders off ``vllm_config.model_config.hf_config``
+with the same defaults, and this package's own shapes live in ``config.py``).  Host layer only — the loop body is the reference's own three tensor ops
 (``flatten/transpose``, ``transpose/unflatten``, ``latents - residual * 0.1``, model.py:117-135); every
 FLOP of ``self.transformer(...)`` runs in libqi_b200.so.
 
@@ -19,7 +20,6 @@ Differences, all host-side and stated here:
 """
 from __future__ import annotations
 
-import os
 from dataclasses import dataclass
 from typing import Any, Optional
 
@@ -35,46 +35,6 @@ class QwenImageOutputs:
     """src/qwen_image_gen/types.py:35-39."""
     latents: torch.Tensor
     pixels: Optional[torch.Tensor] = None
-
-
-@dataclass
-class QwenImageConfig:
-    """src/qwen_image_gen/config.py:10-31 (field for field; dtype default kept as the reference's fp16
-    although the B200 path itself computes in bf16 and says so when asked for anything else)."""
-    model_id: str = "Qwen/Qwen-Image"
-    transformer_subfolder: str = "transformer"
-    vae_subfolder: str = "vae"
-    device: Optional[torch.device] = None
-    dtype: torch.dtype = torch.float16
-    guidance_scale: float = 4.0
-    num_inference_steps: int = 30
-    height: int = 512
-    width: int = 512
-    max_batch_size: int = 4
-    gpu_memory_utilization: float = 0.8
-
-
-def create_qwen_image_config(**kwargs) -> QwenImageConfig:
-    """QWEN_* environment defaults, then keyword overrides; unknown key -> ValueError
-    (src/qwen_image_gen/config.py:34-66)."""
-    config = QwenImageConfig(
-        model_id=os.getenv("QWEN_MODEL_ID", "Qwen/Qwen-Image"),
-        transformer_subfolder=os.getenv("QWEN_TRANSFORMER_SUBFOLDER", "transformer"),
-        vae_subfolder=os.getenv("QWEN_VAE_SUBFOLDER", "vae"),
-        device=torch.device("cuda" if torch.cuda.is_available() else "cpu"),
-        dtype=getattr(torch, os.getenv("QWEN_DTYPE", "float16")),
-        guidance_scale=float(os.getenv("QWEN_GUIDANCE_SCALE", "4.0")),
-        num_inference_steps=int(os.getenv("QWEN_NUM_STEPS", "30")),
-        height=int(os.getenv("QWEN_HEIGHT", "512")),
-        width=int(os.getenv("QWEN_WIDTH", "512")),
-        max_batch_size=int(os.getenv("QWEN_MAX_BATCH_SIZE", "4")),
-        gpu_memory_utilization=float(os.getenv("QWEN_GPU_MEMORY_UTIL", "0.8")),
-    )
-    for key, value in kwargs.items():
-        if not hasattr(config, key):
-            raise ValueError(f"Unknown configuration key: {key}")
-        setattr(config, key, value)
-    return config
 
 
 class QwenImageGenModel(nn.Module):
@@ -103,9 +63,8 @@ class QwenImageGenModel(nn.Module):
         try:
             self.transformer = B200QwenImageTransformer2DModel.from_pretrained(
                 model_id, subfolder=transformer_subfolder, torch_dtype=torch.bfloat16, device=self.device)
-            from .vae import B200QwenImageVAEDecoder
-            self.vae = B200QwenImageVAEDecoder.from_pretrained(model_id, subfolder=vae_subfolder,
-                                                               device=self.device)
+            from .vae import B200QwenImageVAE
+            self.vae = B200QwenImageVAE.from_pretrained(model_id, subfolder=vae_subfolder, device=self.device)
         except ImportError:
             raise
         except Exception as e:
