@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """`ncu -i X.ncu-rep --page raw --csv --print-units base` (stdin or file)  ->  a small tracked CSV:
-one row per (kernel, metric), averaged over the kernel's launches in the report.  bench.py reads
-`roofline.traffic` from such a file (profiles/r02_ncu_mlp_up_batch2.csv).
+one row per (kernel, metric), averaged over the kernel's launches in the report (`launches` = how many), followed
+by one row per individual launch (kernel name suffixed `#i`, launches = 1) so that a warm-up launch or an outlier
+stays visible.  bench.py reads `roofline.traffic` from such a file (profiles/r02_ncu_mlp_up_batch2.csv; it matches
+kernel names by substring and takes the first, i.e. the averaged, row).
 usage: ncu_summary.py raw.csv out.csv ["comment line"]"""
 import csv
 import sys
@@ -24,9 +26,12 @@ def main():
     units = rows[1]
     ki = hdr.index("Kernel Name")
     acc = {}
+    each = []
+    seen = {}
     for r in rows[2:]:
         if len(r) != len(hdr):
             continue
+        idx = seen[r[ki]] = seen.get(r[ki], -1) + 1
         for m in METRICS:
             if m in hdr:
                 j = hdr.index(m)
@@ -37,6 +42,7 @@ def main():
                 a = acc.setdefault((r[ki], m, units[j]), [0.0, 0])
                 a[0] += v
                 a[1] += 1
+                each.append((f"{r[ki]}#{idx}", m, units[j], v))
     with open(out, "w", newline="") as f:
         if comment:
             f.write("# " + comment + "\n")
@@ -44,6 +50,10 @@ def main():
         w.writerow(["kernel", "metric", "unit", "value", "launches"])
         for (k, m, u), (s, n) in acc.items():
             w.writerow([k, m, u, s / n, n])
+        multi = {k for (k, _, _), (_, n) in acc.items() if n > 1}
+        for k, m, u, v in each:
+            if k.rsplit("#", 1)[0] in multi:
+                w.writerow([k, m, u, v, 1])
 
 
 if __name__ == "__main__":

@@ -1,5 +1,7 @@
 """Launches the hot kernels alone at the cfg-2 shapes, as the step issues them (batch 2 = cond + uncond stacked,
-fp32 residual streams), for `ncu --set full`.  usage: prof_kernels.py [all|gemm|mlp_up|qkv|attn|elem] [batch]"""
+fp32 residual streams, the schedule the step uses: the persisted / measured (pair, tile width, rasterisation) of each
+shape is registered first, ops.tune_gemm), for `ncu --set full`.
+usage: prof_kernels.py [all|gemm|mlp_up|qkv|attn|elem] [batch]"""
 import os
 import sys
 
@@ -18,6 +20,16 @@ emp = lambda *s: torch.empty(*s, device=dev, dtype=torch.bfloat16)
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 reps = 3
+
+
+def launch(make):
+    """make(i) -> the launch's problems; the shape's measured schedule is registered before the profiled launches."""
+    ops.tune_gemm(make(0))
+    torch.cuda.synchronize()
+    for i in range(reps):
+        ops.gemm(make(i))
+
+
 xi, xt = r(B, s_img, d), r(B, s_txt, d)
 h32, e32 = r32(B, s_img, d), r32(B, s_txt, d)              # fp32 residual streams
 gate32 = r32(1, d, sc=0.1).expand(B, d)                    # fp32 gate row of the modulation table, shared by the batch
@@ -25,18 +37,15 @@ if which in ("all", "gemm", "mlp_up"):
     w_up = [r(2, 4 * d, d, sc=0.02) for _ in range(reps)]
     b_up = r(2, 4 * d)
     mi, mt = emp(B, s_img, 4 * d), emp(B, s_txt, 4 * d)
-    for i in range(reps):
-        ops.gemm([ops.gemm_problem(xi, w_up[i][0], b_up[0], mi, ops.EPI_BIAS_GELU_TANH),
+    launch(lambda i: [ops.gemm_problem(xi, w_up[i][0], b_up[0], mi, ops.EPI_BIAS_GELU_TANH),
                   ops.gemm_problem(xt, w_up[i][1], b_up[1], mt, ops.EPI_BIAS_GELU_TANH)])
 if which in ("all", "gemm"):
     w_dn = [r(2, d, 4 * d, sc=0.02) for _ in range(reps)]
-    for i in range(reps):
-        ops.gemm([ops.gemm_problem(mi, w_dn[i][0], b_up[0, :d], h32, ops.EPI_GATED_RESIDUAL, h32, gate32),
+    launch(lambda i: [ops.gemm_problem(mi, w_dn[i][0], b_up[0, :d], h32, ops.EPI_GATED_RESIDUAL, h32, gate32),
                   ops.gemm_problem(mt, w_dn[i][1], b_up[1, :d], e32, ops.EPI_GATED_RESIDUAL, e32, gate32)])
     w_o = [r(2, d, d, sc=0.02) for _ in range(reps)]
     att = r(B, S, d)
-    for i in range(reps):
-        ops.gemm([ops.gemm_problem(att[:, s_txt:], w_o[i][0], b_up[0, :d], h32, ops.EPI_GATED_RESIDUAL, h32, gate32),
+    launch(lambda i: [ops.gemm_problem(att[:, s_txt:], w_o[i][0], b_up[0, :d], h32, ops.EPI_GATED_RESIDUAL, h32, gate32),
                   ops.gemm_problem(att[:, :s_txt], w_o[i][1], b_up[1, :d], e32, ops.EPI_GATED_RESIDUAL, e32, gate32)])
 if which in ("all", "gemm", "qkv"):
     w_qkv = [r(2, 3 * d, d, sc=0.02) for _ in range(reps)]
@@ -45,8 +54,7 @@ if which in ("all", "gemm", "qkv"):
     nw_ = r(4, Dh) + 1
     qkv_o = emp(B, S, 3 * d)
     kw = dict(epilogue=ops.EPI_QKV_NORM_ROPE, freqs=fr_, heads=H, head_dim=Dh)
-    for i in range(reps):
-        ops.gemm([ops.gemm_problem(xi, w_qkv[i][0], b_qkv[0], qkv_o[:, s_txt:], qk_norm=(nw_[0], nw_[1]), rope_pos0=s_txt, **kw),
+    launch(lambda i: [ops.gemm_problem(xi, w_qkv[i][0], b_qkv[0], qkv_o[:, s_txt:], qk_norm=(nw_[0], nw_[1]), rope_pos0=s_txt, **kw),
                   ops.gemm_problem(xt, w_qkv[i][1], b_qkv[1], qkv_o[:, :s_txt], qk_norm=(nw_[2], nw_[3]), rope_pos0=0, **kw)])
 if which in ("all", "attn"):
     qkv = r(B, S, 3 * d)
