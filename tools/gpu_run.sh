@@ -46,6 +46,7 @@ case "$T" in
     timeout -s KILL 1500 $NCU_FULL -k regex:"gemm_pair|gemm_bf16|attention_fwd|norm_rows|qknorm|cfg_euler" -c 24 -f -o gpurun_out/ncu_$W python tools/prof_kernels.py "$W" 2 > gpurun_out/ncu_$W.log 2>&1; echo "ncu rc=$?"
     ncu -i gpurun_out/ncu_$W.ncu-rep --page raw --csv --print-units base > gpurun_out/ncu_${W}_raw.csv 2>/dev/null
     python tools/ncu_summary.py gpurun_out/ncu_${W}_raw.csv gpurun_out/ncu_${W}_summary.csv "ncu --set full --clock-control none, tools/prof_kernels.py $W 2 (cfg-2 shapes, batch 2)"
+    [ -n "$KEEP_REP" ] || rm -f gpurun_out/ncu_$W.ncu-rep     # gpurun_out/ comes back only below 64 MiB
     cat gpurun_out/ncu_${W}_summary.csv;;
   ncu_attn)
     timeout -s KILL 300 python tools/prof_attn.py > /dev/null 2>&1 || { echo "plain run failed"; exit 1; }
