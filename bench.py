@@ -273,7 +273,10 @@ def layout_parity(world, rank, dev, wl, use_graph, tiny):
                    negative_prompt_embeds_mask=mask, true_cfg_scale=4.0, num_inference_steps=steps, latents=lat,
                    height=wl["H"], width=wl["W"], output_type="latent").images
         torch.cuda.synchronize()
+        # two bf16-operand paths with different tile shapes / summation orders: their roundings are independent, so
+        # they sit about as far from each other as sqrt(2) x either one's distance to the fp32 oracle
         res["rel_l2_vs_single_gpu_cuda_path"] = O.rel_l2(out.float(), one.float())
+        res["single_gpu_cuda_path_rel_l2"] = O.rel_l2(one.float(), x)
         solo.clear_sessions()
     del den
     torch.cuda.empty_cache()
