@@ -80,16 +80,22 @@ __device__ __forceinline__ float fast_exp2(float x) {
 // 2^x for a pair on the FMA/ALU pipes: j = round(x), f = x - j in [-0.5, 0.5], degree-3 minimax
 // polynomial for 2^f (max relative error 7.5e-5), exponent added as an integer.  x is clamped to
 // >= -126 so the exponent field cannot wrap (masked columns, x = -inf, come out as 2^-126 ~ 0).
+template <int DEG = 3>
 __device__ __forceinline__ float2 exp2_poly2(float2 x) {
   x.x = fmaxf(x.x, -126.f);
   x.y = fmaxf(x.y, -126.f);
   const float2 t = __fadd2_rn(x, make_float2(12582912.f, 12582912.f));          // 1.5 * 2^23 + j
   const float2 jf = __fadd2_rn(t, make_float2(-12582912.f, -12582912.f));
   const float2 f = __ffma2_rn(jf, make_float2(-1.f, -1.f), x);
-  float2 p = __ffma2_rn(make_float2(0.0551716648f, 0.0551716648f), f,
-                        make_float2(0.2426111251f, 0.2426111251f));
-  p = __ffma2_rn(p, f, make_float2(0.6932609677f, 0.6932609677f));
-  p = __ffma2_rn(p, f, make_float2(0.9999280572f, 0.9999280572f));
+  float2 p;
+  if (DEG == 3) {
+    p = __ffma2_rn(make_float2(0.0551716648f, 0.0551716648f), f, make_float2(0.2426111251f, 0.2426111251f));
+    p = __ffma2_rn(p, f, make_float2(0.6932609677f, 0.6932609677f));
+    p = __ffma2_rn(p, f, make_float2(0.9999280572f, 0.9999280572f));
+  } else {   // degree-2 minimax, max relative error 1.73e-3 (bf16 rounding of P: 3.9e-3): one FFMA2 less per pair
+    p = __ffma2_rn(make_float2(0.23842697f, 0.23842697f), f, make_float2(0.7034453f, 0.7034453f));
+    p = __ffma2_rn(p, f, make_float2(1.00044307f, 1.00044307f));
+  }
   float2 r;
   r.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(t.x) << 23));
   r.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(t.y) << 23));
@@ -156,6 +162,8 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
   }
   phase(2);
   // P = exp2(S*scale - m_ref), packed bf16 over the first 64 columns of S
+  constexpr int NE = EMU & 15;                 // pairs of every 8 evaluated on the FMA pipe
+  constexpr int DEG = (EMU & 16) ? 2 : 3;      // polynomial degree of that path
   const float2 sc2 = make_float2(scale_log2, scale_log2);
   const float2 nm2 = make_float2(-m_ref, -m_ref);
   float2 acc[4];
@@ -169,8 +177,8 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
       const float2 x = __ffma2_rn(make_float2(__uint_as_float(r[c][2 * i]), __uint_as_float(r[c][2 * i + 1])),
                                   sc2, nm2);
       float2 p;
-      if (((i % 8) * EMU) % 8 < EMU) {
-        p = exp2_poly2(x);
+      if (((i % 8) * NE) % 8 < NE) {
+        p = exp2_poly2<DEG>(x);
       } else {
         p.x = fast_exp2(x.x);
         p.y = fast_exp2(x.y);
@@ -676,9 +684,9 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, or 16 + EMU = two threads per row
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 23) return QI_ERR_ARG;
+  if (v < -1 || v > 26) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
@@ -777,6 +785,9 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 18: return launch_attention_v<DH, 2, true, true>(P, grid, stream);
     case 19: return launch_attention_v<DH, 3, true, true>(P, grid, stream);
     case 20: return launch_attention_v<DH, 4, true, true>(P, grid, stream);
+    case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
+    case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
+    case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
     default: return QI_ERR_ARG;
   }
 }
