@@ -49,5 +49,7 @@ def test_tiny_step_under_compute_sanitizer(cuda_device, tool):
                        capture_output=True, text=True, timeout=1400)
     tail = (p.stdout + p.stderr)[-3000:]
     print(tail)
+    if "compute-sanitizer is closed on this pool" in tail:
+        pytest.skip("compute-sanitizer is disabled by the GPU pool's wrapper (not a finding about the kernels)")
     assert p.returncode == 0, f"{tool} reported errors:\n{tail}"
     assert "REL_L2" in p.stdout
