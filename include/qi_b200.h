@@ -230,8 +230,18 @@ int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int ba
                              float softmax_scale, const qi_peer_scatter_t* dst /* host */, qi_stream_t stream);
 /* Softmax variant of the attention kernel (tuning / tests): -1 = default (env QI_ATTN_VARIANT, else 11),
  * otherwise EMU + 8 * SPLIT with EMU in {0, 2, 3, 4} = how many of every 8 element pairs evaluate 2^x
- * with the FMA-pipe polynomial instead of MUFU.EX2, SPLIT in {0, 1} = P published in two halves. */
+ * with the FMA-pipe polynomial (degree 3) instead of MUFU.EX2, SPLIT in {0, 1} = P published in two halves;
+ * 16 + EMU = two threads per query row (four softmax warpgroups); 24 / 25 / 26 = degree-2 polynomial on 3 / 4 / 5 of
+ * every 8 pairs.  All variants agree with fp32 SDPA to the same tolerance (tests/test_ops_gpu.py). */
 int qi_attention_set_variant(int variant);
+
+/* Tuning aids (measurement only; not needed by a drop-in caller).
+ * qi_gemm_set_debug: bit 0 skip the fp32 epilogue's residual loads, bit 1 its result stores, bit 2 its bias/gate
+ *   loads (wrong results; used to attribute epilogue time, tools/ab_gemm.py dbg).
+ * qi_attention_set_debug: DEVICE buffer of >= 16 uint64 counters (or NULL to stop): cycles the MMA issuer and the
+ *   first softmax warp spend in each wait / phase, summed over the CTAs of later launches (tools/attn_waits.py). */
+int qi_gemm_set_debug(int mask);
+int qi_attention_set_debug(unsigned long long* counters_dev);
 
 
 /* Peer memory: device allocations that can be mapped by the other ranks of the node (CUDA IPC).

@@ -912,7 +912,7 @@ gemm_pair_bf16_kernel(const __grid_constant__ GemmLaunch L) {
 using namespace qi;
 
 static int g_epi_dbg = 0;
-extern "C" int qi_gemm_set_debug(int mask) {   // profiling aid, not part of the public header
+extern "C" int qi_gemm_set_debug(int mask) {   // profiling aid (see the header)
   g_epi_dbg = mask;
   return QI_OK;
 }
