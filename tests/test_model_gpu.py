@@ -343,6 +343,8 @@ _MGPU_CASES = [
     (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="nccl")),
     # arrival flags folded into the producer / consumer kernels instead of two barrier launches per block
     (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PEER_FOLD="1")),
+    # custom `sigmas=` through the launcher
+    (2, dict(QI_GRAPH="1", QI_PAR_SIGMAS="1")),
     # scatter through 16-byte st.global instead of TMA bulk tensor stores
     (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_SCATTER_TMA="0")),
     (2, dict(QI_GRAPH="1", QI_CFG_PARALLEL="0", QI_SP_EXCHANGE="peer", QI_PAR_H="272", QI_PAR_W="240",

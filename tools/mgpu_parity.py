@@ -32,8 +32,12 @@ def main():
         ref_hw = (12, 20)
         shapes = [[shapes[0][0], (1, 12, 20)]] * batch
     den = ParallelDenoiser(MMDiTConfig.tiny(), dev, world, rank, use_cuda_graph=os.environ.get("QI_GRAPH", "0") == "1", state_dict=sd)
+    # QI_PAR_SIGMAS=1: the same schedule passed explicitly through `sigmas=` (upstream's default list) — the
+    # custom-schedule plumbing of the launcher must reproduce the default run
+    import numpy as np
+    sig = np.linspace(1.0, 1.0 / steps, steps).tolist() if os.environ.get("QI_PAR_SIGMAS", "0") == "1" else None
     den.setup(cond.bfloat16(), uncond.bfloat16(), lat.bfloat16(), Hpx, Wpx, steps, true_cfg_scale=4.0,
-              ref_h=ref_tokens.bfloat16() if edit else None, ref_hw=ref_hw)
+              ref_h=ref_tokens.bfloat16() if edit else None, ref_hw=ref_hw, sigmas=sig)
     for i in range(steps):
         den.step(i)
     out = torch.zeros(batch, lat.shape[1], 64, dtype=torch.bfloat16).pin_memory()

@@ -166,7 +166,7 @@ class ParallelDenoiser:
 
     # -------------------------------------------------------------- setup / IO
     def setup(self, cond_h, uncond_h, lat_h, height, width, num_inference_steps, true_cfg_scale=4.0,
-              ref_h=None, ref_hw=None):
+              ref_h=None, ref_hw=None, sigmas=None):
         """ref_h [B, S_ref, 64] + ref_hw = (h, w) token grid: edit mode — the packed reference-image
         latents ride behind the noise tokens; under sequence parallelism noise and reference tokens are sharded
         separately, so every rank updates an equal share of the latents."""
@@ -190,6 +190,9 @@ class ParallelDenoiser:
         self.j0, self.j1 = j0, j1
         ref = ref_h.to(dev, dt)[:, j0:j1].contiguous() if s_ref else None
         ref_kw = dict(ref_tokens=ref, ref_hw=ref_hw) if s_ref else {}
+        if sigmas is not None:          # custom schedule (upstream's `sigmas=`): same list on every rank
+            ref_kw["sigmas"] = [float(v) for v in sigmas]
+            num_inference_steps = len(ref_kw["sigmas"])
         self.scale = float(true_cfg_scale)
         if lay.cfg_degree == 1:
             cond, uncond = cond_h.to(dev, dt), (uncond_h.to(dev, dt) if uncond_h is not None else None)
@@ -314,14 +317,15 @@ class ParallelDenoiser:
         latents on every rank.  Setup (peer buffers, modulation table, tuning, graph) is kept across calls of the
         same shapes."""
         if sigmas is not None:
-            raise NotImplementedError("custom sigmas are not plumbed through the multi-GPU launcher")
+            num_inference_steps = len(sigmas)
         if uncond is None and self.layout.cfg_degree == 2:
             raise ValueError("CFG-parallel layout needs negative_prompt_embeds (or build with cfg_parallel=False)")
         key = (tuple(cond.shape), None if uncond is None else tuple(uncond.shape), tuple(latents.shape), height, width,
-               num_inference_steps, float(true_cfg_scale), None if ref_tokens is None else (tuple(ref_tokens.shape), ref_hw))
+               num_inference_steps, float(true_cfg_scale), None if ref_tokens is None else (tuple(ref_tokens.shape), ref_hw),
+               None if sigmas is None else tuple(float(v) for v in sigmas))
         if key != self._setup_key:
             self.setup(cond, uncond, latents, height, width, num_inference_steps, true_cfg_scale,
-                       ref_h=ref_tokens, ref_hw=ref_hw)
+                       ref_h=ref_tokens, ref_hw=ref_hw, sigmas=sigmas)
             self._setup_key = key
         else:
             self.load_inputs(cond, uncond, latents, ref_tokens)
