@@ -178,7 +178,7 @@ def test_attention(cuda_device, B, S, H, Dh):
 
 
 @pytest.mark.parametrize("Dh", [128, 64])
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 10, 11, 12, 16, 18, 19, 20, 24, 25, 26])
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 10, 11, 12, 16, 18, 19, 20, 24, 25, 26, 32, 34, 35, 36, 51])
 def test_attention_softmax_variants(cuda_device, variant, Dh):
     """Every softmax variant (MUFU only / 2-3-4 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
     or in two halves, one thread or two threads per query row) matches fp32 SDPA, on a ragged sequence (partial
@@ -201,6 +201,34 @@ def test_attention_softmax_variants(cuda_device, variant, Dh):
         q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
     err = O.rel_l2(out.cpu(), ref.cpu())
     assert err < 6e-3, f"variant={variant} rel_l2={err}"
+
+
+@pytest.mark.parametrize("Dh", [128, 64])
+@pytest.mark.parametrize("S", [40, 64, 100, 128, 168, 936, 1000, 1152])
+def test_attention_half_tile_pipeline_ragged(cuda_device, S, Dh):
+    """The half-tile pipeline (variants 32+) steps through 64-key halves: sequences that end in the first half of a
+    K/V tile (odd number of steps: 40, 168, 936), in the second half (100, 1000), exactly on a half (64) or a tile
+    (128, 1152) boundary, with logits wide enough that the reference maximum moves after the first halves (the O
+    rescale then has to wait for the P*V MMA still in flight)."""
+    ops = _ops()
+    B, H = 2, 2
+    d = H * Dh
+    qkv = _rand((B, S, 3 * d), 52, 1.0)
+    qkv[:, :, :d] *= 3.0
+    qkv[:, S // 2:, d:2 * d] *= 2.0           # later keys score higher: the running maximum keeps moving
+    q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
+    ref = torch.nn.functional.scaled_dot_product_attention(
+        q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
+    for variant in (35, 32):
+        out = torch.zeros(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
+        ops.attention_set_variant(variant)
+        try:
+            ops.attention(q, k, v, out)
+            torch.cuda.synchronize()
+        finally:
+            ops.attention_set_variant(-1)
+        err = O.rel_l2(out.cpu(), ref.cpu())
+        assert err < 6e-3, f"variant={variant} S={S} rel_l2={err}"
 
 
 @pytest.mark.parametrize("bn", [128, 160, 192, 224, 256])

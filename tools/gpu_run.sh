@@ -10,6 +10,7 @@
 #   ncu_mlp_up       ncu --set full of the dominant launch -> profiles-ready CSV (bench.py's roofline.traffic)
 #   ncu_kernels W    ncu --set full of prof_kernels.py W (gemm|qkv|attn|elem|all) -> summary CSV
 #   ncu_step         launch list (gpu__time_duration) of the timed region of a 3-step bench
+#   attn_pipe        attention half-tile pipeline: tests, sweep vs the default, wait counters, step bench
 #   sass             per-kernel SASS mnemonic counts of the in-tree library (no GPU needed, works here too)
 #   sanitizer        compute-sanitizer racecheck + synccheck on the tiny config (opt-in marker)
 set -u
@@ -60,6 +61,26 @@ case "$T" in
     timeout -s KILL 1500 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 1400 --csv \
       --log-file gpurun_out/launch_list_step.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-kernels --no-parity --e2e-steps 4 > gpurun_out/ncu_step.log 2>&1; echo "ncu rc=$?"
     python tools/launch_share.py gpurun_out/launch_list_step.csv;;
+  attn_pipe)
+    # the half-tile pipeline (variants 32+): parity tests, interleaved sweep beside the current default, wait
+    # counters, then a step bench with the fastest variant that passed
+    timeout -s KILL 420 python -m pytest tests/test_ops_gpu.py -x -q -k "attention" > gpurun_out/attn_tests.log 2>&1; RC=$?; echo "attention tests rc=$RC"; tail -4 gpurun_out/attn_tests.log
+    [ $RC -eq 0 ] || exit 1
+    QI_SWEEP_VARIANTS=${QI_SWEEP_VARIANTS:-11,32,34,35,36,51} timeout -s KILL 300 python tools/attn_sweep.py > gpurun_out/attn_pipe_sweep.txt 2>&1; echo "sweep rc=$?"; cat gpurun_out/attn_pipe_sweep.txt
+    timeout -s KILL 120 python tools/attn_waits.py 11 35 > gpurun_out/attn_pipe_waits.txt 2>&1; echo "waits rc=$?"; cat gpurun_out/attn_pipe_waits.txt
+    BEST=$(python - <<'PY'
+import re
+best, bv = None, 0
+for line in open("gpurun_out/attn_pipe_sweep.txt"):
+    m = re.match(r"B=2 S=4608 H=24 variant=\s*(\d+).*median\s+([\d.]+) us", line)
+    if m and (best is None or float(m.group(2)) < best):
+        best, bv = float(m.group(2)), int(m.group(1))
+print(bv)
+PY
+)
+    echo "fastest variant at the step shape: $BEST"
+    QI_ATTN_VARIANT=$BEST timeout -s KILL 600 python bench.py --no-cpu-baseline "$@" > gpurun_out/bench_attn_pipe.json 2> gpurun_out/bench_attn_pipe.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_attn_pipe.err
+    python tools/show_bench.py gpurun_out/bench_attn_pipe.json;;
   sass)
     python tools/sass_summary.py > gpurun_out/sass_summary.txt; cat gpurun_out/sass_summary.txt;;
   sanitizer)

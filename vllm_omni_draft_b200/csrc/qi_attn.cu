@@ -680,13 +680,387 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// PIPE: the same tile shapes, software-pipelined over 64-key HALVES of every K/V tile.
+//
+// In the kernel above one Q tile's work is a dependent chain per K/V tile — S ready -> softmax (1 430 clk) -> second
+// half of P*V -> next Q*K^T -> S ready — because S_{j+1} can only be written once P_j (which lives in S_j's columns)
+// has been consumed: TMEM holds exactly two S tiles and two O tiles.  The two Q tiles hide part of each other's
+// chain, not all of it (measured: MMA warp waits 30 % of its time for P, softmax warps 40 % for S).  Here S of a Q
+// tile is two 64-column regions A/B that hold alternate halves: while the softmax works on half h+1 (region B), the
+// tensor pipe runs P_h*V_h out of region A and refills A with S_{h+2} = Q*K_{h+2}^T.  Per half and Q tile the tensor
+// pipe has 512 clk of work and the softmax ~720, on two Q tiles in parallel: the softmax threads never wait for more
+// than the tensor pipe's own work, and the MMA queue never drains.  MMAs are N = 64 (Q*K^T) and K = 64 (P*V); the
+// tcgen05 rate does not depend on N (cycles per MMA = 128*N/256).
+//
+// The lazy O rescale needs one more edge: P_{h+1} is computed while P_h*V_h may still be queued, so a row whose
+// reference maximum moves at half h+1 waits for that MMA (`pv_done`, committed after every P*V) before it scales O.
+
+// mbarrier wait of the pipelined kernel: a protocol error (or a lost TMA) traps after ~2 s instead of hanging the GPU.
+__device__ __forceinline__ void pipe_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t n = 0;
+  unsigned long long t0 = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++n & 0xffffu) == 0) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 2000000000ull) __trap();
+    }
+  }
+}
+
+template <int DH, bool MASK, int EMU>
+__device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_addr, int kv_valid, int h,
+                                                  float scale_log2, float& m_ref, float& l_sum, uint64_t* p_full,
+                                                  uint64_t* pv_done, int lane) {
+  uint32_t r[2][32];
+  tmem_ld32(s_addr, r[0]);
+  tmem_ld32(s_addr + 32, r[1]);
+  tmem_ld_wait();
+  if (MASK) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: contributes 0
+  }
+  float mxs[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) mxs[q] = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      mxs[i & 7] = fmaxf(fmaxf(mxs[i & 7], __uint_as_float(r[c][2 * i])), __uint_as_float(r[c][2 * i + 1]));
+  const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                         fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+  const float m_new = fmaxf(m_ref, mx * scale_log2);
+  const bool need = (m_new - m_ref) > 8.0f;   // also true on the first half (m_ref = -inf)
+  if (__any_sync(0xffffffffu, need)) {
+    const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on half 0
+    if (need) {
+      l_sum *= f;
+      m_ref = m_new;
+    }
+    if (h > 0) {
+      pipe_wait(pv_done, (h - 1) & 1);   // O must hold every P*V issued so far before it is scaled
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < DH / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(o_addr + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+        tmem_st32(o_addr + c * 32, o);
+      }
+    }
+  }
+  constexpr int NE = EMU & 15;
+  constexpr int DEG = (EMU & 16) ? 2 : 3;
+  const float2 sc2 = make_float2(scale_log2, scale_log2);
+  const float2 nm2 = make_float2(-m_ref, -m_ref);
+  float2 acc[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) acc[q] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float2 x = __ffma2_rn(make_float2(__uint_as_float(r[c][2 * i]), __uint_as_float(r[c][2 * i + 1])),
+                                  sc2, nm2);
+      float2 p;
+      if (((i % 8) * NE) % 8 < NE) {
+        p = exp2_poly2<DEG>(x);
+      } else {
+        p.x = fast_exp2(x.x);
+        p.y = fast_exp2(x.y);
+      }
+      acc[i & 3] = __fadd2_rn(acc[i & 3], p);
+      pk[i] = pack_bf16(p.x, p.y);
+    }
+    tmem_st16(s_addr + c * 16, pk);   // P_h: packed bf16 over the first 32 columns of this region
+  }
+  const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
+  l_sum += (a01.x + a01.y) + (a23.x + a23.y);
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_full);
+}
+
+template <int DH, int EMU>
+__global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __grid_constant__ AttParams P) {
+  using Cfg = AttCfg<DH>;
+  constexpr int W_TMA = 8, W_MMA = 9;
+  constexpr int HALF = ATT_BN / 2;            // keys per pipeline step
+  constexpr int K_HALF_BYTES = HALF * 128;    // 64 key rows of a K sub-tile (rows are 128 B)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::BAR_OFF);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;     // [2]  K/V ring stage
+  uint64_t* k_empty = bars + 3;    // [2]
+  uint64_t* v_full = bars + 5;     // [2]
+  uint64_t* v_empty = bars + 7;    // [2]
+  uint64_t* s_full = bars + 9;     // [2 Q tiles][2 regions]
+  uint64_t* p_full = bars + 13;    // [2 Q tiles][2 regions]
+  uint64_t* pv_done = bars + 17;   // [2 Q tiles], one phase per half
+  uint64_t* o_done = bars + 19;    // [2 Q tiles]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * (2 * ATT_BM);
+  const int head = blockIdx.y;
+  const int b = blockIdx.z;
+  const int n_kv = (P.seq_kv + ATT_BN - 1) / ATT_BN;
+  const int n_half = (P.seq_kv + HALF - 1) / HALF;   // pipeline steps; the last K/V tile may contribute one only
+  pdl_launch_dependents();
+
+  if (warp == W_TMA && lane == 0) {
+    tma_prefetch_desc(&P.tmap_q);
+    tma_prefetch_desc(&P.tmap_k);
+    tma_prefetch_desc(&P.tmap_v);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&pv_done[i], 1);
+      mbar_init(&o_done[i], 1);
+    }
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == W_MMA) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == W_TMA) {
+    // ------------------------------------------------------------------ TMA producer (whole 128-key tiles)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    peer_wait_all_warp(P.wait, lane);
+    if (elect_one()) {
+      mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
+      for (int t = 0; t < 2; ++t)
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_q, q_full,
+                      s * 64, head, q0 + t * ATT_BM, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        pipe_wait(&k_empty[st], ph ^ 1);
+        mbar_expect_tx(&k_full[st], Cfg::TILE_BYTES);
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::K_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_k,
+                      &k_full[st], s * 64, head, j * ATT_BN, b);
+        pipe_wait(&v_empty[st], ph ^ 1);
+        mbar_expect_tx(&v_full[st], Cfg::TILE_BYTES);
+        for (int s = 0; s < Cfg::NSUB; ++s)
+          tma_load_4d(smem + Cfg::V_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_v,
+                      &v_full[st], s * 64, head, j * ATT_BN, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == W_MMA) {
+    // ------------------------------------------------------------------ MMA issuer
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (elect_one()) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, HALF, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
+      const uint32_t s_col[2] = {tmem_base + Cfg::S_COL0, tmem_base + Cfg::S_COL1};
+      const uint32_t o_col[2] = {tmem_base + Cfg::O_COL0, tmem_base + Cfg::O_COL1};
+      const uint32_t q_addr = smem_u32(smem + Cfg::Q_OFF);
+      const uint32_t k_addr = smem_u32(smem + Cfg::K_OFF);
+      const uint32_t v_addr = smem_u32(smem + Cfg::V_OFF);
+
+      // S[t][region hf] = Q_t * K[64*hf .. 64*hf+63]^T : 64 key rows of every K sub-tile start 8 KB in
+      auto issue_qk = [&](int t, int st, int hf) {
+#pragma unroll
+        for (int s = 0; s < Cfg::NSUB; ++s) {
+          const uint64_t da = make_smem_desc(q_addr + t * Cfg::TILE_BYTES + s * Cfg::SUB, 0, 1024);
+          const uint64_t db =
+              make_smem_desc(k_addr + st * Cfg::TILE_BYTES + s * Cfg::SUB + hf * K_HALF_BYTES, 0, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_ss(s_col[t] + hf * HALF, da + 2 * k, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
+        }
+      };
+      // O[t] += P[t][region hf] * V[64*hf .. 64*hf+63] : 16 keys per MMA = 8 packed columns of P, 2048 B of V
+      auto issue_pv = [&](int t, int st, int hf, bool accumulate) {
+#pragma unroll
+        for (int kk = 0; kk < HALF / 16; ++kk) {
+          const uint64_t db = make_smem_desc(v_addr + st * Cfg::TILE_BYTES + (hf * (HALF / 16) + kk) * 2048,
+                                             Cfg::SUB, 1024);
+          mma_ts(o_col[t], s_col[t] + hf * HALF + kk * 8, db, idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
+        }
+      };
+
+      unsigned long long w_v = 0, w_p = 0, w_k = 0, w_q = 0;
+      const long long t_begin = clock64();
+      auto timed_wait = [&](uint64_t* bar, uint32_t parity, unsigned long long& acc) {
+        if (P.dbg) {
+          const long long c0 = clock64();
+          pipe_wait(bar, parity);
+          acc += clock64() - c0;
+        } else {
+          pipe_wait(bar, parity);
+        }
+      };
+      timed_wait(q_full, 0, w_q);
+      timed_wait(&k_full[0], 0, w_q);
+      tc_fence_after();
+      for (int hf = 0; hf < 2 && hf < n_half; ++hf)
+        for (int t = 0; t < 2; ++t) {
+          issue_qk(t, 0, hf);
+          tc_commit(&s_full[t * 2 + hf]);
+        }
+      tc_commit(&k_empty[0]);
+      for (int h = 0; h < n_half; ++h) {
+        const int j = h >> 1, hf = h & 1;
+        const int st = j & 1;
+        const bool last = (h + 1 == n_half);
+        const bool has_next = (h + 2) < n_half;       // half h+2 = the same half of K/V tile j+1, same region
+        const bool next_last = (h + 3 == n_half);
+        const int stn = (j + 1) & 1;
+        const uint32_t phn = ((j + 1) >> 1) & 1;
+        if (hf == 0) timed_wait(&v_full[st], (j >> 1) & 1, w_v);
+        for (int t = 0; t < 2; ++t) {
+          timed_wait(&p_full[t * 2 + hf], j & 1, w_p);
+          tc_fence_after();
+          issue_pv(t, st, hf, h > 0);
+          tc_commit(&pv_done[t]);
+          if (t == 1 && (hf == 1 || last)) tc_commit(&v_empty[st]);
+          if (has_next) {
+            if (t == 0 && hf == 0) {
+              timed_wait(&k_full[stn], phn, w_k);
+              tc_fence_after();
+            }
+            issue_qk(t, stn, hf);
+            tc_commit(&s_full[t * 2 + hf]);
+            if (t == 1 && (hf == 1 || next_last)) tc_commit(&k_empty[stn]);
+          }
+          if (last) tc_commit(&o_done[t]);
+        }
+      }
+      if (P.dbg) {
+        atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
+        atomicAdd(&P.dbg[1], w_v);
+        atomicAdd(&P.dbg[3], w_p);
+        atomicAdd(&P.dbg[4], w_k);
+        atomicAdd(&P.dbg[5], w_q);
+      }
+    }
+    __syncwarp();
+  } else if (warp > W_MMA) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+  } else {
+    // ------------------------------------------------------------------ softmax warpgroups (one thread per row)
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    const int t = warp >> 2;                 // Q tile
+    const int quad = warp & 3;               // TMEM lane quadrant
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_off + (t == 0 ? Cfg::S_COL0 : Cfg::S_COL1);
+    const uint32_t o_addr = tmem_base + lane_off + (t == 0 ? Cfg::O_COL0 : Cfg::O_COL1);
+    float m_ref = -INFINITY;   // reference max (scaled, log2 domain) used for P and O
+    float l_sum = 0.f;
+    const int n_full = P.seq_kv / HALF;      // halves with all 64 keys valid
+    const bool prof = P.dbg != nullptr && threadIdx.x == 0;
+    unsigned long long w_s = 0;
+    const long long t_begin = clock64();
+    for (int h = 0; h < n_half; ++h) {
+      const int hf = h & 1;
+      const long long c0 = prof ? clock64() : 0;
+      pipe_wait(&s_full[t * 2 + hf], (h >> 1) & 1);
+      if (prof) w_s += clock64() - c0;
+      tc_fence_after();
+      if (h < n_full) {
+        softmax_pipe_half<DH, false, EMU>(s_addr + hf * HALF, o_addr, HALF, h, P.scale_log2, m_ref, l_sum,
+                                          &p_full[t * 2 + hf], &pv_done[t], lane);
+      } else {
+        softmax_pipe_half<DH, true, EMU>(s_addr + hf * HALF, o_addr, P.seq_kv - h * HALF, h, P.scale_log2, m_ref,
+                                         l_sum, &p_full[t * 2 + hf], &pv_done[t], lane);
+      }
+    }
+    if (prof) {
+      const long long c0 = clock64();
+      pipe_wait(&o_done[t], 0);
+      atomicAdd(&P.dbg[10], (unsigned long long)(clock64() - c0));
+      atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
+      atomicAdd(&P.dbg[9], w_s);
+    }
+    pipe_wait(&o_done[t], 0);
+    tc_fence_after();
+    // O / l -> bf16 -> global through this tile's idle Q shared memory (same epilogue as the kernel above)
+    const float inv = 1.f / l_sum;
+    constexpr int PPR = DH / 8;          // 16-byte pieces per row
+    constexpr int RPI = 32 / PPR;        // rows per store instruction
+    uint8_t* stage = smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + quad * (32 * DH * 2);
+#pragma unroll 1
+    for (int c = 0; c < DH / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        uint4 o;
+        o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+        o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+        o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+        o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+        *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + (((c * 4 + g) ^ (lane & 7)) << 4)) = o;
+      }
+    }
+    __syncwarp();
+    const int row_base = q0 + t * ATT_BM + quad * 32;
+#pragma unroll 4
+    for (int it = 0; it < 32 / RPI; ++it) {
+      const int rr = it * RPI + lane / PPR;
+      const int piece = lane % PPR;
+      const int row = row_base + rr;
+      const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * (DH * 2) + ((piece ^ (rr & 7)) << 4));
+      if (row < P.seq_q) {
+        __nv_bfloat16* orow;
+        if (P.n_peer > 0) {
+          int p = 0;
+          while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
+          orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
+                 (size_t)head * P.o_hs;
+        } else {
+          orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * P.o_hs;
+        }
+        *reinterpret_cast<uint4*>(orow + piece * 8) = o;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x == 0) peer_notify_last_cta(P.notify, gridDim.x * gridDim.y * gridDim.z);
+  if (warp == W_MMA) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace qi
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 32 + EMU = half-tile pipeline (attention_pipe_kernel), 51 = the same with the degree-2 polynomial on 3 of 8
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 26) return QI_ERR_ARG;
+  if (v < -1 || v > 63) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
@@ -710,6 +1084,16 @@ static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream
     return rc;
   if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT, TWO>, grid, dim3(TWO ? ATT_THREADS2 : ATT_THREADS),
                 AttCfg<DH>::SMEM_BYTES, stream, P) != cudaSuccess)
+    return QI_ERR_CUDA;
+  return QI_OK;
+}
+
+template <int DH, int EMU>
+static int launch_attention_pipe(const AttParams& P, dim3 grid, cudaStream_t stream) {
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_pipe_kernel<DH, EMU>), AttCfg<DH>::SMEM_BYTES))
+    return rc;
+  if (qi_launch(attention_pipe_kernel<DH, EMU>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream, P) !=
+      cudaSuccess)
     return QI_ERR_CUDA;
   return QI_OK;
 }
@@ -788,6 +1172,11 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
     case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
+    case 32: return launch_attention_pipe<DH, 0>(P, grid, stream);
+    case 34: return launch_attention_pipe<DH, 2>(P, grid, stream);
+    case 35: return launch_attention_pipe<DH, 3>(P, grid, stream);
+    case 36: return launch_attention_pipe<DH, 4>(P, grid, stream);
+    case 51: return launch_attention_pipe<DH, 16 + 3>(P, grid, stream);
     default: return QI_ERR_ARG;
   }
 }
