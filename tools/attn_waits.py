@@ -17,12 +17,12 @@ qkv = torch.randn(B, S, 3 * d, device="cuda", generator=g).bfloat16()
 q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
 o = torch.empty(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
 buf = torch.zeros(16, device="cuda", dtype=torch.int64)
-n_cta = ((S + 255) // 256) * H * B
 names = {0: "mma total", 1: "mma wait v_full", 2: "mma wait p_half", 3: "mma wait p_full", 4: "mma wait k_full",
          5: "mma wait q+k first", 8: "softmax total", 9: "softmax wait s_full", 10: "softmax wait o_done",
          11: "softmax S load", 12: "softmax row max", 13: "softmax O rescale", 14: "softmax P first half",
          15: "softmax P second half"}
 for var in [int(x) for x in (sys.argv[1:] or ["11", "19"])]:
+    n_cta = ((S + 127) // 128 if var >= 40 else (S + 255) // 256) * H * B   # variants 40+: one Q tile per CTA
     ops.attention_set_variant(var)
     for _ in range(3):
         ops.attention(q, k, v, o)

@@ -62,12 +62,12 @@ case "$T" in
       --log-file gpurun_out/launch_list_step.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-kernels --no-parity --e2e-steps 4 > gpurun_out/ncu_step.log 2>&1; echo "ncu rc=$?"
     python tools/launch_share.py gpurun_out/launch_list_step.csv;;
   attn_pipe)
-    # the half-tile pipeline (variants 32+): parity tests, interleaved sweep beside the current default, wait
+    # the Q-in-TMEM half-tile pipeline (variants 40+ / 56+): parity tests, interleaved sweep beside the current default, wait
     # counters, then a step bench with the fastest variant that passed
     timeout -s KILL 420 python -m pytest tests/test_ops_gpu.py -x -q -k "attention" > gpurun_out/attn_tests.log 2>&1; RC=$?; echo "attention tests rc=$RC"; tail -4 gpurun_out/attn_tests.log
     [ $RC -eq 0 ] || exit 1
-    QI_SWEEP_VARIANTS=${QI_SWEEP_VARIANTS:-11,32,34,35,36,51} timeout -s KILL 300 python tools/attn_sweep.py > gpurun_out/attn_pipe_sweep.txt 2>&1; echo "sweep rc=$?"; cat gpurun_out/attn_pipe_sweep.txt
-    timeout -s KILL 120 python tools/attn_waits.py 11 35 > gpurun_out/attn_pipe_waits.txt 2>&1; echo "waits rc=$?"; cat gpurun_out/attn_pipe_waits.txt
+    QI_SWEEP_VARIANTS=${QI_SWEEP_VARIANTS:-11,43,59,40,56,42,58,44,60} timeout -s KILL 300 python tools/attn_sweep.py > gpurun_out/attn_pipe_sweep.txt 2>&1; echo "sweep rc=$?"; cat gpurun_out/attn_pipe_sweep.txt
+    timeout -s KILL 120 python tools/attn_waits.py 11 43 59 > gpurun_out/attn_pipe_waits.txt 2>&1; echo "waits rc=$?"; cat gpurun_out/attn_pipe_waits.txt
     BEST=$(python - <<'PY'
 import re
 best, bv = None, 0

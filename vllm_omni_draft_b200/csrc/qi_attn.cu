@@ -53,6 +53,8 @@ struct AttParams {
   CUtensorMap tmap_q, tmap_k, tmap_v;
   __nv_bfloat16* o;
   long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
+  const __nv_bfloat16* q;       // TS kernel: Q rows are read straight from global memory into TMEM
+  long long ld_q, q_bs, q_hs;
   int seq_q, seq_kv, heads;
   float scale_log2;
   int split_p;   // softmax publishes P in two 64-key halves (p_half, then p_full)
@@ -681,20 +683,59 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// PIPE: the same tile shapes, software-pipelined over 64-key HALVES of every K/V tile.
+// TS: one 128-query tile per CTA, Q resident in TMEM, software-pipelined over 64-key HALVES of K/V.
 //
 // In the kernel above one Q tile's work is a dependent chain per K/V tile — S ready -> softmax (1 430 clk) -> second
 // half of P*V -> next Q*K^T -> S ready — because S_{j+1} can only be written once P_j (which lives in S_j's columns)
 // has been consumed: TMEM holds exactly two S tiles and two O tiles.  The two Q tiles hide part of each other's
-// chain, not all of it (measured: MMA warp waits 30 % of its time for P, softmax warps 40 % for S).  Here S of a Q
-// tile is two 64-column regions A/B that hold alternate halves: while the softmax works on half h+1 (region B), the
-// tensor pipe runs P_h*V_h out of region A and refills A with S_{h+2} = Q*K_{h+2}^T.  Per half and Q tile the tensor
-// pipe has 512 clk of work and the softmax ~720, on two Q tiles in parallel: the softmax threads never wait for more
-// than the tensor pipe's own work, and the MMA queue never drains.  MMAs are N = 64 (Q*K^T) and K = 64 (P*V); the
-// tcgen05 rate does not depend on N (cycles per MMA = 128*N/256).
-//
-// The lazy O rescale needs one more edge: P_{h+1} is computed while P_h*V_h may still be queued, so a row whose
-// reference maximum moves at half h+1 waits for that MMA (`pv_done`, committed after every P*V) before it scales O.
+// chain, not all of it (measured: MMA warp waits 30 % of its time for P, softmax warps 40 % for S).  Splitting S into
+// 64-column halves breaks the chain, but an SS-mode Q*K^T with N = 64 costs as much as N = 128 (the A operand is
+// re-read from shared memory for every MMA: measured, profiles/r02_attn_half_tile_pipeline_ss.txt).  So here:
+//   * Q (128 x DH bf16 = DH/2 TMEM columns) is the TMEM-resident A operand of Q*K^T: N = 64 MMAs run at the full
+//     rate and shared memory only feeds B (K or V).
+//   * S lives in three 64-column regions used round robin by successive halves h; P_h is written over the first 32
+//     columns of its region.  The MMA thread issues P_h*V_h and then Q*K_{h+3}^T into the region P_h just left.
+//   * Two softmax warpgroups take alternate halves of the SAME 128 rows (even halves / odd halves), each with its
+//     own running reference, row sum and O accumulator (O_a, O_b); the two partial results are merged once, in
+//     the epilogue.  A warpgroup's next S is produced while it still works on the current one, so it never waits
+//     for more than the tensor pipe's own work (512 clk per half against ~720 clk of softmax on two warpgroups).
+//   * K/V halves stream through a 6-deep TMA ring each.  CL = 2: the two CTAs of a cluster (adjacent Q tiles of one
+//     head) each load half of every K/V half-tile and multicast it into both CTAs' shared memory, so the L2 -> SM
+//     traffic per FLOP stays that of the two-tile kernel.
+//   TMEM columns: Q [0,64)  S regions [64,256)  O_a [256,384)  O_b [384,512).
+template <int DH>
+struct TsCfg {
+  static constexpr int HALF = 64;                        // keys per pipeline step
+  static constexpr int NSUB = DH / 64;
+  static constexpr int SUBH = HALF * 128;                // [64 keys x 64 bf16] swizzled sub-tile
+  static constexpr int HALF_BYTES = SUBH * NSUB;         // one K or V half
+  static constexpr int NST = 6;                          // ring depth in halves, K and V each
+  static constexpr int K_OFF = 0;
+  static constexpr int V_OFF = NST * HALF_BYTES;
+  static constexpr int BAR_OFF = 2 * NST * HALF_BYTES;
+  static constexpr int XCH_OFF = BAR_OFF + 512;          // float [2 warpgroups][128 rows][2] = (m, l)
+  static constexpr int SMEM_BYTES = XCH_OFF + 2048 + 1024;
+  static constexpr int Q_COL = 0, S_COL = 64, O_COL = 256;
+  static_assert(NST * HALF_BYTES >= ATT_BM * DH * 2, "the epilogue stages O through the K ring");
+};
+
+// tcgen05.commit of a cta_group::1 MMA stream that arrives on the same-offset mbarrier of every CTA in `mask`
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
+// TMA load whose box lands at the same shared-memory offset (and signals the same-offset mbarrier) in every CTA of `mask`
+__device__ __forceinline__ void tma_load_4d_mc(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                               int c2, int c3, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(mask)
+      : "memory");
+}
 
 // mbarrier wait of the pipelined kernel: a protocol error (or a lost TMA) traps after ~2 s instead of hanging the GPU.
 __device__ __forceinline__ void pipe_wait(uint64_t* bar, uint32_t parity) {
@@ -791,85 +832,88 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
   if (lane == 0) mbar_arrive(p_full);
 }
 
-template <int DH, int EMU>
-__global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __grid_constant__ AttParams P) {
-  using Cfg = AttCfg<DH>;
-  constexpr int W_TMA = 8, W_MMA = 9;
-  constexpr int HALF = ATT_BN / 2;            // keys per pipeline step
-  constexpr int K_HALF_BYTES = HALF * 128;    // 64 key rows of a K sub-tile (rows are 128 B)
+template <int DH, int EMU, int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(ATT_THREADS, 1)
+attention_ts_kernel(const __grid_constant__ AttParams P) {
+  using Cfg = TsCfg<DH>;
+  constexpr int W_K = 8, W_MMA = 9, W_V = 10;   // warps of the third warpgroup: K loader, MMA issuer, V loader
+  constexpr int HALF = Cfg::HALF, NST = Cfg::NST;
+  constexpr int ROWS = HALF / CL;               // key rows of every half this CTA loads (and multicasts)
+  constexpr uint16_t MC_MASK = (1u << CL) - 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::BAR_OFF);
-  uint64_t* q_full = bars + 0;
-  uint64_t* k_full = bars + 1;     // [2]  K/V ring stage
-  uint64_t* k_empty = bars + 3;    // [2]
-  uint64_t* v_full = bars + 5;     // [2]
-  uint64_t* v_empty = bars + 7;    // [2]
-  uint64_t* s_full = bars + 9;     // [2 Q tiles][2 regions]
-  uint64_t* p_full = bars + 13;    // [2 Q tiles][2 regions]
-  uint64_t* pv_done = bars + 17;   // [2 Q tiles], one phase per half
-  uint64_t* o_done = bars + 19;    // [2 Q tiles]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+  uint64_t* k_full = bars;                  // [NST]
+  uint64_t* k_empty = bars + NST;           // [NST]  one arrival per CTA of the cluster
+  uint64_t* v_full = bars + 2 * NST;        // [NST]
+  uint64_t* v_empty = bars + 3 * NST;       // [NST]
+  uint64_t* s_full = bars + 4 * NST;        // [3 regions]
+  uint64_t* p_full = s_full + 3;            // [3 regions]
+  uint64_t* pv_done = p_full + 3;           // [2 warpgroups], one phase per P*V into that warpgroup's O
+  uint64_t* o_done = pv_done + 2;
+  uint64_t* q_ready = o_done + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+  static_assert((4 * NST + 11) * 8 <= 512, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * (2 * ATT_BM);
+  const int q0 = blockIdx.x * ATT_BM;
   const int head = blockIdx.y;
   const int b = blockIdx.z;
-  const int n_kv = (P.seq_kv + ATT_BN - 1) / ATT_BN;
-  const int n_half = (P.seq_kv + HALF - 1) / HALF;   // pipeline steps; the last K/V tile may contribute one only
+  const int n_half = (P.seq_kv + HALF - 1) / HALF;
+  const uint32_t rank = CL > 1 ? cluster_ctarank() : 0;
   pdl_launch_dependents();
 
-  if (warp == W_TMA && lane == 0) {
-    tma_prefetch_desc(&P.tmap_q);
+  if (warp == W_K && lane == 0) {
     tma_prefetch_desc(&P.tmap_k);
     tma_prefetch_desc(&P.tmap_v);
-    mbar_init(q_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NST; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], 1);
+      mbar_init(&k_empty[i], CL);
       mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], 1);
-      mbar_init(&pv_done[i], 1);
-      mbar_init(&o_done[i], 1);
+      mbar_init(&v_empty[i], CL);
     }
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 3; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
     }
+    mbar_init(&pv_done[0], 1);
+    mbar_init(&pv_done[1], 1);
+    mbar_init(o_done, 1);
+    mbar_init(q_ready, 8);
     fence_barrier_init();
   }
   if (warp == W_MMA) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();   // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
 
-  if (warp == W_TMA) {
-    // ------------------------------------------------------------------ TMA producer (whole 128-key tiles)
+  if (warp == W_K || warp == W_V) {
+    // ------------------------------------------------------------------ TMA producers: K ring, V ring
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    peer_wait_all_warp(P.wait, lane);
+    const bool is_k = warp == W_K;
+    if (is_k) peer_wait_all_warp(P.wait, lane);
     if (elect_one()) {
-      mbar_expect_tx(q_full, 2 * Cfg::TILE_BYTES);
-      for (int t = 0; t < 2; ++t)
-        for (int s = 0; s < Cfg::NSUB; ++s)
-          tma_load_4d(smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_q, q_full,
-                      s * 64, head, q0 + t * ATT_BM, b);
-      for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
-        pipe_wait(&k_empty[st], ph ^ 1);
-        mbar_expect_tx(&k_full[st], Cfg::TILE_BYTES);
-        for (int s = 0; s < Cfg::NSUB; ++s)
-          tma_load_4d(smem + Cfg::K_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_k,
-                      &k_full[st], s * 64, head, j * ATT_BN, b);
-        pipe_wait(&v_empty[st], ph ^ 1);
-        mbar_expect_tx(&v_full[st], Cfg::TILE_BYTES);
-        for (int s = 0; s < Cfg::NSUB; ++s)
-          tma_load_4d(smem + Cfg::V_OFF + st * Cfg::TILE_BYTES + s * Cfg::SUB, &P.tmap_v,
-                      &v_full[st], s * 64, head, j * ATT_BN, b);
+      uint64_t* full = is_k ? k_full : v_full;
+      uint64_t* empty = is_k ? k_empty : v_empty;
+      const CUtensorMap* map = is_k ? &P.tmap_k : &P.tmap_v;
+      uint8_t* ring = smem + (is_k ? Cfg::K_OFF : Cfg::V_OFF);
+      for (int h = 0; h < n_half; ++h) {
+        const int st = h % NST;
+        const uint32_t ph = (h / NST) & 1;
+        pipe_wait(&empty[st], ph ^ 1);     // both CTAs of the cluster are done with this stage
+        mbar_expect_tx(&full[st], Cfg::HALF_BYTES);
+        for (int s = 0; s < Cfg::NSUB; ++s) {
+          uint8_t* dst = ring + st * Cfg::HALF_BYTES + s * Cfg::SUBH + rank * (ROWS * 128);
+          if (CL > 1)
+            tma_load_4d_mc(dst, map, &full[st], s * 64, head, h * HALF + rank * ROWS, b, MC_MASK);
+          else
+            tma_load_4d(dst, map, &full[st], s * 64, head, h * HALF, b);
+        }
       }
     }
     __syncwarp();
@@ -879,32 +923,34 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __
     if (elect_one()) {
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, HALF, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
-      const uint32_t s_col[2] = {tmem_base + Cfg::S_COL0, tmem_base + Cfg::S_COL1};
-      const uint32_t o_col[2] = {tmem_base + Cfg::O_COL0, tmem_base + Cfg::O_COL1};
-      const uint32_t q_addr = smem_u32(smem + Cfg::Q_OFF);
+      const uint32_t q_col = tmem_base + Cfg::Q_COL;
+      const uint32_t s_col = tmem_base + Cfg::S_COL;
+      const uint32_t o_col = tmem_base + Cfg::O_COL;
       const uint32_t k_addr = smem_u32(smem + Cfg::K_OFF);
       const uint32_t v_addr = smem_u32(smem + Cfg::V_OFF);
 
-      // S[t][region hf] = Q_t * K[64*hf .. 64*hf+63]^T : 64 key rows of every K sub-tile start 8 KB in
-      auto issue_qk = [&](int t, int st, int hf) {
+      // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in ring stage st
+      auto issue_qk = [&](int region, int st) {
 #pragma unroll
         for (int s = 0; s < Cfg::NSUB; ++s) {
-          const uint64_t da = make_smem_desc(q_addr + t * Cfg::TILE_BYTES + s * Cfg::SUB, 0, 1024);
-          const uint64_t db =
-              make_smem_desc(k_addr + st * Cfg::TILE_BYTES + s * Cfg::SUB + hf * K_HALF_BYTES, 0, 1024);
+          const uint64_t db = make_smem_desc(k_addr + st * Cfg::HALF_BYTES + s * Cfg::SUBH, 0, 1024);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            mma_ss(s_col[t] + hf * HALF, da + 2 * k, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
+            mma_ts(s_col + region * HALF, q_col + (s * 4 + k) * 8, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
         }
       };
-      // O[t] += P[t][region hf] * V[64*hf .. 64*hf+63] : 16 keys per MMA = 8 packed columns of P, 2048 B of V
-      auto issue_pv = [&](int t, int st, int hf, bool accumulate) {
+      // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; the second 64 columns
+      // of the head dim live one sub-tile (LBO) further
+      auto issue_pv = [&](int wg, int region, int st, bool accumulate) {
 #pragma unroll
         for (int kk = 0; kk < HALF / 16; ++kk) {
-          const uint64_t db = make_smem_desc(v_addr + st * Cfg::TILE_BYTES + (hf * (HALF / 16) + kk) * 2048,
-                                             Cfg::SUB, 1024);
-          mma_ts(o_col[t], s_col[t] + hf * HALF + kk * 8, db, idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
+          const uint64_t db = make_smem_desc(v_addr + st * Cfg::HALF_BYTES + kk * 2048, Cfg::SUBH, 1024);
+          mma_ts(o_col + wg * 128, s_col + region * HALF + kk * 8, db, idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
         }
+      };
+      auto release = [&](uint64_t* bar) {
+        if (CL > 1) tc_commit_mc(bar, MC_MASK);
+        else tc_commit(bar);
       };
 
       unsigned long long w_v = 0, w_p = 0, w_k = 0, w_q = 0;
@@ -918,42 +964,34 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __
           pipe_wait(bar, parity);
         }
       };
-      timed_wait(q_full, 0, w_q);
-      timed_wait(&k_full[0], 0, w_q);
+      timed_wait(q_ready, 0, w_q);
       tc_fence_after();
-      for (int hf = 0; hf < 2 && hf < n_half; ++hf)
-        for (int t = 0; t < 2; ++t) {
-          issue_qk(t, 0, hf);
-          tc_commit(&s_full[t * 2 + hf]);
-        }
-      tc_commit(&k_empty[0]);
+      for (int h = 0; h < 3 && h < n_half; ++h) {
+        timed_wait(&k_full[h % NST], 0, w_q);
+        tc_fence_after();
+        issue_qk(h, h % NST);
+        tc_commit(&s_full[h]);
+        release(&k_empty[h % NST]);
+      }
       for (int h = 0; h < n_half; ++h) {
-        const int j = h >> 1, hf = h & 1;
-        const int st = j & 1;
-        const bool last = (h + 1 == n_half);
-        const bool has_next = (h + 2) < n_half;       // half h+2 = the same half of K/V tile j+1, same region
-        const bool next_last = (h + 3 == n_half);
-        const int stn = (j + 1) & 1;
-        const uint32_t phn = ((j + 1) >> 1) & 1;
-        if (hf == 0) timed_wait(&v_full[st], (j >> 1) & 1, w_v);
-        for (int t = 0; t < 2; ++t) {
-          timed_wait(&p_full[t * 2 + hf], j & 1, w_p);
+        const int region = h % 3, wg = h & 1, st = h % NST;
+        timed_wait(&v_full[st], (h / NST) & 1, w_v);
+        timed_wait(&p_full[region], (h / 3) & 1, w_p);
+        tc_fence_after();
+        issue_pv(wg, region, st, h >= 2);
+        tc_commit(&pv_done[wg]);
+        release(&v_empty[st]);
+        const int hn = h + 3;
+        if (hn < n_half) {
+          const int stn = hn % NST;
+          timed_wait(&k_full[stn], (hn / NST) & 1, w_k);
           tc_fence_after();
-          issue_pv(t, st, hf, h > 0);
-          tc_commit(&pv_done[t]);
-          if (t == 1 && (hf == 1 || last)) tc_commit(&v_empty[st]);
-          if (has_next) {
-            if (t == 0 && hf == 0) {
-              timed_wait(&k_full[stn], phn, w_k);
-              tc_fence_after();
-            }
-            issue_qk(t, stn, hf);
-            tc_commit(&s_full[t * 2 + hf]);
-            if (t == 1 && (hf == 1 || next_last)) tc_commit(&k_empty[stn]);
-          }
-          if (last) tc_commit(&o_done[t]);
+          issue_qk(region, stn);
+          tc_commit(&s_full[region]);
+          release(&k_empty[stn]);
         }
       }
+      tc_commit(o_done);
       if (P.dbg) {
         atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
         atomicAdd(&P.dbg[1], w_v);
@@ -963,69 +1001,116 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __
       }
     }
     __syncwarp();
-  } else if (warp > W_MMA) {
+  } else if (warp > W_V) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   } else {
-    // ------------------------------------------------------------------ softmax warpgroups (one thread per row)
+    // ------------------------------------------------------------------ softmax warpgroups: wg 0 even halves, wg 1 odd
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
-    const int t = warp >> 2;                 // Q tile
+    const int wg = warp >> 2;
     const int quad = warp & 3;               // TMEM lane quadrant
+    const int row_l = quad * 32 + lane;      // this thread's query row inside the tile
     const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
-    const uint32_t s_addr = tmem_base + lane_off + (t == 0 ? Cfg::S_COL0 : Cfg::S_COL1);
-    const uint32_t o_addr = tmem_base + lane_off + (t == 0 ? Cfg::O_COL0 : Cfg::O_COL1);
-    float m_ref = -INFINITY;   // reference max (scaled, log2 domain) used for P and O
+    const uint32_t s_addr = tmem_base + lane_off + Cfg::S_COL;
+    const uint32_t o_addr = tmem_base + lane_off + Cfg::O_COL + wg * 128;
+    {   // Q row -> TMEM: this warpgroup's half of the head dim, straight from global memory (once per CTA)
+      constexpr int NQ = DH / 4;             // packed 32-bit columns per thread
+      uint32_t qv[NQ];
+      const int row = q0 + row_l;
+      if (row < P.seq_q) {
+        const uint4* src = reinterpret_cast<const uint4*>(P.q + (size_t)b * P.q_bs + (size_t)row * P.ld_q +
+                                                          (size_t)head * P.q_hs + wg * (DH / 2));
+#pragma unroll
+        for (int i = 0; i < NQ / 4; ++i) {
+          const uint4 u = __ldg(src + i);
+          qv[4 * i] = u.x, qv[4 * i + 1] = u.y, qv[4 * i + 2] = u.z, qv[4 * i + 3] = u.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) qv[i] = 0u;
+      }
+      if constexpr (NQ == 32) tmem_st32(tmem_base + lane_off + Cfg::Q_COL + wg * NQ, qv);
+      else tmem_st16(tmem_base + lane_off + Cfg::Q_COL + wg * NQ, qv);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_ready);
+    }
+    float m_ref = -INFINITY;   // reference max (scaled, log2 domain) of this warpgroup's halves
     float l_sum = 0.f;
     const int n_full = P.seq_kv / HALF;      // halves with all 64 keys valid
-    const bool prof = P.dbg != nullptr && threadIdx.x == 0;
+    const bool prof = P.dbg != nullptr && (threadIdx.x & 127) == 0 && wg == 0;
     unsigned long long w_s = 0;
     const long long t_begin = clock64();
-    for (int h = 0; h < n_half; ++h) {
-      const int hf = h & 1;
+    for (int h = wg; h < n_half; h += 2) {
+      const int region = h % 3;
       const long long c0 = prof ? clock64() : 0;
-      pipe_wait(&s_full[t * 2 + hf], (h >> 1) & 1);
+      pipe_wait(&s_full[region], (h / 3) & 1);
       if (prof) w_s += clock64() - c0;
       tc_fence_after();
       if (h < n_full) {
-        softmax_pipe_half<DH, false, EMU>(s_addr + hf * HALF, o_addr, HALF, h, P.scale_log2, m_ref, l_sum,
-                                          &p_full[t * 2 + hf], &pv_done[t], lane);
+        softmax_pipe_half<DH, false, EMU>(s_addr + region * HALF, o_addr, HALF, h >> 1, P.scale_log2, m_ref, l_sum,
+                                          &p_full[region], &pv_done[wg], lane);
       } else {
-        softmax_pipe_half<DH, true, EMU>(s_addr + hf * HALF, o_addr, P.seq_kv - h * HALF, h, P.scale_log2, m_ref,
-                                         l_sum, &p_full[t * 2 + hf], &pv_done[t], lane);
+        softmax_pipe_half<DH, true, EMU>(s_addr + region * HALF, o_addr, P.seq_kv - h * HALF, h >> 1, P.scale_log2,
+                                         m_ref, l_sum, &p_full[region], &pv_done[wg], lane);
       }
     }
     if (prof) {
-      const long long c0 = clock64();
-      pipe_wait(&o_done[t], 0);
-      atomicAdd(&P.dbg[10], (unsigned long long)(clock64() - c0));
       atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
       atomicAdd(&P.dbg[9], w_s);
     }
-    pipe_wait(&o_done[t], 0);
+    // merge the two warpgroups' partial softmaxes: O = (O_a*2^(m_a-m) + O_b*2^(m_b-m)) / (l_a*2^(m_a-m) + l_b*2^(m_b-m))
+    float* xch = reinterpret_cast<float*>(smem + Cfg::XCH_OFF);
+    xch[(wg * 128 + row_l) * 2] = m_ref;
+    xch[(wg * 128 + row_l) * 2 + 1] = l_sum;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const float m_o = xch[((wg ^ 1) * 128 + row_l) * 2];
+    const float l_o = xch[((wg ^ 1) * 128 + row_l) * 2 + 1];
+    const bool has_b = n_half > 1;           // with a single half warpgroup 1 never ran: O_b is uninitialised
+    const float m_all = fmaxf(m_ref, m_o);
+    const float a_me = fast_exp2(m_ref - m_all);      // exp2(-inf) = 0 for a warpgroup that saw no keys
+    const float a_ot = fast_exp2(m_o - m_all);
+    const float inv = 1.f / (l_sum * a_me + l_o * a_ot);
+    const float al_a = (wg == 0 ? a_me : a_ot) * inv;
+    const float al_b = (wg == 0 ? a_ot : a_me) * inv;
+    pipe_wait(o_done, 0);
     tc_fence_after();
-    // O / l -> bf16 -> global through this tile's idle Q shared memory (same epilogue as the kernel above)
-    const float inv = 1.f / l_sum;
+    // this warpgroup converts its half of the head-dim columns (of O_a and O_b); rows are staged through the K ring
+    // (all K/V halves have been consumed) so that global stores are DH*2 contiguous bytes per DH/8 lanes
     constexpr int PPR = DH / 8;          // 16-byte pieces per row
     constexpr int RPI = 32 / PPR;        // rows per store instruction
-    uint8_t* stage = smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + quad * (32 * DH * 2);
+    const uint32_t oa = tmem_base + lane_off + Cfg::O_COL + wg * (DH / 2);
+    uint8_t* stage = smem + Cfg::K_OFF + quad * (32 * DH * 2);
 #pragma unroll 1
-    for (int c = 0; c < DH / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld32(o_addr + c * 32, r);
+    for (int c = 0; c < DH / 64; ++c) {
+      uint32_t ra[32], rb[32];
+      tmem_ld32(oa + c * 32, ra);
+      if (has_b) tmem_ld32(oa + 128 + c * 32, rb);
       tmem_ld_wait();
+      if (!has_b) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) rb[i] = 0u;
+      }
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          v[i] = __uint_as_float(ra[g * 8 + i]) * al_a + __uint_as_float(rb[g * 8 + i]) * al_b;
         uint4 o;
-        o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
-        o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
-        o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
-        o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
-        *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + (((c * 4 + g) ^ (lane & 7)) << 4)) = o;
+        o.x = pack_bf16(v[0], v[1]);
+        o.y = pack_bf16(v[2], v[3]);
+        o.z = pack_bf16(v[4], v[5]);
+        o.w = pack_bf16(v[6], v[7]);
+        const int piece = wg * (DH / 16) + c * 4 + g;
+        *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + ((piece ^ (lane & 7)) << 4)) = o;
       }
     }
-    __syncwarp();
-    const int row_base = q0 + t * ATT_BM + quad * 32;
+    pair_sync(2 + quad);                     // the two warps of this lane quadrant have staged their columns
+    const int row_base = q0 + quad * 32;
+    constexpr int ITS = 32 / RPI / 2;        // each of the two warps stores half of the 32 rows
 #pragma unroll 4
-    for (int it = 0; it < 32 / RPI; ++it) {
+    for (int it = wg * ITS; it < (wg + 1) * ITS; ++it) {
       const int rr = it * RPI + lane / PPR;
       const int piece = lane % PPR;
       const int row = row_base + rr;
@@ -1048,17 +1133,19 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_pipe_kernel(const __
   tc_fence_before();
   __syncthreads();
   if (threadIdx.x == 0) peer_notify_last_cta(P.notify, gridDim.x * gridDim.y * gridDim.z);
+  if (CL > 1) cluster_sync_all();   // no CTA leaves while its peer may still arrive on its barriers
   if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
 }
 
+
 }  // namespace qi
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 32 + EMU = half-tile pipeline (attention_pipe_kernel), 51 = the same with the degree-2 polynomial on 3 of 8
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same in clusters of 2 with multicast K/V
 extern "C" int qi_attention_set_variant(int v) {
   if (v < -1 || v > 63) return QI_ERR_ARG;
   g_attn_variant = v;
@@ -1088,11 +1175,21 @@ static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream
   return QI_OK;
 }
 
-template <int DH, int EMU>
-static int launch_attention_pipe(const AttParams& P, dim3 grid, cudaStream_t stream) {
-  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_pipe_kernel<DH, EMU>), AttCfg<DH>::SMEM_BYTES))
+template <int DH, int EMU, int CL>
+static int launch_attention_ts(AttParams P, const void* k, const void* v, int batch, int seq_q, int seq_kv, int heads,
+                               long long ld_kv, long long kv_bs, long long kv_hs, cudaStream_t stream) {
+  // K/V maps with 64-key (CL = 1) or 32-key (CL = 2: half of every half-tile per CTA, multicast) boxes
+  const uint32_t box[4] = {64, 1, (uint32_t)(TsCfg<DH>::HALF / CL), 1};
+  uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_kv, (uint64_t)batch};
+  uint64_t str[3] = {(uint64_t)kv_hs * 2, (uint64_t)ld_kv * 2,
+                     (uint64_t)(batch > 1 ? kv_bs : ld_kv * (long long)seq_kv) * 2};
+  if (int rc = qi_encode_tmap_bf16(&P.tmap_k, k, 4, dims, str, box)) return rc;
+  if (int rc = qi_encode_tmap_bf16(&P.tmap_v, v, 4, dims, str, box)) return rc;
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_ts_kernel<DH, EMU, CL>), TsCfg<DH>::SMEM_BYTES))
     return rc;
-  if (qi_launch(attention_pipe_kernel<DH, EMU>, grid, dim3(ATT_THREADS), AttCfg<DH>::SMEM_BYTES, stream, P) !=
+  const int tiles = (seq_q + ATT_BM - 1) / ATT_BM;
+  dim3 grid((tiles + CL - 1) / CL * CL, heads, batch);
+  if (qi_launch(attention_ts_kernel<DH, EMU, CL>, grid, dim3(ATT_THREADS), TsCfg<DH>::SMEM_BYTES, stream, P) !=
       cudaSuccess)
     return QI_ERR_CUDA;
   return QI_OK;
@@ -1145,6 +1242,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     if (rc) return rc;
   }
   P.o = (__nv_bfloat16*)o;
+  P.q = (const __nv_bfloat16*)q;
+  P.ld_q = ld_q;
+  P.q_bs = q_bs;
+  P.q_hs = q_hs;
   P.ld_o = ld_o;
   P.o_bs = o_bs;
   P.o_hs = o_hs;
@@ -1153,7 +1254,8 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.heads = heads;
   P.scale_log2 = scale * 1.4426950408889634f;
   P.dbg = g_attn_dbg;
-  const int variant = attn_variant();
+  int variant = attn_variant();
+  if (variant >= 40 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
   P.split_p = (variant >> 3) & 1;
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
   switch (variant) {
@@ -1172,11 +1274,11 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
     case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
-    case 32: return launch_attention_pipe<DH, 0>(P, grid, stream);
-    case 34: return launch_attention_pipe<DH, 2>(P, grid, stream);
-    case 35: return launch_attention_pipe<DH, 3>(P, grid, stream);
-    case 36: return launch_attention_pipe<DH, 4>(P, grid, stream);
-    case 51: return launch_attention_pipe<DH, 16 + 3>(P, grid, stream);
+#define QI_TS_CASE(V, EMU, CL) \
+  case V: return launch_attention_ts<DH, EMU, CL>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
+    QI_TS_CASE(40, 0, 1) QI_TS_CASE(42, 2, 1) QI_TS_CASE(43, 3, 1) QI_TS_CASE(44, 4, 1)
+    QI_TS_CASE(56, 0, 2) QI_TS_CASE(58, 2, 2) QI_TS_CASE(59, 3, 2) QI_TS_CASE(60, 4, 2)
+#undef QI_TS_CASE
     default: return QI_ERR_ARG;
   }
 }
