@@ -1,0 +1,85 @@
+// Microbenchmark: cycles per tcgen05.mma (kind::f16, M = 128, K = 16, cta_group::1) by operand source and N.
+//   mode 0/1/2: A and B from shared memory (SS), N = 128 / 64 / 256
+//   mode 3/4/5: A from TMEM (TS),                N = 128 / 64 / 256
+// One thread per CTA issues `groups` x 8 MMAs into one accumulator, commits, waits; clock64 around it.  Run on every
+// SM at once (grid = SM count).  Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -I../../vllm_omni_draft_b200/csrc
+#include "qi_common.cuh"
+#include <cstdio>
+using namespace qi;
+
+template <int N, bool TS>
+__global__ void __launch_bounds__(128, 1) rate_kernel(int groups, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (32768 + 65536) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&slot);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  if (warp == 1 && elect_one()) {
+    constexpr uint32_t idesc = make_idesc_bf16(128, N, 0, 0);
+    const uint32_t a_addr = smem_u32(smem);            // A: 128 rows x 64 bf16 (16 KB), two of them
+    const uint32_t b_addr = smem_u32(smem + 32768);    // B: up to 256 rows x 64 bf16, two sub-tiles
+    const long long t0 = clock64();
+    for (int g = 0; g < groups; ++g) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint64_t da = make_smem_desc(a_addr + s * 16384, 0, 1024);
+        const uint64_t db = make_smem_desc(b_addr + s * 32768, 0, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (TS) mma_ts(tm + 256, tm + (s * 4 + k) * 8, db + 2 * k, idesc, 1u);
+          else mma_ss(tm + 256, da + 2 * k, db + 2 * k, idesc, 1u);
+        }
+      }
+    }
+    tc_commit(&bar);
+    mbar_wait(&bar, 0);
+    const long long t1 = clock64();
+    out[blockIdx.x] = t1 - t0;
+  }
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tm);
+}
+
+template <int N, bool TS>
+static void run(const char* name, int groups, int sms) {
+  long long* d;
+  cudaMalloc(&d, sms * sizeof(long long));
+  const int smem = 32768 + 65536 + 1024;
+  cudaFuncSetAttribute(rate_kernel<N, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  for (int grid : {1, sms}) {
+    rate_kernel<N, TS><<<grid, 128, smem>>>(groups, d);
+    rate_kernel<N, TS><<<grid, 128, smem>>>(groups, d);
+    cudaError_t e = cudaDeviceSynchronize();
+    long long h[256];
+    cudaMemcpy(h, d, grid * sizeof(long long), cudaMemcpyDeviceToHost);
+    long long mx = 0;
+    for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
+    printf("%-10s grid %3d: %7.1f clk per MMA (M=128 N=%d K=16)  -> %.0f%% of the 128*N/256 floor  [%s]\n", name, grid,
+           (double)mx / (groups * 8), N, 100.0 * (128.0 * N / 256.0) / ((double)mx / (groups * 8)), cudaGetErrorString(e));
+  }
+  cudaFree(d);
+}
+
+int main() {
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  const int groups = 2000;
+  run<128, false>("SS N=128", groups, sms);
+  run<64, false>("SS N=64", groups, sms);
+  run<256, false>("SS N=256", groups, sms);
+  run<128, true>("TS N=128", groups, sms);
+  run<64, true>("TS N=64", groups, sms);
+  run<256, true>("TS N=256", groups, sms);
+  return 0;
+}
