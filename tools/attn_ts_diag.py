@@ -1,0 +1,50 @@
+"""Timing experiments on the Q-in-TMEM attention kernel (variants 40+): QI_ATTN_TS_DIAG = 0 (real), 1 (softmax only
+hands the barriers on: the MMA/TMA pipeline alone), 2 (S load + P store without the math) — read per process, so this
+script re-executes itself per mode.  Prints us per launch at the cfg-2 step shape and the MMA-thread wait counters."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+if len(sys.argv) < 2:
+    for mode in ("0", "1", "2"):
+        env = dict(os.environ, QI_ATTN_TS_DIAG=mode)
+        subprocess.run([sys.executable, __file__, mode], env=env, check=False)
+    sys.exit(0)
+
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vllm_omni_draft_b200 import _lib, ops  # noqa: E402
+
+lib = _lib.lib()
+lib.qi_attention_set_debug.argtypes, lib.qi_attention_set_debug.restype = [C.c_void_p], C.c_int
+d, H, Dh, S, B = 3072, 24, 128, 4608, 2
+g = torch.Generator(device="cuda").manual_seed(0)
+qkv = torch.randn(B, S, 3 * d, device="cuda", generator=g).bfloat16()
+q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
+o = torch.empty(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
+buf = torch.zeros(16, device="cuda", dtype=torch.int64)
+for var in [int(x) for x in os.environ.get("QI_DIAG_VARIANTS", "43,59").split(",")]:
+    ops.attention_set_variant(var)
+    for _ in range(3):
+        ops.attention(q, k, v, o)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        ops.attention(q, k, v, o)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / 20
+    buf.zero_()
+    lib.qi_attention_set_debug(buf.data_ptr())
+    ops.attention(q, k, v, o)
+    torch.cuda.synchronize()
+    lib.qi_attention_set_debug(None)
+    c = buf.tolist()
+    n_cta = ((S + 127) // 128) * H * B
+    n_half = (S + 63) // 64
+    print(f"diag {sys.argv[1]} variant {var}: {us:7.1f} us  | per half-step: mma total {c[0] / n_cta / n_half:6.0f} clk, "
+          f"wait v {c[1] / n_cta / n_half:5.0f}, wait p {c[3] / n_cta / n_half:5.0f}, wait k {c[4] / n_cta / n_half:5.0f}, "
+          f"first {c[5] / n_cta:6.0f} per CTA | softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA", flush=True)
+ops.attention_set_variant(-1)

@@ -54,6 +54,7 @@ struct AttParams {
   __nv_bfloat16* o;
   long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
   const __nv_bfloat16* q;       // TS kernel: Q rows are read straight from global memory into TMEM
+  int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math
   long long ld_q, q_bs, q_hs;
   int seq_q, seq_kv, heads;
   float scale_log2;
@@ -1047,6 +1048,26 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       pipe_wait(&s_full[region], (h / 3) & 1);
       if (prof) w_s += clock64() - c0;
       tc_fence_after();
+      if (P.ts_diag) {   // timing experiments only: the result is garbage
+        if (P.ts_diag == 2) {
+          uint32_t r[2][32];
+          tmem_ld32(s_addr + region * HALF, r[0]);
+          tmem_ld32(s_addr + region * HALF + 32, r[1]);
+          tmem_ld_wait();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = r[0][i] ^ r[1][i];
+          tmem_st16(s_addr + region * HALF, pk);
+          tmem_st16(s_addr + region * HALF + 16, pk);
+          tmem_st_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[region]);
+        l_sum = 1.f;
+        m_ref = 0.f;
+        continue;
+      }
       if (h < n_full) {
         softmax_pipe_half<DH, false, EMU>(s_addr + region * HALF, o_addr, HALF, h >> 1, P.scale_log2, m_ref, l_sum,
                                           &p_full[region], &pv_done[wg], lane);
@@ -1254,6 +1275,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.heads = heads;
   P.scale_log2 = scale * 1.4426950408889634f;
   P.dbg = g_attn_dbg;
+  {
+    const char* e = getenv("QI_ATTN_TS_DIAG");
+    P.ts_diag = e ? atoi(e) : 0;
+  }
   int variant = attn_variant();
   if (variant >= 40 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
   P.split_p = (variant >> 3) & 1;
