@@ -51,6 +51,78 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int groups, long long* out
   if (warp == 0) tmem_dealloc<512>(tm);
 }
 
+// The attention pipeline's step: 4 TS MMAs N=128 (P*V) + 8 TS MMAs N=64 (Q*K^T) = 512 clk of tensor work, with
+// `commits` tcgen05.commit (to distinct mbarriers nobody waits on) spread behind the two groups, and optionally one
+// wait per step on a barrier that the previous step's commit completes (a dependent round trip through the pipe).
+template <int COMMITS, int WAITDIST>
+__global__ void __launch_bounds__(128, 1) step_kernel(int steps, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  __shared__ uint64_t bars[8];
+  __shared__ uint64_t done;
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (32768 + 65536) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 8; ++i) mbar_init(&bars[i], 1);
+    mbar_init(&done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&slot);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  if (warp == 1 && elect_one()) {
+    constexpr uint32_t idesc_qk = make_idesc_bf16(128, 64, 0, 0);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(128, 128, 0, 1);
+    const uint32_t b_addr = smem_u32(smem + 32768);
+    const long long t0 = clock64();
+    for (int h = 0; h < steps; ++h) {
+      if (WAITDIST > 0 && h >= WAITDIST) mbar_wait(&bars[0], (h - WAITDIST) & 1);   // completed by the commit of step h - WAITDIST
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const uint64_t db = make_smem_desc(b_addr + kk * 2048, 8192, 1024);
+        mma_ts(tm + 256 + (h & 1) * 128, tm + 64 + (h % 3) * 64 + kk * 8, db, idesc_pv, 1u);
+      }
+      if (COMMITS >= 1) tc_commit(&bars[0]);
+      if (COMMITS >= 3) tc_commit(&bars[1]);
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint64_t db = make_smem_desc(b_addr + 16384 + s * 8192, 0, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mma_ts(tm + 64 + (h % 3) * 64, tm + (s * 4 + k) * 8, db + 2 * k, idesc_qk, (s | k) ? 1u : 0u);
+      }
+      if (COMMITS >= 2) tc_commit(&bars[2]);
+      if (COMMITS >= 4) tc_commit(&bars[3]);
+    }
+    tc_commit(&done);
+    mbar_wait(&done, 0);
+    out[blockIdx.x] = clock64() - t0;
+  }
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tm);
+}
+
+template <int COMMITS, int WAITDIST>
+static void run_step(int steps, int sms) {
+  long long* d;
+  cudaMalloc(&d, sms * sizeof(long long));
+  const int smem = 32768 + 65536 + 1024;
+  cudaFuncSetAttribute(step_kernel<COMMITS, WAITDIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  step_kernel<COMMITS, WAITDIST><<<sms, 128, smem>>>(steps, d);
+  step_kernel<COMMITS, WAITDIST><<<sms, 128, smem>>>(steps, d);
+  cudaError_t e = cudaDeviceSynchronize();
+  long long h[256];
+  cudaMemcpy(h, d, sms * sizeof(long long), cudaMemcpyDeviceToHost);
+  long long mx = 0;
+  for (int i = 0; i < sms; ++i) mx = h[i] > mx ? h[i] : mx;
+  printf("step (4 TS N=128 + 8 TS N=64 = 512 clk), %d commits/step, wait on the commit of %d steps back: %7.1f clk per step [%s]\n",
+         COMMITS, WAITDIST, (double)mx / steps, cudaGetErrorString(e));
+  cudaFree(d);
+}
+
 template <int N, bool TS>
 static void run(const char* name, int groups, int sms) {
   long long* d;
@@ -72,6 +144,7 @@ static void run(const char* name, int groups, int sms) {
 }
 
 int main() {
+  setvbuf(stdout, nullptr, _IONBF, 0);
   int sms = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   const int groups = 2000;
@@ -81,5 +154,10 @@ int main() {
   run<128, true>("TS N=128", groups, sms);
   run<64, true>("TS N=64", groups, sms);
   run<256, true>("TS N=256", groups, sms);
+  run_step<0, 0>(2000, sms);
+  run_step<1, 0>(2000, sms);
+  run_step<2, 0>(2000, sms);
+  run_step<4, 0>(2000, sms);
+  run_step<4, 1>(2000, sms);
   return 0;
 }

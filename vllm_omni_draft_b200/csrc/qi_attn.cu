@@ -903,9 +903,10 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       uint64_t* empty = is_k ? k_empty : v_empty;
       const CUtensorMap* map = is_k ? &P.tmap_k : &P.tmap_v;
       uint8_t* ring = smem + (is_k ? Cfg::K_OFF : Cfg::V_OFF);
-      for (int h = 0; h < n_half; ++h) {
-        const int st = h % NST;
-        const uint32_t ph = (h / NST) & 1;
+      int st = 0;
+      uint32_t ph = 0;
+      for (int h = 0; h < n_half; ++h, ++st) {
+        if (st == NST) st = 0, ph ^= 1;
         pipe_wait(&empty[st], ph ^ 1);     // both CTAs of the cluster are done with this stage
         mbar_expect_tx(&full[st], Cfg::HALF_BYTES);
         for (int s = 0; s < Cfg::NSUB; ++s) {
@@ -930,24 +931,25 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       const uint32_t k_addr = smem_u32(smem + Cfg::K_OFF);
       const uint32_t v_addr = smem_u32(smem + Cfg::V_OFF);
 
-      // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in ring stage st
-      auto issue_qk = [&](int region, int st) {
+      // Descriptors of ring stage st = those of stage 0 + st * KSTEP in the 14-bit address field (shared-memory
+      // addresses are below 256 KB, so the field cannot carry).
+      constexpr uint32_t KSTEP = Cfg::HALF_BYTES >> 4;
+      const uint64_t kdesc0 = make_smem_desc(k_addr, 0, 1024);
+      const uint64_t vdesc0 = make_smem_desc(v_addr, Cfg::SUBH, 1024);
+      // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in a ring stage
+      auto issue_qk = [&](uint32_t d_col, uint64_t kd) {
 #pragma unroll
-        for (int s = 0; s < Cfg::NSUB; ++s) {
-          const uint64_t db = make_smem_desc(k_addr + st * Cfg::HALF_BYTES + s * Cfg::SUBH, 0, 1024);
+        for (int s = 0; s < Cfg::NSUB; ++s)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            mma_ts(s_col + region * HALF, q_col + (s * 4 + k) * 8, db + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
-        }
+            mma_ts(d_col, q_col + (s * 4 + k) * 8, kd + s * (Cfg::SUBH >> 4) + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
       };
       // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; the second 64 columns
       // of the head dim live one sub-tile (LBO) further
-      auto issue_pv = [&](int wg, int region, int st, bool accumulate) {
+      auto issue_pv = [&](uint32_t d_col, uint32_t p_col, uint64_t vd, bool accumulate) {
 #pragma unroll
-        for (int kk = 0; kk < HALF / 16; ++kk) {
-          const uint64_t db = make_smem_desc(v_addr + st * Cfg::HALF_BYTES + kk * 2048, Cfg::SUBH, 1024);
-          mma_ts(o_col + wg * 128, s_col + region * HALF + kk * 8, db, idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
-        }
+        for (int kk = 0; kk < HALF / 16; ++kk)
+          mma_ts(d_col, p_col + kk * 8, vd + kk * (2048 >> 4), idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
       };
       auto release = [&](uint64_t* bar) {
         if (CL > 1) tc_commit_mc(bar, MC_MASK);
@@ -968,29 +970,34 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       timed_wait(q_ready, 0, w_q);
       tc_fence_after();
       for (int h = 0; h < 3 && h < n_half; ++h) {
-        timed_wait(&k_full[h % NST], 0, w_q);
-        tc_fence_after();
-        issue_qk(h, h % NST);
+        timed_wait(&k_full[h], 0, w_q);
+        issue_qk(s_col + h * HALF, kdesc0 + h * KSTEP);
         tc_commit(&s_full[h]);
-        release(&k_empty[h % NST]);
+        release(&k_empty[h]);
       }
+      // A barrier wait costs the tensor pipe ~60 clk when nothing is queued behind it (tools/micro/mma_rate.cu), so
+      // the operands of the NEXT step (V_{h+1}, K_{h+4}) are waited for right after this step's MMAs were issued:
+      // only the wait for P_h is left in front of an MMA.
+      int r = 0, vs = 0, ks = 3;              // region of half h, V stage of half h, K stage of half h + 3 (NST > 3)
+      uint32_t rp = 0, vp = 0, kp = 0;        // and the parities of their barriers
+      timed_wait(&v_full[0], 0, w_v);
+      if (3 < n_half) timed_wait(&k_full[3], 0, w_k);
       for (int h = 0; h < n_half; ++h) {
-        const int region = h % 3, wg = h & 1, st = h % NST;
-        timed_wait(&v_full[st], (h / NST) & 1, w_v);
-        timed_wait(&p_full[region], (h / 3) & 1, w_p);
+        timed_wait(&p_full[r], rp, w_p);
         tc_fence_after();
-        issue_pv(wg, region, st, h >= 2);
-        tc_commit(&pv_done[wg]);
-        release(&v_empty[st]);
-        const int hn = h + 3;
-        if (hn < n_half) {
-          const int stn = hn % NST;
-          timed_wait(&k_full[stn], (hn / NST) & 1, w_k);
-          tc_fence_after();
-          issue_qk(region, stn);
-          tc_commit(&s_full[region]);
-          release(&k_empty[stn]);
+        issue_pv(o_col + (h & 1) * 128, s_col + r * HALF, vdesc0 + vs * KSTEP, h >= 2);
+        tc_commit(&pv_done[h & 1]);
+        release(&v_empty[vs]);
+        if (h + 3 < n_half) {
+          issue_qk(s_col + r * HALF, kdesc0 + ks * KSTEP);
+          tc_commit(&s_full[r]);
+          release(&k_empty[ks]);
         }
+        if (++r == 3) r = 0, rp ^= 1;
+        if (++vs == NST) vs = 0, vp ^= 1;
+        if (++ks == NST) ks = 0, kp ^= 1;
+        if (h + 1 < n_half) timed_wait(&v_full[vs], vp, w_v);
+        if (h + 4 < n_half) timed_wait(&k_full[ks], kp, w_k);
       }
       tc_commit(o_done);
       if (P.dbg) {
@@ -1042,10 +1049,12 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
     const bool prof = P.dbg != nullptr && (threadIdx.x & 127) == 0 && wg == 0;
     unsigned long long w_s = 0;
     const long long t_begin = clock64();
-    for (int h = wg; h < n_half; h += 2) {
-      const int region = h % 3;
+    int region = wg;               // h % 3 and (h / 3) & 1 of this warpgroup's halves h = wg, wg + 2, ...
+    uint32_t rpar = 0;
+    for (int h = wg; h < n_half; h += 2, region += 2) {
+      if (region >= 3) region -= 3, rpar ^= 1;
       const long long c0 = prof ? clock64() : 0;
-      pipe_wait(&s_full[region], (h / 3) & 1);
+      pipe_wait(&s_full[region], rpar);
       if (prof) w_s += clock64() - c0;
       tc_fence_after();
       if (P.ts_diag) {   // timing experiments only: the result is garbage
