@@ -7,7 +7,7 @@ import subprocess
 import sys
 
 if len(sys.argv) < 2:
-    for mode in ("0", "1", "2"):
+    for mode in os.environ.get("QI_DIAG_MODES", "0,1,2,3,4").split(","):
         env = dict(os.environ, QI_ATTN_TS_DIAG=mode)
         subprocess.run([sys.executable, __file__, mode], env=env, check=False)
     sys.exit(0)

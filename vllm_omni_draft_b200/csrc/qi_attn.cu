@@ -54,7 +54,7 @@ struct AttParams {
   __nv_bfloat16* o;
   long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
   const __nv_bfloat16* q;       // TS kernel: Q rows are read straight from global memory into TMEM
-  int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math
+  int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math, 3 = as 1 and the MMA thread does not wait for P, 4 = as 3 and it does not wait for K/V either
   long long ld_q, q_bs, q_hs;
   int seq_q, seq_kv, heads;
   float scale_log2;
@@ -980,10 +980,10 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       // only the wait for P_h is left in front of an MMA.
       int r = 0, vs = 0, ks = 3;              // region of half h, V stage of half h, K stage of half h + 3 (NST > 3)
       uint32_t rp = 0, vp = 0, kp = 0;        // and the parities of their barriers
-      timed_wait(&v_full[0], 0, w_v);
-      if (3 < n_half) timed_wait(&k_full[3], 0, w_k);
+      if (P.ts_diag < 4) timed_wait(&v_full[0], 0, w_v);
+      if (3 < n_half && P.ts_diag < 4) timed_wait(&k_full[3], 0, w_k);
       for (int h = 0; h < n_half; ++h) {
-        timed_wait(&p_full[r], rp, w_p);
+        if (P.ts_diag < 3) timed_wait(&p_full[r], rp, w_p);
         tc_fence_after();
         issue_pv(o_col + (h & 1) * 128, s_col + r * HALF, vdesc0 + vs * KSTEP, h >= 2);
         tc_commit(&pv_done[h & 1]);
@@ -996,8 +996,8 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
         if (++r == 3) r = 0, rp ^= 1;
         if (++vs == NST) vs = 0, vp ^= 1;
         if (++ks == NST) ks = 0, kp ^= 1;
-        if (h + 1 < n_half) timed_wait(&v_full[vs], vp, w_v);
-        if (h + 4 < n_half) timed_wait(&k_full[ks], kp, w_k);
+        if (h + 1 < n_half && P.ts_diag < 4) timed_wait(&v_full[vs], vp, w_v);
+        if (h + 4 < n_half && P.ts_diag < 4) timed_wait(&k_full[ks], kp, w_k);
       }
       tc_commit(o_done);
       if (P.dbg) {
