@@ -690,8 +690,8 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 // half of P*V -> next Q*K^T -> S ready — because S_{j+1} can only be written once P_j (which lives in S_j's columns)
 // has been consumed: TMEM holds exactly two S tiles and two O tiles.  The two Q tiles hide part of each other's
 // chain, not all of it (measured: MMA warp waits 30 % of its time for P, softmax warps 40 % for S).  Splitting S into
-// 64-column halves breaks the chain, but an SS-mode Q*K^T with N = 64 costs as much as N = 128 (the A operand is
-// re-read from shared memory for every MMA: measured, profiles/r02_attn_half_tile_pipeline_ss.txt).  So here:
+// 64-column halves breaks the chain, but an SS-mode Q*K^T with N = 64 takes 48 clk against 32 for the same MMA with A
+// in TMEM (tools/micro/mma_rate.cu: A is re-read from shared memory for every MMA).  So here:
 //   * Q (128 x DH bf16 = DH/2 TMEM columns) is the TMEM-resident A operand of Q*K^T: N = 64 MMAs run at the full
 //     rate and shared memory only feeds B (K or V).
 //   * S lives in three 64-column regions used round robin by successive halves h; P_h is written over the first 32
@@ -700,41 +700,43 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 //     own running reference, row sum and O accumulator (O_a, O_b); the two partial results are merged once, in
 //     the epilogue.  A warpgroup's next S is produced while it still works on the current one, so it never waits
 //     for more than the tensor pipe's own work (512 clk per half against ~720 clk of softmax on two warpgroups).
-//   * K/V halves stream through a 6-deep TMA ring each.  CL = 2: the two CTAs of a cluster (adjacent Q tiles of one
-//     head) each load half of every K/V half-tile and multicast it into both CTAs' shared memory, so the L2 -> SM
-//     traffic per FLOP stays that of the two-tile kernel.
-//   TMEM columns: Q [0,64)  S regions [64,256)  O_a [256,384)  O_b [384,512).
-template <int DH>
+//   * K/V halves stream through deep TMA rings.  One Q tile per CTA doubles the K/V bytes per FLOP that an SM pulls
+//     from L2, and that — not the tensor pipe — then bounds the kernel (measured: 1 180 clk per half with the K/V
+//     waits, 600 without; TMA multicast in clusters of 2 does not reduce it).  PAIR: the two CTAs of a cluster
+//     (adjacent Q tiles of one head) run cta_group::2 MMAs, M = 256: each CTA stages only HALF of every K/V half
+//     (32 keys of K, 64 of the 128 head-dim columns of V) and the tensor cores read both halves, so an SM ingests the
+//     same bytes per FLOP as in the two-tile kernel.  The leader CTA's MMA thread issues for both; both CTAs'
+//     softmax warps arrive on the leader's P barriers; commits are multicast to both CTAs.
+//   TMEM columns (per CTA): Q [0,64)  S regions [64,256)  O_a [256,384)  O_b [384,512).
+template <int DH, bool PAIR>
 struct TsCfg {
-  static constexpr int HALF = 64;                        // keys per pipeline step
+  static constexpr int HALF = 64;                              // keys per pipeline step
+  static constexpr int NCTA = PAIR ? 2 : 1;
   static constexpr int NSUB = DH / 64;
-  static constexpr int SUBH = HALF * 128;                // [64 keys x 64 bf16] swizzled sub-tile
-  static constexpr int HALF_BYTES = SUBH * NSUB;         // one K or V half
-  static constexpr int NST = 6;                          // ring depth in halves, K and V each
+  static constexpr int K_ROWS = HALF / NCTA;                   // key rows of a K half staged by one CTA
+  static constexpr int K_SUB = K_ROWS * 128;                   // [K_ROWS keys x 64 bf16] swizzled sub-tile
+  static constexpr int K_STAGE = K_SUB * NSUB;
+  static constexpr int V_SUB = HALF * 128;                     // [64 keys x 64 head-dim columns]
+  static constexpr int V_STAGE = V_SUB * (PAIR ? 1 : NSUB);    // PAIR: one CTA holds DH/2 = 64 columns of V
+  static constexpr int NST = PAIR ? 10 : 6;                    // ring depth in halves, K and V each
   static constexpr int K_OFF = 0;
-  static constexpr int V_OFF = NST * HALF_BYTES;
-  static constexpr int BAR_OFF = 2 * NST * HALF_BYTES;
-  static constexpr int XCH_OFF = BAR_OFF + 512;          // float [2 warpgroups][128 rows][2] = (m, l)
+  static constexpr int V_OFF = NST * K_STAGE;
+  static constexpr int BAR_OFF = V_OFF + NST * V_STAGE;
+  static constexpr int XCH_OFF = BAR_OFF + 512;                // float [2 warpgroups][128 rows][2] = (m, l)
   static constexpr int SMEM_BYTES = XCH_OFF + 2048 + 1024;
   static constexpr int Q_COL = 0, S_COL = 64, O_COL = 256;
-  static_assert(NST * HALF_BYTES >= ATT_BM * DH * 2, "the epilogue stages O through the K ring");
+  static_assert(!PAIR || DH == 128, "the pair kernel splits V by 64-column sub-tiles");
+  static_assert(NST * K_STAGE >= ATT_BM * DH * 2, "the epilogue stages O through the K ring");
+  static_assert((4 * NST + 11) * 8 <= 512, "barrier block");
 };
 
-// tcgen05.commit of a cta_group::1 MMA stream that arrives on the same-offset mbarrier of every CTA in `mask`
-__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+// D[tmem of both CTAs] (+)= A[tmem, 128 rows per CTA] * B[smem, N/2 rows per CTA]; leader CTA only
+__device__ __forceinline__ void mma_ts_pair(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
   asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-          smem_u32(bar)),
-      "h"(mask)
-      : "memory");
-}
-// TMA load whose box lands at the same shared-memory offset (and signals the same-offset mbarrier) in every CTA of `mask`
-__device__ __forceinline__ void tma_load_4d_mc(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                               int c2, int c3, uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
-      "[%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(smem_u32(smem_dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(mask)
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 
@@ -752,7 +754,14 @@ __device__ __forceinline__ void pipe_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
-template <int DH, bool MASK, int EMU>
+// Arrival on a barrier of this CTA, or (PAIR) on the same barrier of the pair's leader CTA.
+template <bool PAIR>
+__device__ __forceinline__ void ts_arrive(uint64_t* bar) {
+  if (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(bar), 0));
+  else mbar_arrive(bar);
+}
+
+template <int DH, bool MASK, int EMU, bool PAIR>
 __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_addr, int kv_valid, int h,
                                                   float scale_log2, float& m_ref, float& l_sum, uint64_t* p_full,
                                                   uint64_t* pv_done, int lane) {
@@ -830,32 +839,29 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
   tmem_st_wait();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(p_full);
+  if (lane == 0) ts_arrive<PAIR>(p_full);
 }
 
-template <int DH, int EMU, int CL>
-__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(ATT_THREADS, 1)
+template <int DH, int EMU, bool PAIR>
+__global__ void __cluster_dims__(PAIR ? 2 : 1, 1, 1) __launch_bounds__(ATT_THREADS, 1)
 attention_ts_kernel(const __grid_constant__ AttParams P) {
-  using Cfg = TsCfg<DH>;
+  using Cfg = TsCfg<DH, PAIR>;
   constexpr int W_K = 8, W_MMA = 9, W_V = 10;   // warps of the third warpgroup: K loader, MMA issuer, V loader
   constexpr int HALF = Cfg::HALF, NST = Cfg::NST;
-  constexpr int ROWS = HALF / CL;               // key rows of every half this CTA loads (and multicasts)
-  constexpr uint16_t MC_MASK = (1u << CL) - 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::BAR_OFF);
-  uint64_t* k_full = bars;                  // [NST]
-  uint64_t* k_empty = bars + NST;           // [NST]  one arrival per CTA of the cluster
+  uint64_t* k_full = bars;                  // [NST]  (PAIR: the leader's collect both CTAs' TMA bytes)
+  uint64_t* k_empty = bars + NST;           // [NST]
   uint64_t* v_full = bars + 2 * NST;        // [NST]
   uint64_t* v_empty = bars + 3 * NST;       // [NST]
   uint64_t* s_full = bars + 4 * NST;        // [3 regions]
-  uint64_t* p_full = s_full + 3;            // [3 regions]
+  uint64_t* p_full = s_full + 3;            // [3 regions]  (PAIR: the leader's collect both CTAs' softmax warps)
   uint64_t* pv_done = p_full + 3;           // [2 warpgroups], one phase per P*V into that warpgroup's O
   uint64_t* o_done = pv_done + 2;
   uint64_t* q_ready = o_done + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
-  static_assert((4 * NST + 11) * 8 <= 512, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -863,7 +869,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
   const int head = blockIdx.y;
   const int b = blockIdx.z;
   const int n_half = (P.seq_kv + HALF - 1) / HALF;
-  const uint32_t rank = CL > 1 ? cluster_ctarank() : 0;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0;
   pdl_launch_dependents();
 
   if (warp == W_K && lane == 0) {
@@ -871,24 +877,27 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
     tma_prefetch_desc(&P.tmap_v);
     for (int i = 0; i < NST; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], CL);
+      mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], CL);
+      mbar_init(&v_empty[i], 1);
     }
     for (int i = 0; i < 3; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 4);
+      mbar_init(&p_full[i], 4 * Cfg::NCTA);
     }
     mbar_init(&pv_done[0], 1);
     mbar_init(&pv_done[1], 1);
     mbar_init(o_done, 1);
-    mbar_init(q_ready, 8);
+    mbar_init(q_ready, 8 * Cfg::NCTA);
     fence_barrier_init();
   }
-  if (warp == W_MMA) tmem_alloc<512>(tmem_slot);
+  if (warp == W_MMA) {
+    if (PAIR) tmem_alloc_pair<512>(tmem_slot);
+    else tmem_alloc<512>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
-  if (CL > 1) cluster_sync_all();   // the peer's barriers exist before anything is multicast at them
+  if (PAIR) cluster_sync_all();   // both CTAs' barriers and TMEM exist before anything is signalled across the pair
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
@@ -903,57 +912,68 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       uint64_t* empty = is_k ? k_empty : v_empty;
       const CUtensorMap* map = is_k ? &P.tmap_k : &P.tmap_v;
       uint8_t* ring = smem + (is_k ? Cfg::K_OFF : Cfg::V_OFF);
+      const int stage_bytes = is_k ? Cfg::K_STAGE : Cfg::V_STAGE;
       int st = 0;
       uint32_t ph = 0;
       for (int h = 0; h < n_half; ++h, ++st) {
         if (st == NST) st = 0, ph ^= 1;
-        pipe_wait(&empty[st], ph ^ 1);     // both CTAs of the cluster are done with this stage
-        mbar_expect_tx(&full[st], Cfg::HALF_BYTES);
-        for (int s = 0; s < Cfg::NSUB; ++s) {
-          uint8_t* dst = ring + st * Cfg::HALF_BYTES + s * Cfg::SUBH + rank * (ROWS * 128);
-          if (CL > 1)
-            tma_load_4d_mc(dst, map, &full[st], s * 64, head, h * HALF + rank * ROWS, b, MC_MASK);
-          else
-            tma_load_4d(dst, map, &full[st], s * 64, head, h * HALF, b);
+        pipe_wait(&empty[st], ph ^ 1);
+        uint8_t* dst = ring + st * stage_bytes;
+        if (PAIR) {
+          // this CTA's half of the half: 32 of the 64 keys of K, 64 of the 128 head-dim columns of V; the bytes of
+          // both CTAs complete on the leader's barrier
+          if (rank == 0) mbar_expect_tx(&full[st], 2 * stage_bytes);
+          const uint32_t bar = mapa_shared(smem_u32(&full[st]), 0);
+          if (is_k) {
+            for (int s = 0; s < Cfg::NSUB; ++s)
+              tma_load_4d_pair(dst + s * Cfg::K_SUB, map, bar, s * 64, head, h * HALF + (int)rank * Cfg::K_ROWS, b);
+          } else {
+            tma_load_4d_pair(dst, map, bar, (int)rank * 64, head, h * HALF, b);
+          }
+        } else {
+          mbar_expect_tx(&full[st], stage_bytes);
+          for (int s = 0; s < Cfg::NSUB; ++s)
+            tma_load_4d(dst + s * (is_k ? Cfg::K_SUB : Cfg::V_SUB), map, &full[st], s * 64, head, h * HALF, b);
         }
       }
     }
     __syncwarp();
   } else if (warp == W_MMA) {
-    // ------------------------------------------------------------------ MMA issuer
+    // ------------------------------------------------------------------ MMA issuer (PAIR: the leader CTA's only)
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    if (elect_one()) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, HALF, 0, 0);
-      constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM * Cfg::NCTA, HALF, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM * Cfg::NCTA, DH, 0, 1);   // B (=V) is MN-major
       const uint32_t q_col = tmem_base + Cfg::Q_COL;
       const uint32_t s_col = tmem_base + Cfg::S_COL;
       const uint32_t o_col = tmem_base + Cfg::O_COL;
-      const uint32_t k_addr = smem_u32(smem + Cfg::K_OFF);
-      const uint32_t v_addr = smem_u32(smem + Cfg::V_OFF);
-
-      // Descriptors of ring stage st = those of stage 0 + st * KSTEP in the 14-bit address field (shared-memory
-      // addresses are below 256 KB, so the field cannot carry).
-      constexpr uint32_t KSTEP = Cfg::HALF_BYTES >> 4;
-      const uint64_t kdesc0 = make_smem_desc(k_addr, 0, 1024);
-      const uint64_t vdesc0 = make_smem_desc(v_addr, Cfg::SUBH, 1024);
+      // Descriptors of ring stage st = those of stage 0 + st * (stage bytes >> 4) in the 14-bit address field
+      // (shared-memory addresses are below 256 KB, so the field cannot carry).
+      constexpr uint32_t KSTEP = Cfg::K_STAGE >> 4, VSTEP = Cfg::V_STAGE >> 4;
+      const uint64_t kdesc0 = make_smem_desc(smem_u32(smem + Cfg::K_OFF), 0, 1024);
+      const uint64_t vdesc0 = make_smem_desc(smem_u32(smem + Cfg::V_OFF), Cfg::V_SUB, 1024);
+      auto mma = [&](uint32_t d, uint32_t a, uint64_t bd, uint32_t idesc, uint32_t acc) {
+        if (PAIR) mma_ts_pair(d, a, bd, idesc, acc);
+        else mma_ts(d, a, bd, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) {
+        if (PAIR) tc_commit_pair(bar, 3);
+        else tc_commit(bar);
+      };
       // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in a ring stage
       auto issue_qk = [&](uint32_t d_col, uint64_t kd) {
 #pragma unroll
         for (int s = 0; s < Cfg::NSUB; ++s)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            mma_ts(d_col, q_col + (s * 4 + k) * 8, kd + s * (Cfg::SUBH >> 4) + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
+            mma(d_col, q_col + (s * 4 + k) * 8, kd + s * (Cfg::K_SUB >> 4) + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
       };
-      // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; the second 64 columns
-      // of the head dim live one sub-tile (LBO) further
+      // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; one CTA: the second 64
+      // columns of the head dim live one sub-tile (LBO) further; PAIR: they live in the other CTA
       auto issue_pv = [&](uint32_t d_col, uint32_t p_col, uint64_t vd, bool accumulate) {
 #pragma unroll
         for (int kk = 0; kk < HALF / 16; ++kk)
-          mma_ts(d_col, p_col + kk * 8, vd + kk * (2048 >> 4), idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
-      };
-      auto release = [&](uint64_t* bar) {
-        if (CL > 1) tc_commit_mc(bar, MC_MASK);
-        else tc_commit(bar);
+          mma(d_col, p_col + kk * 8, vd + kk * (2048 >> 4), idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
       };
 
       unsigned long long w_v = 0, w_p = 0, w_k = 0, w_q = 0;
@@ -972,8 +992,8 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       for (int h = 0; h < 3 && h < n_half; ++h) {
         timed_wait(&k_full[h], 0, w_q);
         issue_qk(s_col + h * HALF, kdesc0 + h * KSTEP);
-        tc_commit(&s_full[h]);
-        release(&k_empty[h]);
+        commit(&s_full[h]);
+        commit(&k_empty[h]);
       }
       // A barrier wait costs the tensor pipe ~60 clk when nothing is queued behind it (tools/micro/mma_rate.cu), so
       // the operands of the NEXT step (V_{h+1}, K_{h+4}) are waited for right after this step's MMAs were issued:
@@ -985,13 +1005,13 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       for (int h = 0; h < n_half; ++h) {
         if (P.ts_diag < 3) timed_wait(&p_full[r], rp, w_p);
         tc_fence_after();
-        issue_pv(o_col + (h & 1) * 128, s_col + r * HALF, vdesc0 + vs * KSTEP, h >= 2);
-        tc_commit(&pv_done[h & 1]);
-        release(&v_empty[vs]);
+        issue_pv(o_col + (h & 1) * 128, s_col + r * HALF, vdesc0 + vs * VSTEP, h >= 2);
+        commit(&pv_done[h & 1]);
+        commit(&v_empty[vs]);
         if (h + 3 < n_half) {
           issue_qk(s_col + r * HALF, kdesc0 + ks * KSTEP);
-          tc_commit(&s_full[r]);
-          release(&k_empty[ks]);
+          commit(&s_full[r]);
+          commit(&k_empty[ks]);
         }
         if (++r == 3) r = 0, rp ^= 1;
         if (++vs == NST) vs = 0, vp ^= 1;
@@ -999,7 +1019,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
         if (h + 1 < n_half && P.ts_diag < 4) timed_wait(&v_full[vs], vp, w_v);
         if (h + 4 < n_half && P.ts_diag < 4) timed_wait(&k_full[ks], kp, w_k);
       }
-      tc_commit(o_done);
+      commit(o_done);
       if (P.dbg) {
         atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
         atomicAdd(&P.dbg[1], w_v);
@@ -1041,12 +1061,12 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(q_ready);
+      if (lane == 0) ts_arrive<PAIR>(q_ready);
     }
     float m_ref = -INFINITY;   // reference max (scaled, log2 domain) of this warpgroup's halves
     float l_sum = 0.f;
     const int n_full = P.seq_kv / HALF;      // halves with all 64 keys valid
-    const bool prof = P.dbg != nullptr && (threadIdx.x & 127) == 0 && wg == 0;
+    const bool prof = P.dbg != nullptr && (threadIdx.x & 127) == 0 && wg == 0 && rank == 0;
     unsigned long long w_s = 0;
     const long long t_begin = clock64();
     int region = wg;               // h % 3 and (h / 3) & 1 of this warpgroup's halves h = wg, wg + 2, ...
@@ -1072,17 +1092,17 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[region]);
+        if (lane == 0) ts_arrive<PAIR>(&p_full[region]);
         l_sum = 1.f;
         m_ref = 0.f;
         continue;
       }
       if (h < n_full) {
-        softmax_pipe_half<DH, false, EMU>(s_addr + region * HALF, o_addr, HALF, h >> 1, P.scale_log2, m_ref, l_sum,
-                                          &p_full[region], &pv_done[wg], lane);
+        softmax_pipe_half<DH, false, EMU, PAIR>(s_addr + region * HALF, o_addr, HALF, h >> 1, P.scale_log2, m_ref,
+                                                l_sum, &p_full[region], &pv_done[wg], lane);
       } else {
-        softmax_pipe_half<DH, true, EMU>(s_addr + region * HALF, o_addr, P.seq_kv - h * HALF, h >> 1, P.scale_log2,
-                                         m_ref, l_sum, &p_full[region], &pv_done[wg], lane);
+        softmax_pipe_half<DH, true, EMU, PAIR>(s_addr + region * HALF, o_addr, P.seq_kv - h * HALF, h >> 1,
+                                               P.scale_log2, m_ref, l_sum, &p_full[region], &pv_done[wg], lane);
       }
     }
     if (prof) {
@@ -1161,12 +1181,13 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // no CTA leaves while the pair's MMAs or arrivals may still touch it
+  else __syncthreads();
   if (threadIdx.x == 0) peer_notify_last_cta(P.notify, gridDim.x * gridDim.y * gridDim.z);
-  if (CL > 1) cluster_sync_all();   // no CTA leaves while its peer may still arrive on its barriers
   if (warp == W_MMA) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    if (PAIR) tmem_dealloc_pair<512>(tmem_base);
+    else tmem_dealloc<512>(tmem_base);
   }
 }
 
@@ -1175,7 +1196,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same in clusters of 2 with multicast K/V
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same as CTA pairs (cta_group::2, each CTA stages half of every K/V half; head_dim 128 only)
 extern "C" int qi_attention_set_variant(int v) {
   if (v < -1 || v > 63) return QI_ERR_ARG;
   g_attn_variant = v;
@@ -1205,22 +1226,24 @@ static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream
   return QI_OK;
 }
 
-template <int DH, int EMU, int CL>
+template <int DH, int EMU, bool PAIR>
 static int launch_attention_ts(AttParams P, const void* k, const void* v, int batch, int seq_q, int seq_kv, int heads,
                                long long ld_kv, long long kv_bs, long long kv_hs, cudaStream_t stream) {
-  // K/V maps with 64-key (CL = 1) or 32-key (CL = 2: half of every half-tile per CTA, multicast) boxes
-  const uint32_t box[4] = {64, 1, (uint32_t)(TsCfg<DH>::HALF / CL), 1};
+  using Cfg = TsCfg<DH, PAIR>;
+  // K boxes: the key rows of a half that one CTA stages (64, or 32 per CTA of a pair) x 64 head-dim columns;
+  // V boxes: 64 keys x 64 head-dim columns
+  const uint32_t box_k[4] = {64, 1, (uint32_t)Cfg::K_ROWS, 1};
+  const uint32_t box_v[4] = {64, 1, (uint32_t)Cfg::HALF, 1};
   uint64_t dims[4] = {(uint64_t)DH, (uint64_t)heads, (uint64_t)seq_kv, (uint64_t)batch};
   uint64_t str[3] = {(uint64_t)kv_hs * 2, (uint64_t)ld_kv * 2,
                      (uint64_t)(batch > 1 ? kv_bs : ld_kv * (long long)seq_kv) * 2};
-  if (int rc = qi_encode_tmap_bf16(&P.tmap_k, k, 4, dims, str, box)) return rc;
-  if (int rc = qi_encode_tmap_bf16(&P.tmap_v, v, 4, dims, str, box)) return rc;
-  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_ts_kernel<DH, EMU, CL>), TsCfg<DH>::SMEM_BYTES))
+  if (int rc = qi_encode_tmap_bf16(&P.tmap_k, k, 4, dims, str, box_k)) return rc;
+  if (int rc = qi_encode_tmap_bf16(&P.tmap_v, v, 4, dims, str, box_v)) return rc;
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_ts_kernel<DH, EMU, PAIR>), Cfg::SMEM_BYTES))
     return rc;
   const int tiles = (seq_q + ATT_BM - 1) / ATT_BM;
-  dim3 grid((tiles + CL - 1) / CL * CL, heads, batch);
-  if (qi_launch(attention_ts_kernel<DH, EMU, CL>, grid, dim3(ATT_THREADS), TsCfg<DH>::SMEM_BYTES, stream, P) !=
-      cudaSuccess)
+  dim3 grid((tiles + Cfg::NCTA - 1) / Cfg::NCTA * Cfg::NCTA, heads, batch);
+  if (qi_launch(attention_ts_kernel<DH, EMU, PAIR>, grid, dim3(ATT_THREADS), Cfg::SMEM_BYTES, stream, P) != cudaSuccess)
     return QI_ERR_CUDA;
   return QI_OK;
 }
@@ -1308,10 +1331,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
     case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
-#define QI_TS_CASE(V, EMU, CL) \
-  case V: return launch_attention_ts<DH, EMU, CL>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
-    QI_TS_CASE(40, 0, 1) QI_TS_CASE(42, 2, 1) QI_TS_CASE(43, 3, 1) QI_TS_CASE(44, 4, 1)
-    QI_TS_CASE(56, 0, 2) QI_TS_CASE(58, 2, 2) QI_TS_CASE(59, 3, 2) QI_TS_CASE(60, 4, 2)
+#define QI_TS_CASE(V, EMU, PAIR) \
+  case V: return launch_attention_ts<DH, EMU, PAIR && DH == 128>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
+    QI_TS_CASE(40, 0, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
+    QI_TS_CASE(56, 0, true) QI_TS_CASE(58, 2, true) QI_TS_CASE(59, 3, true) QI_TS_CASE(60, 4, true)
 #undef QI_TS_CASE
     default: return QI_ERR_ARG;
   }
