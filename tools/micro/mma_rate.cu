@@ -123,6 +123,77 @@ static void run_step(int steps, int sms) {
   cudaFree(d);
 }
 
+// The same step issued by the leader of a CTA pair: cta_group::2, M = 256, A from each CTA's TMEM, each CTA's shared
+// memory supplies half of B (32 of the 64 keys for Q*K^T, 64 of the 128 head-dim columns for P*V).
+__device__ __forceinline__ void mma_ts_pair_(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+               "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
+}
+template <int MODE>   // 0: the attention step, 1: Q*K^T only (8 x N=64), 2: P*V only (4 x N=128)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) pair_step_kernel(int steps, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  __shared__ uint64_t done;
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (32768 + 65536) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) {
+    mbar_init(&done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc_pair<512>(&slot);
+  fence_proxy_async();
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  if (cluster_ctarank() == 0 && warp == 1 && elect_one()) {
+    constexpr uint32_t idesc_qk = make_idesc_bf16(256, 64, 0, 0);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(256, 128, 0, 1);
+    const uint32_t b_addr = smem_u32(smem + 32768);
+    const long long t0 = clock64();
+    for (int h = 0; h < steps; ++h) {
+      if (MODE != 1) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t db = make_smem_desc(b_addr + kk * 2048, 8192, 1024);
+          mma_ts_pair_(tm + 256 + (h & 1) * 128, tm + 64 + (h % 3) * 64 + kk * 8, db, idesc_pv, 1u);
+        }
+      }
+      if (MODE != 2) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const uint64_t db = make_smem_desc(b_addr + 16384 + s * 4096, 0, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_ts_pair_(tm + 64 + (h % 3) * 64, tm + (s * 4 + k) * 8, db + 2 * k, idesc_qk, (s | k) ? 1u : 0u);
+        }
+      }
+    }
+    tc_commit_pair(&done, 1);
+    mbar_wait(&done, 0);
+    out[blockIdx.x >> 1] = clock64() - t0;
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 0) tmem_dealloc_pair<512>(tm);
+}
+template <int MODE>
+static void run_pair(const char* what, int steps, int sms) {
+  long long* d;
+  cudaMalloc(&d, sms * sizeof(long long));
+  const int smem = 32768 + 65536 + 1024;
+  cudaFuncSetAttribute(pair_step_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  pair_step_kernel<MODE><<<sms / 2 * 2, 128, smem>>>(steps, d);
+  pair_step_kernel<MODE><<<sms / 2 * 2, 128, smem>>>(steps, d);
+  cudaError_t e = cudaDeviceSynchronize();
+  long long h[256];
+  cudaMemcpy(h, d, (sms / 2) * sizeof(long long), cudaMemcpyDeviceToHost);
+  long long mx = 0;
+  for (int i = 0; i < sms / 2; ++i) mx = h[i] > mx ? h[i] : mx;
+  printf("CTA pair (cta_group::2, M=256, TS), %s: %7.1f clk per step [%s]\n", what, (double)mx / steps, cudaGetErrorString(e));
+  cudaFree(d);
+}
+
 template <int N, bool TS>
 static void run(const char* name, int groups, int sms) {
   long long* d;
@@ -159,5 +230,8 @@ int main() {
   run_step<2, 0>(2000, sms);
   run_step<4, 0>(2000, sms);
   run_step<4, 1>(2000, sms);
+  run_pair<0>("4 x N=128 + 8 x N=64 (512 clk at the single-CTA rate)", 2000, sms);
+  run_pair<1>("8 x N=64 (256 clk)", 2000, sms);
+  run_pair<2>("4 x N=128 (256 clk)", 2000, sms);
   return 0;
 }
