@@ -23,7 +23,7 @@ g = torch.Generator(device="cuda").manual_seed(0)
 qkv = torch.randn(B, S, 3 * d, device="cuda", generator=g).bfloat16()
 q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
 o = torch.empty(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
-buf = torch.zeros(16, device="cuda", dtype=torch.int64)
+buf = torch.zeros(16 + 8 * 96, device="cuda", dtype=torch.int64)
 for var in [int(x) for x in os.environ.get("QI_DIAG_VARIANTS", "43,59").split(",")]:
     ops.attention_set_variant(var)
     for _ in range(3):
@@ -47,4 +47,11 @@ for var in [int(x) for x in os.environ.get("QI_DIAG_VARIANTS", "43,59").split(",
     print(f"diag {sys.argv[1]} variant {var}: {us:7.1f} us  | per half-step: mma total {c[0] / n_cta / n_half:6.0f} clk, "
           f"wait v {c[1] / n_cta / n_half:5.0f}, wait p {c[3] / n_cta / n_half:5.0f}, wait k {c[4] / n_cta / n_half:5.0f}, "
           f"first {c[5] / n_cta:6.0f} per CTA | softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA", flush=True)
+    if os.environ.get("QI_DIAG_TRACE", "1") == "1":
+        t = [c[16 + 8 * h:16 + 8 * h + 8] for h in range(min(n_half, 96))]
+        t0 = min(x for row in t for x in row if x > 0)
+        print("    timeline of CTA (0,0,0), clk since the first event: half | K tma issued, V tma issued | mma: K ready, V ready, "
+              "P ready, step issued | softmax: S ready, P published")
+        for h in list(range(0, 20)) + list(range(40, 52)):
+            print(f"    {h:3d} | " + " ".join(f"{(x - t0) if x > 0 else -1:7d}" for x in t[h]))
 ops.attention_set_variant(-1)

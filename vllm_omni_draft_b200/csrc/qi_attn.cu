@@ -718,7 +718,8 @@ struct TsCfg {
   static constexpr int K_STAGE = K_SUB * NSUB;
   static constexpr int V_SUB = HALF * 128;                     // [64 keys x 64 head-dim columns]
   static constexpr int V_STAGE = V_SUB * (PAIR ? 1 : NSUB);    // PAIR: one CTA holds DH/2 = 64 columns of V
-  static constexpr int NST = PAIR ? 10 : 6;                    // ring depth in halves, K and V each
+  static constexpr int NST = 6;                                // ring depth in halves, K and V each (the MMA thread's
+                                                               // loop is unrolled over lcm(3 regions, 2 warpgroups, NST) = 6 steps)
   static constexpr int K_OFF = 0;
   static constexpr int V_OFF = NST * K_STAGE;
   static constexpr int BAR_OFF = V_OFF + NST * V_STAGE;
@@ -842,6 +843,11 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
   if (lane == 0) ts_arrive<PAIR>(p_full);
 }
 
+// tuning aid: timeline of CTA (0,0,0) — dbg[16 + 8*h + i] = clock64 at event i of half h (see tools/attn_ts_diag.py)
+__device__ __forceinline__ void ts_trace(unsigned long long* dbg, bool on, int h, int i) {
+  if (on && h < 96) dbg[16 + 8 * h + i] = clock64();
+}
+
 template <int DH, int EMU, bool PAIR>
 __global__ void __cluster_dims__(PAIR ? 2 : 1, 1, 1) __launch_bounds__(ATT_THREADS, 1)
 attention_ts_kernel(const __grid_constant__ AttParams P) {
@@ -870,6 +876,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
   const int b = blockIdx.z;
   const int n_half = (P.seq_kv + HALF - 1) / HALF;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0;
+  const bool trace = P.dbg != nullptr && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
   pdl_launch_dependents();
 
   if (warp == W_K && lane == 0) {
@@ -918,6 +925,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       for (int h = 0; h < n_half; ++h, ++st) {
         if (st == NST) st = 0, ph ^= 1;
         pipe_wait(&empty[st], ph ^ 1);
+        ts_trace(P.dbg, trace, h, is_k ? 0 : 1);
         uint8_t* dst = ring + st * stage_bytes;
         if (PAIR) {
           // this CTA's half of the half: 32 of the 64 keys of K, 64 of the 128 head-dim columns of V; the bytes of
@@ -991,33 +999,49 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       tc_fence_after();
       for (int h = 0; h < 3 && h < n_half; ++h) {
         timed_wait(&k_full[h], 0, w_q);
+        ts_trace(P.dbg, trace, h, 2);
         issue_qk(s_col + h * HALF, kdesc0 + h * KSTEP);
         commit(&s_full[h]);
         commit(&k_empty[h]);
       }
-      // A barrier wait costs the tensor pipe ~60 clk when nothing is queued behind it (tools/micro/mma_rate.cu), so
-      // the operands of the NEXT step (V_{h+1}, K_{h+4}) are waited for right after this step's MMAs were issued:
-      // only the wait for P_h is left in front of an MMA.
-      int r = 0, vs = 0, ks = 3;              // region of half h, V stage of half h, K stage of half h + 3 (NST > 3)
-      uint32_t rp = 0, vp = 0, kp = 0;        // and the parities of their barriers
+      // The loop below is what bounds the kernel if written naively: one thread issues 12 MMAs per 512 clk of tensor
+      // work, and ~290 scalar instructions per step (descriptor arithmetic, R2UR moves, barrier addressing) took
+      // 1 200 clk (ncu source page: the tensor pipe was 33 % active while this thread never found a barrier closed).
+      // It is therefore unrolled over 6 steps = lcm(3 S regions, 2 O accumulators, 6 ring stages): every TMEM column,
+      // descriptor and barrier is then a base plus a compile-time constant.  The operands of the NEXT step (V_{h+1},
+      // K_{h+4}) are waited for right after this step's MMAs were issued, so only the wait for P_h sits in front of
+      // an MMA with nothing queued behind it.
       if (P.ts_diag < 4) timed_wait(&v_full[0], 0, w_v);
+      ts_trace(P.dbg, trace, 0, 3);
       if (3 < n_half && P.ts_diag < 4) timed_wait(&k_full[3], 0, w_k);
-      for (int h = 0; h < n_half; ++h) {
-        if (P.ts_diag < 3) timed_wait(&p_full[r], rp, w_p);
-        tc_fence_after();
-        issue_pv(o_col + (h & 1) * 128, s_col + r * HALF, vdesc0 + vs * VSTEP, h >= 2);
-        commit(&pv_done[h & 1]);
-        commit(&v_empty[vs]);
-        if (h + 3 < n_half) {
-          issue_qk(s_col + r * HALF, kdesc0 + ks * KSTEP);
-          commit(&s_full[r]);
-          commit(&k_empty[ks]);
+      ts_trace(P.dbg, trace, 3, 2);
+      static_assert(NST == 6, "unrolled over 6 steps");
+      uint32_t bp = 0;                        // parity of the ring barriers for the 6 halves of this pass
+      for (int h0 = 0; h0 < n_half; h0 += 6, bp ^= 1) {
+#pragma unroll
+        for (int u = 0; u < 6; ++u) {
+          const int h = h0 + u;
+          if (h >= n_half) break;
+          const int r = u % 3;                               // S region of half h
+          const uint32_t rp = (u / 3) & 1;                   // h0 / 3 is even
+          const int ks = (u + 3) % 6;                        // K stage of half h + 3
+          if (P.ts_diag < 3) timed_wait(&p_full[r], rp, w_p);
+          ts_trace(P.dbg, trace, h, 4);
+          tc_fence_after();
+          issue_pv(o_col + (u & 1) * 128, s_col + r * HALF, vdesc0 + u * VSTEP, h >= 2);
+          commit(&pv_done[u & 1]);
+          commit(&v_empty[u]);
+          if (h + 3 < n_half) {
+            issue_qk(s_col + r * HALF, kdesc0 + ks * KSTEP);
+            commit(&s_full[r]);
+            commit(&k_empty[ks]);
+          }
+          ts_trace(P.dbg, trace, h, 5);
+          if (h + 1 < n_half && P.ts_diag < 4) timed_wait(&v_full[(u + 1) % 6], bp ^ (u + 1 >= 6 ? 1u : 0u), w_v);
+          ts_trace(P.dbg, trace, h + 1, 3);
+          if (h + 4 < n_half && P.ts_diag < 4) timed_wait(&k_full[(u + 4) % 6], bp ^ (u + 4 >= 6 ? 1u : 0u), w_k);
+          ts_trace(P.dbg, trace, h + 4, 2);
         }
-        if (++r == 3) r = 0, rp ^= 1;
-        if (++vs == NST) vs = 0, vp ^= 1;
-        if (++ks == NST) ks = 0, kp ^= 1;
-        if (h + 1 < n_half && P.ts_diag < 4) timed_wait(&v_full[vs], vp, w_v);
-        if (h + 4 < n_half && P.ts_diag < 4) timed_wait(&k_full[ks], kp, w_k);
       }
       commit(o_done);
       if (P.dbg) {
@@ -1076,6 +1100,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       const long long c0 = prof ? clock64() : 0;
       pipe_wait(&s_full[region], rpar);
       if (prof) w_s += clock64() - c0;
+      ts_trace(P.dbg, trace && (threadIdx.x & 127) == 0, h, 6);
       tc_fence_after();
       if (P.ts_diag) {   // timing experiments only: the result is garbage
         if (P.ts_diag == 2) {
@@ -1104,6 +1129,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
         softmax_pipe_half<DH, true, EMU, PAIR>(s_addr + region * HALF, o_addr, P.seq_kv - h * HALF, h >> 1,
                                                P.scale_log2, m_ref, l_sum, &p_full[region], &pv_done[wg], lane);
       }
+      ts_trace(P.dbg, trace && (threadIdx.x & 127) == 0, h, 7);
     }
     if (prof) {
       atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
