@@ -728,7 +728,7 @@ struct TsCfg {
   static constexpr int Q_COL = 0, S_COL = 64, O_COL = 256;
   static_assert(!PAIR || DH == 128, "the pair kernel splits V by 64-column sub-tiles");
   static_assert(NST * K_STAGE >= ATT_BM * DH * 2, "the epilogue stages O through the K ring");
-  static_assert((4 * NST + 11) * 8 <= 512, "barrier block");
+  static_assert((4 * NST + 14) * 8 + 8 <= 512, "barrier block");
 };
 
 // D[tmem of both CTAs] (+)= A[tmem, 128 rows per CTA] * B[smem, N/2 rows per CTA]; leader CTA only
@@ -852,7 +852,7 @@ template <int DH, int EMU, bool PAIR>
 __global__ void __cluster_dims__(PAIR ? 2 : 1, 1, 1) __launch_bounds__(ATT_THREADS, 1)
 attention_ts_kernel(const __grid_constant__ AttParams P) {
   using Cfg = TsCfg<DH, PAIR>;
-  constexpr int W_K = 8, W_MMA = 9, W_V = 10;   // warps of the third warpgroup: K loader, MMA issuer, V loader
+  constexpr int W_K = 8, W_MMA = 9, W_V = 10, W_QK = 11;   // third warpgroup: K loader, P*V issuer (TMEM owner), V loader, Q*K^T issuer
   constexpr int HALF = Cfg::HALF, NST = Cfg::NST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -867,7 +867,8 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
   uint64_t* pv_done = p_full + 3;           // [2 warpgroups], one phase per P*V into that warpgroup's O
   uint64_t* o_done = pv_done + 2;
   uint64_t* q_ready = o_done + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+  uint64_t* r_free = q_ready + 1;           // [3 regions]  P*V of the half that occupied the region has completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(r_free + 3);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -891,6 +892,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
     for (int i = 0; i < 3; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4 * Cfg::NCTA);
+      mbar_init(&r_free[i], 1);
     }
     mbar_init(&pv_done[0], 1);
     mbar_init(&pv_done[1], 1);
@@ -946,20 +948,19 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else if (warp == W_MMA) {
-    // ------------------------------------------------------------------ MMA issuer (PAIR: the leader CTA's only)
+  } else if (warp == W_MMA || warp == W_QK) {
+    // ------------------------------------------------------------------ MMA issuers (PAIR: the leader CTA's only)
+    // One thread could not issue a step's 12 MMAs, 4 commits and 3 barrier waits in the 512 clk the tensor pipe
+    // needs for them: its scalar instruction stream ran at 10-15 clk per instruction (ncu source page, in-kernel
+    // timeline: 1 200-1 450 clk per step with the tensor pipe 33 % active and every barrier already open).  So P*V
+    // and Q*K^T are issued by two threads in two warps (two SM sub-partitions).  They are ordered through barriers
+    // only: Q*K_{h+3}^T, which overwrites the region of P_h, waits for `r_free` (committed behind P_h*V_h).  Both
+    // loops are unrolled over 6 steps = lcm(3 S regions, 2 O accumulators, 6 ring stages), so that every TMEM
+    // column, descriptor and barrier is a base plus a compile-time constant.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    static_assert(NST == 6, "unrolled over 6 steps");
     if (rank == 0 && elect_one()) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM * Cfg::NCTA, HALF, 0, 0);
-      constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM * Cfg::NCTA, DH, 0, 1);   // B (=V) is MN-major
-      const uint32_t q_col = tmem_base + Cfg::Q_COL;
       const uint32_t s_col = tmem_base + Cfg::S_COL;
-      const uint32_t o_col = tmem_base + Cfg::O_COL;
-      // Descriptors of ring stage st = those of stage 0 + st * (stage bytes >> 4) in the 14-bit address field
-      // (shared-memory addresses are below 256 KB, so the field cannot carry).
-      constexpr uint32_t KSTEP = Cfg::K_STAGE >> 4, VSTEP = Cfg::V_STAGE >> 4;
-      const uint64_t kdesc0 = make_smem_desc(smem_u32(smem + Cfg::K_OFF), 0, 1024);
-      const uint64_t vdesc0 = make_smem_desc(smem_u32(smem + Cfg::V_OFF), Cfg::V_SUB, 1024);
       auto mma = [&](uint32_t d, uint32_t a, uint64_t bd, uint32_t idesc, uint32_t acc) {
         if (PAIR) mma_ts_pair(d, a, bd, idesc, acc);
         else mma_ts(d, a, bd, idesc, acc);
@@ -968,93 +969,74 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
         if (PAIR) tc_commit_pair(bar, 3);
         else tc_commit(bar);
       };
-      // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in a ring stage
-      auto issue_qk = [&](uint32_t d_col, uint64_t kd) {
-#pragma unroll
-        for (int s = 0; s < Cfg::NSUB; ++s)
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            mma(d_col, q_col + (s * 4 + k) * 8, kd + s * (Cfg::K_SUB >> 4) + 2 * k, idesc_qk, (s | k) != 0 ? 1u : 0u);
-      };
-      // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; one CTA: the second 64
-      // columns of the head dim live one sub-tile (LBO) further; PAIR: they live in the other CTA
-      auto issue_pv = [&](uint32_t d_col, uint32_t p_col, uint64_t vd, bool accumulate) {
-#pragma unroll
-        for (int kk = 0; kk < HALF / 16; ++kk)
-          mma(d_col, p_col + kk * 8, vd + kk * (2048 >> 4), idesc_pv, (accumulate || kk != 0) ? 1u : 0u);
-      };
-
-      unsigned long long w_v = 0, w_p = 0, w_k = 0, w_q = 0;
+      // Descriptors of ring stage st = those of stage 0 + st * (stage bytes >> 4) in the 14-bit address field
+      // (shared-memory addresses are below 256 KB, so the field cannot carry).
       const long long t_begin = clock64();
-      auto timed_wait = [&](uint64_t* bar, uint32_t parity, unsigned long long& acc) {
-        if (P.dbg) {
-          const long long c0 = clock64();
-          pipe_wait(bar, parity);
-          acc += clock64() - c0;
-        } else {
-          pipe_wait(bar, parity);
-        }
-      };
-      timed_wait(q_ready, 0, w_q);
-      tc_fence_after();
-      for (int h = 0; h < 3 && h < n_half; ++h) {
-        timed_wait(&k_full[h], 0, w_q);
-        ts_trace(P.dbg, trace, h, 2);
-        issue_qk(s_col + h * HALF, kdesc0 + h * KSTEP);
-        commit(&s_full[h]);
-        commit(&k_empty[h]);
-      }
-      // The loop below is what bounds the kernel if written naively: one thread issues 12 MMAs per 512 clk of tensor
-      // work, and ~290 scalar instructions per step (descriptor arithmetic, R2UR moves, barrier addressing) took
-      // 1 200 clk (ncu source page: the tensor pipe was 33 % active while this thread never found a barrier closed).
-      // It is therefore unrolled over 6 steps = lcm(3 S regions, 2 O accumulators, 6 ring stages): every TMEM column,
-      // descriptor and barrier is then a base plus a compile-time constant.  The operands of the NEXT step (V_{h+1},
-      // K_{h+4}) are waited for right after this step's MMAs were issued, so only the wait for P_h sits in front of
-      // an MMA with nothing queued behind it.
-      if (P.ts_diag < 4) timed_wait(&v_full[0], 0, w_v);
-      ts_trace(P.dbg, trace, 0, 3);
-      if (3 < n_half && P.ts_diag < 4) timed_wait(&k_full[3], 0, w_k);
-      ts_trace(P.dbg, trace, 3, 2);
-      static_assert(NST == 6, "unrolled over 6 steps");
-      uint32_t bp = 0;                        // parity of the ring barriers for the 6 halves of this pass
-      for (int h0 = 0; h0 < n_half; h0 += 6, bp ^= 1) {
+      if (warp == W_QK) {
+        // S[region] = Q * K_h^T : A = Q from TMEM (8 packed columns per 16 dims), B = the K half in a ring stage
+        constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM * Cfg::NCTA, HALF, 0, 0);
+        constexpr uint32_t KSTEP = Cfg::K_STAGE >> 4;
+        const uint32_t q_col = tmem_base + Cfg::Q_COL;
+        const uint64_t kdesc0 = make_smem_desc(smem_u32(smem + Cfg::K_OFF), 0, 1024);
+        mbar_wait(q_ready, 0);
+        tc_fence_after();
+        uint32_t bp = 0;                      // parity of the ring barriers during this pass over the 6 stages
+        for (int h0 = 0; h0 < n_half; h0 += 6, bp ^= 1) {
 #pragma unroll
-        for (int u = 0; u < 6; ++u) {
-          const int h = h0 + u;
-          if (h >= n_half) break;
-          const int r = u % 3;                               // S region of half h
-          const uint32_t rp = (u / 3) & 1;                   // h0 / 3 is even
-          const int ks = (u + 3) % 6;                        // K stage of half h + 3
-          if (P.ts_diag < 3) timed_wait(&p_full[r], rp, w_p);
-          ts_trace(P.dbg, trace, h, 4);
-          tc_fence_after();
-          issue_pv(o_col + (u & 1) * 128, s_col + r * HALF, vdesc0 + u * VSTEP, h >= 2);
-          commit(&pv_done[u & 1]);
-          commit(&v_empty[u]);
-          if (h + 3 < n_half) {
-            issue_qk(s_col + r * HALF, kdesc0 + ks * KSTEP);
+          for (int u = 0; u < 6; ++u) {
+            const int h = h0 + u;
+            if (h >= n_half) break;
+            const int r = u % 3;
+            // the region's previous tenant is half h - 3: its P*V is use number (h - 3) / 3 of r_free[r]
+            if (h >= 3) mbar_wait(&r_free[r], u >= 3 ? 0u : 1u);   // ((h - 3) / 3) & 1 with h0 / 3 even
+            mbar_wait(&k_full[u], bp);
+            tc_fence_after();
+            ts_trace(P.dbg, trace, h, 2);
+            const uint64_t kd = kdesc0 + u * KSTEP;
+#pragma unroll
+            for (int s = 0; s < Cfg::NSUB; ++s)
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                mma(s_col + r * HALF, q_col + (s * 4 + k) * 8, kd + s * (Cfg::K_SUB >> 4) + 2 * k, idesc_qk,
+                    (s | k) != 0 ? 1u : 0u);
             commit(&s_full[r]);
-            commit(&k_empty[ks]);
+            commit(&k_empty[u]);
           }
-          ts_trace(P.dbg, trace, h, 5);
-          if (h + 1 < n_half && P.ts_diag < 4) timed_wait(&v_full[(u + 1) % 6], bp ^ (u + 1 >= 6 ? 1u : 0u), w_v);
-          ts_trace(P.dbg, trace, h + 1, 3);
-          if (h + 4 < n_half && P.ts_diag < 4) timed_wait(&k_full[(u + 4) % 6], bp ^ (u + 4 >= 6 ? 1u : 0u), w_k);
-          ts_trace(P.dbg, trace, h + 4, 2);
         }
-      }
-      commit(o_done);
-      if (P.dbg) {
-        atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
-        atomicAdd(&P.dbg[1], w_v);
-        atomicAdd(&P.dbg[3], w_p);
-        atomicAdd(&P.dbg[4], w_k);
-        atomicAdd(&P.dbg[5], w_q);
+      } else {
+        // O[wg] += P[region] * V_h : 16 keys per MMA = 8 packed columns of P and 2048 B of V; one CTA: the second 64
+        // columns of the head dim live one sub-tile (LBO) further; PAIR: they live in the other CTA
+        constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM * Cfg::NCTA, DH, 0, 1);   // B (=V) is MN-major
+        constexpr uint32_t VSTEP = Cfg::V_STAGE >> 4;
+        const uint32_t o_col = tmem_base + Cfg::O_COL;
+        const uint64_t vdesc0 = make_smem_desc(smem_u32(smem + Cfg::V_OFF), Cfg::V_SUB, 1024);
+        uint32_t bp = 0;
+        for (int h0 = 0; h0 < n_half; h0 += 6, bp ^= 1) {
+#pragma unroll
+          for (int u = 0; u < 6; ++u) {
+            const int h = h0 + u;
+            if (h >= n_half) break;
+            const int r = u % 3;
+            mbar_wait(&v_full[u], bp);
+            if (P.ts_diag < 3) mbar_wait(&p_full[r], (u / 3) & 1);   // (h / 3) & 1 with h0 / 3 even
+            tc_fence_after();
+            ts_trace(P.dbg, trace, h, 4);
+            const uint64_t vd = vdesc0 + u * VSTEP;
+#pragma unroll
+            for (int kk = 0; kk < HALF / 16; ++kk)
+              mma(o_col + (u & 1) * 128, s_col + r * HALF + kk * 8, vd + kk * (2048 >> 4), idesc_pv,
+                  (h >= 2 || kk != 0) ? 1u : 0u);
+            commit(&pv_done[u & 1]);
+            commit(&v_empty[u]);
+            commit(&r_free[r]);
+            ts_trace(P.dbg, trace, h, 5);
+          }
+        }
+        commit(o_done);
+        if (P.dbg) atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
       }
     }
     __syncwarp();
-  } else if (warp > W_V) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   } else {
     // ------------------------------------------------------------------ softmax warpgroups: wg 0 even halves, wg 1 odd
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
