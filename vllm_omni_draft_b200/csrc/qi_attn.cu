@@ -59,7 +59,6 @@ struct AttParams {
   int seq_q, seq_kv, heads;
   float scale_log2;
   int split_p;   // softmax publishes P in two 64-key halves (p_half, then p_full)
-  int split_mma; // the two Q tiles' MMAs are issued by two threads in two warps (env QI_ATTN_SPLIT_MMA, default 1)
   // Ulysses scatter epilogue (n_peer > 0): query row r owned by rank p goes to
   // o_peer[p] + o_chunk_off + b*o_bs + (r - o_prefix[p])*ld_o + head*o_hs   (peer-mapped HBM)
   int n_peer;
@@ -349,12 +348,11 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     tma_prefetch_desc(&P.tmap_k);
     tma_prefetch_desc(&P.tmap_v);
     mbar_init(q_full, 1);
-    const uint32_t n_issuers = P.split_mma ? 2 : 1;   // each MMA-issuing thread releases a K/V stage once
     for (int i = 0; i < 2; ++i) {
       mbar_init(&k_full[i], 1);
-      mbar_init(&k_empty[i], n_issuers);
+      mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
-      mbar_init(&v_empty[i], n_issuers);
+      mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&p_half[i], 4);
@@ -398,17 +396,11 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       }
     }
     __syncwarp();
-  } else if (warp == W_MMA || warp == W_MMA + 2) {
-    // ------------------------------------------------------------------ MMA issuers
-    // split_mma: one thread per Q tile, in two warps (two SM sub-partitions).  A single issuing thread runs its
-    // scalar instruction stream at 10-15 clk per instruction (in-kernel timeline of the TS kernel below), which both
-    // stretches every P -> P*V and P*V -> Q*K^T hand-off and blocks one tile's ready work behind the other tile's
-    // wait.  The two tiles share nothing but the K/V ring, whose stages are released by both threads.
+  } else if (warp == W_MMA) {
+    // ------------------------------------------------------------------ MMA issuer
     if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    const int t_lo = P.split_mma ? (warp == W_MMA ? 0 : 1) : 0;
-    const int t_hi = P.split_mma ? t_lo + 1 : 2;
-    if ((warp == W_MMA || P.split_mma) && elect_one()) {   // elect.sync: ptxas knows a single thread issues
+    if (elect_one()) {   // elect.sync: ptxas knows a single thread issues (no per-instruction elect loops)
       constexpr uint32_t idesc_qk = make_idesc_bf16(ATT_BM, ATT_BN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(ATT_BM, DH, 0, 1);   // B (=V) is MN-major
       const uint32_t s_col[2] = {tmem_base + Cfg::S_COL0, tmem_base + Cfg::S_COL1};
@@ -452,10 +444,10 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       timed_wait(q_full, 0, w_q);
       timed_wait(&k_full[0], 0, w_q);
       tc_fence_after();
-      for (int t = t_lo; t < t_hi; ++t) {
-        issue_qk(t, 0);
-        tc_commit(&s_full[t]);
-      }
+      issue_qk(0, 0);
+      tc_commit(&s_full[0]);
+      issue_qk(1, 0);
+      tc_commit(&s_full[1]);
       tc_commit(&k_empty[0]);
       for (int j = 0; j < n_kv; ++j) {
         const int st = j & 1;
@@ -464,7 +456,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         const int stn = (j + 1) & 1;
         const uint32_t phn = ((j + 1) >> 1) & 1;
         timed_wait(&v_full[st], ph, w_v);
-        for (int t = t_lo; t < t_hi; ++t) {
+        for (int t = 0; t < 2; ++t) {
           if (SPLIT) {
             timed_wait(&p_half[t], j & 1, w_ph);
             tc_fence_after();
@@ -477,15 +469,15 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
             tc_fence_after();
             issue_pv(t, st, j > 0, 0, ATT_BN / 16);
           }
-          if (t == t_hi - 1) tc_commit(&v_empty[st]);
+          if (t == 1) tc_commit(&v_empty[st]);
           if (has_next) {
-            if (t == t_lo) {
+            if (t == 0) {
               timed_wait(&k_full[stn], phn, w_k);
               tc_fence_after();
             }
             issue_qk(t, stn);
             tc_commit(&s_full[t]);
-            if (t == t_hi - 1) tc_commit(&k_empty[stn]);
+            if (t == 1) tc_commit(&k_empty[stn]);
           } else {
             tc_commit(&o_done[t]);
           }
@@ -1330,13 +1322,6 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   int variant = attn_variant();
   if (variant >= 40 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
   P.split_p = (variant >> 3) & 1;
-  {
-    static const int split_mma = [] {
-      const char* e = getenv("QI_ATTN_SPLIT_MMA");
-      return e ? atoi(e) : 1;
-    }();
-    P.split_mma = split_mma;
-  }
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
   switch (variant) {
     case 0: return launch_attention_v<DH, 0, false>(P, grid, stream);
