@@ -1341,7 +1341,8 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
 #define QI_TS_CASE(V, EMU, PAIR) \
   case V: return launch_attention_ts<DH, EMU, PAIR && DH == 128>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
-    QI_TS_CASE(40, 0, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
+    QI_TS_CASE(40, 0, false) QI_TS_CASE(41, 1, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
+    QI_TS_CASE(49, 16 + 1, false) QI_TS_CASE(50, 16 + 2, false) QI_TS_CASE(51, 16 + 3, false) QI_TS_CASE(52, 16 + 4, false)
     QI_TS_CASE(56, 0, true) QI_TS_CASE(58, 2, true) QI_TS_CASE(59, 3, true) QI_TS_CASE(60, 4, true)
 #undef QI_TS_CASE
     default: return QI_ERR_ARG;
