@@ -46,7 +46,9 @@ for var in [int(x) for x in os.environ.get("QI_DIAG_VARIANTS", "43,59").split(",
     n_half = (S + 63) // 64
     print(f"diag {sys.argv[1]} variant {var}: {us:7.1f} us  | per half-step: mma total {c[0] / n_cta / n_half:6.0f} clk, "
           f"wait v {c[1] / n_cta / n_half:5.0f}, wait p {c[3] / n_cta / n_half:5.0f}, wait k {c[4] / n_cta / n_half:5.0f}, "
-          f"first {c[5] / n_cta:6.0f} per CTA | softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA", flush=True)
+          f"first {c[5] / n_cta:6.0f} per CTA | softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA; per own half: "
+          f"S load {c[11] / n_cta / (n_half / 2):5.0f}, max {c[12] / n_cta / (n_half / 2):5.0f}, rescale {c[13] / n_cta / (n_half / 2):5.0f}, "
+          f"P {c[14] / n_cta / (n_half / 2):5.0f}, publish {c[15] / n_cta / (n_half / 2):5.0f}", flush=True)
     if os.environ.get("QI_DIAG_TRACE", "1") == "1":
         t = [c[16 + 8 * h:16 + 8 * h + 8] for h in range(min(n_half, 96))]
         t0 = min(x for row in t for x in row if x > 0)

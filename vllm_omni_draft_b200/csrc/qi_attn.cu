@@ -765,11 +765,20 @@ __device__ __forceinline__ void ts_arrive(uint64_t* bar) {
 template <int DH, bool MASK, int EMU, bool PAIR>
 __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_addr, int kv_valid, int h,
                                                   float scale_log2, float& m_ref, float& l_sum, uint64_t* p_full,
-                                                  uint64_t* pv_done, int lane) {
+                                                  uint64_t* pv_done, int lane, unsigned long long* pc = nullptr) {
   uint32_t r[2][32];
+  long long c_prev = pc ? clock64() : 0;
+  auto phase = [&](int i) {   // tuning aid: cycles per phase (one thread of the CTA)
+    if (pc) {
+      const long long now = clock64();
+      pc[i] += now - c_prev;
+      c_prev = now;
+    }
+  };
   tmem_ld32(s_addr, r[0]);
   tmem_ld32(s_addr + 32, r[1]);
   tmem_ld_wait();
+  phase(0);
   if (MASK) {
 #pragma unroll
     for (int c = 0; c < 2; ++c)
@@ -789,6 +798,7 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
                          fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
   const float m_new = fmaxf(m_ref, mx * scale_log2);
   const bool need = (m_new - m_ref) > 8.0f;   // also true on the first half (m_ref = -inf)
+  phase(1);
   if (__any_sync(0xffffffffu, need)) {
     const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on half 0
     if (need) {
@@ -809,6 +819,7 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
       }
     }
   }
+  phase(2);
   constexpr int NE = EMU & 15;
   constexpr int DEG = (EMU & 16) ? 2 : 3;
   const float2 sc2 = make_float2(scale_log2, scale_log2);
@@ -837,10 +848,12 @@ __device__ __forceinline__ void softmax_pipe_half(uint32_t s_addr, uint32_t o_ad
   }
   const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
   l_sum += (a01.x + a01.y) + (a23.x + a23.y);
+  phase(3);
   tmem_st_wait();
   tc_fence_before();
   __syncwarp();
   if (lane == 0) ts_arrive<PAIR>(p_full);
+  phase(4);
 }
 
 // tuning aid: timeline of CTA (0,0,0) — dbg[16 + 8*h + i] = clock64 at event i of half h (see tools/attn_ts_diag.py)
@@ -1074,6 +1087,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
     const int n_full = P.seq_kv / HALF;      // halves with all 64 keys valid
     const bool prof = P.dbg != nullptr && (threadIdx.x & 127) == 0 && wg == 0 && rank == 0;
     unsigned long long w_s = 0;
+    unsigned long long pcs[5] = {0, 0, 0, 0, 0};   // S load, row max, O rescale, P (exp2 + pack + store), publish
     const long long t_begin = clock64();
     int region = wg;               // h % 3 and (h / 3) & 1 of this warpgroup's halves h = wg, wg + 2, ...
     uint32_t rpar = 0;
@@ -1106,7 +1120,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
       }
       if (h < n_full) {
         softmax_pipe_half<DH, false, EMU, PAIR>(s_addr + region * HALF, o_addr, HALF, h >> 1, P.scale_log2, m_ref,
-                                                l_sum, &p_full[region], &pv_done[wg], lane);
+                                                l_sum, &p_full[region], &pv_done[wg], lane, prof ? pcs : nullptr);
       } else {
         softmax_pipe_half<DH, true, EMU, PAIR>(s_addr + region * HALF, o_addr, P.seq_kv - h * HALF, h >> 1,
                                                P.scale_log2, m_ref, l_sum, &p_full[region], &pv_done[wg], lane);
@@ -1116,6 +1130,7 @@ attention_ts_kernel(const __grid_constant__ AttParams P) {
     if (prof) {
       atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
       atomicAdd(&P.dbg[9], w_s);
+      for (int i = 0; i < 5; ++i) atomicAdd(&P.dbg[11 + i], pcs[i]);
     }
     // merge the two warpgroups' partial softmaxes: O = (O_a*2^(m_a-m) + O_b*2^(m_b-m)) / (l_a*2^(m_a-m) + l_b*2^(m_b-m))
     float* xch = reinterpret_cast<float*>(smem + Cfg::XCH_OFF);
