@@ -21,6 +21,7 @@
 #include "qi_common.cuh"
 #include "../../include/qi_b200.h"
 #include <cstdlib>
+#include <type_traits>
 
 #ifndef QI_ATTN_DEFAULT_VARIANT
 #define QI_ATTN_DEFAULT_VARIANT 11   // EMU = 3 of 8 pairs on the FMA pipe, split P
@@ -430,67 +431,83 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
         }
       };
 
-      unsigned long long w_v = 0, w_ph = 0, w_pf = 0, w_k = 0, w_q = 0;
-      const long long t_begin = clock64();
-      auto timed_wait = [&](uint64_t* bar, uint32_t parity, unsigned long long& acc) {
-        if (P.dbg) {
-          const long long c0 = clock64();
-          mbar_wait(bar, parity);
-          acc += clock64() - c0;
-        } else {
-          mbar_wait(bar, parity);
+      // The hand-offs P ready -> P*V issued and P*V issued -> next Q*K^T issued sit on each Q tile's dependency chain,
+      // and this single thread executes ~10-15 clk per scalar instruction: with the K/V stage and the Q tile as
+      // run-time values, ~30 instructions of descriptor arithmetic (and a stack reload) sat between a barrier opening
+      // and the first MMA behind it.  The loop is therefore unrolled over both ring stages and both Q tiles — every
+      // descriptor, TMEM column and barrier address is loop invariant and stays in uniform registers — and the cycle
+      // counters (qi_attention_set_debug) live in their own instantiation of the loop.
+      auto run = [&](auto dbg_tag) {
+        constexpr bool DBG = decltype(dbg_tag)::value;
+        unsigned long long w_v = 0, w_ph = 0, w_pf = 0, w_k = 0, w_q = 0;
+        const long long t_begin = DBG ? clock64() : 0;
+        auto wait = [&](uint64_t* bar, uint32_t parity, unsigned long long& acc) {
+          if (DBG) {
+            const long long c0 = clock64();
+            mbar_wait(bar, parity);
+            acc += clock64() - c0;
+          } else {
+            mbar_wait(bar, parity);
+          }
+        };
+        wait(q_full, 0, w_q);
+        wait(&k_full[0], 0, w_q);
+        tc_fence_after();
+        issue_qk(0, 0);
+        tc_commit(&s_full[0]);
+        issue_qk(1, 0);
+        tc_commit(&s_full[1]);
+        tc_commit(&k_empty[0]);
+        for (int j0 = 0; j0 < n_kv; j0 += 2) {
+          const uint32_t ph = (j0 >> 1) & 1;   // parity of the ring barriers for K/V tiles j0 (stage 0) and j0 + 1 (stage 1)
+#pragma unroll
+          for (int st = 0; st < 2; ++st) {
+            const int j = j0 + st;
+            if (j >= n_kv) break;
+            const bool has_next = (j + 1) < n_kv;
+            const int stn = st ^ 1;
+            const uint32_t phn = st == 0 ? ph : ph ^ 1;   // ((j + 1) >> 1) & 1
+            wait(&v_full[st], ph, w_v);
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              if (SPLIT) {
+                wait(&p_half[t], st, w_ph);   // j & 1 == st
+                tc_fence_after();
+                issue_pv(t, st, j > 0, 0, ATT_BN / 32);
+                wait(&p_full[t], st, w_pf);
+                tc_fence_after();
+                issue_pv(t, st, j > 0, ATT_BN / 32, ATT_BN / 16);
+              } else {
+                wait(&p_full[t], st, w_pf);
+                tc_fence_after();
+                issue_pv(t, st, j > 0, 0, ATT_BN / 16);
+              }
+              if (t == 1) tc_commit(&v_empty[st]);
+              if (has_next) {
+                if (t == 0) {
+                  wait(&k_full[stn], phn, w_k);
+                  tc_fence_after();
+                }
+                issue_qk(t, stn);
+                tc_commit(&s_full[t]);
+                if (t == 1) tc_commit(&k_empty[stn]);
+              } else {
+                tc_commit(&o_done[t]);
+              }
+            }
+          }
+        }
+        if (DBG) {
+          atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
+          atomicAdd(&P.dbg[1], w_v);
+          atomicAdd(&P.dbg[2], w_ph);
+          atomicAdd(&P.dbg[3], w_pf);
+          atomicAdd(&P.dbg[4], w_k);
+          atomicAdd(&P.dbg[5], w_q);
         }
       };
-      timed_wait(q_full, 0, w_q);
-      timed_wait(&k_full[0], 0, w_q);
-      tc_fence_after();
-      issue_qk(0, 0);
-      tc_commit(&s_full[0]);
-      issue_qk(1, 0);
-      tc_commit(&s_full[1]);
-      tc_commit(&k_empty[0]);
-      for (int j = 0; j < n_kv; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
-        const bool has_next = (j + 1) < n_kv;
-        const int stn = (j + 1) & 1;
-        const uint32_t phn = ((j + 1) >> 1) & 1;
-        timed_wait(&v_full[st], ph, w_v);
-        for (int t = 0; t < 2; ++t) {
-          if (SPLIT) {
-            timed_wait(&p_half[t], j & 1, w_ph);
-            tc_fence_after();
-            issue_pv(t, st, j > 0, 0, ATT_BN / 32);
-            timed_wait(&p_full[t], j & 1, w_pf);
-            tc_fence_after();
-            issue_pv(t, st, j > 0, ATT_BN / 32, ATT_BN / 16);
-          } else {
-            timed_wait(&p_full[t], j & 1, w_pf);
-            tc_fence_after();
-            issue_pv(t, st, j > 0, 0, ATT_BN / 16);
-          }
-          if (t == 1) tc_commit(&v_empty[st]);
-          if (has_next) {
-            if (t == 0) {
-              timed_wait(&k_full[stn], phn, w_k);
-              tc_fence_after();
-            }
-            issue_qk(t, stn);
-            tc_commit(&s_full[t]);
-            if (t == 1) tc_commit(&k_empty[stn]);
-          } else {
-            tc_commit(&o_done[t]);
-          }
-        }
-      }
-      if (P.dbg) {
-        atomicAdd(&P.dbg[0], (unsigned long long)(clock64() - t_begin));
-        atomicAdd(&P.dbg[1], w_v);
-        atomicAdd(&P.dbg[2], w_ph);
-        atomicAdd(&P.dbg[3], w_pf);
-        atomicAdd(&P.dbg[4], w_k);
-        atomicAdd(&P.dbg[5], w_q);
-      }
+      if (P.dbg) run(std::true_type{});
+      else run(std::false_type{});
     }
     __syncwarp();
   } else if (warp > W_MMA) {
