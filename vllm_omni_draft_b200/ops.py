@@ -418,7 +418,8 @@ def gemm_set_tile_n(bn: int) -> None:
 
 
 def attention_set_variant(variant: int) -> None:
-    """-1 default; else EMU (0/2/3/4 of 8 pairs on the FMA-pipe exp2 polynomial) + 8 * SPLIT."""
+    """-1 default; else EMU (0/2/3/4 of 8 pairs on the FMA-pipe exp2 polynomial) + 8 * SPLIT; 40+ / 56+ select the
+    Q-in-TMEM half-tile kernel (single CTA / CTA pair).  The full table is in include/qi_b200.h."""
     check(_lib.lib().qi_attention_set_variant(int(variant)), "qi_attention_set_variant")
 
 
