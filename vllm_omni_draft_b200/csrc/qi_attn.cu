@@ -314,11 +314,116 @@ __device__ __forceinline__ void softmax_half_tile(uint32_t s_addr, uint32_t o_ad
   phase(4);
 }
 
-template <int DH, int EMU, bool SPLIT, bool TWO>
+// COOP: the two softmax warpgroups work on the SAME Q tile at the same time — warpgroup g owns keys [64 g, 64 g + 64)
+// of every K/V tile and columns [g DH/2, +DH/2) of O, for both Q tiles in turn — so a tile's S -> P latency, which
+// sits on the tile's dependency chain, is that of 64 columns instead of 128, and neither warpgroup idles while the
+// other tile's MMAs run.  Unlike TWO there is no per-tile exchange on that chain: the common reference maximum of a
+// row is updated from the local maxima of the PREVIOUS K/V tile (the partner's arrives through shared memory, ordered
+// by the P / S barriers of the tile in between), so both threads of a row take identical rescale decisions without
+// meeting.  Only the first K/V tile, whose reference cannot lag, meets at a named barrier.  The lag costs nothing in
+// accuracy (P = 2^(x - m_ref) is exact for any reference; the row sum and O carry the same factor) as long as a
+// row's scores do not grow by more than 2^96 within one K/V tile beyond everything seen before: such elements are
+// clamped for that one tile (logits 66 nats above the running maximum do not occur behind a QK-RMSNorm).
+// P of keys [64 g, 64 g + 64) is written over this thread's own S columns [64 g, 64 g + 32).
+template <int DH, bool MASK, int EMU>
+__device__ __forceinline__ void softmax_coop_tile(uint32_t s_addr, uint32_t o_addr, int half, int kv_valid, int j,
+                                                  float scale_log2, float& m_ref, float& l_part, float& mx_prev,
+                                                  float* xch_mine, const float* xch_other,
+                                                  const float* xch_other_prev, int bar_id, uint64_t* p_done,
+                                                  int lane) {
+  uint32_t r[2][32];
+  tmem_ld32(s_addr + half * 64, r[0]);
+  tmem_ld32(s_addr + half * 64 + 32, r[1]);
+  tmem_ld_wait();
+  if (MASK) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (half * 64 + c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;
+  }
+  float mxs[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) mxs[q] = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 2; ++c)
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      mxs[i & 7] = fmaxf(fmaxf(mxs[i & 7], __uint_as_float(r[c][2 * i])), __uint_as_float(r[c][2 * i + 1]));
+  const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
+                         fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
+  *xch_mine = mx;   // read by the partner during the NEXT K/V tile (and at the barrier below for tile 0)
+  if (j == 0) {
+    pair_sync(bar_id);
+    m_ref = fmaxf(mx, *xch_other) * scale_log2;   // key 0 is valid, so the row maximum is finite
+  } else {
+    const float m_new = fmaxf(m_ref, fmaxf(mx_prev, *xch_other_prev) * scale_log2);
+    const bool need = (m_new - m_ref) > 8.0f;
+    if (__any_sync(0xffffffffu, need)) {
+      const float f = need ? fast_exp2(m_ref - m_new) : 1.0f;
+      if (need) {
+        l_part *= f;
+        m_ref = m_new;
+      }
+#pragma unroll 1
+      for (int c = 0; c < DH / 64; ++c) {
+        uint32_t o[32];
+        tmem_ld32(o_addr + half * (DH / 2) + c * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+        tmem_st32(o_addr + half * (DH / 2) + c * 32, o);
+      }
+    }
+    if (__any_sync(0xffffffffu, mx * scale_log2 - m_ref > 96.0f)) {   // see above: keeps 2^x finite
+      const float cap = (m_ref + 96.0f) / scale_log2;
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) r[c][i] = __float_as_uint(fminf(__uint_as_float(r[c][i]), cap));
+    }
+  }
+  mx_prev = mx;
+  constexpr int NE = EMU & 15;
+  constexpr int DEG = (EMU & 16) ? 2 : 3;
+  const float2 sc2 = make_float2(scale_log2, scale_log2);
+  const float2 nm2 = make_float2(-m_ref, -m_ref);
+  float2 acc[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) acc[q] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float2 x = __ffma2_rn(make_float2(__uint_as_float(r[c][2 * i]), __uint_as_float(r[c][2 * i + 1])),
+                                  sc2, nm2);
+      float2 p;
+      if (((i % 8) * NE) % 8 < NE) {
+        p = exp2_poly2<DEG>(x);
+      } else {
+        p.x = fast_exp2(x.x);
+        p.y = fast_exp2(x.y);
+      }
+      acc[i & 3] = __fadd2_rn(acc[i & 3], p);
+      pk[i] = pack_bf16(p.x, p.y);
+    }
+    tmem_st16(s_addr + half * 64 + c * 16, pk);
+  }
+  const float2 a01 = __fadd2_rn(acc[0], acc[1]), a23 = __fadd2_rn(acc[2], acc[3]);
+  l_part += (a01.x + a01.y) + (a23.x + a23.y);
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_done);
+}
+
+template <int DH, int EMU, bool SPLIT, bool TWO, bool COOP = false>
 __global__ void __launch_bounds__(TWO ? ATT_THREADS2 : ATT_THREADS, 1)
 attention_fwd_kernel(const __grid_constant__ AttParams P) {
   using Cfg = AttCfg<DH>;
   static_assert(!TWO || SPLIT, "two threads per row publish P in two halves by construction");
+  static_assert(!COOP || (SPLIT && !TWO), "cooperating warpgroups publish the two key halves of P separately");
   constexpr int W_TMA = TWO ? 16 : 8;   // first warp of the last warpgroup
   constexpr int W_MMA = W_TMA + 1;
   extern __shared__ uint8_t smem_raw[];
@@ -427,7 +532,9 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
           // of the head dim live one sub-tile (LBO) further.
           const uint64_t db =
               make_smem_desc(v_addr + st * Cfg::TILE_BYTES + k * 2048, Cfg::SUB, 1024);
-          mma_ts(o_col[t], s_col[t] + k * 8, db, idesc_pv, (accumulate || k != 0) ? 1u : 0u);
+          // COOP: P of keys 64..127 sits over S columns [64, 96) (each warpgroup writes over its own S columns)
+          const int p_off = COOP ? (k < ATT_BN / 32 ? k * 8 : 64 + (k - ATT_BN / 32) * 8) : k * 8;
+          mma_ts(o_col[t], s_col[t] + p_off, db, idesc_pv, (accumulate || k != 0) ? 1u : 0u);
         }
       };
 
@@ -513,6 +620,99 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   } else if (warp > W_MMA) {
     if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+  } else if (COOP) {
+    // ------------------------------------------------------------------ softmax, warpgroups cooperating on each Q tile
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    const int half = warp >> 2;              // which 64 keys of every K/V tile, which half of O's columns
+    const int quad = warp & 3;               // TMEM lane quadrant (warp % 4)
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const uint32_t s_addr[2] = {tmem_base + lane_off + Cfg::S_COL0, tmem_base + lane_off + Cfg::S_COL1};
+    const uint32_t o_addr[2] = {tmem_base + lane_off + Cfg::O_COL0, tmem_base + lane_off + Cfg::O_COL1};
+    float* xch = reinterpret_cast<float*>(smem + Cfg::XCH_OFF);   // [2 parities][2 tiles][2 halves][128 rows]
+    const int xrow = quad * 32 + lane;
+    const int bar_id = 1 + quad;             // the two warps (one per warpgroup) that share this lane quadrant
+    float m_ref[2] = {-INFINITY, -INFINITY}, l_part[2] = {0.f, 0.f}, mx_prev[2] = {-INFINITY, -INFINITY};
+    const int n_full = P.seq_kv / ATT_BN;
+    const bool prof = P.dbg != nullptr && threadIdx.x == 0;
+    unsigned long long w_s = 0;
+    const long long t_begin = clock64();
+    for (int j = 0; j < n_kv; ++j) {
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        float* xm = xch + (((j & 1) * 2 + t) * 2 + half) * 128 + xrow;
+        const float* xo = xch + (((j & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+        const float* xop = xch + ((((j & 1) ^ 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+        uint64_t* p_done = half ? &p_full[t] : &p_half[t];
+        const long long c0 = prof ? clock64() : 0;
+        mbar_wait(&s_full[t], j & 1);
+        if (prof) w_s += clock64() - c0;
+        tc_fence_after();
+        if (j < n_full) {
+          softmax_coop_tile<DH, false, EMU>(s_addr[t], o_addr[t], half, ATT_BN, j, P.scale_log2, m_ref[t], l_part[t],
+                                            mx_prev[t], xm, xo, xop, bar_id, p_done, lane);
+        } else {
+          softmax_coop_tile<DH, true, EMU>(s_addr[t], o_addr[t], half, P.seq_kv - j * ATT_BN, j, P.scale_log2,
+                                           m_ref[t], l_part[t], mx_prev[t], xm, xo, xop, bar_id, p_done, lane);
+        }
+      }
+    }
+    if (prof) {
+      atomicAdd(&P.dbg[8], (unsigned long long)(clock64() - t_begin));
+      atomicAdd(&P.dbg[9], w_s);
+    }
+    constexpr int PPR = DH / 8;
+    constexpr int RPI = 32 / PPR;
+    constexpr int ITS = 32 / RPI / 2;        // each of the two warps stores half of the 32 rows
+#pragma unroll 1
+    for (int t = 0; t < 2; ++t) {
+      // row sum = both halves (a slot no earlier reader still needs: parity of tile n_kv, which nobody wrote)
+      float* xm = xch + (((n_kv & 1) * 2 + t) * 2 + half) * 128 + xrow;
+      const float* xo = xch + (((n_kv & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+      pair_sync(bar_id);                     // the partner has read this slot's previous value (tile n_kv - 2)
+      *xm = l_part[t];
+      pair_sync(bar_id);
+      const float inv = 1.f / (l_part[t] + *xo);
+      mbar_wait(&o_done[t], 0);
+      tc_fence_after();
+      uint8_t* stage = smem + Cfg::Q_OFF + t * Cfg::TILE_BYTES + quad * (32 * DH * 2);
+#pragma unroll 1
+      for (int c = 0; c < DH / 64; ++c) {
+        uint32_t r[32];
+        tmem_ld32(o_addr[t] + half * (DH / 2) + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 o;
+          o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+          o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+          o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+          o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+          const int piece = half * (DH / 16) + c * 4 + g;
+          *reinterpret_cast<uint4*>(stage + lane * (DH * 2) + ((piece ^ (lane & 7)) << 4)) = o;
+        }
+      }
+      pair_sync(bar_id);
+      const int row_base = q0 + t * ATT_BM + quad * 32;
+#pragma unroll 4
+      for (int it = half * ITS; it < (half + 1) * ITS; ++it) {
+        const int rr = it * RPI + lane / PPR;
+        const int piece = lane % PPR;
+        const int row = row_base + rr;
+        const uint4 o = *reinterpret_cast<const uint4*>(stage + rr * (DH * 2) + ((piece ^ (rr & 7)) << 4));
+        if (row < P.seq_q) {
+          __nv_bfloat16* orow;
+          if (P.n_peer > 0) {
+            int p = 0;
+            while (p + 1 < P.n_peer && row >= P.o_prefix[p + 1]) ++p;
+            orow = P.o_peer[p] + P.o_chunk_off + (size_t)b * P.o_bs + (size_t)(row - P.o_prefix[p]) * P.ld_o +
+                   (size_t)head * P.o_hs;
+          } else {
+            orow = P.o + (size_t)b * P.o_bs + (size_t)row * P.ld_o + (size_t)head * P.o_hs;
+          }
+          *reinterpret_cast<uint4*>(orow + piece * 8) = o;
+        }
+      }
+    }
   } else if (TWO) {
     // ------------------------------------------------------------------ softmax, two threads per query row
     asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
@@ -1238,7 +1438,7 @@ using namespace qi;
 
 static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same as CTA pairs (cta_group::2, each CTA stages half of every K/V half; head_dim 128 only)
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 63) return QI_ERR_ARG;
+  if (v < -1 || v > 68) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
@@ -1256,11 +1456,11 @@ static int attn_variant() {
   return v >= 0 ? v : QI_ATTN_DEFAULT_VARIANT;
 }
 
-template <int DH, int EMU, bool SPLIT, bool TWO = false>
+template <int DH, int EMU, bool SPLIT, bool TWO = false, bool COOP = false>
 static int launch_attention_v(const AttParams& P, dim3 grid, cudaStream_t stream) {
-  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_fwd_kernel<DH, EMU, SPLIT, TWO>), AttCfg<DH>::SMEM_BYTES))
+  if (int rc = qi_set_max_smem(reinterpret_cast<const void*>(attention_fwd_kernel<DH, EMU, SPLIT, TWO, COOP>), AttCfg<DH>::SMEM_BYTES))
     return rc;
-  if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT, TWO>, grid, dim3(TWO ? ATT_THREADS2 : ATT_THREADS),
+  if (qi_launch(attention_fwd_kernel<DH, EMU, SPLIT, TWO, COOP>, grid, dim3(TWO ? ATT_THREADS2 : ATT_THREADS),
                 AttCfg<DH>::SMEM_BYTES, stream, P) != cudaSuccess)
     return QI_ERR_CUDA;
   return QI_OK;
@@ -1352,7 +1552,7 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     P.ts_diag = e ? atoi(e) : 0;
   }
   int variant = attn_variant();
-  if (variant >= 40 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
+  if (variant >= 40 && variant < 64 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
   P.split_p = (variant >> 3) & 1;
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
   switch (variant) {
@@ -1371,6 +1571,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
     case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
+    case 64: return launch_attention_v<DH, 0, true, false, true>(P, grid, stream);   // cooperating warpgroups
+    case 66: return launch_attention_v<DH, 2, true, false, true>(P, grid, stream);
+    case 67: return launch_attention_v<DH, 3, true, false, true>(P, grid, stream);
+    case 68: return launch_attention_v<DH, 4, true, false, true>(P, grid, stream);
 #define QI_TS_CASE(V, EMU, PAIR) \
   case V: return launch_attention_ts<DH, EMU, PAIR && DH == 128>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
     QI_TS_CASE(40, 0, false) QI_TS_CASE(41, 1, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
