@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(TWO ? ATT_THREADS2 : ATT_THREADS, 1)
 attention_fwd_kernel(const __grid_constant__ AttParams P) {
   using Cfg = AttCfg<DH>;
   static_assert(!TWO || SPLIT, "two threads per row publish P in two halves by construction");
-  static_assert(!COOP || (SPLIT && !TWO), "cooperating warpgroups publish the two key halves of P separately");
+  static_assert(!COOP || SPLIT, "cooperating warpgroups publish the two key halves of P separately");
   constexpr int W_TMA = TWO ? 16 : 8;   // first warp of the last warpgroup
   constexpr int W_MMA = W_TMA + 1;
   extern __shared__ uint8_t smem_raw[];
@@ -620,7 +620,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
   } else if (warp > W_MMA) {
     if (TWO) asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-  } else if (COOP) {
+  } else if (COOP && !TWO) {
     // ------------------------------------------------------------------ softmax, warpgroups cooperating on each Q tile
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
     const int half = warp >> 2;              // which 64 keys of every K/V tile, which half of O's columns
@@ -728,6 +728,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     uint64_t* p_done = half ? &p_full[t] : &p_half[t];
     float m_ref = -INFINITY;
     float l_sum = 0.f;                       // this thread's 64 keys only
+    float mx_prev = -INFINITY;               // COOP: this thread's maximum over the previous K/V tile
     const int n_full = P.seq_kv / ATT_BN;
     const bool prof = P.dbg != nullptr && threadIdx.x == 0;
     unsigned long long w_s = 0;
@@ -740,7 +741,15 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
       mbar_wait(&s_full[t], j & 1);
       if (prof) w_s += clock64() - c0;
       tc_fence_after();
-      if (j < n_full) {
+      if (COOP) {   // reference maximum from the previous tile's maxima: no meeting on the tile's chain (see softmax_coop_tile)
+        const float* xop = xch + ((((j & 1) ^ 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+        if (j < n_full)
+          softmax_coop_tile<DH, false, EMU>(s_addr, o_addr, half, ATT_BN, j, P.scale_log2, m_ref, l_sum, mx_prev, xm,
+                                            xo, xop, bar_id, p_done, lane);
+        else
+          softmax_coop_tile<DH, true, EMU>(s_addr, o_addr, half, P.seq_kv - j * ATT_BN, j, P.scale_log2, m_ref, l_sum,
+                                           mx_prev, xm, xo, xop, bar_id, p_done, lane);
+      } else if (j < n_full) {
         softmax_half_tile<DH, false, EMU>(s_addr, o_addr, half, ATT_BN, j == 0, P.scale_log2, m_ref, l_sum, xm, xo,
                                           bar_id, p_done, lane, prof ? pcs : nullptr);
       } else {
@@ -751,6 +760,7 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
     {   // row sum = both halves
       float* xm = xch + (((n_kv & 1) * 2 + t) * 2 + half) * 128 + xrow;
       const float* xo = xch + (((n_kv & 1) * 2 + t) * 2 + (half ^ 1)) * 128 + xrow;
+      if (COOP) pair_sync(bar_id);           // the partner read this slot (tile n_kv - 2's maximum) during its last tile
       *xm = l_sum;
       pair_sync(bar_id);
       l_sum += *xo;
@@ -1438,7 +1448,7 @@ using namespace qi;
 
 static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same as CTA pairs (cta_group::2, each CTA stages half of every K/V half; head_dim 128 only)
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 68) return QI_ERR_ARG;
+  if (v < -1 || v > 84) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
@@ -1575,6 +1585,10 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 66: return launch_attention_v<DH, 2, true, false, true>(P, grid, stream);
     case 67: return launch_attention_v<DH, 3, true, false, true>(P, grid, stream);
     case 68: return launch_attention_v<DH, 4, true, false, true>(P, grid, stream);
+    case 80: return launch_attention_v<DH, 0, true, true, true>(P, grid, stream);    // four warpgroups, no per-tile exchange
+    case 82: return launch_attention_v<DH, 2, true, true, true>(P, grid, stream);
+    case 83: return launch_attention_v<DH, 3, true, true, true>(P, grid, stream);
+    case 84: return launch_attention_v<DH, 4, true, true, true>(P, grid, stream);
 #define QI_TS_CASE(V, EMU, PAIR) \
   case V: return launch_attention_ts<DH, EMU, PAIR && DH == 128>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
     QI_TS_CASE(40, 0, false) QI_TS_CASE(41, 1, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
