@@ -1571,6 +1571,7 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 3: return launch_attention_v<DH, 3, false>(P, grid, stream);
     case 4: return launch_attention_v<DH, 4, false>(P, grid, stream);
     case 8: return launch_attention_v<DH, 0, true>(P, grid, stream);
+    case 9: return launch_attention_v<DH, 1, true>(P, grid, stream);
     case 10: return launch_attention_v<DH, 2, true>(P, grid, stream);
     case 11: return launch_attention_v<DH, 3, true>(P, grid, stream);
     case 12: return launch_attention_v<DH, 4, true>(P, grid, stream);
