@@ -194,6 +194,106 @@ static void run_pair(const char* what, int steps, int sms) {
   cudaFree(d);
 }
 
+// MUFU.EX2 throughput per SM: f32 (one value per lane and instruction) against packed f16x2 (two).
+template <int MODE>   // 0: ex2.approx.ftz.f32, 1: ex2.approx.f16x2
+__global__ void __launch_bounds__(512, 1) ex2_kernel(int iters, long long* out, uint32_t* sink) {
+  uint32_t v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = MODE ? 0xb800b400u + threadIdx.x : __float_as_uint(-0.5f - 0.001f * i);
+  __syncthreads();
+  const long long t0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (MODE) asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(v[i]));
+      else asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+r"(v[i]));
+    }
+  }
+  const long long t1 = clock64();
+  uint32_t x = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) x ^= v[i];
+  if (x == 0x12345678u) sink[0] = x;
+  if (threadIdx.x == 0) out[blockIdx.x] = t1 - t0;
+}
+template <int MODE>
+static void run_ex2(const char* name, int sms) {
+  long long* d;
+  uint32_t* sink;
+  cudaMalloc(&d, sms * sizeof(long long));
+  cudaMalloc(&sink, 4);
+  const int iters = 4000;
+  ex2_kernel<MODE><<<sms, 512>>>(iters, d, sink);
+  ex2_kernel<MODE><<<sms, 512>>>(iters, d, sink);
+  cudaError_t e = cudaDeviceSynchronize();
+  long long h[256];
+  cudaMemcpy(h, d, sms * sizeof(long long), cudaMemcpyDeviceToHost);
+  long long mx = 0;
+  for (int i = 0; i < sms; ++i) mx = h[i] > mx ? h[i] : mx;
+  const double instr = (double)iters * 8 * 16;   // warp instructions per SM (16 warps)
+  printf("%-22s: %6.2f clk per warp instruction per SM sub-partition, %5.1f values per clk per SM [%s]\n", name,
+         (double)mx / (instr / 4), instr * 32 * (MODE ? 2 : 1) / (double)mx, cudaGetErrorString(e));
+  cudaFree(d);
+  cudaFree(sink);
+}
+
+// Does kind::f16 accept A = f16 (in TMEM) with B = bf16 (in shared memory)?  A = 0.5 everywhere, B = 2.0 everywhere,
+// one M = 128, N = 64, K = 16 MMA: every element of D must be 16.
+__global__ void __launch_bounds__(128, 1) mixed_kernel(float* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x40004000u;   // bf16 2.0
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&slot);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+  uint32_t a[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = 0x38003800u;   // f16 0.5 | 0.5
+  tmem_st16(tm + lane_off, a);
+  tmem_st_wait();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1 && elect_one()) {
+    // c_format F32 (bit 4), a_format F16 (0 at bit 7), b_format BF16 (1 at bit 10), N = 64, M = 128
+    const uint32_t idesc = (1u << 4) | (0u << 7) | (1u << 10) | ((64u >> 3) << 17) | ((128u >> 4) << 24);
+    const uint64_t db = make_smem_desc(smem_u32(smem), 0, 1024);
+    mma_ts(tm + 64, tm, db, idesc, 0u);
+    tc_commit(&bar);
+  }
+  mbar_wait(&bar, 0);
+  tc_fence_after();
+  uint32_t r[16];
+  tmem_ld16(tm + lane_off + 64, r);
+  tmem_ld_wait();
+  out[threadIdx.x] = __uint_as_float(r[0]) + __uint_as_float(r[15]);
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tm);
+}
+static void run_mixed() {
+  float* d;
+  cudaMalloc(&d, 128 * sizeof(float));
+  cudaFuncSetAttribute(mixed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768);
+  mixed_kernel<<<1, 128, 32768>>>(d);
+  cudaError_t e = cudaDeviceSynchronize();
+  float h[128];
+  cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  printf("kind::f16 with A = f16 (TMEM) x B = bf16 (smem): D[0][0] + D[0][15] = %g, row 127: %g (32 expected if the formats are honoured) [%s]\n",
+         h[0], h[127], cudaGetErrorString(e));
+  cudaFree(d);
+}
+
 template <int N, bool TS>
 static void run(const char* name, int groups, int sms) {
   long long* d;
@@ -219,6 +319,9 @@ int main() {
   int sms = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   const int groups = 2000;
+  run_ex2<0>("ex2.approx.ftz.f32", sms);
+  run_ex2<1>("ex2.approx.f16x2", sms);
+  run_mixed();
   run<128, false>("SS N=128", groups, sms);
   run<64, false>("SS N=64", groups, sms);
   run<256, false>("SS N=256", groups, sms);
