@@ -1,13 +1,15 @@
 """Timing experiments on the Q-in-TMEM attention kernel (variants 40+): QI_ATTN_TS_DIAG = 0 (real), 1 (softmax only
-hands the barriers on: the MMA/TMA pipeline alone), 2 (S load + P store without the math) — read per process, so this
-script re-executes itself per mode.  Prints us per launch at the cfg-2 step shape and the MMA-thread wait counters."""
+hands the barriers on: the MMA/TMA pipeline alone), 2 (S load + P store without the math), 3 (as 1, and the P*V issuer
+does not wait for P) — read per process, so this script re-executes itself per mode.  Prints us per launch at the
+cfg-2 step shape, the softmax phase counters of one thread and (QI_DIAG_TRACE=1) the timeline of CTA (0,0,0):
+K/V TMA issue, K ready (Q*K^T issuer), P ready / step issued (P*V issuer), S ready / P published (softmax)."""
 import ctypes as C
 import os
 import subprocess
 import sys
 
 if len(sys.argv) < 2:
-    for mode in os.environ.get("QI_DIAG_MODES", "0,1,2,3,4").split(","):
+    for mode in os.environ.get("QI_DIAG_MODES", "0,1,2,3").split(","):
         env = dict(os.environ, QI_ATTN_TS_DIAG=mode)
         subprocess.run([sys.executable, __file__, mode], env=env, check=False)
     sys.exit(0)
@@ -44,16 +46,15 @@ for var in [int(x) for x in os.environ.get("QI_DIAG_VARIANTS", "43,59").split(",
     c = buf.tolist()
     n_cta = ((S + 127) // 128) * H * B
     n_half = (S + 63) // 64
-    print(f"diag {sys.argv[1]} variant {var}: {us:7.1f} us  | per half-step: mma total {c[0] / n_cta / n_half:6.0f} clk, "
-          f"wait v {c[1] / n_cta / n_half:5.0f}, wait p {c[3] / n_cta / n_half:5.0f}, wait k {c[4] / n_cta / n_half:5.0f}, "
-          f"first {c[5] / n_cta:6.0f} per CTA | softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA; per own half: "
+    print(f"diag {sys.argv[1]} variant {var}: {us:7.1f} us  | P*V issuer: {c[0] / n_cta / n_half:6.0f} clk per half-step | "
+          f"softmax wg0 total {c[8] / n_cta:7.0f}, wait s {c[9] / n_cta:7.0f} per CTA; per own half: "
           f"S load {c[11] / n_cta / (n_half / 2):5.0f}, max {c[12] / n_cta / (n_half / 2):5.0f}, rescale {c[13] / n_cta / (n_half / 2):5.0f}, "
           f"P {c[14] / n_cta / (n_half / 2):5.0f}, publish {c[15] / n_cta / (n_half / 2):5.0f}", flush=True)
     if os.environ.get("QI_DIAG_TRACE", "1") == "1":
         t = [c[16 + 8 * h:16 + 8 * h + 8] for h in range(min(n_half, 96))]
         t0 = min(x for row in t for x in row if x > 0)
-        print("    timeline of CTA (0,0,0), clk since the first event: half | K tma issued, V tma issued | mma: K ready, V ready, "
-              "P ready, step issued | softmax: S ready, P published")
+        print("    timeline of CTA (0,0,0), clk since the first event (-1 = not recorded): half | K tma issued, V tma issued | "
+              "K ready, -, P ready, P*V issued | softmax: S ready, P published")
         for h in list(range(0, 20)) + list(range(40, 52)):
             print(f"    {h:3d} | " + " ".join(f"{(x - t0) if x > 0 else -1:7d}" for x in t[h]))
 ops.attention_set_variant(-1)

@@ -55,7 +55,7 @@ struct AttParams {
   __nv_bfloat16* o;
   long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
   const __nv_bfloat16* q;       // TS kernel: Q rows are read straight from global memory into TMEM
-  int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math, 3 = as 1 and the MMA thread does not wait for P, 4 = as 3 and it does not wait for K/V either
+  int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math, 3 = as 1 and the P*V issuer does not wait for P
   long long ld_q, q_bs, q_hs;
   int seq_q, seq_kv, heads;
   float scale_log2;
