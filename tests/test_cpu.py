@@ -87,6 +87,19 @@ def test_library_exports_every_declared_symbol(built):
     assert built.lib().qi_version() == 100
 
 
+def test_attention_variant_switch_validates_its_argument(built):
+    """qi_attention_set_variant is host-only state: the documented range (include/qi_b200.h: -1 = default, 0..84) is
+    accepted, anything else is QI_ERR_ARG, and the default is restored afterwards."""
+    lib = built.lib()
+    try:
+        for v in (-1, 0, 11, 43, 59, 67, 84):
+            assert lib.qi_attention_set_variant(v) == 0
+        for v in (-2, 85, 1000):
+            assert lib.qi_attention_set_variant(v) != 0
+    finally:
+        assert lib.qi_attention_set_variant(-1) == 0
+
+
 def test_compute_entry_points_fail_loudly_without_gpu(built):
     if torch.cuda.is_available():
         pytest.skip("GPU present")
