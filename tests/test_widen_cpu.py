@@ -226,6 +226,46 @@ def test_prompt_embeds_template_drop_and_padding():
                                         prompt="x", prompt_template_encode=template, prompt_template_encode_start_idx=drop)
 
 
+def test_prompt_embeds_through_the_real_qwen2_5_vl_class():
+    """Row f4 against the real encoder class: a tiny random-init ``Qwen2_5_VLForConditionalGeneration`` (transformers;
+    the 7B weights and the tokenizer files are not on the box) goes through ``get_qwen_prompt_embeds`` and the
+    adapter's inline path.  What is checked is the contract with the HF class — ``output_hidden_states=True`` ->
+    ``hidden_states[-1]`` of shape [B, T, hidden], padding excluded by the attention mask, template prefix dropped —
+    by comparing with a direct call of the model on the same ids."""
+    tf = pytest.importorskip("transformers")
+    if not hasattr(tf, "Qwen2_5_VLForConditionalGeneration"):
+        pytest.skip("transformers without Qwen2.5-VL")
+    from types import SimpleNamespace
+    from vllm_omni_draft_b200 import prompt as P
+    cfg = tf.Qwen2_5_VLConfig()
+    for k, v in dict(hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+                     num_key_value_heads=2, vocab_size=64, max_position_embeddings=256).items():
+        setattr(cfg.text_config, k, v)
+    cfg.text_config.rope_parameters = {"rope_type": "default", "rope_theta": 1000000.0, "mrope_section": [2, 3, 3]}
+    for k, v in dict(depth=1, hidden_size=32, intermediate_size=64, num_heads=2, out_hidden_size=64).items():
+        if hasattr(cfg.vision_config, k):
+            setattr(cfg.vision_config, k, v)
+    torch.manual_seed(0)
+    model = tf.Qwen2_5_VLForConditionalGeneration(cfg).eval()
+    tok = _StubTokenizer()                                   # ids = word lengths < vocab_size, right padding
+    template, drop = "sys a b c {} end", 4
+    prompts = ["red cat", "a very long prompt here"]
+    with torch.no_grad():
+        emb, mask = P.get_qwen_prompt_embeds(model, tok, prompts, prompt_template_encode=template,
+                                             prompt_template_encode_start_idx=drop)
+        t = tok([template.format(p) for p in prompts])
+        ref = model(input_ids=t.input_ids, attention_mask=t.attention_mask, output_hidden_states=True).hidden_states[-1]
+    assert emb.shape == (2, 6, 64) and mask.tolist() == [[1, 1, 1, 0, 0, 0], [1, 1, 1, 1, 1, 1]]
+    assert torch.equal(emb[0, :3], ref[0, drop:drop + 3]) and torch.equal(emb[1], ref[1, drop:drop + 6])
+    assert emb[0, 3:].abs().max() == 0                       # padding rows are zeros, not the model's padded positions
+    w = SimpleNamespace(qwen_text_encoder=model, qwen_tokenizer=tok, qwen_processor=None)
+    with torch.no_grad():
+        h, m = P.encode_prompt_inline(w, "a bb ccc", "cpu")
+        direct = model(input_ids=torch.tensor([[1, 2, 3]]), attention_mask=torch.ones(1, 3, dtype=torch.long),
+                       output_hidden_states=True).hidden_states[-1]
+    assert h.shape == (1, 3, 64) and torch.equal(h, direct) and m.tolist() == [[1, 1, 1]]
+
+
 def test_adapter_inline_prompt_errors_match_reference():
     from types import SimpleNamespace
     from vllm_omni_draft_b200 import prompt as P
