@@ -178,7 +178,7 @@ def test_attention(cuda_device, B, S, H, Dh):
 
 
 @pytest.mark.parametrize("Dh", [128, 64])
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 9, 10, 11, 12, 16, 18, 19, 20, 24, 25, 26, 40, 42, 43, 44, 56, 58, 59, 60, 64, 66, 67, 68, 80, 82, 83, 84])
+@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 9, 10, 11, 12, 16, 18, 19, 20, 24, 25, 26, 27, 40, 42, 43, 44, 56, 58, 59, 60, 64, 66, 67, 68, 80, 82, 83, 84])
 def test_attention_softmax_variants(cuda_device, variant, Dh):
     """Every softmax variant (MUFU only / 2-3-4 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
     or in two halves, one thread or two threads per query row) matches fp32 SDPA, on a ragged sequence (partial

@@ -122,25 +122,42 @@ __device__ __forceinline__ void softmax_tile(uint32_t s_addr, uint32_t o_addr, i
       c_prev = now;
     }
   };
-#pragma unroll
-  for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
-  tmem_ld_wait();
-  phase(0);
-  if (MASK) {
-#pragma unroll
-    for (int c = 0; c < ATT_BN / 32; ++c)
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: contributes 0
-  }
+  // STAG (EMU bit 5): the second half of S is loaded from TMEM while the row maximum runs over the first half
+  // (tcgen05.wait::ld waits for every outstanding load, so the loads are issued in two groups).
+  constexpr bool STAG = (EMU & 32) != 0;
   float mxs[8];
 #pragma unroll
   for (int q = 0; q < 8; ++q) mxs[q] = -INFINITY;
+  auto mask_and_max = [&](int c) {
+    if (MASK) {
 #pragma unroll
-  for (int c = 0; c < ATT_BN / 32; ++c)
+      for (int i = 0; i < 32; ++i)
+        if (c * 32 + i >= kv_valid) r[c][i] = 0xff800000u;   // -inf: contributes 0
+    }
 #pragma unroll
     for (int i = 0; i < 16; ++i)
       mxs[i & 7] = fmaxf(fmaxf(mxs[i & 7], __uint_as_float(r[c][2 * i])), __uint_as_float(r[c][2 * i + 1]));
+  };
+  if (STAG) {
+    tmem_ld32(s_addr, r[0]);
+    tmem_ld32(s_addr + 32, r[1]);
+    tmem_ld_wait();
+    tmem_ld32(s_addr + 64, r[2]);
+    tmem_ld32(s_addr + 96, r[3]);
+    mask_and_max(0);
+    mask_and_max(1);
+    tmem_ld_wait();
+    phase(0);
+    mask_and_max(2);
+    mask_and_max(3);
+  } else {
+#pragma unroll
+    for (int c = 0; c < ATT_BN / 32; ++c) tmem_ld32(s_addr + c * 32, r[c]);
+    tmem_ld_wait();
+    phase(0);
+#pragma unroll
+    for (int c = 0; c < ATT_BN / 32; ++c) mask_and_max(c);
+  }
   const float mx = fmaxf(fmaxf(fmaxf(mxs[0], mxs[1]), fmaxf(mxs[2], mxs[3])),
                          fmaxf(fmaxf(mxs[4], mxs[5]), fmaxf(mxs[6], mxs[7])));
   const float m_new = fmaxf(m_ref, mx * scale_log2);
@@ -1030,6 +1047,7 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 24: return launch_attention_v<DH, 16 + 3, true>(P, grid, stream);   // degree-2 polynomial, 3/4/5 of 8 pairs
     case 25: return launch_attention_v<DH, 16 + 4, true>(P, grid, stream);
     case 26: return launch_attention_v<DH, 16 + 5, true>(P, grid, stream);
+    case 27: return launch_attention_v<DH, 32 + 3, true>(P, grid, stream);   // 11 with the S load staggered under the row maximum
     case 64: return launch_attention_v<DH, 0, true, false, true>(P, grid, stream);   // cooperating warpgroups
     case 66: return launch_attention_v<DH, 2, true, false, true>(P, grid, stream);
     case 67: return launch_attention_v<DH, 3, true, false, true>(P, grid, stream);
