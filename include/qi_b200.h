@@ -236,7 +236,7 @@ int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int ba
  * attention_ts_kernel: one 128-query tile per CTA, Q resident in TMEM, K/V pipelined in 64-key halves over three S
  * regions and two softmax warpgroups; 56 + EMU = the same as CTA pairs (cta_group::2, head_dim 128); 64 + EMU = both
  * softmax warpgroups on the same Q tile (64 keys each, reference maximum from the previous K/V tile's maxima) and
- * 80 + EMU = the same with four warpgroups; 9 = 1 of 8 pairs on the polynomial.  All of these measured slower than the
+ * 80 + EMU = the same with four warpgroups; 9 = 1 of 8 pairs on the polynomial; 27 = 11 with the S load in two groups.  All of these measured slower than the
  * default on the benchmarked shapes and are kept as tested variants.  Valid range: -1 .. 84.  All variants agree with
  * fp32 SDPA to the same tolerance (tests/test_ops_gpu.py). */
 int qi_attention_set_variant(int variant);
