@@ -264,6 +264,32 @@ int qi_peer_unmap(void* ptr);
 int qi_peer_barrier(void* const* signal_ptrs_dev, int n_peers, int my_index, uint32_t* state_dev,
                     unsigned int timeout_ms, qi_stream_t stream);
 
+/* qi_peer_barrier without any device memory of the caller's for its bookkeeping.  This entry point has no
+ * counterpart in the reference; it exists for hosts that cannot allocate on the GPU when they need a barrier:
+ * a serving worker that gave all remaining HBM to the engine's block pool after memory profiling (a late
+ * cudaMalloc fails or eats into that pool), a denoising loop that cannot afford the device-wide synchronisation
+ * cudaMalloc / cudaFree imply, or a C / Go / Rust host that binds this library and owns no device allocator.
+ * The pointer table and the {epoch, timeout flag} words that qi_peer_barrier takes as signal_ptrs_dev / state_dev
+ * live in a fixed 256-byte array inside the library instead (present on every GPU that loads the library, until
+ * the process exits).  The call itself performs no cudaMalloc / cudaFree and calls nothing that allocates.
+ *   signal_ptrs   HOST array of n_peers DEVICE pointers, entry p = rank p's u32[n_peers] signal array
+ *                 (zero-initialised, peer-mapped — still the caller's: they are the barrier's input/output).
+ *                 Read before the call returns.
+ *   n_peers       1 .. QI_PEER_BARRIER_STATIC_MAX_PEERS; more is refused with QI_ERR_ARG and a message in
+ *                 qi_last_cuda_error() (qi_peer_barrier has the same limit today; here it is the table's size).
+ *   restart       The array is shared by every call on the device and keeps what the last call left in it.  The
+ *                 epoch must carry over from one barrier to the next on the same signal arrays, so it is NOT
+ *                 cleared by default.  Pass non-zero on the first barrier over freshly zeroed signal arrays
+ *                 (every rank, same call): epoch and timeout flag are then reset on `stream` first.
+ *   state_out_dev DEVICE u32[2] or NULL: receives {epoch, timeout flag} after this barrier (what qi_peer_barrier
+ *                 leaves in state_dev), so a timeout can be seen by the host.
+ * One group per device at a time: two barriers that use this entry point and overlap on the same GPU (different
+ * streams, or two groups) race on the shared words.  The first call on each device looks up the array's device
+ * address (cudaGetSymbolAddress, with that device current); make that first call outside any stream capture. */
+#define QI_PEER_BARRIER_STATIC_MAX_PEERS 8
+int qi_peer_barrier_static(void* const* signal_ptrs /* host */, int n_peers, int my_index, int restart,
+                           uint32_t* state_out_dev, unsigned int timeout_ms, qi_stream_t stream);
+
 /* ---- K5: true-CFG combine + per-token norm rescale + FlowMatch Euler update in one pass
  * (replaces QwenImagePipeline's comb_pred/cond_norm/noise_norm lines and
  * FlowMatchEulerDiscreteScheduler.step).  uncond == NULL skips CFG.  dt = sigma_next - sigma is read

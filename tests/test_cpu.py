@@ -222,3 +222,12 @@ def test_bench_reference_arm_prints_the_contract_line():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                        capture_output=True, text=True, timeout=120, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
     assert r.returncode == 0 and not [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+
+
+def test_static_barrier_size_limit_is_checked_before_any_cuda_call(built):
+    """qi_peer_barrier_static (the entry point for hosts that cannot allocate device memory) keeps its pointer table
+    in a fixed array; a group larger than that table is refused up front, with a message, GPU or not."""
+    lib = built.lib()
+    table = (ctypes.c_void_p * 9)(*([1] * 9))
+    assert lib.qi_peer_barrier_static(table, 9, 0, 1, None, 2000, None) == -1
+    assert b"n_peers = 9" in lib.qi_last_cuda_error()

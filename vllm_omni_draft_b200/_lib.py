@@ -79,6 +79,7 @@ _SIGNATURES = {
     "qi_peer_import": (_i, [_vp, C.POINTER(_vp)]),
     "qi_peer_unmap": (_i, [_vp]),
     "qi_peer_barrier": (_i, [_vp, _i, _i, _vp, C.c_uint, _vp]),
+    "qi_peer_barrier_static": (_i, [C.POINTER(_vp), _i, _i, _i, _vp, C.c_uint, _vp]),
     "qi_attention_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _ll, _ll, _ll, _ll, _ll, _ll, _f, _vp]),
     "qi_adaln_modulate": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _ll, _i, _f, _vp]),
     "qi_adaln_modulate_multi": (_i, [C.POINTER(NormRows), _i, _i, _f, _vp]),

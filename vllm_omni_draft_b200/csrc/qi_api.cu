@@ -10,6 +10,8 @@
 static std::string g_last_error;
 
 static void set_err(const std::string& s) { g_last_error = s; }
+// for the other translation units of the library
+void qi_set_last_error(const char* msg) { g_last_error = msg ? msg : ""; }
 
 extern "C" int qi_version(void) { return 100; }
 extern "C" const char* qi_last_cuda_error(void) { return g_last_error.c_str(); }

@@ -18,6 +18,9 @@
 // hanging the GPU; once the flag is set every later barrier returns immediately.
 #include "qi_common.cuh"
 #include "../../include/qi_b200.h"
+#include <cstring>
+#include <mutex>
+#include <string>
 
 namespace qi {
 
@@ -120,5 +123,117 @@ extern "C" int qi_peer_barrier(void* const* signal_ptrs_dev, int n_peers, int my
                 reinterpret_cast<uint32_t* const*>(signal_ptrs_dev), n_peers, my_index, state_dev,
                 ns) != cudaSuccess)
     return QI_ERR_CUDA;
+  return QI_OK;
+}
+
+// ------------------------------------------------------------------ qi_peer_barrier_static
+// The same barrier kernel for callers that cannot obtain device memory for its bookkeeping.
+//
+// qi_peer_barrier needs two small pieces of device memory besides the peer-mapped signal arrays it signals
+// through: the table of signal-array pointers the kernel indexes, and the {epoch, timeout flag} words.  Those are
+// scratch, and the caller normally allocates them.  A serving worker whose HBM has been handed wholesale to the
+// engine's block pool after memory profiling, a step loop that must not take cudaMalloc's device-wide
+// synchronisation, or a C / Go host that binds this library and owns no device allocator has no way to do that.
+// For them the scratch lives here, in a fixed array inside the library image: 256 bytes on every GPU that loads
+// the library, held until the process exits.
+//
+//   bytes [0, 64)   pointer table, QI_PEER_BARRIER_STATIC_MAX_PEERS (8) entries
+//   bytes [64, 72)  state: epoch of the last barrier, sticky timeout flag
+//
+// `g_barrier_scratch` below is only a handle in host code: the kernel must be given the address that
+// cudaGetSymbolAddress reports for the device that is current, which is looked up once per device.
+static constexpr int kStaticMaxPeers = QI_PEER_BARRIER_STATIC_MAX_PEERS;
+static constexpr size_t kStaticTableBytes = kStaticMaxPeers * sizeof(void*);
+static constexpr size_t kStaticBytes = 256;
+static_assert(kStaticTableBytes + 2 * sizeof(uint32_t) <= kStaticBytes, "scratch layout");
+static __device__ __align__(256) unsigned char g_barrier_scratch[kStaticBytes];
+
+void qi_set_last_error(const char* msg);   // qi_api.cu
+
+namespace qi {
+struct StaticPeerTable {
+  uint32_t* p[kStaticMaxPeers];
+};
+// Writes the caller's signal-array pointers into the table part of the scratch (device code may name the
+// array directly).  The barrier kernel that follows in the stream reads them after griddepcontrol.wait.
+__global__ void __launch_bounds__(32) peer_static_table_kernel(StaticPeerTable t, int n) {
+  pdl_launch_dependents();
+  pdl_wait();   // an earlier barrier of the stream may still be reading the previous table
+  if (threadIdx.x < n) reinterpret_cast<uint32_t**>(g_barrier_scratch)[threadIdx.x] = t.p[threadIdx.x];
+}
+}  // namespace qi
+
+static std::mutex g_static_mutex;
+static unsigned char* g_static_addr[64];            // device address of g_barrier_scratch, per device ordinal
+static void* g_static_table[64][kStaticMaxPeers];   // what the table on that device holds (host copy)
+
+// Device address of the scratch on the current device (nullptr + error string on failure).  The first call on a
+// device does the cudaGetSymbolAddress look-up, with that device current.
+static unsigned char* static_scratch_for_current_device(int* dev_out) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    qi_set_last_error("qi_peer_barrier_static: no current CUDA device");
+    return nullptr;
+  }
+  *dev_out = dev;
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_addr[dev]) {
+    unsigned char* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_barrier_scratch);
+    if (e != cudaSuccess || !p) {
+      qi_set_last_error((std::string("qi_peer_barrier_static: cudaGetSymbolAddress: ") +
+                         cudaGetErrorString(e)).c_str());
+      return nullptr;
+    }
+    g_static_addr[dev] = p;
+  }
+  return g_static_addr[dev];
+}
+
+extern "C" int qi_peer_barrier_static(void* const* signal_ptrs /* host */, int n_peers, int my_index,
+                                      int restart, uint32_t* state_out_dev, unsigned int timeout_ms,
+                                      cudaStream_t stream) {
+  if (n_peers > kStaticMaxPeers) {
+    qi_set_last_error(("qi_peer_barrier_static: n_peers = " + std::to_string(n_peers) +
+                       " does not fit the library's fixed pointer table (" +
+                       std::to_string(kStaticMaxPeers) + " entries)").c_str());
+    return QI_ERR_ARG;
+  }
+  if (!signal_ptrs || n_peers < 1 || my_index < 0 || my_index >= n_peers) return QI_ERR_ARG;
+  for (int p = 0; p < n_peers; ++p)
+    if (!signal_ptrs[p]) return QI_ERR_ARG;
+  if (qi_num_sms() <= 0) return QI_ERR_CUDA;
+  int dev = 0;
+  unsigned char* scratch = static_scratch_for_current_device(&dev);
+  if (!scratch) return QI_ERR_CUDA;
+  uint32_t* const* table = reinterpret_cast<uint32_t* const*>(scratch);
+  uint32_t* state = reinterpret_cast<uint32_t*>(scratch + kStaticTableBytes);
+  // The array still holds whatever the previous call left.  The epoch and the timeout flag carry over on
+  // purpose, except when the caller starts a new count on freshly zeroed signal arrays; the table is rewritten
+  // whenever it differs from what the previous call on this device stored.
+  cudaError_t e = cudaSuccess;
+  bool same;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    same = memcmp(g_static_table[dev], signal_ptrs, n_peers * sizeof(void*)) == 0;
+    if (!same) memcpy(g_static_table[dev], signal_ptrs, n_peers * sizeof(void*));
+  }
+  if (!same || restart) {
+    StaticPeerTable t = {};
+    for (int p = 0; p < n_peers; ++p) t.p[p] = static_cast<uint32_t*>(signal_ptrs[p]);
+    e = qi_launch(peer_static_table_kernel, dim3(1), dim3(32), 0, stream, t, n_peers);
+  }
+  if (e == cudaSuccess && restart) e = cudaMemsetAsync(state, 0, 2 * sizeof(uint32_t), stream);
+  const unsigned long long ns = (unsigned long long)(timeout_ms ? timeout_ms : 2000) * 1000000ull;
+  if (e == cudaSuccess)
+    e = qi_launch(peer_barrier_kernel, dim3(1), dim3(32), 0, stream, table, n_peers, my_index, state, ns);
+  if (e == cudaSuccess && state_out_dev)
+    e = cudaMemcpyAsync(state_out_dev, state, 2 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream);
+  if (e != cudaSuccess) {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    memset(g_static_table[dev], 0, sizeof(g_static_table[dev]));   // unknown device contents: rewrite next time
+    qi_set_last_error((std::string("qi_peer_barrier_static: ") + cudaGetErrorString(e)).c_str());
+    return QI_ERR_CUDA;
+  }
   return QI_OK;
 }
