@@ -376,3 +376,39 @@ def test_multi_gpu_parity(cuda_device, n, env):
                        capture_output=True, text=True, timeout=600, env=dict(os.environ, **env))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "MGPU_PARITY" in r.stdout
+
+
+def test_pipeline_sessions_follow_weight_reloads_and_cache_limit(cuda_device):
+    """(1) a cached session (hoisted modulation table + captured graph) must not survive a weight
+    reload or a flip of the kernel switches it was captured under — the same-shape call after the reload has to
+    match the oracle on the NEW weights; (2) max_cached_sessions = 0 means "keep nothing", not a crash."""
+    from vllm_omni_draft_b200.pipeline import B200QwenImagePipeline
+    ocfg = O.tiny_config()
+    sd_a = O.init_state_dict(ocfg, seed=0, bias_std=0.02, norm_weight_std=0.1)
+    sd_b = O.init_state_dict(ocfg, seed=5, bias_std=0.02, norm_weight_std=0.1)
+    tr = _build(ocfg, sd_a)
+    lat, cond, uncond, mask, shapes = O.synthetic_inputs(ocfg, 256, 256, 32)
+    kw = dict(prompt_embeds=cond, prompt_embeds_mask=mask, negative_prompt_embeds=uncond,
+              negative_prompt_embeds_mask=mask, true_cfg_scale=4.0, num_inference_steps=3, height=256, width=256,
+              latents=lat, output_type="latent")
+    ref_a = O.denoise_loop(sd_a, ocfg, lat, cond, mask, uncond, mask, 3, 4.0, img_shapes=shapes)
+    ref_b = O.denoise_loop(sd_b, ocfg, lat, cond, mask, uncond, mask, 3, 4.0, img_shapes=shapes)
+    assert O.rel_l2(ref_a, ref_b) > 0.05            # the two weight sets are tell-apart-able
+    pipe = B200QwenImagePipeline(tr)
+    pipe.use_cuda_graph = True
+    assert O.rel_l2(pipe(**kw).images.float().cpu(), ref_a) < TOL
+    first = next(iter(pipe._sessions.values()))
+    assert O.rel_l2(pipe(**kw).images.float().cpu(), ref_a) < TOL and next(iter(pipe._sessions.values())) is first
+    tr.load_diffusers_state_dict(sd_b)              # same shapes, new weights
+    assert O.rel_l2(pipe(**kw).images.float().cpu(), ref_b) < TOL
+    assert len(pipe._sessions) == 1 and next(iter(pipe._sessions.values())) is not first
+    second = next(iter(pipe._sessions.values()))
+    tr.fuse_qknorm_rope = not tr.fuse_qknorm_rope   # a different kernel sequence than the captured one
+    assert O.rel_l2(pipe(**kw).images.float().cpu(), ref_b) < TOL
+    assert next(iter(pipe._sessions.values())) is not second
+    tr.fuse_qknorm_rope = not tr.fuse_qknorm_rope
+    pipe.clear_sessions()
+    pipe.max_cached_sessions = 0
+    for _ in range(2):
+        assert O.rel_l2(pipe(**kw).images.float().cpu(), ref_b) < TOL
+        assert not pipe._sessions

@@ -322,7 +322,7 @@ class ParallelDenoiser:
             raise ValueError("CFG-parallel layout needs negative_prompt_embeds (or build with cfg_parallel=False)")
         key = (tuple(cond.shape), None if uncond is None else tuple(uncond.shape), tuple(latents.shape), height, width,
                num_inference_steps, float(true_cfg_scale), None if ref_tokens is None else (tuple(ref_tokens.shape), ref_hw),
-               None if sigmas is None else tuple(float(v) for v in sigmas))
+               None if sigmas is None else tuple(float(v) for v in sigmas), self.tr.state_signature())
         if key != self._setup_key:
             self.setup(cond, uncond, latents, height, width, num_inference_steps, true_cfg_scale,
                        ref_h=ref_tokens, ref_hw=ref_hw, sigmas=sigmas)

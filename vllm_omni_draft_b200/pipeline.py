@@ -241,8 +241,8 @@ class DenoiseSession:
             self.mod_cur.copy_(self.mod_table[0:1])
             self.dt_cur.copy_(self.dts[0:1])
             side = torch.cuda.Stream()
+            keep = (self.cur32 if self.precise else self.cur).clone()   # before the fork: the warm-up step updates it
             side.wait_stream(torch.cuda.current_stream())
-            keep = (self.cur32 if self.precise else self.cur).clone()
             with torch.cuda.stream(side):     # warm-up launch outside capture (sets func attributes)
                 self._run_step(self.dt_cur, self.mod_cur)
             torch.cuda.current_stream().wait_stream(side)
@@ -322,6 +322,7 @@ class B200QwenImagePipeline:
         # modulation table, the tuned GEMM schedules and the captured CUDA graph (0 disables the cache)
         self.max_cached_sessions = 2
         self._sessions = {}
+        self._sessions_sig = None    # transformer.state_signature() the cached sessions were built under
         self.last_step_latents: List[torch.Tensor] = []
 
     def to(self, device):
@@ -490,9 +491,14 @@ class B200QwenImagePipeline:
                    None if sigmas is None else tuple(float(v) for v in sigmas), float(true_cfg_scale),
                    None if ref_tokens is None else (ref_tokens.shape[1], ref_hw), self.use_cuda_graph,
                    self.batched_cfg)
+            sig = self.transformer.state_signature()
+            if sig != self._sessions_sig:       # weights reloaded / kernel switches flipped: tables and graphs are stale
+                self.clear_sessions()
+                self._sessions_sig = sig
             sess = self._sessions.get(key)
             if sess is None:
-                while len(self._sessions) >= self.max_cached_sessions:      # each holds a workspace + a graph
+                # each cached session holds a workspace + a graph; a limit <= 0 keeps none (nothing to evict)
+                while self._sessions and len(self._sessions) >= max(self.max_cached_sessions, 1):
                     self._sessions.pop(next(iter(self._sessions))).close()
                 sess = DenoiseSession(self, cond, uncond, latents.to(dev), Hl, Wl, num_inference_steps,
                                       true_cfg_scale, use_cuda_graph=self.use_cuda_graph,

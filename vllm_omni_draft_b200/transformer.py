@@ -125,6 +125,9 @@ class B200QwenImageTransformer2DModel(nn.Module):
         self._ws: Dict[Tuple[int, int, int], _Workspace] = {}
         self._freqs: Dict[tuple, torch.Tensor] = {}
         self._mod_table: Optional[torch.Tensor] = None      # [steps, n_mod] hoisted modulation
+        # bumped by every weight (re)load: whatever was derived from the weights (hoisted modulation tables, CUDA
+        # graphs captured over them) is keyed on state_signature() by its owner (pipeline sessions, launcher setup)
+        self.weights_generation = 0
         self._mod_steps: Optional[torch.Tensor] = None
         self._sp = None              # UlyssesContext when sequence-parallel
         self._sp_freqs: Optional[torch.Tensor] = None
@@ -224,6 +227,7 @@ class B200QwenImageTransformer2DModel(nn.Module):
         cp(self.mod_w[r0:], sd["norm_out.linear.weight"]); cp(self.mod_b[r0:], sd["norm_out.linear.bias"])
         cp(self.proj_out_w, sd["proj_out.weight"]); cp(self.proj_out_b, sd["proj_out.bias"])
         self._mod_table = None
+        self.weights_generation += 1
 
     def diffusers_param(self, name: str) -> torch.Tensor:
         """Inverse of `load_diffusers_state_dict` for ONE diffusers-named tensor: a view
@@ -293,7 +297,15 @@ class B200QwenImageTransformer2DModel(nn.Module):
                     n = min(step, flat.numel() - i)
                     flat[i:i + n] = (torch.randn(n, device=self.device, generator=g) * weight_std).to(p.dtype)
         self._mod_table = None
+        self.weights_generation += 1
         return self
+
+    def state_signature(self) -> tuple:
+        """Everything a cached denoising setup depends on besides shapes and schedule: the weights' generation and
+        the two switches that change which kernels / buffer dtypes a captured step uses.  A cache whose signature
+        differs from this must be rebuilt (in-place edits of the parameters that bypass load_diffusers_state_dict /
+        init_random_ need `weights_generation += 1` by hand)."""
+        return (self.weights_generation, bool(self.fuse_qknorm_rope), str(self.residual_dtype))
 
     # ------------------------------------------------------------------ GEMM schedule autotuning
     @torch.no_grad()
