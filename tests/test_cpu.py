@@ -4,6 +4,7 @@ import ctypes
 import hashlib
 import os
 import re
+import sys
 
 import pytest
 import torch
@@ -84,7 +85,7 @@ def test_library_exports_every_declared_symbol(built):
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in qi_b200.h but not exported"
     assert declared == set(built.EXPORTED_SYMBOLS)
-    assert built.lib().qi_version() == 100
+    assert built.lib().qi_version() == 101
 
 
 def test_attention_variant_switch_validates_its_argument(built):
@@ -231,3 +232,20 @@ def test_static_barrier_size_limit_is_checked_before_any_cuda_call(built):
     table = (ctypes.c_void_p * 9)(*([1] * 9))
     assert lib.qi_peer_barrier_static(table, 9, 0, 1, None, 2000, None) == -1
     assert b"n_peers = 9" in lib.qi_last_cuda_error()
+
+
+def test_shipped_schedules_are_pinned_to_this_gemm_source(built):
+    """schedules timed on an older build must not be reused silently.  The in-tree file carries the
+    hash of the GEMM sources it was measured on and only keys of the current qi_version(); changing qi_gemm.cu /
+    qi_common.cuh without bumping the version, re-tuning and re-pinning (tools/pin_schedules.py) fails here."""
+    import json
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import pin_schedules
+    with open(os.path.join(ROOT, "vllm_omni_draft_b200", "tuned_schedules.json")) as fh:
+        shipped = json.load(fh)
+    assert shipped.pop(pin_schedules.PIN_KEY) == pin_schedules.gemm_source_sha256(), \
+        "GEMM source changed: bump qi_version(), re-tune on a B200, run tools/pin_schedules.py"
+    tag = f"/v{built.lib().qi_version()}/"
+    assert shipped and all(tag in k for k in shipped)
+    from vllm_omni_draft_b200 import ops
+    assert not any(k.startswith("__") for k in ops.tuned_schedules())

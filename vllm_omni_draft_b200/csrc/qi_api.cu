@@ -13,7 +13,10 @@ static void set_err(const std::string& s) { g_last_error = s; }
 // for the other translation units of the library
 void qi_set_last_error(const char* msg) { g_last_error = msg ? msg : ""; }
 
-extern "C" int qi_version(void) { return 100; }
+// Keys the persisted GEMM schedules (ops._persist_key): bump it with every change to the GEMM kernels or their
+// scheduling, then re-tune and re-pin vllm_omni_draft_b200/tuned_schedules.json (tools/pin_schedules.py;
+// tests/test_cpu.py::test_shipped_schedules_are_pinned_to_this_gemm_source fails until that is done).
+extern "C" int qi_version(void) { return 101; }
 extern "C" const char* qi_last_cuda_error(void) { return g_last_error.c_str(); }
 
 // Per-device caches (a process may drive several GPUs; the current device decides).  Guarded by one mutex: the

@@ -209,7 +209,8 @@ def _tune_schedule(problems: Sequence[GemmProblem], launches: int, groups: int) 
 
 
 # ------------------------------------------------------------------ persisted schedules
-# Tuned schedules are keyed by (SM count, library version, problem dims) and kept in two JSON files: one shipped
+# Tuned schedules are keyed by (SM count, library version = qi_version(), bumped with every GEMM kernel change,
+# problem dims) and kept in two JSON files: one shipped
 # in-tree with the benchmark shapes (read-only) and one in the user's cache directory (read/write), so a new
 # process — and a new session in it — does not re-tune shapes that were measured before.
 _SCHEDULE_FILES = [os.path.join(os.path.dirname(os.path.abspath(__file__)), "tuned_schedules.json"),
@@ -232,8 +233,8 @@ def _load_persisted() -> dict:
         if os.environ.get("QI_GEMM_SCHEDULE_CACHE", "1") != "0":
             for f in _SCHEDULE_FILES:
                 try:
-                    with open(f) as fh:
-                        _persisted.update(json.load(fh))
+                    with open(f) as fh:   # "__..." keys are file metadata (the source pin of the in-tree file)
+                        _persisted.update({k: v for k, v in json.load(fh).items() if not k.startswith("__")})
                 except (OSError, ValueError):
                     pass
     return _persisted
