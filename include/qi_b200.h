@@ -228,26 +228,18 @@ int qi_attention_fwd_scatter(const void* q, const void* k, const void* v, int ba
                              long long q_batch_stride, long long kv_batch_stride, long long o_batch_stride,
                              long long q_head_stride, long long kv_head_stride, long long o_head_stride,
                              float softmax_scale, const qi_peer_scatter_t* dst /* host */, qi_stream_t stream);
-/* Softmax variant of the attention kernel (tuning / tests): -1 = default (env QI_ATTN_VARIANT, else 11),
- * otherwise EMU + 8 * SPLIT with EMU in {0, 2, 3, 4} = how many of every 8 element pairs evaluate 2^x
- * with the FMA-pipe polynomial (degree 3) instead of MUFU.EX2, SPLIT in {0, 1} = P published in two halves;
- * 16 + EMU = two threads per query row (four softmax warpgroups); 24 / 25 / 26 = degree-2 polynomial on 3 / 4 / 5 of
- * every 8 pairs; 40 + EMU (EMU 0..4) and 48 + n (degree-2 polynomial on n = 1..4 of 8) = the second kernel,
- * attention_ts_kernel: one 128-query tile per CTA, Q resident in TMEM, K/V pipelined in 64-key halves over three S
- * regions and two softmax warpgroups; 56 + EMU = the same as CTA pairs (cta_group::2, head_dim 128); 64 + EMU = both
- * softmax warpgroups on the same Q tile (64 keys each, reference maximum from the previous K/V tile's maxima) and
- * 80 + EMU = the same with four warpgroups; 9 = 1 of 8 pairs on the polynomial; 27 = 11 with the S load in two groups.  All of these measured slower than the
- * default on the benchmarked shapes and are kept as tested variants.  Valid range: -1 .. 84.  All variants agree with
- * fp32 SDPA to the same tolerance (tests/test_ops_gpu.py). */
+/* Softmax form of the attention kernel, one A/B switch: -1 = default (env QI_ATTN_VARIANT, else 11), otherwise
+ * EMU + 8 * SPLIT with EMU in {0, 3} = how many of every 8 element pairs evaluate 2^x with the degree-3 FMA-pipe
+ * polynomial instead of MUFU.EX2 and SPLIT in {0, 1} = P handed to the P*V MMA in two halves; i.e. 0, 3, 8 or 11.
+ * Anything else is QI_ERR_ARG.  All four agree with fp32 SDPA to the same tolerance (tests/test_ops_gpu.py); 11 is
+ * the fastest on the benchmarked shapes.  The other kernels and mixes that were built and measured slower
+ * (profiles/) are not part of this library: tools/experiments/Makefile builds them into a
+ * separate libqi_b200_exp.so for the sweep tools. */
 int qi_attention_set_variant(int variant);
 
-/* Tuning aids (measurement only; not needed by a drop-in caller).
- * qi_gemm_set_debug: bit 0 skip the fp32 epilogue's residual loads, bit 1 its result stores, bit 2 its bias/gate
- *   loads (wrong results; used to attribute epilogue time, tools/ab_gemm.py dbg).
- * qi_attention_set_debug: DEVICE buffer of >= 16 uint64 counters (or NULL to stop): cycles the MMA issuer and the
- *   first softmax warp spend in each wait / phase, summed over the CTAs of later launches (tools/attn_waits.py). */
+/* Tuning aid (measurement only; not needed by a drop-in caller): bit 0 skips the fp32 epilogue's residual loads,
+ * bit 1 its result stores, bit 2 its bias/gate loads (wrong results; attributes epilogue time, tools/ab_gemm.py). */
 int qi_gemm_set_debug(int mask);
-int qi_attention_set_debug(unsigned long long* counters_dev);
 
 
 /* Peer memory: device allocations that can be mapped by the other ranks of the node (CUDA IPC).

@@ -89,16 +89,18 @@ def test_library_exports_every_declared_symbol(built):
 
 
 def test_attention_variant_switch_validates_its_argument(built):
-    """qi_attention_set_variant is host-only state: the documented range (include/qi_b200.h: -1 = default, 0..84) is
-    accepted, anything else is QI_ERR_ARG, and the default is restored afterwards."""
+    """qi_attention_set_variant is host-only state: the four shipped softmax forms (include/qi_b200.h: -1 = default,
+    EMU in {0, 3} + 8 * SPLIT) are accepted, anything else — including the experiment variants that now live in
+    tools/experiments — is QI_ERR_ARG, and the default is restored afterwards."""
     lib = built.lib()
     try:
-        for v in (-1, 0, 11, 43, 59, 67, 84):
+        for v in (-1, 0, 3, 8, 11):
             assert lib.qi_attention_set_variant(v) == 0
-        for v in (-2, 85, 1000):
+        for v in (-2, 2, 9, 19, 43, 59, 67, 84, 85, 1000):
             assert lib.qi_attention_set_variant(v) != 0
     finally:
         assert lib.qi_attention_set_variant(-1) == 0
+    assert not hasattr(lib, "qi_attention_set_debug")   # measurement hooks are not in the product library
 
 
 def test_compute_entry_points_fail_loudly_without_gpu(built):

@@ -178,10 +178,10 @@ def test_attention(cuda_device, B, S, H, Dh):
 
 
 @pytest.mark.parametrize("Dh", [128, 64])
-@pytest.mark.parametrize("variant", [0, 2, 3, 4, 8, 9, 10, 11, 12, 16, 18, 19, 20, 24, 25, 26, 27, 40, 42, 43, 44, 56, 58, 59, 60, 64, 66, 67, 68, 80, 82, 83, 84])
+@pytest.mark.parametrize("variant", [0, 3, 8, 11])
 def test_attention_softmax_variants(cuda_device, variant, Dh):
-    """Every softmax variant (MUFU only / 2-3-4 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
-    or in two halves, one thread or two threads per query row) matches fp32 SDPA, on a ragged sequence (partial
+    """Every shipped softmax form (MUFU only / 3 of 8 pairs on the FMA-pipe exp2 polynomial, P published whole
+    or in two halves) matches fp32 SDPA, on a ragged sequence (partial
     last K/V tile, partial Q tile) with large-magnitude logits so the lazy rescale and the polynomial's range
     reduction are exercised."""
     ops = _ops()
@@ -205,12 +205,11 @@ def test_attention_softmax_variants(cuda_device, variant, Dh):
 
 @pytest.mark.parametrize("Dh", [128, 64])
 @pytest.mark.parametrize("S", [40, 64, 100, 128, 168, 300, 936, 1000, 1152])
-def test_attention_half_tile_pipeline_ragged(cuda_device, S, Dh):
-    """The Q-in-TMEM half-tile pipeline (variants 40+ single CTA, 56+ clusters of two with multicast K/V) steps through
-    64-key halves taken alternately by two softmax warpgroups: one half only (40, 64: the second warpgroup never
-    runs), odd and even numbers of halves, sequences ending inside a half (100, 168, 300, 936, 1000) or on a boundary
-    (128, 1152), odd numbers of Q tiles (40, 300: the cluster's second CTA has no rows to store), with logits wide
-    enough that the reference maximum keeps moving (the O rescale has to wait for the P*V MMA still in flight)."""
+def test_attention_ragged_lengths_moving_maximum(cuda_device, S, Dh):
+    """Sequence ends everywhere relative to the 128-key K/V tile and the 256-row Q tile pair: shorter than one tile
+    (40, 64, 100), on a boundary (128, 1152), inside a tile (168, 300, 936, 1000), an odd number of Q tiles (40, 300:
+    the second tile of the pair has no rows to store); later keys score higher, so the running maximum keeps moving
+    and the lazy O rescale has to wait for the P*V MMA still in flight.  Default form and the MUFU-only unsplit one."""
     ops = _ops()
     B, H = 2, 2
     d = H * Dh
@@ -220,7 +219,7 @@ def test_attention_half_tile_pipeline_ragged(cuda_device, S, Dh):
     q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
     ref = torch.nn.functional.scaled_dot_product_attention(
         q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)).transpose(1, 2)
-    for variant in (43, 59, 40, 67, 64, 83):
+    for variant in (-1, 0):
         out = torch.zeros(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
         ops.attention_set_variant(variant)
         try:

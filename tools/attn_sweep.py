@@ -1,7 +1,11 @@
 """Times every softmax variant of the attention kernel (EMU + 8*SPLIT) at the cfg-2 step shape (batch 2 =
 stacked cond/uncond, 4608 tokens, 24 heads) and at the per-rank shape of cfg2 x ulysses4 (6 heads).
 Variants are interleaved over several rounds (boost clocks decay over the first seconds of load, so a
-sequential sweep favours whatever runs first); SM clock and board power are sampled through NVML."""
+sequential sweep favours whatever runs first); SM clock and board power are sampled through NVML.
+
+Needs the experiments library for any variant other than 0, 3, 8, 11 (and for the cycle counters / DIAG modes):
+    make -C tools/experiments && QI_LIB_PATH=tools/experiments/libqi_b200_exp.so python tools/attn_sweep.py ...
+"""
 import os
 import sys
 import time

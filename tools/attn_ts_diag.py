@@ -2,7 +2,11 @@
 hands the barriers on: the MMA/TMA pipeline alone), 2 (S load + P store without the math), 3 (as 1, and the P*V issuer
 does not wait for P) — read per process, so this script re-executes itself per mode.  Prints us per launch at the
 cfg-2 step shape, the softmax phase counters of one thread and (QI_DIAG_TRACE=1) the timeline of CTA (0,0,0):
-K/V TMA issue, K ready (Q*K^T issuer), P ready / step issued (P*V issuer), S ready / P published (softmax)."""
+K/V TMA issue, K ready (Q*K^T issuer), P ready / step issued (P*V issuer), S ready / P published (softmax).
+
+Needs the experiments library for any variant other than 0, 3, 8, 11 (and for the cycle counters / DIAG modes):
+    make -C tools/experiments && QI_LIB_PATH=tools/experiments/libqi_b200_exp.so python tools/attn_ts_diag.py ...
+"""
 import ctypes as C
 import os
 import subprocess

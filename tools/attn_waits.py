@@ -1,5 +1,9 @@
 """Where do the attention kernel's MMA-issuer and softmax warps wait?  Cycle counters (qi_attention_set_debug, a
-tuning aid outside the ABI) summed over the CTAs of one launch at the cfg-2 shape, printed per CTA."""
+tuning aid outside the ABI) summed over the CTAs of one launch at the cfg-2 shape, printed per CTA.
+
+Needs the experiments library for any variant other than 0, 3, 8, 11 (and for the cycle counters / DIAG modes):
+    make -C tools/experiments && QI_LIB_PATH=tools/experiments/libqi_b200_exp.so python tools/attn_waits.py ...
+"""
 import ctypes as C
 import os
 import sys

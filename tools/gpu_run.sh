@@ -63,7 +63,9 @@ case "$T" in
     python tools/launch_share.py gpurun_out/launch_list_step.csv;;
   attn_pipe)
     # the Q-in-TMEM half-tile pipeline (variants 40+ / 56+): parity tests, interleaved sweep beside the current default, wait
-    # counters, then a step bench with the fastest variant that passed
+    # counters, then a step bench with the fastest variant that passed.  These variants live in the experiments library
+    # (build it first: make -C tools/experiments); the sweep, the counters and the bench below load it via QI_LIB_PATH.
+    export QI_LIB_PATH=${QI_LIB_PATH:-$PWD/tools/experiments/libqi_b200_exp.so}
     timeout -s KILL 420 python -m pytest tests/test_ops_gpu.py -x -q -k "attention" > gpurun_out/attn_tests.log 2>&1; RC=$?; echo "attention tests rc=$RC"; tail -4 gpurun_out/attn_tests.log
     [ $RC -eq 0 ] || exit 1
     QI_SWEEP_VARIANTS=${QI_SWEEP_VARIANTS:-11,43,59,40,56,42,58,44,60} timeout -s KILL 300 python tools/attn_sweep.py > gpurun_out/attn_pipe_sweep.txt 2>&1; echo "sweep rc=$?"; cat gpurun_out/attn_pipe_sweep.txt

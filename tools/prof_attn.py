@@ -1,6 +1,10 @@
 """Launches attention alone at the cfg-2 shape (batch 2, 4608 tokens, 24 x 128 heads) for ncu: our kernel in each
-variant listed in QI_ATTN_VARIANTS (default "11,19"), then — the library bar, VERDICT r1 item 4 — cuDNN's fused SDPA
-on the same tensors, so one report holds both kernels' pipe utilisation, instruction mix and launch geometry."""
+variant listed in QI_ATTN_VARIANTS (default "11"), then — the library bar, VERDICT r1 item 4 — cuDNN's fused SDPA
+on the same tensors, so one report holds both kernels' pipe utilisation, instruction mix and launch geometry.
+
+Needs the experiments library for any variant other than 0, 3, 8, 11 (and for the cycle counters / DIAG modes):
+    make -C tools/experiments && QI_LIB_PATH=tools/experiments/libqi_b200_exp.so python tools/prof_attn.py ...
+"""
 import os
 import sys
 
@@ -16,7 +20,7 @@ g = torch.Generator(device="cuda").manual_seed(0)
 qkv = torch.randn(B, S, 3 * d, device="cuda", generator=g).bfloat16()
 q, k, v = [qkv[:, :, i * d:(i + 1) * d].unflatten(-1, (H, Dh)) for i in range(3)]
 o = torch.empty(B, S, H, Dh, device="cuda", dtype=torch.bfloat16)
-for var in [int(x) for x in os.environ.get("QI_ATTN_VARIANTS", "11,19").split(",")]:
+for var in [int(x) for x in os.environ.get("QI_ATTN_VARIANTS", "11").split(",")]:
     ops.attention_set_variant(var)
     for i in range(2):
         ops.attention(q, k, v, o)

@@ -64,7 +64,6 @@ _SIGNATURES = {
     "qi_gemm_set_cta_pair": (_i, [_i]),
     "qi_attention_set_variant": (_i, [_i]),
     "qi_gemm_set_debug": (_i, [_i]),
-    "qi_attention_set_debug": (_i, [_vp]),
     "qi_gemm_set_schedule": (_i, [_vp, _i, _i, _i]),
     "qi_gemm_clear_schedules": (_i, []),
     "qi_gemm_set_group_m": (_i, [_i]),

@@ -55,7 +55,9 @@ struct AttParams {
   __nv_bfloat16* o;
   long long ld_o, o_bs, o_hs;   // token, batch and head strides of the output (elements)
   const __nv_bfloat16* q;       // TS kernel: Q rows are read straight from global memory into TMEM
+#ifdef QI_ATTN_EXPERIMENTS
   int ts_diag;                  // tuning aid (env QI_ATTN_TS_DIAG): 1 = softmax only hands the barriers on, 2 = S load + P store without the math, 3 = as 1 and the P*V issuer does not wait for P
+#endif
   long long ld_q, q_bs, q_hs;
   int seq_q, seq_kv, heads;
   float scale_log2;
@@ -929,21 +931,34 @@ attention_fwd_kernel(const __grid_constant__ AttParams P) {
 
 }  // namespace qi
 
+// The product library ships the two-tile kernel above in four softmax forms (variants 0, 3, 8, 11).  Everything
+// else that was built and measured slower (two threads per row, cooperating warpgroups, the Q-in-TMEM half-tile
+// kernel of tools/experiments/qi_attn_ts.cuh, other exp2 mixes) is compiled only into the experiments library
+// (tools/experiments/Makefile, -DQI_ATTN_EXPERIMENTS); the measurements are under profiles/ and in DESIGN.md section 4.
+#ifdef QI_ATTN_EXPERIMENTS
 #include "qi_attn_ts.cuh"
+#endif
 
 using namespace qi;
 
-static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8*SPLIT, 16 + EMU = two threads per row, 24..26 = degree-2 polynomial on 3..5 of 8 pairs, 40 + EMU = one Q tile per CTA with Q in TMEM and the half-tile pipeline (attention_ts_kernel), 56 + EMU = the same as CTA pairs (cta_group::2, each CTA stages half of every K/V half; head_dim 128 only)
+static int g_attn_variant = -1;   // -1: env QI_ATTN_VARIANT or default; else EMU + 8 * SPLIT (include/qi_b200.h)
+#ifdef QI_ATTN_EXPERIMENTS
+static bool attn_variant_known(int v) { return v >= 0 && v <= 84; }   // the switch in launch_attention decides
+#else
+static bool attn_variant_known(int v) { return v == 0 || v == 3 || v == 8 || v == 11; }
+#endif
 extern "C" int qi_attention_set_variant(int v) {
-  if (v < -1 || v > 84) return QI_ERR_ARG;
+  if (v != -1 && !attn_variant_known(v)) return QI_ERR_ARG;
   g_attn_variant = v;
   return QI_OK;
 }
+#ifdef QI_ATTN_EXPERIMENTS
 static unsigned long long* g_attn_dbg = nullptr;   // device buffer of >= 16 counters, or null
 extern "C" int qi_attention_set_debug(unsigned long long* buf) {
   g_attn_dbg = buf;
   return QI_OK;
 }
+#endif
 static int attn_variant() {
   static const int env = [] {
     const char* e = getenv("QI_ATTN_VARIANT");   // tuning aid: EMU (0,2,3,4) + 8 * SPLIT
@@ -1021,24 +1036,39 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
   P.seq_kv = seq_kv;
   P.heads = heads;
   P.scale_log2 = scale * 1.4426950408889634f;
+#ifdef QI_ATTN_EXPERIMENTS
   P.dbg = g_attn_dbg;
   {
     const char* e = getenv("QI_ATTN_TS_DIAG");
     P.ts_diag = e ? atoi(e) : 0;
   }
+#else
+  P.dbg = nullptr;   // the cycle counters are an experiments-library aid
+#endif
   int variant = attn_variant();
-  if (variant >= 40 && variant < 64 && P.wait.slots) variant = 11;   // folded peer flags are polled by the two-tile kernel's TMA warp only
+#ifdef QI_ATTN_EXPERIMENTS
+  // The Q-in-TMEM kernel does not poll folded peer flags (only its K loader would, leaving Q and V unordered:
+  // ADVICE round 2); an exchange that needs them runs the shipped kernel.
+  if (variant >= 40 && variant < 64 && P.wait.slots) variant = 11;
+#endif
   P.split_p = (variant >> 3) & 1;
   dim3 grid((seq_q + 2 * ATT_BM - 1) / (2 * ATT_BM), heads, batch);
   switch (variant) {
     case 0: return launch_attention_v<DH, 0, false>(P, grid, stream);
+#ifdef QI_ATTN_EXPERIMENTS
     case 2: return launch_attention_v<DH, 2, false>(P, grid, stream);
+#endif
     case 3: return launch_attention_v<DH, 3, false>(P, grid, stream);
+#ifdef QI_ATTN_EXPERIMENTS
     case 4: return launch_attention_v<DH, 4, false>(P, grid, stream);
+#endif
     case 8: return launch_attention_v<DH, 0, true>(P, grid, stream);
+#ifdef QI_ATTN_EXPERIMENTS
     case 9: return launch_attention_v<DH, 1, true>(P, grid, stream);
     case 10: return launch_attention_v<DH, 2, true>(P, grid, stream);
+#endif
     case 11: return launch_attention_v<DH, 3, true>(P, grid, stream);
+#ifdef QI_ATTN_EXPERIMENTS
     case 12: return launch_attention_v<DH, 4, true>(P, grid, stream);
     case 16: return launch_attention_v<DH, 0, true, true>(P, grid, stream);
     case 18: return launch_attention_v<DH, 2, true, true>(P, grid, stream);
@@ -1056,12 +1086,15 @@ static int launch_attention(const void* q, const void* k, const void* v, void* o
     case 82: return launch_attention_v<DH, 2, true, true, true>(P, grid, stream);
     case 83: return launch_attention_v<DH, 3, true, true, true>(P, grid, stream);
     case 84: return launch_attention_v<DH, 4, true, true, true>(P, grid, stream);
+#endif
+#ifdef QI_ATTN_EXPERIMENTS
 #define QI_TS_CASE(V, EMU, PAIR) \
   case V: return launch_attention_ts<DH, EMU, PAIR && DH == 128>(P, k, v, batch, seq_q, seq_kv, heads, ld_kv, kv_bs, kv_hs, stream);
     QI_TS_CASE(40, 0, false) QI_TS_CASE(41, 1, false) QI_TS_CASE(42, 2, false) QI_TS_CASE(43, 3, false) QI_TS_CASE(44, 4, false)
     QI_TS_CASE(49, 16 + 1, false) QI_TS_CASE(50, 16 + 2, false) QI_TS_CASE(51, 16 + 3, false) QI_TS_CASE(52, 16 + 4, false)
     QI_TS_CASE(56, 0, true) QI_TS_CASE(58, 2, true) QI_TS_CASE(59, 3, true) QI_TS_CASE(60, 4, true)
 #undef QI_TS_CASE
+#endif
     default: return QI_ERR_ARG;
   }
 }

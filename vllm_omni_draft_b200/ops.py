@@ -419,8 +419,8 @@ def gemm_set_tile_n(bn: int) -> None:
 
 
 def attention_set_variant(variant: int) -> None:
-    """-1 default; else EMU (0/2/3/4 of 8 pairs on the FMA-pipe exp2 polynomial) + 8 * SPLIT; 40+ / 56+ select the
-    Q-in-TMEM half-tile kernel (single CTA / CTA pair).  The full table is in include/qi_b200.h."""
+    """-1 default (11); else EMU (0 or 3 of 8 pairs on the FMA-pipe exp2 polynomial) + 8 * SPLIT, i.e. 0, 3, 8, 11.
+    The experiment variants (tools/experiments) exist only in libqi_b200_exp.so (QI_LIB_PATH)."""
     check(_lib.lib().qi_attention_set_variant(int(variant)), "qi_attention_set_variant")
 
 
