@@ -43,15 +43,21 @@ def test_forward_60_blocks_vs_fp32_oracle(model60):
     assert max(r["e"] for r in res["per_block"]) <= TOL
 
 
-def test_denoise_8_steps_60_blocks_vs_fp32_oracle(model60):
+@pytest.mark.parametrize("steps", [8, 50])
+def test_denoise_loop_60_blocks_vs_fp32_oracle(model60, steps):
+    """8 steps (large dt, the round-2 case) and the 50-step schedule BASELINE.json configs[1] quotes the metric on
+    (/root/reference/src/performance_enhancement/test_performance.py:249,263 num_inference_steps: 50): every one of
+    the per-step latents within 1e-2 of the fp32 oracle, decoded image >= 40 dB.  The fp32 oracle costs ~3 s per
+    step on the GPU, so the 50-step case takes ~2.5 min."""
     from depth_parity import _init_vae_, loop_depth
     from vllm_omni_draft_b200.vae import B200QwenImageVAEDecoder
     tr, ocfg = model60
     vae = B200QwenImageVAEDecoder(device="cuda:0")          # real dims: base 96, mult (1,2,4,4), 2 res blocks
     _init_vae_(vae)
-    res = loop_depth(tr, ocfg, steps=8, vae=vae, use_cuda_graph=True)
+    res = loop_depth(tr, ocfg, steps=steps, vae=vae, use_cuda_graph=True)
     print("DEPTH_LOOP " + json.dumps(res))
-    _dump("depth_loop.json", res)
+    _dump("depth_loop.json" if steps == 8 else f"depth_loop_{steps}steps.json", res)
+    assert len(res["per_step"]) == steps
     assert all(r["rel_l2"] <= TOL for r in res["per_step"]), res["per_step"]
     assert res["image_std"] > 0.02
     assert res["psnr_db"] >= 40.0
