@@ -19,6 +19,9 @@ if "ms_per_step" in j:
         print("INVALID:", j["invalid"])
     if "cpu_baseline" in j:
         print("cpu_baseline:", {k: v for k, v in j["cpu_baseline"].items() if k != "sample"})
+rw = j.get("roofline_worst")
+if rw:
+    print(f"roofline_worst: {rw['kernel']} {rw['achieved']:.0f} TF/s of {rw['peak']:.0f} = {rw['frac']:.3f}; launch {rw['launch_us']:.1f} us; share of block {rw['share_of_block']:.3f}")
 r = j.get("roofline")
 if r:
     print(f"roofline: {r['achieved']:.0f} TF/s of {r['peak']:.0f} = {r['frac']:.3f}; launch {r['launch_us']:.1f} us; cublas {r.get('cublas_same_shape_tflops')}; traffic {r.get('traffic')} vs alg {r.get('algorithmic_bytes')}")

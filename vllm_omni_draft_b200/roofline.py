@@ -178,4 +178,19 @@ def kernel_rooflines(burst_tf: float, sustained_tf: float, hbm_gbs: float, src: 
            + 2 * kern["adaln_modulate_img"]["us_l2_resident"] * (S / s_img))
     kern["block_sum_us"] = blk
     kern["step_from_kernel_sum_ms"] = blk * 60 / 1e3 * (2 / B)
-    return {"roofline": roof, "kernels": kern}
+    # `roofline` describes the dominant kernel (the largest share of the step); `roofline_worst` is the tensor-bound
+    # kernel furthest below the same peak, i.e. the one that decides whether the step meets its target
+    # (the headline object must not flatter).  Same peak, same timing method as `roofline`.
+    tensor = {n: kv for n, kv in kern.items() if isinstance(kv, dict) and "tflops" in kv}
+    tensor["gemm_mlp_up_gelu"] = {"us": roof["launch_us"], "tflops": roof["achieved"]}
+    wname = min(tensor, key=lambda n: tensor[n]["tflops"])
+    w = tensor[wname]
+    worst = {"bound": "tensor", "kernel": wname, "achieved": w["tflops"], "peak": burst_tf, "unit": "TFLOP/s",
+             "frac": w["tflops"] / burst_tf, "frac_of_sustained": w["tflops"] / sustained_tf,
+             "frac_of_nominal_2250": w["tflops"] / 2250.0, "launch_us": w["us"],
+             "share_of_block": w["us"] / blk, "peak_source": roof.get("peak_source"), "traffic": None}
+    if "sdpa_same_shape_tflops" in w:
+        worst["library_same_shape_tflops"] = w["sdpa_same_shape_tflops"]
+    elif "cublas_same_shape_tflops" in w:
+        worst["library_same_shape_tflops"] = w["cublas_same_shape_tflops"]
+    return {"roofline": roof, "roofline_worst": worst, "kernels": kern}
