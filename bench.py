@@ -558,7 +558,7 @@ def main():
                 print(json.dumps(partial), flush=True)
             os._exit(0)
 
-        watchdog = threading.Timer(float(os.environ.get("QI_SECONDARY_BUDGET_S", "420")), give_up)
+        watchdog = threading.Timer(float(os.environ.get("QI_SECONDARY_BUDGET_S", "300")), give_up)
         watchdog.daemon = True
         watchdog.start()
         for name in sec_names:
